@@ -1,0 +1,162 @@
+/*
+ * omplcu.h -- C ABI of the B200-native OMPL hot path (libomplcu.so).
+ *
+ * Drop-in boundary.  Plain pointers and sizes only; every entry
+ * point returns an int status (0 = OMPLCU_OK) and never throws; the message of
+ * the last failure on the calling thread is omplcu_last_error().  Host-pointer
+ * entry points copy in/out themselves; *_device entry points take device
+ * pointers on the handle's GPU and a cudaStream_t passed as void*.
+ *
+ * What each entry point replaces in the reference (/root/reference/src/ompl):
+ *   omplcu_space_*         base/StateSpace.h distance / interpolate / validSegmentCount
+ *                          (base/src/StateSpace.cpp:851-854,1068-1116;
+ *                           base/spaces/src/RealVectorStateSpace.cpp:230-265,
+ *                           SO2StateSpace.cpp:116-155, SO3StateSpace.cpp:254-318)
+ *   omplcu_nn_add          NearestNeighbors<_T>::add            datastructures/NearestNeighbors.h:78-85
+ *   omplcu_nn_remove       NearestNeighbors<_T>::remove         NearestNeighbors.h:88
+ *   omplcu_nn_clear/size/list                                   NearestNeighbors.h:75,106,109
+ *   omplcu_nn_knn          NearestNeighborsLinear::nearestK     NearestNeighborsLinear.h:119-132
+ *   omplcu_nn_radius       NearestNeighborsLinear::nearestR     NearestNeighborsLinear.h:135-142
+ *   omplcu_nn_knn(k=1)     NearestNeighborsLinear::nearest      NearestNeighborsLinear.h:98-116
+ *   omplcu_check_states    StateValidityChecker::isValid        base/StateValidityChecker.h:111
+ *   omplcu_check_motions   DiscreteMotionValidator::checkMotion base/src/DiscreteMotionValidator.cpp:48-145
+ *   omplcu_checker_create_hypercube   demos/HypercubeBenchmark.cpp:57-72
+ *   omplcu_checker_create_chain       demos/KinematicChain.h:193-276
+ *   omplcu_checker_create_circles     tests/resources/circles2D.h:139-149
+ *   omplcu_checker_create_se3         (not in the reference; specified in DESIGN.md)
+ *
+ * Neighbour order is the total order (distance, id): NearestNeighborsLinear's
+ * result with ties broken by insertion index.  Ids are insertion sequence
+ * numbers (first id of a handle is its id base, default 0) and never change.
+ */
+#ifndef OMPLCU_H
+#define OMPLCU_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OMPLCU_OK 0
+#define OMPLCU_ERR_INVALID 1   /* bad argument */
+#define OMPLCU_ERR_CUDA 2      /* CUDA runtime failure */
+#define OMPLCU_ERR_NOT_FOUND 3 /* remove(): id absent (reference returns false) */
+#define OMPLCU_ERR_EMPTY 4     /* nearest on empty structure ("No elements found ...") */
+#define OMPLCU_ERR_INTERNAL 5
+
+#define OMPLCU_ID_NONE UINT64_MAX
+
+enum { OMPLCU_RV = 0, OMPLCU_SO2 = 1, OMPLCU_SO3 = 2, OMPLCU_CHAIN = 3 };
+#define OMPLCU_MAX_COMPONENTS 8
+
+/* One (sub)space.  dim = stored doubles (RV: dimension; SO2: 1; SO3: 4 in
+ * x,y,z,w order; CHAIN: links).  lvs = StateSpace::getLongestValidSegmentLength()
+ * of that (sub)space, factor = getValidSegmentCountFactor(). */
+typedef struct
+{
+    int32_t type;
+    int32_t dim;
+    double weight;
+    double lvs;
+    uint32_t factor;
+    uint32_t _pad;
+    double param; /* CHAIN: link length */
+} omplcu_component;
+
+typedef struct omplcu_space_s *omplcu_space_t;
+typedef struct omplcu_nn_s *omplcu_nn_t;
+typedef struct omplcu_checker_s *omplcu_checker_t;
+
+const char *omplcu_last_error(void);
+int omplcu_version(void);
+int omplcu_device_count(int *count);
+void omplcu_free(void *p);
+/* FP32 FMA pipe peak of `device` in TFLOP/s (FMA = 2 flop), measured with a
+ * register-only micro-benchmark: scalar FFMA and packed FFMA2.  This is the
+ * roofline denominator for the FP32-bound kNN scan. */
+int omplcu_measure_fp32_peak(int device, double *tflops_ffma, double *tflops_ffma2);
+
+/* ---- state space ---- */
+/* compound != 0: CompoundStateSpace semantics (weighted sum of component
+ * distances; validSegmentCount = max over components).  compound == 0
+ * requires ncomp == 1. */
+int omplcu_space_create(const omplcu_component *comps, int ncomp, int compound, omplcu_space_t *out);
+int omplcu_space_destroy(omplcu_space_t sp);
+int omplcu_space_stride(omplcu_space_t sp, int *stride);
+/* batched space math on `device` (host buffers): rows of `stride` doubles */
+int omplcu_space_distance(omplcu_space_t sp, int device, const double *a, const double *b, size_t n, double *out);
+int omplcu_space_interpolate(omplcu_space_t sp, int device, const double *from, const double *to, const double *t,
+                             size_t n, double *out);
+int omplcu_space_segment_count(omplcu_space_t sp, int device, const double *a, const double *b, size_t n,
+                               uint32_t *out);
+
+/* ---- nearest neighbours ---- */
+int omplcu_nn_create(omplcu_space_t sp, int device, omplcu_nn_t *out);
+int omplcu_nn_destroy(omplcu_nn_t nn);
+/* ids handed out are id_base + insertion sequence (sharded roadmaps give each
+ * rank a disjoint base).  Must be called while the structure is empty. */
+int omplcu_nn_set_id_base(omplcu_nn_t nn, uint64_t id_base);
+int omplcu_nn_add(omplcu_nn_t nn, const double *rows, size_t n, uint64_t *first_id);
+int omplcu_nn_remove(omplcu_nn_t nn, uint64_t id);
+int omplcu_nn_clear(omplcu_nn_t nn);
+int omplcu_nn_size(omplcu_nn_t nn, size_t *n);
+int omplcu_nn_list(omplcu_nn_t nn, uint64_t *ids, size_t cap, size_t *n);
+/* Read back the stored coordinates of `id` (stride doubles). */
+int omplcu_nn_get(omplcu_nn_t nn, uint64_t id, double *row);
+/* k nearest per query.  ids/dists are nq x k row-major, rows padded with
+ * OMPLCU_ID_NONE / +inf beyond counts[i] = min(k, size).  dists and counts may
+ * be NULL. */
+int omplcu_nn_knn(omplcu_nn_t nn, const double *queries, size_t nq, size_t k, uint64_t *ids, double *dists,
+                  uint32_t *counts);
+/* All neighbours with distance <= radii[i], sorted.  offsets has nq+1
+ * entries; *ids / *dists are allocated by the library (release with
+ * omplcu_free); dists may be NULL. */
+int omplcu_nn_radius(omplcu_nn_t nn, const double *queries, size_t nq, const double *radii, uint64_t **ids,
+                     double **dists, uint64_t *offsets);
+/* device-resident variant: d_queries (nq x stride), d_ids / d_dists (nq x k)
+ * live on the handle's GPU.  Synchronises `stream` before returning. */
+int omplcu_nn_knn_device(omplcu_nn_t nn, const double *d_queries, size_t nq, size_t k, uint64_t *d_ids,
+                         double *d_dists, void *stream);
+/* Merge nparts partial results laid out [part][nq][k] (as produced by an
+ * all-gather of omplcu_nn_knn_device outputs) into the k best per query by
+ * (distance, id).  Device pointers. */
+int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq,
+                             size_t k, double *d_out_dists, uint64_t *d_out_ids, void *stream);
+/* Tuning / introspection.  key: "force_exact" (0/1), "last_fallbacks" (read),
+ * "last_path" (read: 1 fast scan, 2 exact sort), "launches" (read: kernels
+ * launched by this handle so far). */
+int omplcu_nn_set_option(omplcu_nn_t nn, const char *key, long value);
+int omplcu_nn_get_stat(omplcu_nn_t nn, const char *key, long *value);
+
+/* ---- validity ---- */
+int omplcu_checker_create_allvalid(int device, omplcu_checker_t *out);
+int omplcu_checker_create_hypercube(int device, int dim, double edge_width, omplcu_checker_t *out);
+/* env: nenv x (x0,y0,x1,y1) */
+int omplcu_checker_create_chain(int device, int nlinks, double link_length, const double *env, int nenv,
+                                omplcu_checker_t *out);
+/* robot: nrobot x (ox,oy,oz,r); sph: nsph x (cx,cy,cz,r); box: nbox x (cx,cy,cz,hx,hy,hz) */
+int omplcu_checker_create_se3(int device, const double *robot, int nrobot, const double *sph, int nsph,
+                              const double *box, int nbox, omplcu_checker_t *out);
+/* circ: n x (x,y,r) */
+int omplcu_checker_create_circles(int device, const double *circ, int n, omplcu_checker_t *out);
+int omplcu_checker_destroy(omplcu_checker_t c);
+int omplcu_checker_get_stat(omplcu_checker_t c, const char *key, long *value);
+
+/* valid[i] = isValid(states[i]); rows of `stride` doubles. */
+int omplcu_check_states(omplcu_checker_t c, int stride, const double *states, size_t n, uint8_t *valid);
+/* valid[i] = checkMotion(s1[i], s2[i]).  If last_t != NULL the lastValid
+ * overload is evaluated: last_t[i] = lastValid.second on failure, 1.0 on
+ * success; last_state (n x stride, may be NULL) = lastValid.first on failure. */
+int omplcu_check_motions(omplcu_checker_t c, omplcu_space_t sp, const double *s1, const double *s2, size_t n,
+                         uint8_t *valid, double *last_t, double *last_state);
+int omplcu_check_states_device(omplcu_checker_t c, int stride, const double *d_states, size_t n, uint8_t *d_valid,
+                               void *stream);
+int omplcu_check_motions_device(omplcu_checker_t c, omplcu_space_t sp, const double *d_s1, const double *d_s2,
+                                size_t n, uint8_t *d_valid, double *d_last_t, double *d_last_state, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

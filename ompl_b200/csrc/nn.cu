@@ -1,0 +1,998 @@
+// nn.cu -- device-resident nearest-neighbour index behind omplcu_nn_*.
+//
+// Replaces NearestNeighborsLinear (datastructures/NearestNeighborsLinear.h:56-173)
+// for batched queries; results equal Linear's with ties broken by insertion
+// index (total order (distance, id)).
+//
+//   fast path   plain RealVector space, dim <= 16, k <= 40:
+//                 query_prep -> knn_scan (FP32 filter, knn_scan.cuh) -> knn_rerank (exact FP64)
+//                 + exact sort path for the (rare) queries whose band check fails
+//   exact path  any space / any k: FP64 distance rows + stable segmented radix
+//                 sort by (distance, slot); also serves radius queries.
+#include "nn.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <cub/cub.cuh>
+
+#include "knn_scan.cuh"
+
+namespace omplcu
+{
+    namespace
+    {
+        constexpr int KNN_MAX_FAST_DIM = 16;
+        constexpr size_t EXACT_PAIR_BUDGET = (size_t)1 << 25;
+
+        __device__ __forceinline__ float inff()
+        {
+            return __int_as_float(0x7f800000);
+        }
+
+        // ---- filter-copy maintenance ----
+        // rows [first, first+n): coords 0, norm +inf  ("dead": never passes the filter)
+        __global__ void filt_fill_dead_kernel(float *filt, int rowf, int D, size_t first, size_t n)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= n * rowf)
+                return;
+            int c = (int)(i % rowf);
+            filt[first * rowf + i] = (c == D) ? inff() : 0.f;
+        }
+
+        // pt = fl32(p - c); pn = fl32(sum pt^2) (sum in FP64 of exact squares)
+        __global__ void filt_append_kernel(const double *pts, const double *center, float *filt, unsigned *pmax2,
+                                           int D, int rowf, size_t first, size_t n)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            float pn = 0.f;
+            if (i < n)
+            {
+                const double *p = pts + (first + i) * D;
+                float *f = filt + (first + i) * rowf;
+                double acc = 0.0;
+                for (int c = 0; c < D; ++c)
+                {
+                    float v = __double2float_rn(p[c] - center[c]);
+                    f[c] = v;
+                    acc += (double)v * (double)v;
+                }
+                pn = __double2float_rn(acc);
+                f[D] = pn;
+                for (int c = D + 1; c < rowf; ++c)
+                    f[c] = 0.f;
+            }
+            // block max of pn (non-negative floats order like their bit patterns)
+            unsigned b = __float_as_uint(pn);
+            for (int o = 16; o > 0; o >>= 1)
+                b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
+            if ((threadIdx.x & 31) == 0 && b)
+                atomicMax(pmax2, b);
+        }
+
+        __global__ void mark_dead_kernel(uint8_t *alive, float *filt, int rowf, int D, size_t slot)
+        {
+            alive[slot] = 0;
+            if (filt)
+                filt[slot * rowf + D] = inff();
+        }
+
+        __global__ void fill_ids_kernel(uint64_t *ids, uint8_t *alive, size_t first, size_t n, uint64_t id0)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i < n)
+            {
+                ids[first + i] = id0 + i;
+                alive[first + i] = 1;
+            }
+        }
+
+        __global__ void gather_rows_kernel(const double *src, double *dst, const uint64_t *src_ids, uint64_t *dst_ids,
+                                           const uint32_t *live_slots, size_t nlive, int stride)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nlive * stride)
+                return;
+            size_t r = i / stride;
+            int c = (int)(i % stride);
+            dst[i] = src[(size_t)live_slots[r] * stride + c];
+            if (c == 0)
+                dst_ids[r] = src_ids[live_slots[r]];
+        }
+
+        // ---- query preparation for the scan ----
+        // qp[c][q] = -2 * fl32(q_c - center_c); qaux[q] = (|qt|^2, |qt|) in FP64
+        __global__ void query_prep_kernel(const double *q, size_t nq, const double *center, int D, float *qp,
+                                          double *qaux, uint32_t qpad)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= qpad)
+                return;
+            double qn = 0.0;
+            for (int c = 0; c < D; ++c)
+            {
+                float v = 0.f;
+                if (i < nq)
+                    v = __double2float_rn(q[i * D + c] - center[c]);
+                qp[(size_t)c * qpad + i] = -2.f * v;
+                qn += (double)v * (double)v;
+            }
+            qaux[2 * i + 0] = qn;
+            qaux[2 * i + 1] = sqrt(qn);
+        }
+
+        // ---- exact re-rank of the scan's candidate lists (one warp per query) ----
+        // Exact distance = RealVectorStateSpace::distance (RealVectorStateSpace.cpp:230-242)
+        // with argument order (element, query) as in NearestNeighborsLinear.h:159-172.
+        // Selection = the kk smallest by (distance, slot), written in that order.
+        // Band check: let Dk be the kk-th selected exact distance.  Any true
+        // member p* of the kk best has dist(p*) <= Dk, hence ("filter
+        // bound") its scan value s(p*) <= tau(Dk).  A point the scan dropped from
+        // a full list has s >= that list's maximum vL; if vL > tau for every full
+        // list, no dropped point can be p*.  Otherwise the query is flagged and
+        // redone exactly.
+        template <int MAXC>
+        __global__ void __launch_bounds__(128) knn_rerank_kernel(
+            const float *cand_vals, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
+            const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
+            const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
+            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count)
+        {
+            __shared__ double s_key[4][MAXC];
+            __shared__ uint32_t s_slot[4][MAXC];
+            __shared__ double s_dk[4];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t qi = blockIdx.x * 4ull + w;
+            if (qi >= nq)
+                return;
+            const uint32_t n = smax * L;
+            const double *qrow = q + qi * D;
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const uint32_t slot = cand_ids[(size_t)c * qpad + qi];
+                double key = __longlong_as_double(0x7ff0000000000000ll);
+                if (slot != SLOT_NONE)
+                    key = rv_distance(pts + (size_t)slot * D, qrow, D);
+                s_key[w][c] = key;
+                s_slot[w][c] = slot;
+            }
+            if (lane == 0)
+                s_dk[w] = 0.0;
+            __syncwarp();
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const uint32_t slot = s_slot[w][c];
+                if (slot == SLOT_NONE)
+                    continue;
+                const double key = s_key[w][c];
+                uint32_t rank = 0;
+                for (uint32_t o = 0; o < n; ++o)
+                {
+                    const double ko = s_key[w][o];
+                    const uint32_t so = s_slot[w][o];
+                    rank += (ko < key || (ko == key && so < slot)) ? 1u : 0u;
+                }
+                if (rank < kk)
+                {
+                    out_ids[qi * kstride + rank] = slot_ids[slot];
+                    if (out_dists)
+                        out_dists[qi * kstride + rank] = key;
+                    if (rank == kk - 1)
+                        s_dk[w] = key;
+                }
+            }
+            __syncwarp();
+            // ---- band check ----
+            const double u = 5.9604644775390625e-08;  // 2^-24
+            const double dk = s_dk[w];
+            const double qn = qaux[2 * qi], qnorm = qaux[2 * qi + 1];
+            const double pmax2 = (double)__uint_as_float(*pmax2_bits) * (1.0 + 2.0 * u);
+            const double pmax = sqrt(pmax2) * (1.0 + 1e-9);
+            const double delta = (double)(D + 4) * 1.1102230246251565e-16;
+            const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
+            const double A = dk * (1.0 + delta) + rho + 1e-150;
+            const double e1 = (double)(D + 3) * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+            const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
+            const float tau = __double2float_ru(tau64);
+            bool bad = !(tau64 == tau64) || !(tau64 < 1e37);  // NaN / overflow -> redo exactly
+            for (uint32_t s = lane; s < smax; s += 32)
+            {
+                bool full = true;
+                float vmax = -inff();
+                for (uint32_t i = 0; i < L; ++i)
+                {
+                    const size_t o = ((size_t)s * L + i) * qpad + qi;
+                    full = full && (cand_ids[o] != SLOT_NONE);
+                    vmax = fmaxf(vmax, cand_vals[o]);
+                }
+                if (full && !(vmax > tau))
+                    bad = true;
+            }
+            bad = __any_sync(0xffffffffu, bad);
+            if (bad && lane == 0)
+            {
+                unsigned pos = atomicAdd(ovf_count, 1u);
+                ovf_list[pos] = (uint32_t)qi;
+            }
+        }
+
+        // ---- exact path ----
+        // keys[b][slot] = exact distance(point slot, query sel[b]) (+inf for dead slots)
+        __global__ void dist_rows_kernel(SpaceDesc sp, const double *pts, const uint8_t *alive, size_t nslots,
+                                         const double *q, const uint32_t *sel, size_t b0, size_t nb, double *keys,
+                                         uint32_t *vals)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * nslots)
+                return;
+            size_t b = i / nslots, slot = i % nslots;
+            size_t qi = sel ? sel[b0 + b] : (b0 + b);
+            double d = __longlong_as_double(0x7ff0000000000000ll);
+            if (alive[slot])
+                d = space_distance(sp, pts + slot * sp.stride, q + qi * sp.stride);
+            keys[i] = d;
+            vals[i] = (uint32_t)slot;
+        }
+
+        __global__ void exact_emit_kernel(const double *keys, const uint32_t *vals, size_t nslots,
+                                          const uint64_t *slot_ids, const uint32_t *sel, size_t b0, size_t nb,
+                                          uint32_t kk, uint32_t kstride, uint64_t *out_ids, double *out_dists)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * kk)
+                return;
+            size_t b = i / kk, r = i % kk;
+            size_t qi = sel ? sel[b0 + b] : (b0 + b);
+            out_ids[qi * kstride + r] = slot_ids[vals[b * nslots + r]];
+            if (out_dists)
+                out_dists[qi * kstride + r] = keys[b * nslots + r];
+        }
+
+        // pad columns [kk, kstride) with OMPLCU_ID_NONE / +inf
+        __global__ void pad_rows_kernel(uint64_t *ids, double *dists, size_t nq, uint32_t kk, uint32_t kstride)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            uint32_t w = kstride - kk;
+            if (i >= nq * w)
+                return;
+            size_t qi = i / w, r = kk + i % w;
+            ids[qi * kstride + r] = OMPLCU_ID_NONE;
+            if (dists)
+                dists[qi * kstride + r] = __longlong_as_double(0x7ff0000000000000ll);
+        }
+
+        // radius: count of sorted keys <= r per row (binary search), then gather
+        __global__ void radius_count_kernel(const double *keys, size_t nslots, const double *radii, size_t b0,
+                                            size_t nb, size_t nlive_cap, uint32_t *counts)
+        {
+            size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (b >= nb)
+                return;
+            const double r = radii[b0 + b];
+            const double *row = keys + b * nslots;
+            size_t lo = 0, hi = nlive_cap;  // dead slots (+inf keys) sort last and are never counted
+            while (lo < hi)
+            {
+                size_t mid = (lo + hi) / 2;
+                if (row[mid] <= r)
+                    lo = mid + 1;
+                else
+                    hi = mid;
+            }
+            counts[b] = (uint32_t)lo;
+        }
+
+        __global__ void radius_gather_kernel(const double *keys, const uint32_t *vals, size_t nslots,
+                                             const uint64_t *slot_ids, const uint32_t *counts,
+                                             const unsigned long long *offs, size_t nb, uint64_t *out_ids,
+                                             double *out_dists)
+        {
+            size_t b = blockIdx.y;
+            if (b >= nb)
+                return;
+            for (size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x; r < counts[b];
+                 r += (size_t)gridDim.x * blockDim.x)
+            {
+                out_ids[offs[b] + r] = slot_ids[vals[b * nslots + r]];
+                out_dists[offs[b] + r] = keys[b * nslots + r];
+            }
+        }
+
+        // ---- merge of per-shard partial results (one warp per query) ----
+        __global__ void __launch_bounds__(128) merge_topk_kernel(const double *dists, const uint64_t *ids, int nparts,
+                                                                 size_t nq, uint32_t k, double *out_d,
+                                                                 uint64_t *out_i)
+        {
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t qi = blockIdx.x * 4ull + w;
+            if (qi >= nq)
+                return;
+            const uint32_t n = (uint32_t)nparts * k;
+            // pre-fill (fewer than k valid entries overall)
+            for (uint32_t r = lane; r < k; r += 32)
+            {
+                out_i[qi * k + r] = OMPLCU_ID_NONE;
+                out_d[qi * k + r] = __longlong_as_double(0x7ff0000000000000ll);
+            }
+            __syncwarp();
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const size_t oc = ((size_t)(c / k) * nq + qi) * k + (c % k);
+                const uint64_t id = ids[oc];
+                if (id == OMPLCU_ID_NONE)
+                    continue;
+                const double key = dists[oc];
+                uint32_t rank = 0;
+                for (uint32_t o = 0; o < n; ++o)
+                {
+                    const size_t oo = ((size_t)(o / k) * nq + qi) * k + (o % k);
+                    const uint64_t io = ids[oo];
+                    const double ko = dists[oo];
+                    rank += (io != OMPLCU_ID_NONE && (ko < key || (ko == key && io < id))) ? 1u : 0u;
+                }
+                if (rank < k)
+                {
+                    out_i[qi * k + rank] = id;
+                    out_d[qi * k + rank] = key;
+                }
+            }
+        }
+
+        inline unsigned nblk(size_t n, unsigned bs)
+        {
+            return (unsigned)((n + bs - 1) / bs);
+        }
+    }  // namespace
+
+    // ==================================================================
+    // NNIndex
+    // ==================================================================
+    NNIndex::NNIndex(const SpaceDesc &sp, int device) : device_(device), sp_(sp)
+    {
+        DeviceGuard g(device_);
+        CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+        cudaDeviceProp prop;
+        CUDA_CHECK(cudaGetDeviceProperties(&prop, device_));
+        sm_count_ = prop.multiProcessorCount;
+        fast_space_ = (!sp_.compound && sp_.ncomp == 1 && sp_.comp[0].type == OMPLCU_RV &&
+                       sp_.comp[0].dim >= 1 && sp_.comp[0].dim <= KNN_MAX_FAST_DIM);
+        if (fast_space_)
+        {
+            D_ = sp_.comp[0].dim;
+            rowf_ = scan_rowf(D_);
+            center_.reserve(D_);
+            pmax2_.reserve(1);
+            CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
+        }
+        counters_.reserve(4);
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+    }
+
+    NNIndex::~NNIndex()
+    {
+        DeviceGuard g(device_);
+        if (stream_)
+        {
+            cudaStreamSynchronize(stream_);
+            cudaStreamDestroy(stream_);
+        }
+    }
+
+    void NNIndex::set_id_base(uint64_t base)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        REQUIRE(nslots_ == 0, "omplcu_nn_set_id_base: structure is not empty");
+        id_base_ = base;
+    }
+
+    void NNIndex::reserve_slots(size_t n)
+    {
+        const size_t st = (size_t)sp_.stride;
+        pts64_.reserve(n * st, true, stream_);
+        ids_.reserve(n, true, stream_);
+        alive_.reserve(n, true, stream_);
+        if (fast_space_)
+        {
+            size_t rows = ((n + SCAN_PT - 1) / SCAN_PT) * SCAN_PT;
+            if (rows > filt_rows_)
+            {
+                // grow geometrically so repeated single adds stay amortised O(1)
+                size_t want = std::max(rows, filt_rows_ * 2);
+                want = ((want + SCAN_PT - 1) / SCAN_PT) * SCAN_PT;
+                filt_.reserve(want * rowf_, true, stream_);
+                want = (filt_.cap / rowf_ / SCAN_PT) * SCAN_PT;
+                size_t fresh = want - filt_rows_;
+                filt_fill_dead_kernel<<<nblk(fresh * rowf_, 256), 256, 0, stream_>>>(filt_.p, rowf_, D_, filt_rows_,
+                                                                                    fresh);
+                launches_++;
+                CUDA_CHECK(cudaGetLastError());
+                filt_rows_ = want;
+            }
+        }
+    }
+
+    uint64_t NNIndex::add(const double *rows, size_t n)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        const uint64_t first_id = id_base_ + next_seq_;
+        if (n == 0)
+            return first_id;
+        REQUIRE(rows != nullptr, "omplcu_nn_add: rows is NULL");
+        REQUIRE(nslots_ + n < (size_t)0xFFFFFFF0u, "omplcu_nn_add: more than 2^32 slots");
+        const size_t st = (size_t)sp_.stride;
+        reserve_slots(nslots_ + n);
+        CUDA_CHECK(cudaMemcpyAsync(pts64_.p + nslots_ * st, rows, n * st * sizeof(double), cudaMemcpyHostToDevice,
+                                   stream_));
+        fill_ids_kernel<<<nblk(n, 256), 256, 0, stream_>>>(ids_.p, alive_.p, nslots_, n, first_id);
+        launches_++;
+        if (fast_space_)
+        {
+            if (!have_center_)
+            {
+                // centre = mean of the first batch (any fixed vector is valid; a
+                // central one keeps the FP32 error bound tight)
+                std::vector<double> c(D_, 0.0);
+                for (size_t i = 0; i < n; ++i)
+                    for (int d = 0; d < D_; ++d)
+                        c[d] += rows[i * st + d];
+                for (int d = 0; d < D_; ++d)
+                {
+                    c[d] /= (double)n;
+                    if (!std::isfinite(c[d]))
+                        c[d] = 0.0;
+                }
+                CUDA_CHECK(
+                    cudaMemcpyAsync(center_.p, c.data(), D_ * sizeof(double), cudaMemcpyHostToDevice, stream_));
+                CUDA_CHECK(cudaStreamSynchronize(stream_));  // c is a stack-scoped vector
+                have_center_ = true;
+            }
+            filt_append_kernel<<<nblk(n, 256), 256, 0, stream_>>>(pts64_.p, center_.p, filt_.p, pmax2_.p, D_, rowf_,
+                                                                  nslots_, n);
+            launches_++;
+        }
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaStreamSynchronize(stream_));  // caller may free `rows`
+        h_ids_.reserve(nslots_ + n);
+        for (size_t i = 0; i < n; ++i)
+            h_ids_.push_back(first_id + i);
+        h_alive_.insert(h_alive_.end(), n, 1);
+        nslots_ += n;
+        nlive_ += n;
+        next_seq_ += n;
+        return first_id;
+    }
+
+    void NNIndex::remove(uint64_t id)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        auto it = std::lower_bound(h_ids_.begin(), h_ids_.end(), id);
+        if (it == h_ids_.end() || *it != id || !h_alive_[it - h_ids_.begin()])
+            throw Error(OMPLCU_ERR_NOT_FOUND, "omplcu_nn_remove: id not present");
+        const size_t slot = it - h_ids_.begin();
+        h_alive_[slot] = 0;
+        nlive_--;
+        mark_dead_kernel<<<1, 1, 0, stream_>>>(alive_.p, fast_space_ ? filt_.p : nullptr, rowf_, D_, slot);
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+        const size_t dead = nslots_ - nlive_;
+        if (dead > 1024 && dead > nlive_)
+            compact();
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+    }
+
+    // Drop dead slots, keeping insertion order (so slot order stays id order).
+    void NNIndex::compact()
+    {
+        const size_t st = (size_t)sp_.stride;
+        std::vector<uint32_t> live;
+        live.reserve(nlive_);
+        std::vector<uint64_t> nids;
+        nids.reserve(nlive_);
+        for (size_t s = 0; s < nslots_; ++s)
+            if (h_alive_[s])
+            {
+                live.push_back((uint32_t)s);
+                nids.push_back(h_ids_[s]);
+            }
+        if (!live.empty())
+        {
+            DevBuf<uint32_t> d_live;
+            DevBuf<double> npts;
+            DevBuf<uint64_t> nidb;
+            d_live.reserve(live.size());
+            npts.reserve(live.size() * st);
+            nidb.reserve(live.size());
+            CUDA_CHECK(cudaMemcpyAsync(d_live.p, live.data(), live.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                       stream_));
+            gather_rows_kernel<<<nblk(live.size() * st, 256), 256, 0, stream_>>>(pts64_.p, npts.p, ids_.p, nidb.p,
+                                                                                 d_live.p, live.size(), (int)st);
+            launches_++;
+            CUDA_CHECK(cudaMemcpyAsync(pts64_.p, npts.p, live.size() * st * sizeof(double), cudaMemcpyDeviceToDevice,
+                                       stream_));
+            CUDA_CHECK(
+                cudaMemcpyAsync(ids_.p, nidb.p, live.size() * sizeof(uint64_t), cudaMemcpyDeviceToDevice, stream_));
+            CUDA_CHECK(cudaMemsetAsync(alive_.p, 1, live.size(), stream_));
+            CUDA_CHECK(cudaStreamSynchronize(stream_));
+        }
+        const size_t old_slots = nslots_;
+        nslots_ = live.size();
+        h_ids_.swap(nids);
+        h_alive_.assign(nslots_, 1);
+        if (fast_space_)
+        {
+            // rebuild the filter copy for the surviving rows, kill the vacated ones
+            if (nslots_)
+            {
+                filt_append_kernel<<<nblk(nslots_, 256), 256, 0, stream_>>>(pts64_.p, center_.p, filt_.p, pmax2_.p,
+                                                                            D_, rowf_, 0, nslots_);
+                launches_++;
+            }
+            if (old_slots > nslots_)
+            {
+                filt_fill_dead_kernel<<<nblk((old_slots - nslots_) * rowf_, 256), 256, 0, stream_>>>(
+                    filt_.p, rowf_, D_, nslots_, old_slots - nslots_);
+                launches_++;
+            }
+            CUDA_CHECK(cudaGetLastError());
+        }
+    }
+
+    void NNIndex::clear()
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        if (fast_space_ && nslots_)
+        {
+            filt_fill_dead_kernel<<<nblk(nslots_ * rowf_, 256), 256, 0, stream_>>>(filt_.p, rowf_, D_, 0, nslots_);
+            launches_++;
+            CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
+            CUDA_CHECK(cudaStreamSynchronize(stream_));
+        }
+        have_center_ = false;
+        nslots_ = nlive_ = 0;
+        h_ids_.clear();
+        h_alive_.clear();
+        // ids keep increasing across clear() so stale ids can never alias new points
+    }
+
+    size_t NNIndex::list(uint64_t *ids, size_t cap) const
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        size_t c = 0;
+        for (size_t s = 0; s < nslots_; ++s)
+            if (h_alive_[s])
+            {
+                if (c < cap && ids)
+                    ids[c] = h_ids_[s];
+                c++;
+            }
+        return c;
+    }
+
+    void NNIndex::get(uint64_t id, double *row)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        auto it = std::lower_bound(h_ids_.begin(), h_ids_.end(), id);
+        if (it == h_ids_.end() || *it != id || !h_alive_[it - h_ids_.begin()])
+            throw Error(OMPLCU_ERR_NOT_FOUND, "omplcu_nn_get: id not present");
+        const size_t slot = it - h_ids_.begin();
+        CUDA_CHECK(cudaMemcpyAsync(row, pts64_.p + slot * sp_.stride, sp_.stride * sizeof(double),
+                                   cudaMemcpyDeviceToHost, stream_));
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+    }
+
+    void NNIndex::set_option(const char *key, long v)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!strcmp(key, "force_exact"))
+            force_exact_ = v != 0;
+        else
+            throw Error(OMPLCU_ERR_INVALID, std::string("unknown option ") + key);
+    }
+
+    long NNIndex::get_stat(const char *key) const
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!strcmp(key, "last_fallbacks"))
+            return last_fallbacks_;
+        if (!strcmp(key, "last_path"))
+            return last_path_;
+        if (!strcmp(key, "launches"))
+            return launches_;
+        if (!strcmp(key, "slots"))
+            return (long)nslots_;
+        if (!strcmp(key, "fast_space"))
+            return fast_space_ ? 1 : 0;
+        throw Error(OMPLCU_ERR_INVALID, std::string("unknown stat ") + key);
+    }
+
+    // ==================================================================
+    // queries
+    // ==================================================================
+    bool NNIndex::fast_eligible(size_t kk) const
+    {
+        return fast_space_ && !force_exact_ && kk >= 1 && kk <= 40 && nslots_ >= 1;
+    }
+
+    namespace
+    {
+        // action 0: report resident CTAs per SM; action 1: launch
+        template <int D, int RQ, int L>
+        void scan_action(int action, const ScanParams *P, unsigned grid, cudaStream_t s, int *occ)
+        {
+            const size_t smem = scan_smem_bytes(D, RQ, L);
+            static bool configured[64] = {};  // per device
+            int dev = 0;
+            cudaGetDevice(&dev);
+            if (!configured[dev & 63])
+            {
+                CUDA_CHECK(cudaFuncSetAttribute(knn_scan_kernel<D, RQ, L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                                (int)smem));
+                configured[dev & 63] = true;
+            }
+            if (action == 0)
+                CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, knn_scan_kernel<D, RQ, L>, SCAN_THREADS,
+                                                                         smem));
+            else
+                knn_scan_kernel<D, RQ, L><<<grid, SCAN_THREADS, smem, s>>>(*P);
+        }
+
+        template <int RQ, int L>
+        void dispatch_scan(int D, int action, const ScanParams *P, unsigned grid, cudaStream_t s, int *occ)
+        {
+            switch (D)
+            {
+#define OMPLCU_SCAN_CASE(d)                                  \
+    case d:                                                  \
+        scan_action<d, RQ, L>(action, P, grid, s, occ);      \
+        break;
+                OMPLCU_SCAN_CASE(1)
+                OMPLCU_SCAN_CASE(2)
+                OMPLCU_SCAN_CASE(3)
+                OMPLCU_SCAN_CASE(4)
+                OMPLCU_SCAN_CASE(5)
+                OMPLCU_SCAN_CASE(6)
+                OMPLCU_SCAN_CASE(7)
+                OMPLCU_SCAN_CASE(8)
+                OMPLCU_SCAN_CASE(9)
+                OMPLCU_SCAN_CASE(10)
+                OMPLCU_SCAN_CASE(11)
+                OMPLCU_SCAN_CASE(12)
+                OMPLCU_SCAN_CASE(13)
+                OMPLCU_SCAN_CASE(14)
+                OMPLCU_SCAN_CASE(15)
+                OMPLCU_SCAN_CASE(16)
+#undef OMPLCU_SCAN_CASE
+                default:
+                    throw Error(OMPLCU_ERR_INTERNAL, "scan: unsupported dimension");
+            }
+        }
+
+        // (RQ, L) per k range: k<=10 -> (4,12); k<=14 -> (4,16); k<=40 -> (2,42)
+        void scan_any(int cfg, int D, int action, const ScanParams *P, unsigned grid, cudaStream_t s, int *occ)
+        {
+            if (cfg == 0)
+                dispatch_scan<4, 12>(D, action, P, grid, s, occ);
+            else if (cfg == 1)
+                dispatch_scan<4, 16>(D, action, P, grid, s, occ);
+            else
+                dispatch_scan<2, 42>(D, action, P, grid, s, occ);
+        }
+    }  // namespace
+
+    // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
+    void NNIndex::knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+                           double *d_dists, cudaStream_t s)
+    {
+        const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
+        const int RQ = cfg == 2 ? 2 : 4, L = cfg == 0 ? 12 : (cfg == 1 ? 16 : 42);
+        const size_t QT = (size_t)SCAN_THREADS * RQ;
+        const size_t qtiles = (nq + QT - 1) / QT;
+        const uint32_t qpad = (uint32_t)(qtiles * QT);
+        const unsigned long long U = (nslots_ + SCAN_PT - 1) / SCAN_PT;
+        const unsigned long long TU = qtiles * U;
+        int resident = 1;  // CTAs per SM: one persistent CTA per resident slot
+        scan_any(cfg, D_, 0, nullptr, 0, s, &resident);
+        resident = std::max(resident, 1);
+        const unsigned max_seg = 512 / L;  // candidate slots per query <= 512
+        unsigned long long G = (unsigned long long)sm_count_ * resident;
+        G = std::min<unsigned long long>(G, TU);
+        G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
+        G = std::max<unsigned long long>(G, 1);
+        // pieces overlapping one query tile (same formulas as the kernel)
+        uint32_t smax = 1;
+        for (size_t t = 0; t < qtiles; ++t)
+        {
+            unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
+            unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
+            unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
+            smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
+        }
+        if ((size_t)smax * L > 512)
+            throw Error(OMPLCU_ERR_INTERNAL, "scan: too many segments per query tile");
+
+        qp_.reserve((size_t)D_ * qpad);
+        qaux_.reserve(2 * (size_t)qpad);
+        cand_vals_.reserve((size_t)smax * L * qpad);
+        cand_ids_.reserve((size_t)smax * L * qpad);
+        ovf_list_.reserve(nq);
+
+        CUDA_CHECK(cudaMemsetAsync(cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(counters_.p, 0, sizeof(unsigned), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, qp_.p, qaux_.p, qpad);
+        launches_++;
+
+        ScanParams P;
+        P.filt = filt_.p;
+        P.qp = qp_.p;
+        P.cand_vals = cand_vals_.p;
+        P.cand_ids = cand_ids_.p;
+        P.units = U;
+        P.total_units = TU;
+        P.qpad = qpad;
+        P.smax = smax;
+        scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+
+        knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(cand_vals_.p, cand_ids_.p, smax, (uint32_t)L, qpad,
+                                                          pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
+                                                          (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists,
+                                                          ovf_list_.p, counters_.p);
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+        unsigned novf = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&novf, counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        last_fallbacks_ = novf;
+        if (novf)
+            knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
+    }
+
+    void NNIndex::knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                            uint64_t *d_ids, double *d_dists, cudaStream_t s)
+    {
+        if (nsel == 0 || nslots_ == 0)
+            return;
+        REQUIRE(nslots_ < ((size_t)1 << 31), "exact path: too many slots");
+        size_t nb_max = std::max<size_t>(1, std::min(nsel, EXACT_PAIR_BUDGET / nslots_));
+        ex_keys_.reserve(nb_max * nslots_);
+        ex_keys2_.reserve(nb_max * nslots_);
+        ex_vals_.reserve(nb_max * nslots_);
+        ex_vals2_.reserve(nb_max * nslots_);
+        ex_offs_.reserve(nb_max + 1);
+        std::vector<int> offs(nb_max + 1);
+        for (size_t b = 0; b <= nb_max; ++b)
+            offs[b] = (int)(b * nslots_);
+        CUDA_CHECK(cudaMemcpyAsync(ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        for (size_t b0 = 0; b0 < nsel; b0 += nb_max)
+        {
+            const size_t nb = std::min(nb_max, nsel - b0);
+            const size_t items = nb * nslots_;
+            REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
+            dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(sp_, pts64_.p, alive_.p, nslots_, d_q, d_sel, b0, nb,
+                                                              ex_keys_.p, ex_vals_.p);
+            launches_++;
+            CUDA_CHECK(cudaGetLastError());
+            size_t tmp = 0;
+            if (nb == 1)
+            {
+                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
+                                                           ex_vals2_.p, (int)items, 0, 64, s));
+                cub_tmp_.reserve(tmp);
+                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
+                                                           ex_vals2_.p, (int)items, 0, 64, s));
+            }
+            else
+            {
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
+                                                                    ex_vals2_.p, (int)items, (int)nb, ex_offs_.p,
+                                                                    ex_offs_.p + 1, 0, 64, s));
+                cub_tmp_.reserve(tmp);
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p,
+                                                                    ex_vals_.p, ex_vals2_.p, (int)items, (int)nb,
+                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
+            }
+            launches_ += 8;
+            exact_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(ex_keys2_.p, ex_vals2_.p, nslots_, ids_.p, d_sel, b0,
+                                                                 nb, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists);
+            launches_++;
+            CUDA_CHECK(cudaGetLastError());
+        }
+        CUDA_CHECK(cudaStreamSynchronize(s));
+    }
+
+    void NNIndex::knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                             cudaStream_t s)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        if (nq == 0 || k == 0)
+            return;
+        REQUIRE(d_q && d_ids, "omplcu_nn_knn: NULL buffer");
+        REQUIRE(k < ((size_t)1 << 31), "omplcu_nn_knn: k too large");
+        const size_t kk = std::min(k, nlive_);
+        last_fallbacks_ = 0;
+        if (kk > 0)
+        {
+            if (fast_eligible(kk))
+            {
+                last_path_ = 1;
+                knn_fast(d_q, nq, kk, k, d_ids, d_dists, s);
+            }
+            else
+            {
+                last_path_ = 2;
+                knn_exact(d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
+            }
+        }
+        if (kk < k)
+        {
+            pad_rows_kernel<<<nblk(nq * (k - kk), 256), 256, 0, s>>>(d_ids, d_dists, nq, (uint32_t)kk, (uint32_t)k);
+            launches_++;
+            CUDA_CHECK(cudaGetLastError());
+        }
+        CUDA_CHECK(cudaStreamSynchronize(s));
+    }
+
+    void NNIndex::knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts)
+    {
+        if (nq == 0)
+            return;
+        REQUIRE(q && ids, "omplcu_nn_knn: NULL buffer");
+        const size_t st = (size_t)sp_.stride;
+        size_t kk;
+        {
+            DeviceGuard g(device_);
+            // staging buffers are per-handle: serialise host-pointer calls
+            std::lock_guard<std::mutex> hl(host_mu_);
+            {
+                std::lock_guard<std::mutex> lk(mu_);
+                q_stage_.reserve(nq * st);
+                out_i_.reserve(nq * std::max<size_t>(k, 1));
+                out_d_.reserve(nq * std::max<size_t>(k, 1));
+                kk = std::min(k, nlive_);
+            }
+            CUDA_CHECK(cudaMemcpyAsync(q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, stream_));
+            if (k > 0)
+            {
+                knn_device(q_stage_.p, nq, k, out_i_.p, out_d_.p, stream_);
+                CUDA_CHECK(cudaMemcpyAsync(ids, out_i_.p, nq * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream_));
+                if (dists)
+                    CUDA_CHECK(
+                        cudaMemcpyAsync(dists, out_d_.p, nq * k * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+            }
+            CUDA_CHECK(cudaStreamSynchronize(stream_));
+        }
+        if (counts)
+            for (size_t i = 0; i < nq; ++i)
+                counts[i] = (uint32_t)kk;
+    }
+
+    // NearestNeighborsLinear::nearestR (NearestNeighborsLinear.h:135-142): all
+    // elements with distance <= radius (inclusive), sorted; via the exact path.
+    void NNIndex::radius_host(const double *q, size_t nq, const double *radii, uint64_t **ids, double **dists,
+                              uint64_t *offsets)
+    {
+        REQUIRE(ids && offsets, "omplcu_nn_radius: NULL output");
+        *ids = nullptr;
+        if (dists)
+            *dists = nullptr;
+        offsets[0] = 0;
+        if (nq == 0)
+            return;
+        REQUIRE(q && radii, "omplcu_nn_radius: NULL buffer");
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        cudaStream_t s = stream_;
+        const size_t st = (size_t)sp_.stride;
+        std::vector<uint64_t> all_ids;
+        std::vector<double> all_d;
+        if (nslots_ > 0 && nlive_ > 0)
+        {
+            REQUIRE(nslots_ < ((size_t)1 << 31), "radius: too many slots");
+            q_stage_.reserve(nq * st);
+            DevBuf<double> d_r;
+            d_r.reserve(nq);
+            CUDA_CHECK(cudaMemcpyAsync(q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, s));
+            CUDA_CHECK(cudaMemcpyAsync(d_r.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
+            size_t nb_max = std::max<size_t>(1, std::min(nq, EXACT_PAIR_BUDGET / nslots_));
+            ex_keys_.reserve(nb_max * nslots_);
+            ex_keys2_.reserve(nb_max * nslots_);
+            ex_vals_.reserve(nb_max * nslots_);
+            ex_vals2_.reserve(nb_max * nslots_);
+            ex_offs_.reserve(nb_max + 1);
+            DevBuf<uint32_t> d_cnt;
+            DevBuf<unsigned long long> d_off;
+            d_cnt.reserve(nb_max);
+            d_off.reserve(nb_max);
+            std::vector<int> offs(nb_max + 1);
+            for (size_t b = 0; b <= nb_max; ++b)
+                offs[b] = (int)(b * nslots_);
+            CUDA_CHECK(
+                cudaMemcpyAsync(ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+            std::vector<uint32_t> cnt(nb_max);
+            std::vector<unsigned long long> boff(nb_max);
+            for (size_t b0 = 0; b0 < nq; b0 += nb_max)
+            {
+                const size_t nb = std::min(nb_max, nq - b0);
+                const size_t items = nb * nslots_;
+                dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(sp_, pts64_.p, alive_.p, nslots_, q_stage_.p,
+                                                                  nullptr, b0, nb, ex_keys_.p, ex_vals_.p);
+                size_t tmp = 0;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
+                                                                    ex_vals2_.p, (int)items, (int)nb, ex_offs_.p,
+                                                                    ex_offs_.p + 1, 0, 64, s));
+                cub_tmp_.reserve(tmp);
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p,
+                                                                    ex_vals_.p, ex_vals2_.p, (int)items, (int)nb,
+                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
+                radius_count_kernel<<<nblk(nb, 128), 128, 0, s>>>(ex_keys2_.p, nslots_, d_r.p, b0, nb, nlive_,
+                                                                  d_cnt.p);
+                launches_ += 10;
+                CUDA_CHECK(cudaMemcpyAsync(cnt.data(), d_cnt.p, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                unsigned long long tot = 0;
+                for (size_t b = 0; b < nb; ++b)
+                {
+                    boff[b] = tot;
+                    tot += cnt[b];
+                    offsets[b0 + b + 1] = offsets[b0 + b] + cnt[b];
+                }
+                if (tot)
+                {
+                    DevBuf<uint64_t> d_oi;
+                    DevBuf<double> d_od;
+                    d_oi.reserve(tot);
+                    d_od.reserve(tot);
+                    CUDA_CHECK(cudaMemcpyAsync(d_off.p, boff.data(), nb * sizeof(unsigned long long),
+                                               cudaMemcpyHostToDevice, s));
+                    dim3 grid(std::max<unsigned>(1, std::min<unsigned>(64, nblk(nlive_, 256))), (unsigned)nb);
+                    radius_gather_kernel<<<grid, 256, 0, s>>>(ex_keys2_.p, ex_vals2_.p, nslots_, ids_.p, d_cnt.p,
+                                                              d_off.p, nb, d_oi.p, d_od.p);
+                    launches_++;
+                    CUDA_CHECK(cudaGetLastError());
+                    const size_t base = all_ids.size();
+                    all_ids.resize(base + tot);
+                    all_d.resize(base + tot);
+                    CUDA_CHECK(cudaMemcpyAsync(all_ids.data() + base, d_oi.p, tot * sizeof(uint64_t),
+                                               cudaMemcpyDeviceToHost, s));
+                    CUDA_CHECK(cudaMemcpyAsync(all_d.data() + base, d_od.p, tot * sizeof(double),
+                                               cudaMemcpyDeviceToHost, s));
+                    CUDA_CHECK(cudaStreamSynchronize(s));
+                }
+            }
+        }
+        else
+            for (size_t i = 0; i < nq; ++i)
+                offsets[i + 1] = 0;
+        const size_t tot = all_ids.size();
+        *ids = (uint64_t *)malloc(std::max<size_t>(tot, 1) * sizeof(uint64_t));
+        REQUIRE(*ids != nullptr, "omplcu_nn_radius: out of host memory");
+        memcpy(*ids, all_ids.data(), tot * sizeof(uint64_t));
+        if (dists)
+        {
+            *dists = (double *)malloc(std::max<size_t>(tot, 1) * sizeof(double));
+            REQUIRE(*dists != nullptr, "omplcu_nn_radius: out of host memory");
+            memcpy(*dists, all_d.data(), tot * sizeof(double));
+        }
+    }
+
+    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq, size_t k,
+                           double *d_out_dists, uint64_t *d_out_ids, cudaStream_t s)
+    {
+        DeviceGuard g(device);
+        REQUIRE(nparts >= 1 && d_dists && d_ids && d_out_dists && d_out_ids, "omplcu_merge_topk: bad arguments");
+        if (nq == 0 || k == 0)
+            return;
+        merge_topk_kernel<<<nblk(nq, 4), 128, 0, s>>>(d_dists, d_ids, nparts, nq, (uint32_t)k, d_out_dists,
+                                                      d_out_ids);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaStreamSynchronize(s));
+    }
+}  // namespace omplcu

@@ -1,0 +1,106 @@
+// nn.cuh -- device-resident nearest-neighbour index (host-side class).
+#pragma once
+#include <mutex>
+#include <vector>
+
+#include "common.cuh"
+
+namespace omplcu
+{
+    struct Space
+    {
+        SpaceDesc desc;
+    };
+
+    // Device mirror of NearestNeighbors<_T>'s element set
+    // (datastructures/NearestNeighbors.h:46-115): coordinates only; the C++
+    // adapter keeps id -> _T.  Slots are kept in insertion order, so slot order
+    // == id order and "ties by insertion index" is "ties by slot".
+    class NNIndex
+    {
+    public:
+        NNIndex(const SpaceDesc &sp, int device);
+        ~NNIndex();
+
+        void set_id_base(uint64_t base);
+        uint64_t add(const double *rows, size_t n);
+        void remove(uint64_t id);
+        void clear();
+        size_t size() const
+        {
+            return nlive_;
+        }
+        size_t list(uint64_t *ids, size_t cap) const;
+        void get(uint64_t id, double *row);
+
+        // device pointers; synchronises the stream
+        void knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists, cudaStream_t s);
+        void knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts);
+        void radius_host(const double *q, size_t nq, const double *radii, uint64_t **ids, double **dists,
+                         uint64_t *offsets);
+
+        void set_option(const char *key, long v);
+        long get_stat(const char *key) const;
+
+        int device() const
+        {
+            return device_;
+        }
+        const SpaceDesc &space() const
+        {
+            return sp_;
+        }
+
+    private:
+        void reserve_slots(size_t n);
+        void compact();
+        bool fast_eligible(size_t kk) const;
+        void knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
+                      cudaStream_t s);
+        // exact sort path over the selected queries (d_sel == nullptr: all nq)
+        void knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                       uint64_t *d_ids, double *d_dists, cudaStream_t s);
+
+        int device_;
+        SpaceDesc sp_;
+        cudaStream_t stream_ = nullptr;
+        mutable std::mutex mu_, host_mu_;
+
+        size_t nslots_ = 0, nlive_ = 0;
+        uint64_t id_base_ = 0, next_seq_ = 0;
+        std::vector<uint64_t> h_ids_;
+        std::vector<uint8_t> h_alive_;
+
+        DevBuf<double> pts64_;
+        DevBuf<uint64_t> ids_;
+        DevBuf<uint8_t> alive_;
+
+        // FP32 filter copy (plain RealVector spaces with dim <= 16)
+        bool fast_space_ = false;
+        int D_ = 0, rowf_ = 0;
+        size_t filt_rows_ = 0;  // rows initialised (multiple of SCAN_PT)
+        DevBuf<float> filt_;
+        DevBuf<double> center_;
+        DevBuf<unsigned> pmax2_;  // bits of max fl32(|pt|^2)
+        bool have_center_ = false;
+
+        // query scratch
+        DevBuf<double> q_stage_, out_d_;
+        DevBuf<uint64_t> out_i_;
+        DevBuf<float> qp_, cand_vals_;
+        DevBuf<double> qaux_;
+        DevBuf<uint32_t> cand_ids_, ovf_list_;
+        DevBuf<unsigned> counters_;
+        DevBuf<double> ex_keys_, ex_keys2_;
+        DevBuf<uint32_t> ex_vals_, ex_vals2_;
+        DevBuf<int> ex_offs_;
+        DevBuf<unsigned char> cub_tmp_;
+
+        int sm_count_ = 148;
+        bool force_exact_ = false;
+        long last_fallbacks_ = 0, last_path_ = 0, launches_ = 0;
+    };
+
+    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq, size_t k,
+                           double *d_out_dists, uint64_t *d_out_ids, cudaStream_t s);
+}  // namespace omplcu

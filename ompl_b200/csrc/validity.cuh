@@ -1,0 +1,79 @@
+// validity.cuh -- host-side classes for batched validity checking.
+#pragma once
+#include <atomic>
+#include <mutex>
+
+#include "common.cuh"
+
+namespace omplcu
+{
+    enum
+    {
+        OMPLCU_CHK_ALLVALID = 0,
+        OMPLCU_CHK_HYPERCUBE = 1,
+        OMPLCU_CHK_CHAIN = 2,
+        OMPLCU_CHK_SE3 = 3,
+        OMPLCU_CHK_CIRCLES = 4
+    };
+    constexpr int MAX_CHAIN_LINKS = 128;
+
+    // passed to kernels by value; pointers are device pointers owned by Checker
+    struct CheckerDesc
+    {
+        int kind;
+        int dim;
+        double edge_width;
+        int nlinks;
+        int nenv;
+        double link_length;
+        const double *env;
+        int nrobot, nsph, nbox, ncirc;
+        const double *robot, *sph, *box, *circ;
+        int stage_smem;
+        int _pad;
+    };
+
+    class Checker
+    {
+    public:
+        Checker(int device, const CheckerDesc &proto, const double *env, const double *robot, const double *sph,
+                const double *box, const double *circ);
+        ~Checker();
+
+        void check_states_device(int stride, const double *d_states, size_t n, uint8_t *d_valid, cudaStream_t s);
+        void check_motions_device(const SpaceDesc &sp, const double *d_s1, const double *d_s2, size_t n,
+                                  uint8_t *d_valid, double *d_last_t, double *d_last_state, cudaStream_t s);
+        void check_states_host(int stride, const double *states, size_t n, uint8_t *valid);
+        void check_motions_host(const SpaceDesc &sp, const double *s1, const double *s2, size_t n, uint8_t *valid,
+                                double *last_t, double *last_state);
+        long get_stat(const char *key) const;
+        int device() const
+        {
+            return device_;
+        }
+
+    private:
+        int device_;
+        CheckerDesc desc_;
+        cudaStream_t stream_ = nullptr;
+        std::mutex mu_;
+        DevBuf<double> params_;
+        size_t smem_bytes_ = 0;
+        // scratch
+        DevBuf<uint32_t> nd_;
+        DevBuf<unsigned long long> cnt_, offs_;
+        DevBuf<unsigned> code_;
+        DevBuf<unsigned char> cub_tmp_;
+        DevBuf<double> st_a_, st_b_, st_t_, st_ls_;
+        DevBuf<uint8_t> st_v_;
+        long launches_ = 0;
+        long last_states_ = 0;
+    };
+
+    // batched space math (host buffers) used by the parity tests and adapters
+    void space_distance_host(const SpaceDesc &sp, int device, const double *a, const double *b, size_t n, double *out);
+    void space_interpolate_host(const SpaceDesc &sp, int device, const double *a, const double *b, const double *t,
+                                size_t n, double *out);
+    void space_segment_count_host(const SpaceDesc &sp, int device, const double *a, const double *b, size_t n,
+                                  uint32_t *out);
+}  // namespace omplcu
