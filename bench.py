@@ -1,0 +1,351 @@
+#!/usr/bin/env python
+"""bench.py -- the reference's headline metric for the hot path on B200.
+
+metric   kNN queries/s, k = 10, 1M states (BASELINE.json `metric`)
+workload BASELINE configs[2]: RealVectorStateSpace(7), 1M states uniform in
+         [0,1]^7, one batch of 65536 queries, k = 10 (synthetic, seeded)
+step     one batched nearestK over the whole query batch
+
+  value      device-resident: queries / ids / distances live in HBM
+  e2e        through the host-pointer C-ABI call omplcu_nn_knn (what the C++
+             adapter NearestNeighborsCUDA::nearestKBatch calls): H2D of the
+             queries and D2H of ids + distances inside the timed region
+  roofline   the scan kernel (knn_scan_kernel), FP32-pipe bound; its duration
+             is measured live with CUDA events on the launching stream
+  cpu_baseline / --impl reference
+             the reference's own NearestNeighborsGNAT (oracle/_ref, compiled
+             from the reference headers) on all host threads; falls back to the
+             oracle port of NearestNeighborsLinear when _ref was not built
+
+N > 1 (torchrun, one rank per GPU): the 1M states are sharded by insertion
+index across ranks (strong scaling); every rank answers all queries on its
+shard, the per-rank top-k lists are exchanged with one NCCL all-gather and
+merged by (distance, id).
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
+METRIC = "kNN queries/sec (k=10, 1M states)"
+UNIT = "queries/s"
+
+
+def make_inputs(n_states=N_STATES, n_queries=N_QUERIES):
+    pts = np.random.default_rng(1).random((n_states, DIM))
+    qs = np.random.default_rng(1001).random((n_queries, DIM))
+    return pts, qs
+
+
+# ---------------------------------------------------------------------------
+# clocks: sample nvidia-smi during the timed region
+# ---------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.rows, self.proc, self.index = [], None, index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.index)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for ln in self.proc.stdout:
+            self.rows.append([x.strip() for x in ln.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# reference arm / cpu baseline (the ONLY place bench.py executes oracle/)
+# ---------------------------------------------------------------------------
+def host_threads():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+def build_cpu_reference(pts):
+    from oracle import oracle_py as orc
+
+    sp = orc.space_rv(DIM)
+    if orc.have_ref():
+        t0 = time.perf_counter()
+        nn = orc.RefNN(orc.RefNN.GNAT, sp)
+        nn.add(pts, reserve_query_slots=4096)
+        build_s = time.perf_counter() - t0
+
+        def run(q, nthreads):
+            t0 = time.perf_counter()
+            nn.knn(q, K, nthreads)
+            return time.perf_counter() - t0
+
+        return "reference", "NearestNeighborsGNAT (reference headers, oracle/_ref)", build_s, run
+
+    def run(q, nthreads):
+        t0 = time.perf_counter()
+        orc.knn(sp, pts, q, K, nthreads)
+        return time.perf_counter() - t0
+
+    return "port", "NearestNeighborsLinear restatement (oracle port)", 0.0, run
+
+
+def cpu_sample_size(kind, cores):
+    # ~10-20 s of CPU work: GNAT ~800 q/s/thread, Linear port ~150 q/s/thread at N = 1M
+    per = 8192 if kind == "reference" else 1024
+    return per * cores
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    pts, qs_all = make_inputs()
+    cores = host_threads()
+    kind, what, build_s, run = build_cpu_reference(pts)
+    per_step = max(cores * (256 if kind == "reference" else 32), 64)
+    qs = np.random.default_rng(7).random((per_step * (args.steps + args.warmup), DIM))
+    for w in range(args.warmup):
+        run(qs[w * per_step:(w + 1) * per_step], cores)
+    t = 0.0
+    for s in range(args.warmup, args.warmup + args.steps):
+        t += run(qs[s * per_step:(s + 1) * per_step], cores)
+    value = per_step * args.steps / t
+    sample = f"{per_step} queries/step x {args.steps} steps vs 1M states, {cores} threads, {what}"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": "RealVectorStateSpace(7), 1M states, k=10 (bounded query sample per step)",
+                   "n_states": N_STATES, "k": K, "queries_per_step": per_step},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                         "build_s": build_s},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------
+def run_gpu_arm(args):
+    import torch
+
+    import ompl_b200 as ob
+    from ompl_b200._lib import check, lib
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+    L = lib()
+
+    pts, qs = make_inputs()
+    lo, hi = N_STATES * rank // world, N_STATES * (rank + 1) // world
+    sp = ob.RealVectorStateSpace(DIM, device=local)
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.set_id_base(lo)
+    nn.add_rows(pts[lo:hi])
+    nn.set_option("profile", 1)
+
+    d_q = torch.from_numpy(qs).to(dev)
+    d_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
+    d_d = torch.empty((N_QUERIES, K), dtype=torch.float64, device=dev)
+    if world > 1:
+        g_ids = torch.empty((world, N_QUERIES, K), dtype=torch.int64, device=dev)
+        g_d = torch.empty((world, N_QUERIES, K), dtype=torch.float64, device=dev)
+        m_ids, m_d = torch.empty_like(d_ids), torch.empty_like(d_d)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream()
+    sptr = C.c_void_p(stream.cuda_stream)
+
+    def step_device():
+        check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), N_QUERIES, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
+        if world > 1:
+            dist.all_gather_into_tensor(g_ids, d_ids)
+            dist.all_gather_into_tensor(g_d, d_d)
+            check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
+                                             m_d.data_ptr(), m_ids.data_ptr(), sptr))
+
+    h_ids = np.empty((N_QUERIES, K), dtype=np.uint64)
+    h_d = np.empty((N_QUERIES, K), dtype=np.float64)
+    h_cnt = np.empty(N_QUERIES, dtype=np.uint32)
+    pin = lambda a: torch.cuda.cudart().cudaHostRegister(a.ctypes.data, a.nbytes, 0)  # noqa: E731
+    for a in (qs, h_ids, h_d):
+        pin(a)
+
+    def step_e2e():
+        # host buffers in, host buffers out: the reference-facing call
+        check(L.omplcu_nn_knn(nn.handle, qs.ctypes.data, N_QUERIES, K, h_ids.ctypes.data, h_d.ctypes.data,
+                              h_cnt.ctypes.data))
+        if world > 1:
+            # sharded roadmap: merge needs the other shards' lists; exchange on the device
+            d_ids.copy_(torch.from_numpy(h_ids.view(np.int64)), non_blocking=True)
+            d_d.copy_(torch.from_numpy(h_d), non_blocking=True)
+            dist.all_gather_into_tensor(g_ids, d_ids)
+            dist.all_gather_into_tensor(g_d, d_d)
+            check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
+                                             m_d.data_ptr(), m_ids.data_ptr(), sptr))
+            h_ids.view(np.int64)[:] = m_ids.cpu().numpy()
+            h_d[:] = m_d.cpu().numpy()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(step, steps, warmup, sampler=None):
+        for _ in range(warmup):
+            flush.fill_(1)
+            step()
+        barrier()
+        if sampler:
+            sampler.start()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        wall = 0.0
+        for a, b in ev:
+            flush.fill_(1)  # L2 flush between timed iterations (not timed)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            a.record(stream)
+            step()
+            b.record(stream)
+            b.synchronize()
+            wall += time.perf_counter() - t0
+        barrier()
+        clocks = sampler.stop() if sampler else None
+        dev_ms = sum(a.elapsed_time(b) for a, b in ev)
+        # the host-pointer path synchronises inside the call; wall and device time agree there
+        ms = max(dev_ms, 0.0)
+        t = torch.tensor([ms, wall * 1e3], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t[0]), float(t[1]), clocks
+
+    l0 = nn.stat("launches")
+    nn.set_option("profile", 1)
+    sampler = ClockSampler(local) if rank == 0 else None
+    dev_ms, _, clocks = timed(step_device, args.steps, args.warmup, sampler)
+    launches = nn.stat("launches") - l0 + (args.steps + args.warmup) * (1 if world > 1 else 0)
+    launches_timed = launches * args.steps // (args.steps + args.warmup)
+    scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
+    fallbacks = nn.stat("last_fallbacks")
+    _, e2e_wall_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
+
+    # sanity: device-resident and host-pointer results agree (same code path underneath)
+    res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
+    assert (res_ids == h_ids).all(), "device and host entry points disagree"
+
+    if rank == 0:
+        t_step = dev_ms / args.steps
+        value = N_QUERIES / (t_step * 1e-3)
+        e2e_val = N_QUERIES / (e2e_wall_ms / args.steps * 1e-3)
+        # roofline of the dominant kernel (the scan), FP32 pipe
+        ffma, ffma2 = C.c_double(), C.c_double()
+        check(L.omplcu_measure_fp32_peak(local, C.byref(ffma), C.byref(ffma2)))
+        peak = max(ffma.value, ffma2.value)
+        pairs = float(N_QUERIES) * (hi - lo)
+        alg_flops = 3.0 * DIM * pairs           # sub, mul, add per dimension
+        exe_flops = 2.0 * DIM * pairs           # what the kernel issues: DIM FMAs per pair
+        ach = alg_flops / (scan_ns * 1e-9) / 1e12
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except OSError:
+            pass
+        hbm_peak = peaks.get("hbm_gbs", 6650.0)
+        scan_bytes = 4.0 * 8 * (hi - lo) * (N_QUERIES / 512.0)  # every query tile streams the filter copy (L2-resident)
+        roofline = {
+            "bound": "fp32", "kernel": "knn_scan_kernel<7,4,12>", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
+            "frac": ach / peak if peak else None, "traffic": None,
+            "peak_source": "FP32 FMA pipe measured live on this GPU (omplcu_measure_fp32_peak: FFMA "
+                           f"{ffma.value:.1f}, FFMA2 {ffma2.value:.1f} TFLOP/s); MEASURED_PEAKS.json has no FP32 figure",
+            "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * DIM,
+            "frac_executed": exe_flops / (scan_ns * 1e-9) / 1e12 / peak if peak else None,
+            "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
+            "hbm_view": {"l2_stream_gbs": scan_bytes / (scan_ns * 1e-9) / 1e9, "hbm_peak_gbs": hbm_peak,
+                         "note": "filter copy (32 MB) is L2-resident; HBM is not the bound for batched queries"},
+        }
+        out = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32 filter + f64 exact re-rank", "data": "synthetic",
+            "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
+                       "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
+                       "sharding": f"states split by insertion index over {world} rank(s); NCCL all-gather + merge"
+                       if world > 1 else "single GPU",
+                       "l2": "flushed between timed iterations (256 MB write)"},
+            "clocks": clocks,
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes),
+                    "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes)},
+            "gpu_launches": int(launches_timed),
+            "roofline": roofline,
+            "exact_fallback_queries": int(fallbacks),
+        }
+        if world == 1 and not args.no_cpu:
+            cores = host_threads()
+            kind, what, build_s, run = build_cpu_reference(pts)
+            nsamp = min(cpu_sample_size(kind, cores), N_QUERIES)
+            secs = run(qs[:nsamp], cores)
+            out["cpu_baseline"] = {"value": nsamp / secs, "unit": UNIT, "cores": cores, "kind": kind,
+                                   "sample": f"first {nsamp} of the 65536 queries vs the same 1M states, "
+                                             f"{cores} threads, {what}; build {build_s:.2f} s not counted"}
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -366,6 +366,8 @@ namespace omplcu
             CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
         }
         counters_.reserve(4);
+        CUDA_CHECK(cudaEventCreate(&ev0_));
+        CUDA_CHECK(cudaEventCreate(&ev1_));
         CUDA_CHECK(cudaStreamSynchronize(stream_));
     }
 
@@ -377,6 +379,10 @@ namespace omplcu
             cudaStreamSynchronize(stream_);
             cudaStreamDestroy(stream_);
         }
+        if (ev0_)
+            cudaEventDestroy(ev0_);
+        if (ev1_)
+            cudaEventDestroy(ev1_);
     }
 
     void NNIndex::set_id_base(uint64_t base)
@@ -590,6 +596,13 @@ namespace omplcu
         std::lock_guard<std::mutex> lk(mu_);
         if (!strcmp(key, "force_exact"))
             force_exact_ = v != 0;
+        else if (!strcmp(key, "profile"))
+        {
+            // time the scan kernel with CUDA events on the launching stream
+            profile_ = v != 0;
+            scan_ns_total_ = 0;
+            scan_count_ = 0;
+        }
         else
             throw Error(OMPLCU_ERR_INVALID, std::string("unknown option ") + key);
     }
@@ -603,6 +616,12 @@ namespace omplcu
             return last_path_;
         if (!strcmp(key, "launches"))
             return launches_;
+        if (!strcmp(key, "last_scan_ns"))
+            return last_scan_ns_;
+        if (!strcmp(key, "scan_ns_total"))
+            return scan_ns_total_;
+        if (!strcmp(key, "scan_count"))
+            return scan_count_;
         if (!strcmp(key, "slots"))
             return (long)nslots_;
         if (!strcmp(key, "fast_space"))
@@ -735,9 +754,13 @@ namespace omplcu
         P.total_units = TU;
         P.qpad = qpad;
         P.smax = smax;
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev0_, s));
         scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev1_, s));
 
         knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(cand_vals_.p, cand_ids_.p, smax, (uint32_t)L, qpad,
                                                           pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
@@ -749,6 +772,14 @@ namespace omplcu
         CUDA_CHECK(cudaMemcpyAsync(&novf, counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
         last_fallbacks_ = novf;
+        if (profile_)
+        {
+            float ms = 0.f;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev1_));
+            last_scan_ns_ = (long)(ms * 1e6);
+            scan_ns_total_ += last_scan_ns_;
+            scan_count_++;
+        }
         if (novf)
             knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }

@@ -97,7 +97,9 @@ namespace omplcu
         DevBuf<unsigned char> cub_tmp_;
 
         int sm_count_ = 148;
-        bool force_exact_ = false;
+        bool force_exact_ = false, profile_ = false;
+        cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
+        long last_scan_ns_ = 0, scan_ns_total_ = 0, scan_count_ = 0;
         long last_fallbacks_ = 0, last_path_ = 0, launches_ = 0;
     };
 

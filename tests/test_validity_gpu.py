@@ -1,0 +1,235 @@
+"""GPU parity tests for batched state validity and batched motion validity
+(through the C ABI) against the oracle's restatement of the demo checkers and
+DiscreteMotionValidator (base/src/DiscreteMotionValidator.cpp:48-145).
+
+Bar: booleans and lastValid times bit-identical.
+"""
+import numpy as np
+import pytest
+
+import helpers
+import ompl_b200 as ob
+from oracle import oracle_py as orc
+
+pytestmark = pytest.mark.gpu
+PI = np.pi
+
+
+def _spaces(name):
+    if name == "rv8":
+        return ob.RealVectorStateSpace(8), orc.space_rv(8)
+    if name == "so2":
+        return ob.SO2StateSpace(), orc.space_so2()
+    if name == "so3":
+        return ob.SO3StateSpace(), orc.space_so3()
+    if name == "se2":
+        return ob.SE2StateSpace(), orc.space_se2()
+    if name == "se3":
+        return ob.SE3StateSpace(-1.0, 1.0), orc.space_se3(-1.0, 1.0)
+    if name == "chain10":
+        return ob.KinematicChainSpace(10, 0.1), orc.space_chain(10, 0.1)
+    raise KeyError(name)
+
+
+def _states(name, seed, n):
+    if name == "rv8":
+        return helpers.uniform_points(seed, n, 8)
+    if name == "so2":
+        return helpers.rng(seed).uniform(-PI, PI, (n, 1))
+    if name == "so3":
+        return helpers.random_quaternions(seed, n)
+    if name == "se2":
+        return helpers.se2_states(seed, n)
+    if name == "se3":
+        return helpers.se3_states(seed, n)
+    return helpers.rng(seed).uniform(-PI, PI, (n, 10))
+
+
+# ---------------------------------------------------------------- space math
+@pytest.mark.parametrize("name", ["rv8", "so2", "se2"])
+def test_space_math_bit_exact(gpu, name):
+    sp, osp = _spaces(name)
+    a, b = _states(name, 1, 3000), _states(name, 2, 3000)
+    assert (sp.distance(a, b) == orc.distance(osp, a, b)).all()
+    for t in (0.0, 0.25, 0.5, 1.0):
+        assert (sp.interpolate(a, b, t) == orc.interpolate(osp, a, b, t)).all()
+    assert (sp.validSegmentCount(a, b) == orc.segment_count(osp, a, b)).all()
+
+
+@pytest.mark.parametrize("name", ["so3", "se3", "chain10"])
+def test_space_math_transcendental(gpu, name):
+    """acos / sin / cos spaces: at most a last-bit difference from glibc."""
+    sp, osp = _spaces(name)
+    a, b = _states(name, 1, 3000), _states(name, 2, 3000)
+    assert (helpers.ulp_diff(sp.distance(a, b), orc.distance(osp, a, b)) <= 2).all()
+    got, want = sp.interpolate(a, b, 0.3), orc.interpolate(osp, a, b, 0.3)
+    assert np.allclose(got, want, rtol=0, atol=4e-16)
+    assert (sp.validSegmentCount(a, b) == orc.segment_count(osp, a, b)).all()
+
+
+def test_so2_wraparound_known_answers(gpu):
+    sp = ob.SO2StateSpace()
+    assert abs(sp.distance([[-PI + 0.1]], [[PI - 0.1]])[0] - 0.2) < 1e-3
+    assert abs(sp.interpolate([[PI - 0.08]], [[-PI + 0.1]], 0.5)[0, 0] - (-PI + 0.01)) < 1e-3
+    assert abs(sp.interpolate([[PI - 0.1]], [[0.1]], 0.5)[0, 0] - PI / 2) < 1e-3
+
+
+# ---------------------------------------------------------------- state validity
+def test_hypercube_states(gpu):
+    for d in (2, 8, 25):
+        chk, ochk = ob.HypercubeValidityChecker(d), orc.checker_hypercube(d)
+        s = np.vstack([helpers.uniform_points(d, 20000, d), helpers.hypercube_valid_states(d, 2000, d)])
+        # boundary values of both strict comparisons
+        s[:50, 0] = 0.9
+        s[50:100, -1] = 0.1
+        v = chk.isValidBatch(s)
+        assert (v == orc.check_states(ochk, s)).all() and v[-2000:].all() and not v.all()
+
+
+def test_circles_states_and_fixture(gpu):
+    z = helpers.load_circles()
+    chk = ob.Circles2DValidityChecker(z["circles"])
+    q = z["queries"]
+    assert (chk.isValidBatch(q[:, :2]) == z["start_valid"]).all()
+    assert (chk.isValidBatch(q[:, 2:]) == z["goal_valid"]).all()
+    lo, hi = z["low"], z["high"]
+    s = helpers.rng(1).uniform(lo, hi, (50000, 2))
+    assert (chk.isValidBatch(s) == orc.check_states(orc.checker_circles(z["circles"]), s, nthreads=8)).all()
+
+
+@pytest.mark.parametrize("links", [10, 100])
+def test_chain_states(gpu, links):
+    L = 1.0 / links
+    env = orc.horn_environment(links, np.log(links) / links)
+    assert len(env) == 2 * (links - 1)
+    chk, ochk = ob.KinematicChainValidityChecker(links, L, env), orc.checker_chain(links, L, env)
+    n = 6000 if links == 10 else 600
+    r = helpers.rng(links)
+    s = np.vstack([r.uniform(-PI, PI, (n, links)), r.normal(0, 0.15, (n, links))])  # the second half is mostly valid
+    v = chk.isValidBatch(s)
+    ov = orc.check_states(ochk, s, nthreads=8)
+    assert (v == ov).all() and 0 < v.sum() < len(v)
+
+
+def test_se3_states(gpu):
+    sph, box = helpers.se3_obstacles()
+    robot = helpers.se3_robot()
+    chk, ochk = ob.SE3ObstacleValidityChecker(robot, sph, box), orc.checker_se3(robot, sph, box)
+    s = helpers.se3_states(3, 40000)
+    v = chk.isValidBatch(s)
+    assert (v == orc.check_states(ochk, s, nthreads=8)).all() and 0 < v.sum() < len(v)
+    # only spheres / only boxes / no obstacles
+    for sp_, bx_ in ((sph, box[:0]), (sph[:0], box), (sph[:0], box[:0])):
+        c2, o2 = ob.SE3ObstacleValidityChecker(robot, sp_, bx_), orc.checker_se3(robot, sp_, bx_)
+        assert (c2.isValidBatch(s[:5000]) == orc.check_states(o2, s[:5000], nthreads=8)).all()
+
+
+def test_allvalid_and_single_state(gpu):
+    chk = ob.AllValidStateValidityChecker()
+    assert chk.isValidBatch(np.zeros((5, 3))).all()
+    assert ob.HypercubeValidityChecker(3).isValid([0.5, 0.95, 0.95])
+    assert not ob.HypercubeValidityChecker(3).isValid([0.5, 0.5, 0.95])
+
+
+# ---------------------------------------------------------------- motion validity
+def _motion_parity(sp, osp, chk, ochk, a, b, last_state=True):
+    mv = ob.BatchedDiscreteMotionValidator(sp, chk)
+    v = mv.checkMotionBatch(a, b)
+    ov, ot = orc.check_motions(osp, ochk, a, b, last_valid=True, nthreads=8)
+    assert (v == ov).all(), f"{(v != ov).sum()} of {len(v)} motion booleans differ"
+    v2, t, st = mv.checkMotionBatch(a, b, last_valid=True, last_state=last_state)
+    assert (v2 == ov).all()
+    assert (t[~ov] == ot[~ov]).all()
+    assert mv.getValidMotionCount() == 2 * int(ov.sum()) and mv.getCheckedMotionCount() == 2 * len(a)
+    return v, t, st
+
+
+def test_motion_hypercube_resolution_0001(gpu):
+    """HypercubeBenchmark: d = 8, resolution 0.001 (demos/HypercubeBenchmark.cpp:93-97)."""
+    d = 8
+    sp, osp = ob.RealVectorStateSpace(d), orc.space_rv(d, 0.0, 1.0, 0.001)
+    sp.setLongestValidSegmentFraction(0.001)
+    chk, ochk = ob.HypercubeValidityChecker(d), orc.checker_hypercube(d)
+    a = helpers.hypercube_valid_states(1, 4000, d)
+    r = helpers.rng(2)
+    b = np.clip(a + r.normal(0, 0.03, a.shape), 0, 1)
+    b[::3] = helpers.hypercube_valid_states(3, len(b[::3]), d)
+    v, t, st = _motion_parity(sp, osp, chk, ochk, a, b)
+    assert 0 < v.sum() < len(v)
+    # lastValid.first is the interpolated state at lastValid.second
+    bad = np.where(~v)[0][:200]
+    want = orc.interpolate(osp, a[bad], b[bad], t[bad])
+    assert (st[bad] == want).all()
+
+
+def test_motion_circle_world_fixture(gpu):
+    z = helpers.load_circles()
+    sp = ob.RealVectorStateSpace(2, z["low"], z["high"])
+    mv = ob.BatchedDiscreteMotionValidator(sp, ob.Circles2DValidityChecker(z["circles"]))
+    q = z["queries"]
+    v, t, _ = mv.checkMotionBatch(q[:, :2], q[:, 2:], last_valid=True, last_state=True)
+    assert (v == z["motion_valid"]).all() and (t[~v] == z["last_t"][~v]).all()
+    assert (sp.validSegmentCount(q[:, :2], q[:, 2:]) == z["nd"]).all()
+    # single-segment overloads, as SpaceInformation::checkMotion calls them
+    for i in range(0, 100, 9):
+        assert mv.checkMotion(q[i, :2], q[i, 2:]) == bool(z["motion_valid"][i])
+        lv = [np.zeros(2), -1.0]
+        ok = mv.checkMotion(q[i, :2], q[i, 2:], lv)
+        assert ok == bool(z["motion_valid"][i])
+        if not ok:
+            assert lv[1] == z["last_t"][i]
+
+
+def test_motion_se2_circles(gpu):
+    sp, osp = _spaces("se2")
+    circ = np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1], [0.8, 0.2, 0.15]])
+    a, b = helpers.se2_states(1, 5000), helpers.se2_states(2, 5000)
+    _motion_parity(sp, osp, ob.Circles2DValidityChecker(circ), orc.checker_circles(circ), a, b)
+
+
+def test_motion_se3_obstacles(gpu):
+    sp, osp = _spaces("se3")
+    sph, box = helpers.se3_obstacles()
+    robot = helpers.se3_robot()
+    a, b = helpers.se3_states(1, 20000), helpers.se3_states(2, 20000)
+    # a share of short segments so that some motions are valid
+    b[::2, :3] = a[::2, :3] + helpers.rng(3).normal(0, 0.02, (10000, 3))
+    b[::2, 3:] = a[::2, 3:]
+    v, _, _ = _motion_parity(sp, osp, ob.SE3ObstacleValidityChecker(robot, sph, box),
+                             orc.checker_se3(robot, sph, box), a, b, last_state=False)
+    assert 0 < v.sum() < len(v)
+
+
+def test_motion_chain(gpu):
+    links = 10
+    sp, osp = _spaces("chain10")
+    env = orc.horn_environment(links, np.log(links) / links)
+    chk, ochk = ob.KinematicChainValidityChecker(links, 0.1, env), orc.checker_chain(links, 0.1, env)
+    r = helpers.rng(5)
+    a = r.normal(0, 0.15, (3000, links))
+    b = a + r.normal(0, 0.2, a.shape)
+    v, _, _ = _motion_parity(sp, osp, chk, ochk, a, b, last_state=False)
+    assert 0 < v.sum() < len(v)
+
+
+def test_motion_degenerate_segments(gpu):
+    """nd = 0 (identical states) and nd = 1 check only s2 (DiscreteMotionValidator.cpp:103-109)."""
+    sp, osp = ob.RealVectorStateSpace(2), orc.space_rv(2)
+    circ = np.array([[0.5, 0.5, 0.2]])
+    chk, ochk = ob.Circles2DValidityChecker(circ), orc.checker_circles(circ)
+    a = np.array([[0.1, 0.1], [0.5, 0.5], [0.1, 0.1], [0.5, 0.5], [0.1, 0.1]])
+    b = np.array([[0.1, 0.1], [0.5, 0.5], [0.1, 0.105], [0.5, 0.505], [0.9, 0.9]])
+    v, t, _ = _motion_parity(sp, osp, chk, ochk, a, b)
+    assert v.tolist() == [True, False, True, False, False]
+
+
+def test_motion_count_factor_and_empty(gpu):
+    sp, osp = ob.RealVectorStateSpace(3), orc.space_rv(3)
+    sp.setValidSegmentCountFactor(3)
+    osp.comp[0].factor = 3
+    a, b = helpers.uniform_points(1, 500, 3), helpers.uniform_points(2, 500, 3)
+    assert (sp.validSegmentCount(a, b) == orc.segment_count(osp, a, b)).all()
+    chk = ob.HypercubeValidityChecker(3)
+    _motion_parity(sp, osp, chk, orc.checker_hypercube(3), a, b)
+    mv = ob.BatchedDiscreteMotionValidator(sp, chk)
+    assert len(mv.checkMotionBatch(np.zeros((0, 3)), np.zeros((0, 3)))) == 0
