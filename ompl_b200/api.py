@@ -396,8 +396,11 @@ class NearestNeighborsCUDA:
         check(lib().omplcu_nn_radius(self._h, _ptr(q), len(q), _ptr(r), C.byref(pi), C.byref(pd), _ptr(offs)))
         tot = int(offs[-1])
         try:
-            ids = np.ctypeslib.as_array(C.cast(pi, C.POINTER(C.c_uint64)), shape=(max(tot, 1),))[:tot].copy()
-            d = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_double)), shape=(max(tot, 1),))[:tot].copy()
+            if tot == 0 or not pi.value:
+                ids, d = np.empty(0, dtype=np.uint64), np.empty(0, dtype=np.float64)
+            else:
+                ids = np.ctypeslib.as_array(C.cast(pi, C.POINTER(C.c_uint64)), shape=(tot,)).copy()
+                d = np.ctypeslib.as_array(C.cast(pd, C.POINTER(C.c_double)), shape=(tot,)).copy()
         finally:
             lib().omplcu_free(pi)
             lib().omplcu_free(pd)

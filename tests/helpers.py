@@ -76,9 +76,10 @@ def hypercube_valid_states(seed, n, d, edge=0.1):
     for i in range(n):
         k = r.integers(0, d)
         s = np.empty(d)
-        s[:k] = r.uniform(0, edge, size=k)
+        # dims above k stay inside the edge, dim k roams, dims below k hug the far face
+        s[:k] = r.uniform(1 - edge, 1, size=k)
         s[k] = r.uniform(0, 1)
-        s[k + 1:] = r.uniform(1 - edge, 1, size=d - k - 1)
+        s[k + 1:] = r.uniform(0, edge, size=d - k - 1)
         out[i] = s
     return out
 
