@@ -185,6 +185,8 @@ def run_gpu_arm(args):
     nn.set_id_base(lo)
     nn.add_rows(pts[lo:hi])
     nn.set_option("profile", 1)
+    if args.scan_ctas:
+        nn.set_option("scan_ctas_per_sm", args.scan_ctas)
 
     d_q = torch.from_numpy(qs).to(dev)
     d_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
@@ -339,6 +341,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--scan-ctas", type=int, default=0, help="tuning: cap resident scan CTAs per SM")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -9,8 +9,8 @@
 //        s = pn + sum_c (-2 qt_c) * pt_c ,   pn = fl32(|pt|^2)
 // which approximates |qt - pt|^2 - |qt|^2.  Each thread owns RQ queries and
 // keeps, per query, the L smallest s seen in its segment of the point set (an
-// unsorted list in shared memory with the running maximum cached in a
-// register as the insertion threshold).  The re-rank recomputes the exact
+// unsorted list in shared memory; the running maximum, tagged with its slot, is
+// cached in a register as the insertion threshold).  The re-rank recomputes the exact
 // distance of every listed point and proves, per query, that nothing outside
 // the lists can belong to the k best (the "band check"); queries for which the
 // proof fails are redone by the exact sort path.  So the scan only has to be
@@ -36,6 +36,7 @@ namespace omplcu
     constexpr int SCAN_PT = 256;       // points per shared-memory tile
     constexpr int SCAN_STAGES = 3;     // TMA ring depth
     constexpr int SCAN_THREADS = 128;  // 4 warps per CTA
+    constexpr int SCAN_GP = 4;         // points per group in the inner loop (SCAN_PT % SCAN_GP == 0)
     constexpr uint32_t SLOT_NONE = 0xFFFFFFFFu;
 
     __host__ __device__ constexpr int scan_rowf(int D)
@@ -47,8 +48,8 @@ namespace omplcu
     {
         const float *filt;      // [units*SCAN_PT][ROWF]
         const float *qp;        // [D][qpad]  (-2 * qt_c)
-        float *cand_vals;       // [smax*L][qpad]
-        uint32_t *cand_ids;     // [smax*L][qpad]
+        float *cand_thr;        // [smax][qpad]   final list threshold per (segment, query)
+        uint32_t *cand_ids;     // [smax*L][qpad] SLOT_NONE where the list did not fill
         unsigned long long units;        // point tiles
         unsigned long long total_units;  // qtiles * units
         uint32_t qpad;
@@ -106,26 +107,79 @@ namespace omplcu
         return *reinterpret_cast<float2 *>(&rd);
     }
 
+    // ---- candidate lists ----
+    // Each query keeps the L smallest scan values of its segment in shared
+    // memory: LS = L rounded up to 4 floats, contiguous per query so the whole
+    // list is read back with LS/4 LDS.128.  A stored value carries its own slot
+    // index in the low 6 mantissa bits and is rounded UP to make room for it
+    // (stored >= true value > stored - 128 ulp), so one FMNMX3 tree over the
+    // list yields both the new threshold and the slot to overwrite next.  The
+    // threshold is therefore never below the true L-th smallest value (nothing
+    // is wrongly rejected); eviction may pick an element within 128 ulp of the
+    // true maximum, which the re-rank's band check accounts for (nn.cu).
+    constexpr uint32_t TAG_MASK = 63u;
+    constexpr uint32_t EMPTY_BITS = 0x7f000000u;  // 1.7e38 | slot: larger than any real scan value
+
+    __host__ __device__ constexpr int scan_ls(int L)
+    {
+        return (L + 3) & ~3;
+    }
+
+    __device__ __forceinline__ float tag_up(float v, uint32_t slot)
+    {
+        const uint32_t b = __float_as_uint(v);
+        const uint32_t m = b & 0x7fffffffu;
+        const uint32_t pos = ((b + 64u) & ~TAG_MASK) | slot;                     // v >= +0
+        const uint32_t neg = 0x80000000u | (((m - 64u) & ~TAG_MASK) | slot);     // v < 0, |v| not tiny
+        const uint32_t r = (b & 0x80000000u) ? (m >= 128u ? neg : slot) : pos;
+        return __uint_as_float(r);
+    }
+
+    template <int N>
+    __device__ __forceinline__ float max_tree(const float (&x)[N])
+    {
+        float y[(N + 2) / 3];
+#pragma unroll
+        for (int i = 0; i < (N + 2) / 3; ++i)
+        {
+            float m = x[3 * i];
+            if (3 * i + 1 < N)
+                m = fmaxf(m, x[3 * i + 1]);
+            if (3 * i + 2 < N)
+                m = fmaxf(m, x[3 * i + 2]);
+            y[i] = m;
+        }
+        if constexpr ((N + 2) / 3 == 1)
+            return y[0];
+        else
+            return max_tree<(N + 2) / 3>(y);
+    }
+
     constexpr size_t scan_smem_bytes(int D, int RQ, int L)
     {
         return (size_t)SCAN_STAGES * SCAN_PT * scan_rowf(D) * sizeof(float)  // tile ring
-               + (size_t)L * SCAN_THREADS * RQ * 8                            // list values + ids
-               + SCAN_STAGES * sizeof(uint64_t) + 64;
+               + (size_t)scan_ls(L) * SCAN_THREADS * RQ * 8                   // list values + ids
+               + SCAN_STAGES * (sizeof(uint64_t) + sizeof(unsigned)) + 64;
     }
 
     template <int D, int RQ, int L>
     __global__ void __launch_bounds__(SCAN_THREADS) knn_scan_kernel(const ScanParams P)
     {
         static_assert(RQ % 2 == 0, "queries are processed as packed pairs");
+        static_assert(L <= 64, "slot tags are 6 bits");
+        static_assert(SCAN_PT % SCAN_GP == 0, "tile must hold whole groups");
         constexpr int ROWF = scan_rowf(D);
+        constexpr int RW = ROWF / 4;           // float4 per filter row
+        constexpr int LS = scan_ls(L);
         constexpr int QT = SCAN_THREADS * RQ;  // queries per CTA
         constexpr uint32_t TILE_BYTES = SCAN_PT * ROWF * sizeof(float);
 
         extern __shared__ __align__(128) unsigned char smem_raw[];
         float *tiles = reinterpret_cast<float *>(smem_raw);
-        float *lvals = tiles + SCAN_STAGES * SCAN_PT * ROWF;
-        uint32_t *lids = reinterpret_cast<uint32_t *>(lvals + L * QT);
-        uint64_t *bars = reinterpret_cast<uint64_t *>(lids + L * QT);
+        float *lvals = tiles + SCAN_STAGES * SCAN_PT * ROWF;              // [QT][LS]
+        uint32_t *lids = reinterpret_cast<uint32_t *>(lvals + LS * QT);    // [QT][LS]
+        uint64_t *bars = reinterpret_cast<uint64_t *>(lids + LS * QT);
+        unsigned *done = reinterpret_cast<unsigned *>(bars + SCAN_STAGES);  // warps finished with a stage
 
         const int tid = threadIdx.x;
         const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
@@ -136,7 +190,10 @@ namespace omplcu
         if (tid == 0)
         {
             for (int s = 0; s < SCAN_STAGES; ++s)
+            {
                 mbar_init(&bars[s], 1);
+                done[s] = 0;
+            }
             mbar_fence_init();
         }
         __syncthreads();
@@ -152,8 +209,10 @@ namespace omplcu
 
         float2 qq[RQ / 2][D];
         float thr[RQ];
-        int maxpos[RQ];
         unsigned long long cur_tile = ~0ull;
+
+        // query j of this thread is column j*SCAN_THREADS + tid of the query tile
+        auto list_of = [&](int j) { return (j * SCAN_THREADS + tid) * LS; };
 
         auto flush = [&](unsigned long long t) {
             // ordinal of this piece among the pieces that overlap query tile t
@@ -163,15 +222,31 @@ namespace omplcu
 #pragma unroll
             for (int j = 0; j < RQ; ++j)
             {
-                const int col = j * SCAN_THREADS + tid;
-                const size_t q = (size_t)t * QT + col;
+                const size_t q = (size_t)t * QT + j * SCAN_THREADS + tid;
+                P.cand_thr[(size_t)seg * P.qpad + q] = thr[j];
+                const uint32_t *li = lids + list_of(j);
                 for (int i = 0; i < L; ++i)
-                {
-                    const size_t o = ((size_t)seg * L + i) * P.qpad + q;
-                    P.cand_vals[o] = lvals[i * QT + col];
-                    P.cand_ids[o] = lids[i * QT + col];
-                }
+                    P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = li[i];
             }
+        };
+
+        // put v (scan value of point id) into query j's list; returns the new threshold
+        auto insert = [&](int j, float v, uint32_t id) {
+            float *lv = lvals + list_of(j);
+            const uint32_t slot = __float_as_uint(thr[j]) & TAG_MASK;
+            lv[slot] = tag_up(v, slot);
+            lids[list_of(j) + slot] = id;
+            float x[LS];
+#pragma unroll
+            for (int w = 0; w < LS / 4; ++w)
+            {
+                const float4 f = reinterpret_cast<const float4 *>(lv)[w];
+                x[4 * w + 0] = f.x;
+                x[4 * w + 1] = f.y;
+                x[4 * w + 2] = f.z;
+                x[4 * w + 3] = f.w;
+            }
+            thr[j] = max_tree<LS>(x);
         };
 
         for (unsigned long long u = u0; u < u1; ++u)
@@ -194,14 +269,16 @@ namespace omplcu
 #pragma unroll
                 for (int j = 0; j < RQ; ++j)
                 {
-                    thr[j] = __int_as_float(0x7f800000);
-                    maxpos[j] = 0;
-                    const int col = j * SCAN_THREADS + tid;
-                    for (int i = 0; i < L; ++i)
+                    float *lv = lvals + list_of(j);
+                    uint32_t *li = lids + list_of(j);
+                    for (int i = 0; i < LS; ++i)
                     {
-                        lvals[i * QT + col] = __int_as_float(0x7f800000);
-                        lids[i * QT + col] = SLOT_NONE;
+                        // real slots: empty marker (filled from slot L-1 downwards);
+                        // padding slots: never the maximum
+                        lv[i] = i < L ? __uint_as_float(EMPTY_BITS | (uint32_t)i) : __int_as_float(0xff800000);
+                        li[i] = SLOT_NONE;
                     }
+                    thr[j] = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
                 }
             }
 
@@ -211,68 +288,108 @@ namespace omplcu
 
             const float4 *tp = reinterpret_cast<const float4 *>(tiles + stage * SCAN_PT * ROWF);
             const uint32_t base = (uint32_t)(pt * SCAN_PT);
-#pragma unroll 4
-            for (int i = 0; i < SCAN_PT; ++i)
+            // Points are taken SCAN_GP at a time: the FMA chains of a group are
+            // independent (SCAN_GP * RQ/2 packed chains in flight), the rows of
+            // the NEXT group are already on their way from shared memory while
+            // this one is computed, and one predicate decides whether any
+            // (point, query) of the group beats its query's threshold.  Only then
+            // (rare after the first few tiles) the group is replayed in point order.
+            float4 nx[SCAN_GP][RW];
+#pragma unroll
+            for (int p = 0; p < SCAN_GP; ++p)
+#pragma unroll
+                for (int w = 0; w < RW; ++w)
+                    nx[p][w] = tp[p * RW + w];
+#pragma unroll 1
+            for (int i = 0; i < SCAN_PT; i += SCAN_GP)
             {
-                float pv[ROWF];
+                float pv[SCAN_GP][ROWF];
 #pragma unroll
-                for (int w = 0; w < ROWF / 4; ++w)
+                for (int p = 0; p < SCAN_GP; ++p)
+#pragma unroll
+                    for (int w = 0; w < RW; ++w)
+                    {
+                        pv[p][4 * w + 0] = nx[p][w].x;
+                        pv[p][4 * w + 1] = nx[p][w].y;
+                        pv[p][4 * w + 2] = nx[p][w].z;
+                        pv[p][4 * w + 3] = nx[p][w].w;
+                    }
                 {
-                    const float4 v = tp[i * (ROWF / 4) + w];
-                    pv[4 * w + 0] = v.x;
-                    pv[4 * w + 1] = v.y;
-                    pv[4 * w + 2] = v.z;
-                    pv[4 * w + 3] = v.w;
-                }
-                float2 acc[RQ / 2];
+                    // wraps to the first group on the last iteration (harmless re-read)
+                    const int in = (i + SCAN_GP) & (SCAN_PT - 1);
 #pragma unroll
-                for (int jj = 0; jj < RQ / 2; ++jj)
-                    acc[jj] = make_float2(pv[D], pv[D]);
+                    for (int p = 0; p < SCAN_GP; ++p)
+#pragma unroll
+                        for (int w = 0; w < RW; ++w)
+                            nx[p][w] = tp[(in + p) * RW + w];
+                }
+                float2 acc[SCAN_GP][RQ / 2];
+#pragma unroll
+                for (int p = 0; p < SCAN_GP; ++p)
+#pragma unroll
+                    for (int jj = 0; jj < RQ / 2; ++jj)
+                        acc[p][jj] = make_float2(pv[p][D], pv[p][D]);
 #pragma unroll
                 for (int c = 0; c < D; ++c)
 #pragma unroll
-                    for (int jj = 0; jj < RQ / 2; ++jj)
-                        acc[jj] = ffma2(qq[jj][c], make_float2(pv[c], pv[c]), acc[jj]);
-                bool hit = false;
+                    for (int p = 0; p < SCAN_GP; ++p)
+#pragma unroll
+                        for (int jj = 0; jj < RQ / 2; ++jj)
+                            acc[p][jj] = ffma2(qq[jj][c], make_float2(pv[p][c], pv[p][c]), acc[p][jj]);
+                // per-query minimum over the group: one compare per query decides the group
+                float gm[RQ];
 #pragma unroll
                 for (int jj = 0; jj < RQ / 2; ++jj)
-                    hit = hit | (acc[jj].x < thr[2 * jj]) | (acc[jj].y < thr[2 * jj + 1]);
+                {
+                    float mx = acc[0][jj].x, my = acc[0][jj].y;
+#pragma unroll
+                    for (int p = 1; p < SCAN_GP; ++p)
+                    {
+                        mx = fminf(mx, acc[p][jj].x);
+                        my = fminf(my, acc[p][jj].y);
+                    }
+                    gm[2 * jj] = mx;
+                    gm[2 * jj + 1] = my;
+                }
+                bool hit = false;
+#pragma unroll
+                for (int j = 0; j < RQ; ++j)
+                    hit = hit | (gm[j] < thr[j]);
                 if (hit)
                 {
+                    // slow path: only the queries whose group minimum passed look at the points
 #pragma unroll
                     for (int j = 0; j < RQ; ++j)
-                    {
-                        const float v = (j & 1) ? acc[j / 2].y : acc[j / 2].x;
-                        if (v < thr[j])
+                        if (gm[j] < thr[j])
                         {
-                            const int col = j * SCAN_THREADS + tid;
-                            lvals[maxpos[j] * QT + col] = v;
-                            lids[maxpos[j] * QT + col] = base + i;
-                            float m = lvals[col];
-                            int mp = 0;
 #pragma unroll
-                            for (int l = 1; l < L; ++l)
+                            for (int p = 0; p < SCAN_GP; ++p)
                             {
-                                const float x = lvals[l * QT + col];
-                                if (x > m)
-                                {
-                                    m = x;
-                                    mp = l;
-                                }
+                                const float v = (j & 1) ? acc[p][j / 2].y : acc[p][j / 2].x;
+                                if (v < thr[j])
+                                    insert(j, v, base + i + p);
                             }
-                            thr[j] = m;
-                            maxpos[j] = mp;
                         }
-                    }
                 }
             }
-            __syncthreads();  // every warp is done with this stage before it is refilled
-            if (tid == 0 && u + SCAN_STAGES < u1)
+            // Warps run the ring independently (no block barrier): the last warp to
+            // finish a stage refills it.  Every lane's reads of the stage are complete
+            // (their values were consumed above) before lane 0 counts the warp in.
+            __syncwarp();
+            if ((tid & 31) == 0)
             {
-                const unsigned long long npt = (u + SCAN_STAGES) % U;
-                mbar_expect_tx(&bars[stage], TILE_BYTES);
-                tma_bulk_g2s(tiles + stage * SCAN_PT * ROWF, P.filt + npt * SCAN_PT * ROWF, TILE_BYTES,
-                             &bars[stage]);
+                const unsigned prev = atomicAdd(&done[stage], 1u);
+                if (prev == SCAN_THREADS / 32 - 1)
+                {
+                    done[stage] = 0;  // the other warps cannot pass the barrier wait before the refill lands
+                    if (u + SCAN_STAGES < u1)
+                    {
+                        const unsigned long long npt = (u + SCAN_STAGES) % U;
+                        mbar_expect_tx(&bars[stage], TILE_BYTES);
+                        tma_bulk_g2s(tiles + stage * SCAN_PT * ROWF, P.filt + npt * SCAN_PT * ROWF, TILE_BYTES,
+                                     &bars[stage]);
+                    }
+                }
             }
         }
         flush(cur_tile);

@@ -134,7 +134,7 @@ namespace omplcu
         // redone exactly.
         template <int MAXC>
         __global__ void __launch_bounds__(128) knn_rerank_kernel(
-            const float *cand_vals, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
+            const float *cand_thr, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
             const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
             const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
             double *out_dists, uint32_t *ovf_list, unsigned *ovf_count)
@@ -194,19 +194,14 @@ namespace omplcu
             const double A = dk * (1.0 + delta) + rho + 1e-150;
             const double e1 = (double)(D + 3) * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
             const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
-            const float tau = __double2float_ru(tau64);
             bool bad = !(tau64 == tau64) || !(tau64 < 1e37);  // NaN / overflow -> redo exactly
             for (uint32_t s = lane; s < smax; s += 32)
             {
-                bool full = true;
-                float vmax = -inff();
-                for (uint32_t i = 0; i < L; ++i)
-                {
-                    const size_t o = ((size_t)s * L + i) * qpad + qi;
-                    full = full && (cand_ids[o] != SLOT_NONE);
-                    vmax = fmaxf(vmax, cand_vals[o]);
-                }
-                if (full && !(vmax > tau))
+                // final threshold of the segment's list; an EMPTY marker (> 1e38) means
+                // the list never filled, i.e. nothing was dropped from that segment.
+                // Stored values are rounded up by < 128 ulp (knn_scan.cuh): step back 2^-16.
+                const double vmax = (double)cand_thr[(size_t)s * qpad + qi];
+                if (vmax < 1e38 && !(vmax - fabs(vmax) * 1.52587890625e-05 - 1e-37 > tau64))
                     bad = true;
             }
             bad = __any_sync(0xffffffffu, bad);
@@ -596,6 +591,8 @@ namespace omplcu
         std::lock_guard<std::mutex> lk(mu_);
         if (!strcmp(key, "force_exact"))
             force_exact_ = v != 0;
+        else if (!strcmp(key, "scan_ctas_per_sm"))
+            scan_ctas_per_sm_ = (int)v;  // 0 = as many as fit
         else if (!strcmp(key, "profile"))
         {
             // time the scan kernel with CUDA events on the launching stream
@@ -717,6 +714,8 @@ namespace omplcu
         int resident = 1;  // CTAs per SM: one persistent CTA per resident slot
         scan_any(cfg, D_, 0, nullptr, 0, s, &resident);
         resident = std::max(resident, 1);
+        if (scan_ctas_per_sm_ > 0)
+            resident = std::min(resident, scan_ctas_per_sm_);
         const unsigned max_seg = 512 / L;  // candidate slots per query <= 512
         unsigned long long G = (unsigned long long)sm_count_ * resident;
         G = std::min<unsigned long long>(G, TU);
@@ -736,11 +735,12 @@ namespace omplcu
 
         qp_.reserve((size_t)D_ * qpad);
         qaux_.reserve(2 * (size_t)qpad);
-        cand_vals_.reserve((size_t)smax * L * qpad);
+        cand_vals_.reserve((size_t)smax * qpad);
         cand_ids_.reserve((size_t)smax * L * qpad);
         ovf_list_.reserve(nq);
 
         CUDA_CHECK(cudaMemsetAsync(cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
         CUDA_CHECK(cudaMemsetAsync(counters_.p, 0, sizeof(unsigned), s));
         query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, qp_.p, qaux_.p, qpad);
         launches_++;
@@ -748,7 +748,7 @@ namespace omplcu
         ScanParams P;
         P.filt = filt_.p;
         P.qp = qp_.p;
-        P.cand_vals = cand_vals_.p;
+        P.cand_thr = cand_vals_.p;
         P.cand_ids = cand_ids_.p;
         P.units = U;
         P.total_units = TU;

@@ -96,7 +96,7 @@ namespace omplcu
         DevBuf<int> ex_offs_;
         DevBuf<unsigned char> cub_tmp_;
 
-        int sm_count_ = 148;
+        int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool force_exact_ = false, profile_ = false;
         cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
         long last_scan_ns_ = 0, scan_ns_total_ = 0, scan_count_ = 0;
