@@ -1,0 +1,354 @@
+/*
+ * NearestNeighborsCUDA.h -- ompl::NearestNeighbors<_T> with the element set
+ * mirrored on a B200 (libomplcu.so, C ABI in include/omplcu.h).
+ *
+ * Drop-in for NearestNeighborsLinear / NearestNeighborsGNAT behind the
+ * reference interface datastructures/NearestNeighbors.h:46-115: same virtuals,
+ * same results as NearestNeighborsLinear (NearestNeighborsLinear.h:98-142) with
+ * ties broken by insertion order, same exception text on an empty structure
+ * (NearestNeighborsLinear.h:115).  Header-only; needs only the reference's
+ * NearestNeighbors.h / Exception.h (no Boost), so it also builds in this
+ * repository's test tree.
+ *
+ * The reference hands a structure nothing but an opaque distance function.
+ * A GPU structure needs coordinates, so two extra setters exist:
+ *   setSpace(desc)        which metric: RealVector / SO2 / SO3 / compound ...
+ *   setRowFunction(f)     f(elem, double *row) writes the element's state in
+ *                         StateSpace::copyToReals order (StateSpace.cpp:329-335)
+ * ompl_b200/OmplBridge.h derives both from a base::StateSpacePtr and a
+ * State accessor.  The distance function is kept for getDistanceFunction()
+ * and is NOT called by queries.
+ *
+ * Batch entry points (what PRM/FMT-star/BIT-star batch call sites use):
+ *   nearestKBatch / nearestRBatch.
+ */
+#ifndef OMPL_B200_NEAREST_NEIGHBORS_CUDA_H
+#define OMPL_B200_NEAREST_NEIGHBORS_CUDA_H
+
+#include <cstdint>
+#include <functional>
+#include <limits>
+#include <mutex>
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+#include "ompl/datastructures/NearestNeighbors.h"
+#include "ompl/util/Exception.h"
+#include "omplcu.h"
+
+namespace ompl
+{
+    namespace b200
+    {
+        /** What the device must know about the metric space. */
+        struct SpaceDescription
+        {
+            std::vector<omplcu_component> components;
+            bool compound{false};
+
+            unsigned int stride() const
+            {
+                unsigned int s = 0;
+                for (const auto &c : components)
+                    s += c.dim;
+                return s;
+            }
+            static omplcu_component component(int type, int dim, double weight, double lvs, unsigned factor = 1,
+                                              double param = 0.)
+            {
+                omplcu_component c{};
+                c.type = type;
+                c.dim = dim;
+                c.weight = weight;
+                c.lvs = lvs;
+                c.factor = factor;
+                c.param = param;
+                return c;
+            }
+            /** RealVectorStateSpace(dim) with longest valid segment lvs (only used by motion checks). */
+            static SpaceDescription realVector(int dim, double lvs = 1.0)
+            {
+                SpaceDescription d;
+                d.components.push_back(component(OMPLCU_RV, dim, 1.0, lvs));
+                return d;
+            }
+        };
+
+        inline void check(int rc)
+        {
+            if (rc != OMPLCU_OK)
+                throw ompl::Exception(std::string(omplcu_last_error()));
+        }
+
+        /** RAII owner of an omplcu_space_t. */
+        class SpaceHandle
+        {
+        public:
+            SpaceHandle() = default;
+            explicit SpaceHandle(const SpaceDescription &d)
+            {
+                reset(d);
+            }
+            SpaceHandle(const SpaceHandle &) = delete;
+            SpaceHandle &operator=(const SpaceHandle &) = delete;
+            ~SpaceHandle()
+            {
+                omplcu_space_destroy(h_);
+            }
+            void reset(const SpaceDescription &d)
+            {
+                omplcu_space_destroy(h_);
+                h_ = nullptr;
+                check(omplcu_space_create(d.components.data(), (int)d.components.size(), d.compound ? 1 : 0, &h_));
+                stride_ = d.stride();
+            }
+            omplcu_space_t get() const
+            {
+                return h_;
+            }
+            unsigned int stride() const
+            {
+                return stride_;
+            }
+
+        private:
+            omplcu_space_t h_{nullptr};
+            unsigned int stride_{0};
+        };
+    }  // namespace b200
+
+    template <typename _T>
+    class NearestNeighborsCUDA : public NearestNeighbors<_T>
+    {
+    public:
+        using RowFunction = std::function<void(const _T &, double *)>;
+
+        NearestNeighborsCUDA() = default;
+        explicit NearestNeighborsCUDA(const b200::SpaceDescription &space, RowFunction rows = RowFunction(),
+                                      int device = 0)
+          : rowFun_(std::move(rows)), device_(device)
+        {
+            setSpace(space);
+        }
+        NearestNeighborsCUDA(const NearestNeighborsCUDA &) = delete;
+        NearestNeighborsCUDA &operator=(const NearestNeighborsCUDA &) = delete;
+
+        ~NearestNeighborsCUDA() override
+        {
+            omplcu_nn_destroy(nn_);
+        }
+
+        /** Must be called while the structure is empty. */
+        void setSpace(const b200::SpaceDescription &space)
+        {
+            if (nn_ != nullptr && size() != 0)
+                throw Exception("NearestNeighborsCUDA: setSpace() on a non-empty structure");
+            omplcu_nn_destroy(nn_);
+            nn_ = nullptr;
+            space_.reset(space);
+            b200::check(omplcu_nn_create(space_.get(), device_, &nn_));
+        }
+        void setRowFunction(RowFunction f)
+        {
+            rowFun_ = std::move(f);
+        }
+        void setDevice(int device)
+        {
+            device_ = device;
+        }
+
+        bool reportsSortedResults() const override
+        {
+            return true;  // FMT relies on it (fmt/src/FMT.cpp:105-110)
+        }
+
+        void clear() override
+        {
+            if (nn_ != nullptr)
+                b200::check(omplcu_nn_clear(nn_));
+            elems_.clear();
+            idsOf_.clear();
+        }
+
+        void add(const _T &data) override
+        {
+            ready();
+            row_.resize(space_.stride());
+            rowFun_(data, row_.data());
+            std::uint64_t id = 0;
+            b200::check(omplcu_nn_add(nn_, row_.data(), 1, &id));
+            remember(id, data);
+        }
+
+        /** One bulk upload (NearestNeighbors.h:81-85 loops over add(x)). */
+        void add(const std::vector<_T> &data) override
+        {
+            if (data.empty())
+                return;
+            ready();
+            const std::size_t st = space_.stride();
+            std::vector<double> rows(data.size() * st);
+            for (std::size_t i = 0; i < data.size(); ++i)
+                rowFun_(data[i], rows.data() + i * st);
+            std::uint64_t first = 0;
+            b200::check(omplcu_nn_add(nn_, rows.data(), data.size(), &first));
+            for (std::size_t i = 0; i < data.size(); ++i)
+                remember(first + i, data[i]);
+        }
+
+        /** Removes the most recently added element equal to data
+            (NearestNeighborsLinear::remove searches from the back, :86-96). */
+        bool remove(const _T &data) override
+        {
+            auto range = idsOf_.equal_range(data);
+            if (range.first == range.second)
+                return false;
+            auto best = range.first;
+            for (auto it = range.first; it != range.second; ++it)
+                if (it->second > best->second)
+                    best = it;
+            const std::uint64_t id = best->second;
+            const int rc = omplcu_nn_remove(nn_, id);
+            if (rc == OMPLCU_ERR_NOT_FOUND)
+                return false;
+            b200::check(rc);
+            idsOf_.erase(best);
+            elems_.erase(id);
+            return true;
+        }
+
+        _T nearest(const _T &data) const override
+        {
+            if (size() == 0)
+                throw Exception("No elements found in nearest neighbors data structure");
+            std::vector<_T> nbh;
+            nearestK(data, 1, nbh);
+            return nbh[0];
+        }
+
+        void nearestK(const _T &data, std::size_t k, std::vector<_T> &nbh) const override
+        {
+            std::vector<std::vector<_T>> out;
+            nearestKBatch(std::vector<_T>(1, data), k, out);
+            nbh.swap(out[0]);
+        }
+
+        void nearestR(const _T &data, double radius, std::vector<_T> &nbh) const override
+        {
+            std::vector<std::vector<_T>> out;
+            nearestRBatch(std::vector<_T>(1, data), std::vector<double>(1, radius), out);
+            nbh.swap(out[0]);
+        }
+
+        std::size_t size() const override
+        {
+            std::size_t n = 0;
+            if (nn_ != nullptr)
+                b200::check(omplcu_nn_size(nn_, &n));
+            return n;
+        }
+
+        /** Elements in insertion order (NearestNeighborsLinear::list, :149-152). */
+        void list(std::vector<_T> &data) const override
+        {
+            data.clear();
+            const std::size_t n = size();
+            std::vector<std::uint64_t> ids(n);
+            std::size_t got = 0;
+            if (n != 0)
+                b200::check(omplcu_nn_list(nn_, ids.data(), n, &got));
+            data.reserve(got);
+            for (std::size_t i = 0; i < got; ++i)
+                data.push_back(elems_.at(ids[i]));
+        }
+
+        // ---- batch-submit entry points ----
+        /** out[i] = the min(k, size()) nearest elements of queries[i], sorted by (distance, insertion order).
+            dists (optional) receives the exact distances, row-major with out[i].size() entries per row. */
+        void nearestKBatch(const std::vector<_T> &queries, std::size_t k, std::vector<std::vector<_T>> &out,
+                           std::vector<double> *dists = nullptr) const
+        {
+            ready();
+            const std::size_t nq = queries.size(), st = space_.stride();
+            out.assign(nq, std::vector<_T>());
+            if (dists != nullptr)
+                dists->clear();
+            if (nq == 0 || k == 0)
+                return;
+            std::vector<double> rows(nq * st);
+            for (std::size_t i = 0; i < nq; ++i)
+                rowFun_(queries[i], rows.data() + i * st);
+            std::vector<std::uint64_t> ids(nq * k);
+            std::vector<double> d(dists != nullptr ? nq * k : 0);
+            std::vector<std::uint32_t> counts(nq);
+            b200::check(omplcu_nn_knn(nn_, rows.data(), nq, k, ids.data(), dists != nullptr ? d.data() : nullptr,
+                                      counts.data()));
+            for (std::size_t i = 0; i < nq; ++i)
+            {
+                out[i].reserve(counts[i]);
+                for (std::uint32_t j = 0; j < counts[i]; ++j)
+                {
+                    out[i].push_back(elems_.at(ids[i * k + j]));
+                    if (dists != nullptr)
+                        dists->push_back(d[i * k + j]);
+                }
+            }
+        }
+
+        /** out[i] = all elements within radii[i] of queries[i] (inclusive), sorted. */
+        void nearestRBatch(const std::vector<_T> &queries, const std::vector<double> &radii,
+                           std::vector<std::vector<_T>> &out) const
+        {
+            ready();
+            const std::size_t nq = queries.size(), st = space_.stride();
+            if (radii.size() != nq)
+                throw Exception("NearestNeighborsCUDA::nearestRBatch: one radius per query");
+            out.assign(nq, std::vector<_T>());
+            if (nq == 0)
+                return;
+            std::vector<double> rows(nq * st);
+            for (std::size_t i = 0; i < nq; ++i)
+                rowFun_(queries[i], rows.data() + i * st);
+            std::vector<std::uint64_t> offs(nq + 1);
+            std::uint64_t *ids = nullptr;
+            b200::check(omplcu_nn_radius(nn_, rows.data(), nq, radii.data(), &ids, nullptr, offs.data()));
+            for (std::size_t i = 0; i < nq; ++i)
+            {
+                out[i].reserve(offs[i + 1] - offs[i]);
+                for (std::uint64_t j = offs[i]; j < offs[i + 1]; ++j)
+                    out[i].push_back(elems_.at(ids[j]));
+            }
+            omplcu_free(ids);
+        }
+
+        omplcu_nn_t handle() const
+        {
+            return nn_;
+        }
+
+    private:
+        void ready() const
+        {
+            if (nn_ == nullptr)
+                throw Exception("NearestNeighborsCUDA: setSpace() was not called");
+            if (!rowFun_)
+                throw Exception("NearestNeighborsCUDA: setRowFunction() was not called");
+        }
+        void remember(std::uint64_t id, const _T &e)
+        {
+            elems_.emplace(id, e);
+            idsOf_.emplace(e, id);
+        }
+
+        RowFunction rowFun_;
+        int device_{0};
+        b200::SpaceHandle space_;
+        omplcu_nn_t nn_{nullptr};
+        std::unordered_map<std::uint64_t, _T> elems_;       // id -> element
+        std::unordered_multimap<_T, std::uint64_t> idsOf_;  // element -> ids (for remove)
+        mutable std::vector<double> row_;
+    };
+}  // namespace ompl
+
+#endif

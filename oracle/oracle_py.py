@@ -337,3 +337,96 @@ class RefNN:
         if r < 0:
             raise RuntimeError(err.value.decode())
         return r
+
+
+# ---- the reference's own state spaces + DiscreteMotionValidator (oracle/_ref/libompl_refbase.so) ----
+REFBASE_SO = os.path.join(HERE, "_ref", "libompl_refbase.so")
+_rb = None
+
+
+def have_refbase():
+    return os.path.exists(REFBASE_SO)
+
+
+def refbase():
+    global _rb
+    if _rb is None:
+        r = C.CDLL(REFBASE_SO)
+        r.refb_create.restype = C.c_void_p
+        r.refb_create.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_double, C.c_uint]
+        r.refb_destroy.restype = None
+        r.refb_destroy.argtypes = [C.c_void_p]
+        r.refb_stride.restype = C.c_uint
+        r.refb_stride.argtypes = [C.c_void_p]
+        r.refb_max_extent.restype = C.c_double
+        r.refb_max_extent.argtypes = [C.c_void_p]
+        r.refb_longest_valid_segment.restype = C.c_double
+        r.refb_longest_valid_segment.argtypes = [C.c_void_p]
+        r.refb_distance.restype = None
+        r.refb_distance.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        r.refb_interpolate.restype = None
+        r.refb_interpolate.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        r.refb_segment_count.restype = None
+        r.refb_segment_count.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+        r.refb_check_motions.restype = None
+        r.refb_check_motions.argtypes = [C.c_void_p, C.POINTER(OrcChecker), C.c_void_p, C.c_void_p, C.c_size_t,
+                                         C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+        _rb = r
+    return _rb
+
+
+class RefBase:
+    """A reference state space (RealVector / SO2 / SO3 / SE2 / SE3) after setup(), with the
+    reference's DiscreteMotionValidator on top; rows are copyToReals order."""
+
+    KINDS = {"rv": 0, "so2": 1, "so3": 2, "se2": 3, "se3": 4}
+
+    def __init__(self, kind, dim=0, low=0.0, high=1.0, fraction=0.01, factor=1):
+        nb = {"rv": dim, "se2": 2, "se3": 3}.get(kind, 0)
+        lo = _arr(np.broadcast_to(low, (max(nb, 1),)))
+        hi = _arr(np.broadcast_to(high, (max(nb, 1),)))
+        self.h = refbase().refb_create(self.KINDS[kind], dim, _p(lo), _p(hi), fraction, factor)
+        self.stride = refbase().refb_stride(self.h)
+
+    def __del__(self):
+        try:
+            refbase().refb_destroy(self.h)
+        except Exception:
+            pass
+
+    def max_extent(self):
+        return refbase().refb_max_extent(self.h)
+
+    def longest_valid_segment(self):
+        return refbase().refb_longest_valid_segment(self.h)
+
+    def distance(self, a, b):
+        a, b = _arr(a).reshape(-1, self.stride), _arr(b).reshape(-1, self.stride)
+        out = np.empty(len(a))
+        refbase().refb_distance(self.h, _p(a), _p(b), len(a), _p(out))
+        return out
+
+    def interpolate(self, a, b, t):
+        a, b = _arr(a).reshape(-1, self.stride), _arr(b).reshape(-1, self.stride)
+        t = _arr(np.broadcast_to(np.asarray(t, dtype=np.float64), (len(a),)))
+        out = np.empty_like(a)
+        refbase().refb_interpolate(self.h, _p(a), _p(b), _p(t), len(a), _p(out))
+        return out
+
+    def segment_count(self, a, b):
+        a, b = _arr(a).reshape(-1, self.stride), _arr(b).reshape(-1, self.stride)
+        out = np.empty(len(a), dtype=np.uint32)
+        refbase().refb_segment_count(self.h, _p(a), _p(b), len(a), _p(out))
+        return out
+
+    def check_motions(self, chk, s1, s2, last_valid=False, last_state=False):
+        a, b = _arr(s1).reshape(-1, self.stride), _arr(s2).reshape(-1, self.stride)
+        v = np.empty(len(a), dtype=np.uint8)
+        t = np.empty(len(a)) if last_valid else None
+        st = np.zeros_like(a) if (last_valid and last_state) else None
+        cnt = np.zeros(2, dtype=np.uint32)
+        refbase().refb_check_motions(self.h, C.byref(chk.c), _p(a), _p(b), len(a), _p(v), _p(t), _p(st), _p(cnt))
+        self.counts = cnt
+        if last_valid:
+            return v.astype(bool), t, st
+        return v.astype(bool)

@@ -92,6 +92,51 @@ def knn_golden():
     print("knn_linear_se3:", ids.shape)
 
 
+def ref_spaces_dmv():
+    """Outputs of the reference's OWN compiled StateSpace / spaces / DiscreteMotionValidator code
+    (oracle/_ref/libompl_refbase.so): distance, interpolate(0.37), validSegmentCount, checkMotion
+    booleans and lastValid.second.  Validity predicates are the oracle's demo-checker restatements."""
+    out = {}
+    r = helpers.rng(21)
+    n = 400
+    # SE3 in [-1,1]^3 vs 500 spheres + 500 boxes (BASELINE config 4 shape), resolution 0.01
+    rb = orc.RefBase("se3", 0, -1.0, 1.0)
+    sph, box = helpers.se3_obstacles()
+    robot = helpers.se3_robot()
+    chk = orc.checker_se3(robot, sph, box)
+    a, b = helpers.se3_states(31, n), helpers.se3_states(32, n)
+    b[::2, :3] = a[::2, :3] + r.normal(0, 0.02, (n // 2, 3))
+    b[::2, 3:] = a[::2, 3:]
+    v, t, _ = rb.check_motions(chk, a, b, True, True)
+    out.update(se3_a=a, se3_b=b, se3_dist=rb.distance(a, b), se3_interp=rb.interpolate(a, b, 0.37),
+               se3_nd=rb.segment_count(a, b), se3_valid=v, se3_last_t=t, se3_sph=sph, se3_box=box, se3_robot=robot)
+    # SE2 [0,1]^2 vs three circles
+    rb = orc.RefBase("se2", 0, 0.0, 1.0)
+    circ = np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1], [0.8, 0.2, 0.15]])
+    chk = orc.checker_circles(circ)
+    a, b = helpers.se2_states(33, n), helpers.se2_states(34, n)
+    v, t, _ = rb.check_motions(chk, a, b, True, True)
+    out.update(se2_a=a, se2_b=b, se2_dist=rb.distance(a, b), se2_interp=rb.interpolate(a, b, 0.37),
+               se2_nd=rb.segment_count(a, b), se2_valid=v, se2_last_t=t, se2_circ=circ)
+    # hypercube d = 8, resolution 0.001 (demos/HypercubeBenchmark.cpp:93-97)
+    rb = orc.RefBase("rv", 8, 0.0, 1.0, fraction=0.001)
+    chk = orc.checker_hypercube(8)
+    a = helpers.hypercube_valid_states(35, n, 8)
+    b = np.clip(a + r.normal(0, 0.03, a.shape), 0, 1)
+    b[::3] = helpers.hypercube_valid_states(36, len(b[::3]), 8)
+    v, t, _ = rb.check_motions(chk, a, b, True, True)
+    out.update(hc_a=a, hc_b=b, hc_dist=rb.distance(a, b), hc_nd=rb.segment_count(a, b), hc_valid=v, hc_last_t=t)
+    # SO3 alone (arc length + slerp)
+    rb = orc.RefBase("so3")
+    a, b = helpers.random_quaternions(37, n), helpers.random_quaternions(38, n)
+    out.update(so3_a=a, so3_b=b, so3_dist=rb.distance(a, b), so3_interp=rb.interpolate(a, b, 0.37),
+               so3_nd=rb.segment_count(a, b))
+    np.savez_compressed(os.path.join(OUT, "ref_spaces_dmv.npz"), **out)
+    print("ref_spaces_dmv: se3 valid", int(out["se3_valid"].sum()), "se2 valid", int(out["se2_valid"].sum()),
+          "hypercube valid", int(out["hc_valid"].sum()))
+
+
 if __name__ == "__main__":
     circle_world()
     knn_golden()
+    ref_spaces_dmv()

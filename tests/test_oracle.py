@@ -247,3 +247,110 @@ def test_oracle_equals_linear_when_no_tie_at_boundary():
     uniq[:, :-1] &= od[:, :-1] != od[:, 1:]
     uniq[:, -1] = False  # boundary membership may differ under a tie with rank k+1
     assert (rid[uniq] == oid[uniq]).all()
+
+
+# ---------------------------------------------------------------- (d) the reference's own state spaces + DiscreteMotionValidator
+needs_refbase = pytest.mark.skipif(not orc.have_refbase(), reason="oracle/_ref/libompl_refbase.so not built")
+
+
+def _ref_and_oracle(kind):
+    if kind == "rv":
+        return orc.RefBase("rv", 7), orc.space_rv(7), lambda s, n: helpers.uniform_points(s, n, 7)
+    if kind == "so2":
+        return orc.RefBase("so2"), orc.space_so2(), lambda s, n: helpers.rng(s).uniform(-PI, PI, (n, 1))
+    if kind == "so3":
+        return orc.RefBase("so3"), orc.space_so3(), helpers.random_quaternions
+    if kind == "se2":
+        return orc.RefBase("se2", 0, 0.0, 1.0), orc.space_se2(), helpers.se2_states
+    return orc.RefBase("se3", 0, -1.0, 1.0), orc.space_se3(-1.0, 1.0), helpers.se3_states
+
+
+@needs_refbase
+@pytest.mark.parametrize("kind", ["rv", "so2", "so3", "se2", "se3"])
+def test_oracle_space_math_equals_reference_code(kind):
+    """distance / interpolate / validSegmentCount of the restatement are bit-identical to the
+    reference's compiled StateSpace.cpp + spaces/src/*.cpp (same libm, same flags)."""
+    rb, osp, gen = _ref_and_oracle(kind)
+    n = 4000
+    a, b = gen(1, n), gen(2, n)
+    a[:50] = b[:50]  # zero distances, nd = 0
+    assert rb.stride == osp.stride
+    assert (rb.distance(a, b) == orc.distance(osp, a, b)).all()
+    for t in (0.0, 0.125, 0.37, 0.5, 1.0):
+        assert (rb.interpolate(a, b, t) == orc.interpolate(osp, a, b, t)).all()
+    assert (rb.segment_count(a, b) == orc.segment_count(osp, a, b)).all()
+    # longest valid segment: extent * 0.01 per (sub)space, StateSpace.cpp:237-248
+    if not osp.compound:
+        assert rb.longest_valid_segment() == osp.comp[0].lvs
+
+
+@needs_refbase
+def test_oracle_segment_count_factor_and_resolution():
+    rb = orc.RefBase("rv", 8, 0.0, 1.0, fraction=0.001, factor=3)
+    osp = orc.space_rv(8, 0.0, 1.0, 0.001)
+    osp.comp[0].factor = 3
+    a, b = helpers.uniform_points(3, 2000, 8), helpers.uniform_points(4, 2000, 8)
+    assert (rb.segment_count(a, b) == orc.segment_count(osp, a, b)).all()
+
+
+@needs_refbase
+@pytest.mark.parametrize("case", ["circles_rv2", "hypercube_rv8", "se3_obstacles", "se2_circles"])
+def test_oracle_motion_validator_equals_reference_code(case):
+    """Both checkMotion overloads of the restated DiscreteMotionValidator against the reference's
+    compiled DiscreteMotionValidator.cpp (booleans, lastValid.second, lastValid.first, counters)."""
+    r = helpers.rng(11)
+    if case == "circles_rv2":
+        z = helpers.load_circles()
+        rb, osp = orc.RefBase("rv", 2, z["low"], z["high"]), orc.space_rv(2, z["low"], z["high"])
+        chk = orc.checker_circles(z["circles"])
+        a = np.vstack([z["queries"][:, :2], r.uniform(z["low"], z["high"], (1500, 2))])
+        b = np.vstack([z["queries"][:, 2:], r.uniform(z["low"], z["high"], (1500, 2))])
+    elif case == "hypercube_rv8":
+        rb, osp = orc.RefBase("rv", 8, 0.0, 1.0, fraction=0.001), orc.space_rv(8, 0.0, 1.0, 0.001)
+        chk = orc.checker_hypercube(8)
+        a = helpers.hypercube_valid_states(1, 600, 8)
+        b = np.clip(a + r.normal(0, 0.03, a.shape), 0, 1)
+        b[::3] = helpers.hypercube_valid_states(3, len(b[::3]), 8)
+    elif case == "se3_obstacles":
+        rb, osp = orc.RefBase("se3", 0, -1.0, 1.0), orc.space_se3(-1.0, 1.0)
+        sph, box = helpers.se3_obstacles()
+        chk = orc.checker_se3(helpers.se3_robot(), sph, box)
+        a, b = helpers.se3_states(1, 1500), helpers.se3_states(2, 1500)
+        b[::2, :3] = a[::2, :3] + r.normal(0, 0.02, (750, 3))
+        b[::2, 3:] = a[::2, 3:]
+    else:
+        rb, osp = orc.RefBase("se2", 0, 0.0, 1.0), orc.space_se2()
+        chk = orc.checker_circles(np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1], [0.8, 0.2, 0.15]]))
+        a, b = helpers.se2_states(1, 1500), helpers.se2_states(2, 1500)
+    rv = rb.check_motions(chk, a, b)
+    assert tuple(rb.counts) == (int(rv.sum()), int((~rv).sum()))  # one count per segment, :139-142
+    rv2, rt, rst = rb.check_motions(chk, a, b, last_valid=True, last_state=True)
+    ov, ot = orc.check_motions(osp, chk, a, b, last_valid=True)
+    assert (rv == ov).all() and (rv2 == ov).all() and 0 < ov.sum() < len(ov)
+    assert (rt[~ov] == ot[~ov]).all()
+    for i in np.where(~ov)[0][:100]:
+        ok, t, st = orc.check_motion_last(osp, chk, a[i], b[i])
+        assert not ok and t == rt[i] and (st == rst[i]).all()
+
+
+def test_oracle_matches_reference_spaces_dmv_fixture():
+    """tests/golden/ref_spaces_dmv.npz was produced by the reference's compiled code
+    (scripts/gen_golden.py::ref_spaces_dmv); it pins the restatement where _ref cannot travel."""
+    z = np.load(os.path.join(helpers.GOLDEN, "ref_spaces_dmv.npz"))
+    se3, se2, so3 = orc.space_se3(-1.0, 1.0), orc.space_se2(), orc.space_so3()
+    hc = orc.space_rv(8, 0.0, 1.0, 0.001)
+    for name, sp in (("se3", se3), ("se2", se2), ("so3", so3)):
+        a, b = z[name + "_a"], z[name + "_b"]
+        assert (orc.distance(sp, a, b) == z[name + "_dist"]).all()
+        assert (orc.interpolate(sp, a, b, 0.37) == z[name + "_interp"]).all()
+        assert (orc.segment_count(sp, a, b) == z[name + "_nd"]).all()
+    assert (orc.distance(hc, z["hc_a"], z["hc_b"]) == z["hc_dist"]).all()
+    assert (orc.segment_count(hc, z["hc_a"], z["hc_b"]) == z["hc_nd"]).all()
+    cases = (
+        ("se3", se3, orc.checker_se3(z["se3_robot"], z["se3_sph"], z["se3_box"])),
+        ("se2", se2, orc.checker_circles(z["se2_circ"])),
+        ("hc", hc, orc.checker_hypercube(8)),
+    )
+    for name, sp, chk in cases:
+        v, t = orc.check_motions(sp, chk, z[name + "_a"], z[name + "_b"], last_valid=True)
+        assert (v == z[name + "_valid"]).all() and (t[~v] == z[name + "_last_t"][~v]).all()

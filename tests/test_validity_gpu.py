@@ -235,3 +235,50 @@ def test_motion_count_factor_and_empty(gpu):
     _motion_parity(sp, osp, chk, orc.checker_hypercube(3), a, b)
     mv = ob.BatchedDiscreteMotionValidator(sp, chk)
     assert len(mv.checkMotionBatch(np.zeros((0, 3)), np.zeros((0, 3)))) == 0
+
+
+# ---------------------------------------------------------------- vs the reference's own compiled code
+def test_gpu_matches_reference_spaces_dmv_fixture(gpu):
+    """tests/golden/ref_spaces_dmv.npz: outputs of the reference's compiled StateSpace / spaces /
+    DiscreteMotionValidator (scripts/gen_golden.py).  RealVector / SE2 results are bit-exact;
+    SO3 / SE3 go through acos / sin and may differ from glibc in the last bit."""
+    import os
+
+    z = np.load(os.path.join(helpers.GOLDEN, "ref_spaces_dmv.npz"))
+    se2 = ob.SE2StateSpace()
+    a, b = z["se2_a"], z["se2_b"]
+    assert (se2.distance(a, b) == z["se2_dist"]).all()
+    assert (se2.interpolate(a, b, 0.37) == z["se2_interp"]).all()
+    assert (se2.validSegmentCount(a, b) == z["se2_nd"]).all()
+    mv = ob.BatchedDiscreteMotionValidator(se2, ob.Circles2DValidityChecker(z["se2_circ"]))
+    v, t, _ = mv.checkMotionBatch(a, b, last_valid=True)
+    assert (v == z["se2_valid"]).all() and (t[~v] == z["se2_last_t"][~v]).all()
+
+    hc = ob.RealVectorStateSpace(8)
+    hc.setLongestValidSegmentFraction(0.001)
+    a, b = z["hc_a"], z["hc_b"]
+    assert (hc.distance(a, b) == z["hc_dist"]).all() and (hc.validSegmentCount(a, b) == z["hc_nd"]).all()
+    mv = ob.BatchedDiscreteMotionValidator(hc, ob.HypercubeValidityChecker(8))
+    v, t, _ = mv.checkMotionBatch(a, b, last_valid=True)
+    assert (v == z["hc_valid"]).all() and (t[~v] == z["hc_last_t"][~v]).all()
+
+    se3 = ob.SE3StateSpace(-1.0, 1.0)
+    a, b = z["se3_a"], z["se3_b"]
+    assert (helpers.ulp_diff(se3.distance(a, b), z["se3_dist"]) <= 2).all()
+    assert np.allclose(se3.interpolate(a, b, 0.37), z["se3_interp"], rtol=0, atol=2e-15)
+    assert (se3.validSegmentCount(a, b) == z["se3_nd"]).all()
+    mv = ob.BatchedDiscreteMotionValidator(se3, ob.SE3ObstacleValidityChecker(z["se3_robot"], z["se3_sph"], z["se3_box"]))
+    v, t, _ = mv.checkMotionBatch(a, b, last_valid=True)
+    assert (v == z["se3_valid"]).all() and (t[~v] == z["se3_last_t"][~v]).all()
+
+
+@pytest.mark.skipif(not orc.have_refbase(), reason="oracle/_ref/libompl_refbase.so did not travel")
+def test_gpu_vs_live_reference_motion_validator(gpu):
+    """Larger live differential run against the reference's compiled DiscreteMotionValidator."""
+    rb = orc.RefBase("se2", 0, 0.0, 1.0)
+    circ = np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1], [0.8, 0.2, 0.15], [0.3, 0.3, 0.05]])
+    a, b = helpers.se2_states(41, 20000), helpers.se2_states(42, 20000)
+    rv, rt, rst = rb.check_motions(orc.checker_circles(circ), a, b, last_valid=True, last_state=True)
+    mv = ob.BatchedDiscreteMotionValidator(ob.SE2StateSpace(), ob.Circles2DValidityChecker(circ))
+    v, t, st = mv.checkMotionBatch(a, b, last_valid=True, last_state=True)
+    assert (v == rv).all() and (t[~v] == rt[~v]).all() and (st[~v] == rst[~v]).all()
