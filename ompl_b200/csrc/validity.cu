@@ -14,13 +14,23 @@
 // j = 1..nd-1, nd = validSegmentCount(s1, s2), is valid.  The reference visits
 // them in bisection order and stops at the first failure
 // (DiscreteMotionValidator.cpp:115-134); the checkers are pure, so the result
-// does not depend on the order and all states of all segments are checked in
-// one flat launch: thread e of the grid owns one (segment, j) pair found by
-// binary search in the exclusive prefix sum of per-segment state counts, and
-// the per-segment outcome is the MINIMUM failing j (atomicMin), which is what
-// the lastValid overload reports (DiscreteMotionValidator.cpp:60-72).
-// All arithmetic is FP64 with the reference's operation order (common.cuh).
+// does not depend on the order.  Here a GROUP of G lanes (G = 4..32, chosen from
+// the mean state count per segment) owns one segment at a time: the lanes take
+// the states j = 1, 2, ... in increasing order, G per pass, then s2; one warp
+// ballot per pass finds the first failing state, which ends the segment (early
+// exit) and is exactly what the lastValid overload reports
+// (DiscreteMotionValidator.cpp:60-72).  Groups pull segments from a global
+// counter, so long and short segments balance across the persistent grid.
+//
+// Interpolation and the deciding predicate are FP64 with the reference's
+// operation order (common.cuh).  The SE3 checker puts an FP32 bounding-sphere
+// filter in front of the FP64 predicate (se3_valid_fast); the filter is
+// conservative by a proven margin, so the booleans are those of the exact test.
 #include "validity.cuh"
+
+#include <algorithm>
+#include <limits>
+#include <vector>
 
 #include <cub/cub.cuh>
 
@@ -181,49 +191,141 @@ namespace omplcu
             return true;  // AllValidStateValidityChecker, base/StateValidityChecker.h:165-182
         }
 
-        // copy the SE3 obstacle set into shared memory (all threads participate)
-        template <int KIND>
-        __device__ __forceinline__ void stage_obstacles(const CheckerDesc &c, double *smem, const double *&robot,
-                                                        const double *&sph, const double *&box)
+        // ---- SE3: FP32 bounding-sphere filter in front of the FP64 predicate ----
+        //
+        // Every obstacle j gets a bounding sphere (centre o_j, radius rho_j: the sphere
+        // itself, or |half extents| for a box) and the robot one around the body origin p
+        // (radius rho_rob = max_i(|offset_i| + r_i), inflated by 2^-10).  A robot sphere
+        // can touch obstacle j only if |o_j - p| < rho_j + rho_rob =: sqrt(W_j), i.e. only if
+        //     (|o_j|^2 - W_j) - 2 o_j.p  <  -|p|^2.
+        // The left side is 3 FP32 FMAs per obstacle on the row (o_j, |o_j|^2 - W_j) kept in
+        // shared memory; the right side is one value per state.  With A >= every |o_c|,
+        // |p_c| and sqrt(W_j), the FP32 evaluation of both sides is off by less than
+        // 64 u A^2 (u = 2^-24; 12 u A^2 from rounding o and p, 27 u A^2 + 3 u W from the three
+        // FMAs, 3 u A^2 + u W from the stored norm, 18 u A^2 from the right side); the test
+        // uses a margin of 2^-16 A^2, four times that, so an obstacle that fails the filter
+        // provably cannot collide.  Survivors (about two per state in the benchmark
+        // world) go through the exact FP64 expressions of se3_valid for that obstacle.
+        // The body rotation maps offset o to (1-s) o + s R o with s = |q|^2, so
+        // |c_i - p| <= (|1-s| + s)|o_i|; states with |s - 1| > 2e-4 skip the filter.
+        template <typename PS>
+        __device__ __forceinline__ bool se3_pair_hits(const CheckerDesc &c, int j, PS st)
         {
-            robot = c.robot;
-            sph = c.sph;
-            box = c.box;
-            if (KIND == OMPLCU_CHK_SE3 && c.stage_smem)
+            const double px = st[0], py = st[1], pz = st[2];
+            const double qx = st[3], qy = st[4], qz = st[5], qw = st[6];
+            for (int i = 0; i < c.nrobot; ++i)
             {
-                double *r = smem, *sp = r + 4 * c.nrobot, *bx = sp + 4 * c.nsph;
-                for (int i = threadIdx.x; i < 4 * c.nrobot; i += blockDim.x)
-                    r[i] = c.robot[i];
-                for (int i = threadIdx.x; i < 4 * c.nsph; i += blockDim.x)
-                    sp[i] = c.sph[i];
-                for (int i = threadIdx.x; i < 6 * c.nbox; i += blockDim.x)
-                    bx[i] = c.box[i];
-                __syncthreads();
-                robot = r;
-                sph = sp;
-                box = bx;
+                const double ox = c.robot[4 * i + 0], oy = c.robot[4 * i + 1], oz = c.robot[4 * i + 2];
+                const double rr = c.robot[4 * i + 3];
+                const double tx = dmul(2.0, dsub(dmul(qy, oz), dmul(qz, oy)));
+                const double ty = dmul(2.0, dsub(dmul(qz, ox), dmul(qx, oz)));
+                const double tz = dmul(2.0, dsub(dmul(qx, oy), dmul(qy, ox)));
+                const double cx = dadd(px, dadd(dadd(ox, dmul(qw, tx)), dsub(dmul(qy, tz), dmul(qz, ty))));
+                const double cy = dadd(py, dadd(dadd(oy, dmul(qw, ty)), dsub(dmul(qz, tx), dmul(qx, tz))));
+                const double cz = dadd(pz, dadd(dadd(oz, dmul(qw, tz)), dsub(dmul(qx, ty), dmul(qy, tx))));
+                if (j < c.nsph)
+                {
+                    const double *sp = c.sph + 4 * j;
+                    const double dx = dsub(sp[0], cx);
+                    const double dy = dsub(sp[1], cy);
+                    const double dz = dsub(sp[2], cz);
+                    const double R = dadd(sp[3], rr);
+                    if (dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz)) < dmul(R, R))
+                        return true;
+                }
+                else
+                {
+                    const double *bx = c.box + 6 * (j - c.nsph);
+                    double ex = dsub(fabs(dsub(cx, bx[0])), bx[3]);
+                    double ey = dsub(fabs(dsub(cy, bx[1])), bx[4]);
+                    double ez = dsub(fabs(dsub(cz, bx[2])), bx[5]);
+                    if (ex < 0.0)
+                        ex = 0.0;
+                    if (ey < 0.0)
+                        ey = 0.0;
+                    if (ez < 0.0)
+                        ez = 0.0;
+                    if (dadd(dadd(dmul(ex, ex), dmul(ey, ey)), dmul(ez, ez)) < dmul(rr, rr))
+                        return true;
+                }
             }
+            return false;
+        }
+
+        template <typename PS>
+        __device__ __forceinline__ bool se3_valid_fast(const CheckerDesc &c, const float4 *F, PS st)
+        {
+            const float px = (float)st[0], py = (float)st[1], pz = (float)st[2];
+            const float qx = (float)st[3], qy = (float)st[4], qz = (float)st[5], qw = (float)st[6];
+            const float s = qx * qx + qy * qy + qz * qz + qw * qw;
+            if (!(fabsf(s - 1.0f) <= 2e-4f))
+                return se3_valid(c, c.robot, c.sph, c.box, st);
+            const float A = fmaxf(c.filt_amax, fmaxf(fabsf(px), fmaxf(fabsf(py), fabsf(pz)))) * 1.0001f;
+            const float pn = px * px + py * py + pz * pz;
+            const float tau = A * A * 1.52587890625e-05f - pn;
+            const float mx = -2.0f * px, my = -2.0f * py, mz = -2.0f * pz;
+            const int nf = c.nfilt_pad;
+#pragma unroll 2
+            for (int j = 0; j < nf; j += 4)
+            {
+                const float4 o0 = F[j], o1 = F[j + 1], o2 = F[j + 2], o3 = F[j + 3];
+                const float s0 = fmaf(mz, o0.z, fmaf(my, o0.y, fmaf(mx, o0.x, o0.w)));
+                const float s1 = fmaf(mz, o1.z, fmaf(my, o1.y, fmaf(mx, o1.x, o1.w)));
+                const float s2 = fmaf(mz, o2.z, fmaf(my, o2.y, fmaf(mx, o2.x, o2.w)));
+                const float s3 = fmaf(mz, o3.z, fmaf(my, o3.y, fmaf(mx, o3.x, o3.w)));
+                if ((s0 <= tau) | (s1 <= tau) | (s2 <= tau) | (s3 <= tau))
+                {
+                    if (s0 <= tau && se3_pair_hits(c, j, st))
+                        return false;
+                    if (s1 <= tau && se3_pair_hits(c, j + 1, st))
+                        return false;
+                    if (s2 <= tau && se3_pair_hits(c, j + 2, st))
+                        return false;
+                    if (s3 <= tau && se3_pair_hits(c, j + 3, st))
+                        return false;
+                }
+            }
+            return true;
+        }
+
+        template <int KIND, typename PS>
+        __device__ __forceinline__ bool state_valid_f(const CheckerDesc &c, const float4 *F, PS s)
+        {
+            if (KIND == OMPLCU_CHK_SE3)
+                return se3_valid_fast(c, F, s);
+            return state_valid<KIND>(c, c.robot, c.sph, c.box, s);
+        }
+
+        // copy the SE3 filter rows into shared memory (all threads participate)
+        template <int KIND>
+        __device__ __forceinline__ const float4 *stage_filter(const CheckerDesc &c, float4 *smem)
+        {
+            if (KIND != OMPLCU_CHK_SE3 || !c.stage_smem)
+                return c.filt;
+            for (int i = threadIdx.x; i < c.nfilt_pad; i += blockDim.x)
+                smem[i] = c.filt[i];
+            __syncthreads();
+            return smem;
         }
 
         template <int KIND, int MAXS>
         __global__ void __launch_bounds__(128) check_states_kernel(CheckerDesc c, int stride, const double *states,
                                                                    size_t n, uint8_t *valid)
         {
-            extern __shared__ double smem_obs[];
-            const double *robot, *sph, *box;
-            stage_obstacles<KIND>(c, smem_obs, robot, sph, box);
-            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-            if (i >= n)
-                return;
-            double st[MAXS];
-            for (int d = 0; d < stride && d < MAXS; ++d)
-                st[d] = states[i * stride + d];
-            valid[i] = state_valid<KIND>(c, robot, sph, box, st) ? 1 : 0;
+            extern __shared__ float4 smem_filt[];
+            const float4 *F = stage_filter<KIND>(c, smem_filt);
+            for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (size_t)blockDim.x)
+            {
+                double st[MAXS];
+                for (int d = 0; d < stride && d < MAXS; ++d)
+                    st[d] = states[i * stride + d];
+                valid[i] = state_valid_f<KIND>(c, F, st) ? 1 : 0;
+            }
         }
 
         // nd and the number of states to check per segment: (nd-1 interior if nd >= 2) + s2
         __global__ void segment_count_kernel(SpaceDesc sp, const double *s1, const double *s2, size_t n, uint32_t *nd,
-                                             unsigned long long *cnt, unsigned *code)
+                                             unsigned long long *cnt)
         {
             const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
             if (i >= n)
@@ -232,53 +334,92 @@ namespace omplcu
             nd[i] = v;
             if (cnt)
                 cnt[i] = (v >= 2 ? (unsigned long long)(v - 1) : 0ull) + 1ull;
-            if (code)
-                code[i] = CODE_VALID;
         }
 
-        template <int KIND, int MAXS>
-        __global__ void __launch_bounds__(128) motion_states_kernel(
-            CheckerDesc c, SpaceDesc sp, const double *s1, const double *s2, size_t n, const uint32_t *nd,
-            const unsigned long long *offs, unsigned long long total, unsigned *code, int want_first)
+        // ctr[0]: next segment to hand out, ctr[1]: states evaluated (statistics)
+        template <int KIND, int MAXS, int G>
+        __global__ void __launch_bounds__(128) motion_group_kernel(CheckerDesc c, SpaceDesc sp, const double *s1,
+                                                                   const double *s2, size_t n, const uint32_t *nd,
+                                                                   unsigned *code, unsigned long long *ctr)
         {
-            extern __shared__ double smem_obs[];
-            const double *robot, *sph, *box;
-            stage_obstacles<KIND>(c, smem_obs, robot, sph, box);
-            const unsigned long long e = blockIdx.x * (unsigned long long)blockDim.x + threadIdx.x;
-            if (e >= total)
-                return;
-            // segment = last index with offs[seg] <= e
-            size_t lo = 0, hi = n;
-            while (hi - lo > 1)
+            extern __shared__ float4 smem_filt[];
+            const float4 *F = stage_filter<KIND>(c, smem_filt);
+            constexpr unsigned FULL = 0xffffffffu;
+            const unsigned lane = threadIdx.x & 31u, gl = lane % G, gbase = lane - gl;
+            const unsigned gmask = (G == 32) ? FULL : (((1u << G) - 1u) << gbase);
+            size_t seg = 0;
+            unsigned cnt = 0, base = 0, ndv = 0;
+            unsigned long long evaluated = 0;
+            bool need = true, done = false;
+            while (true)
             {
-                const size_t mid = (lo + hi) >> 1;
-                if (offs[mid] <= e)
-                    lo = mid;
-                else
-                    hi = mid;
+                const bool fetch = need && !done;
+                unsigned long long sidx = 0;
+                if (fetch && gl == 0)
+                    sidx = atomicAdd(&ctr[0], 1ull);
+                sidx = __shfl_sync(FULL, sidx, gbase);
+                if (fetch)
+                {
+                    if (sidx >= n)
+                        done = true;
+                    else
+                    {
+                        seg = (size_t)sidx;
+                        ndv = nd[seg];
+                        cnt = (ndv >= 2 ? ndv - 1 : 0u) + 1u;
+                        base = 0;
+                        need = false;
+                    }
+                }
+                if (__all_sync(FULL, done))
+                    break;
+                // item m < cnt-1 is the interior state j = m+1, item cnt-1 is s2
+                const unsigned m = base + gl;
+                bool bad = false;
+                if (!done && m < cnt)
+                {
+                    const double *a = s1 + seg * sp.stride, *b = s2 + seg * sp.stride;
+                    double st[MAXS];
+                    if (m == cnt - 1)
+                    {
+                        for (int d = 0; d < sp.stride && d < MAXS; ++d)
+                            st[d] = b[d];
+                    }
+                    else
+                    {
+                        // t = (double)j / (double)nd, DiscreteMotionValidator.cpp:63,121
+                        const double t = ddiv((double)(m + 1), (double)ndv);
+                        space_interpolate(sp, a, b, t, st);
+                    }
+                    bad = !state_valid_f<KIND>(c, F, st);
+                    evaluated++;
+                }
+                const unsigned hit = __ballot_sync(FULL, bad) & gmask;
+                if (!done)
+                {
+                    if (hit)
+                    {
+                        const unsigned first = base + (unsigned)(__ffs(hit) - 1) - gbase;
+                        if (gl == 0)
+                            code[seg] = (first == cnt - 1) ? CODE_S2 : first + 1;
+                        need = true;
+                    }
+                    else
+                    {
+                        base += G;
+                        if (base >= cnt)
+                        {
+                            if (gl == 0)
+                                code[seg] = CODE_VALID;
+                            need = true;
+                        }
+                    }
+                }
             }
-            const size_t seg = lo;
-            const unsigned r = (unsigned)(e - offs[seg]);
-            const unsigned my = (r == 0) ? CODE_S2 : r;
-            // early exit: a failure that already decides this segment
-            const unsigned cur = code[seg];
-            if (want_first ? (cur <= my) : (cur != CODE_VALID))
-                return;
-            const double *a = s1 + seg * sp.stride, *b = s2 + seg * sp.stride;
-            double st[MAXS];
-            if (r == 0)
-            {
-                for (int d = 0; d < sp.stride && d < MAXS; ++d)
-                    st[d] = b[d];
-            }
-            else
-            {
-                // t = (double)j / (double)nd, DiscreteMotionValidator.cpp:63,121
-                const double t = ddiv((double)r, (double)nd[seg]);
-                space_interpolate(sp, a, b, t, st);
-            }
-            if (!state_valid<KIND>(c, robot, sph, box, st))
-                atomicMin(&code[seg], my);
+            for (int o = 16; o > 0; o >>= 1)
+                evaluated += __shfl_down_sync(FULL, evaluated, o);
+            if (lane == 0 && evaluated)
+                atomicAdd(&ctr[1], evaluated);
         }
 
         // valid flag, lastValid.second and lastValid.first per segment
@@ -357,14 +498,65 @@ namespace omplcu
         CUDA_CHECK(cudaStreamSynchronize(stream_));
         smem_bytes_ = 0;
         desc_.stage_smem = 0;
+        desc_.filt = nullptr;
+        desc_.nfilt_pad = 0;
+        desc_.filt_amax = 0.f;
         if (desc_.kind == OMPLCU_CHK_SE3)
+            build_se3_filter(robot, sph, box);
+        int dev_sms = 0;
+        CUDA_CHECK(cudaDeviceGetAttribute(&dev_sms, cudaDevAttrMultiProcessorCount, device_));
+        sms_ = dev_sms;
+        ctr_.reserve(2);
+    }
+
+    // Bounding-sphere rows for se3_valid_fast (see the comment there).  Everything is
+    // computed in FP64 and rounded so that the FP32 row can only widen the sphere.
+    void Checker::build_se3_filter(const double *robot, const double *sph, const double *box)
+    {
+        double rho_rob = 0.0;
+        for (int i = 0; i < desc_.nrobot; ++i)
         {
-            const size_t need = (n_rob + n_sph + n_box) * sizeof(double);
-            if (need <= 96 * 1024)
+            const double *o = robot + 4 * i;
+            rho_rob = std::max(rho_rob, std::sqrt(o[0] * o[0] + o[1] * o[1] + o[2] * o[2]) + std::fabs(o[3]));
+        }
+        rho_rob *= 1.0 + 1.0 / 1024.0;
+        const int nf = desc_.nsph + desc_.nbox;
+        const int pad = (nf + 3) / 4 * 4;
+        std::vector<float> rows(4 * (size_t)std::max(pad, 4));
+        double amax = 0.0;
+        for (int j = 0; j < pad; ++j)
+        {
+            float *r = rows.data() + 4 * (size_t)j;
+            if (j >= nf)
             {
-                smem_bytes_ = need;
-                desc_.stage_smem = 1;
+                r[0] = r[1] = r[2] = 0.f;
+                r[3] = std::numeric_limits<float>::infinity();  // never passes the filter
+                continue;
             }
+            const double *o = j < desc_.nsph ? sph + 4 * j : box + 6 * (j - desc_.nsph);
+            double rho;
+            if (j < desc_.nsph)
+                rho = std::fabs(o[3]);
+            else
+                rho = std::sqrt(o[3] * o[3] + o[4] * o[4] + o[5] * o[5]);
+            const double w = (rho + rho_rob) * (rho + rho_rob) * (1.0 + 1e-6);
+            r[0] = (float)o[0];
+            r[1] = (float)o[1];
+            r[2] = (float)o[2];
+            r[3] = (float)(o[0] * o[0] + o[1] * o[1] + o[2] * o[2] - w);
+            for (double v : {std::fabs(o[0]), std::fabs(o[1]), std::fabs(o[2]), std::sqrt(w)})
+                amax = std::max(amax, v);
+        }
+        filt_.reserve(rows.size() / 4);
+        CUDA_CHECK(cudaMemcpyAsync(filt_.p, rows.data(), rows.size() * sizeof(float), cudaMemcpyHostToDevice, stream_));
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+        desc_.filt = filt_.p;
+        desc_.nfilt_pad = pad;
+        desc_.filt_amax = (float)(amax * (1.0 + 1e-6));
+        if ((size_t)pad * sizeof(float4) <= 64 * 1024)
+        {
+            smem_bytes_ = (size_t)pad * sizeof(float4);
+            desc_.stage_smem = 1;
         }
     }
 
@@ -384,56 +576,79 @@ namespace omplcu
             return launches_;
         if (!strcmp(key, "last_states"))
             return last_states_;
+        if (!strcmp(key, "last_states_evaluated"))
+            return last_evaluated_;
+        if (!strcmp(key, "last_group"))
+            return last_group_;
         throw Error(OMPLCU_ERR_INVALID, std::string("unknown stat ") + key);
     }
 
     namespace
     {
         template <int KIND, int MAXS>
-        void launch_states(const CheckerDesc &c, size_t smem, int stride, const double *st, size_t n, uint8_t *v,
-                           cudaStream_t s)
+        void launch_states(const CheckerDesc &c, size_t smem, int sms, int stride, const double *st, size_t n,
+                           uint8_t *v, cudaStream_t s)
         {
             if (smem > 48 * 1024)
                 CUDA_CHECK(cudaFuncSetAttribute(check_states_kernel<KIND, MAXS>,
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            check_states_kernel<KIND, MAXS><<<nblk(n, 128), 128, smem, s>>>(c, stride, st, n, v);
+            const unsigned grid = std::min<unsigned>(nblk(n, 128), (unsigned)sms * 16u);
+            check_states_kernel<KIND, MAXS><<<grid, 128, smem, s>>>(c, stride, st, n, v);
+        }
+
+        template <int KIND, int MAXS, int G>
+        void launch_motion_g(const CheckerDesc &c, size_t smem, int sms, const SpaceDesc &sp, const double *s1,
+                             const double *s2, size_t n, const uint32_t *nd, unsigned *code, unsigned long long *ctr,
+                             cudaStream_t s)
+        {
+            if (smem > 48 * 1024)
+                CUDA_CHECK(cudaFuncSetAttribute(motion_group_kernel<KIND, MAXS, G>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            // persistent grid: a multiple of the SM count, no more groups than segments
+            const size_t groups_per_cta = 128 / G;
+            const unsigned want = (unsigned)std::min<size_t>((n + groups_per_cta - 1) / groups_per_cta,
+                                                             (size_t)sms * 8u);
+            motion_group_kernel<KIND, MAXS, G><<<std::max(want, 1u), 128, smem, s>>>(c, sp, s1, s2, n, nd, code, ctr);
         }
 
         template <int KIND, int MAXS>
-        void launch_motion(const CheckerDesc &c, size_t smem, const SpaceDesc &sp, const double *s1, const double *s2,
-                           size_t n, const uint32_t *nd, const unsigned long long *offs, unsigned long long total,
-                           unsigned *code, int want_first, cudaStream_t s)
+        void launch_motion(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
+                           const double *s1, const double *s2, size_t n, const uint32_t *nd, unsigned *code,
+                           unsigned long long *ctr, cudaStream_t s)
         {
-            if (smem > 48 * 1024)
-                CUDA_CHECK(cudaFuncSetAttribute(motion_states_kernel<KIND, MAXS>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            motion_states_kernel<KIND, MAXS>
-                <<<nblk(total, 128), 128, smem, s>>>(c, sp, s1, s2, n, nd, offs, total, code, want_first);
+            if (group >= 32)
+                launch_motion_g<KIND, MAXS, 32>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+            else if (group >= 16)
+                launch_motion_g<KIND, MAXS, 16>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+            else if (group >= 8)
+                launch_motion_g<KIND, MAXS, 8>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+            else
+                launch_motion_g<KIND, MAXS, 4>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
         }
 
         template <int KIND>
-        void states_by_stride(const CheckerDesc &c, size_t smem, int stride, const double *st, size_t n, uint8_t *v,
-                              cudaStream_t s)
+        void states_by_stride(const CheckerDesc &c, size_t smem, int sms, int stride, const double *st, size_t n,
+                              uint8_t *v, cudaStream_t s)
         {
             if (stride <= 8)
-                launch_states<KIND, 8>(c, smem, stride, st, n, v, s);
+                launch_states<KIND, 8>(c, smem, sms, stride, st, n, v, s);
             else if (stride <= 32)
-                launch_states<KIND, 32>(c, smem, stride, st, n, v, s);
+                launch_states<KIND, 32>(c, smem, sms, stride, st, n, v, s);
             else
-                launch_states<KIND, MAX_STRIDE>(c, smem, stride, st, n, v, s);
+                launch_states<KIND, MAX_STRIDE>(c, smem, sms, stride, st, n, v, s);
         }
 
         template <int KIND>
-        void motion_by_stride(const CheckerDesc &c, size_t smem, const SpaceDesc &sp, const double *s1,
-                              const double *s2, size_t n, const uint32_t *nd, const unsigned long long *offs,
-                              unsigned long long total, unsigned *code, int want_first, cudaStream_t s)
+        void motion_by_stride(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
+                              const double *s1, const double *s2, size_t n, const uint32_t *nd, unsigned *code,
+                              unsigned long long *ctr, cudaStream_t s)
         {
             if (sp.stride <= 8)
-                launch_motion<KIND, 8>(c, smem, sp, s1, s2, n, nd, offs, total, code, want_first, s);
+                launch_motion<KIND, 8>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
             else if (sp.stride <= 32)
-                launch_motion<KIND, 32>(c, smem, sp, s1, s2, n, nd, offs, total, code, want_first, s);
+                launch_motion<KIND, 32>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
             else
-                launch_motion<KIND, MAX_STRIDE>(c, smem, sp, s1, s2, n, nd, offs, total, code, want_first, s);
+                launch_motion<KIND, MAX_STRIDE>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
         }
 
         void check_stride(const CheckerDesc &c, int stride)
@@ -461,19 +676,19 @@ namespace omplcu
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                states_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, stride, d_states, n, d_valid, s);
+                states_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, stride, d_states, n, d_valid, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                states_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, stride, d_states, n, d_valid, s);
+                states_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, stride, d_states, n, d_valid, s);
                 break;
             case OMPLCU_CHK_SE3:
-                states_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, stride, d_states, n, d_valid, s);
+                states_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, stride, d_states, n, d_valid, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                states_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, stride, d_states, n, d_valid, s);
+                states_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, stride, d_states, n, d_valid, s);
                 break;
             default:
-                states_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, stride, d_states, n, d_valid, s);
+                states_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, stride, d_states, n, d_valid, s);
         }
         launches_++;
         last_states_ = (long)n;
@@ -493,51 +708,54 @@ namespace omplcu
         check_stride(desc_, sp.stride);
         nd_.reserve(n);
         cnt_.reserve(n);
-        offs_.reserve(n + 1);
+        offs_.reserve(1);
         code_.reserve(n);
-        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd_.p, cnt_.p, code_.p);
+        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd_.p, cnt_.p);
         CUDA_CHECK(cudaGetLastError());
         size_t tmp = 0;
-        CUDA_CHECK(cub::DeviceScan::ExclusiveSum(nullptr, tmp, cnt_.p, offs_.p, (int)n, s));
+        CUDA_CHECK(cub::DeviceReduce::Sum(nullptr, tmp, cnt_.p, offs_.p, (int)n, s));
         cub_tmp_.reserve(tmp);
-        CUDA_CHECK(cub::DeviceScan::ExclusiveSum(cub_tmp_.p, tmp, cnt_.p, offs_.p, (int)n, s));
-        unsigned long long last_off = 0, last_cnt = 0;
-        CUDA_CHECK(cudaMemcpyAsync(&last_off, offs_.p + (n - 1), sizeof(last_off), cudaMemcpyDeviceToHost, s));
-        CUDA_CHECK(cudaMemcpyAsync(&last_cnt, cnt_.p + (n - 1), sizeof(last_cnt), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cub::DeviceReduce::Sum(cub_tmp_.p, tmp, cnt_.p, offs_.p, (int)n, s));
+        unsigned long long total = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&total, offs_.p, sizeof(total), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemsetAsync(ctr_.p, 0, 2 * sizeof(unsigned long long), s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        const unsigned long long total = last_off + last_cnt;
-        REQUIRE(total < (1ull << 40), "omplcu_check_motions: too many interpolated states in one batch");
-        const int want_first = d_last_t ? 1 : 0;
-        // at most 2^31-1 blocks of 128 threads per launch: split very large batches
+        // lanes per segment: the power of two nearest below 1.5 x the mean state count
+        const double mean = (double)total / (double)n;
+        const int group = mean >= 24.0 ? 32 : mean >= 12.0 ? 16 : mean >= 6.0 ? 8 : 4;
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sp, d_s1, d_s2, n, nd_.p, offs_.p, total, code_.p,
-                                                       want_first, s);
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                                                       ctr_.p, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sp, d_s1, d_s2, n, nd_.p, offs_.p, total, code_.p,
-                                                   want_first, s);
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p, ctr_.p,
+                                                   s);
                 break;
             case OMPLCU_CHK_SE3:
-                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sp, d_s1, d_s2, n, nd_.p, offs_.p, total,
-                                                 code_.p, want_first, s);
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                                                 ctr_.p, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sp, d_s1, d_s2, n, nd_.p, offs_.p, total, code_.p,
-                                                     want_first, s);
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p, ctr_.p,
+                                                     s);
                 break;
             default:
-                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sp, d_s1, d_s2, n, nd_.p, offs_.p, total, code_.p,
-                                                      want_first, s);
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                                                      ctr_.p, s);
         }
         CUDA_CHECK(cudaGetLastError());
         motion_finalize_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd_.p, code_.p, d_valid, d_last_t,
                                                             d_last_state);
         CUDA_CHECK(cudaGetLastError());
+        unsigned long long ctr_host[2] = {0, 0};
+        CUDA_CHECK(cudaMemcpyAsync(ctr_host, ctr_.p, sizeof(ctr_host), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
         launches_ += 4;
         last_states_ = (long)total;
-        CUDA_CHECK(cudaStreamSynchronize(s));
+        last_evaluated_ = (long)ctr_host[1];
+        last_group_ = group;
     }
 
     void Checker::check_states_host(int stride, const double *states, size_t n, uint8_t *valid)
@@ -668,7 +886,7 @@ namespace omplcu
         dout.reserve(n);
         CUDA_CHECK(cudaMemcpyAsync(da.p, a, n * st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
         CUDA_CHECK(cudaMemcpyAsync(db.p, b, n * st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
-        segment_count_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, da.p, db.p, n, dout.p, nullptr, nullptr);
+        segment_count_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, da.p, db.p, n, dout.p, nullptr);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaMemcpyAsync(out, dout.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ts.s));
         CUDA_CHECK(cudaStreamSynchronize(ts.s));

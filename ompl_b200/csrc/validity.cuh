@@ -30,6 +30,9 @@ namespace omplcu
         int nrobot, nsph, nbox, ncirc;
         const double *robot, *sph, *box, *circ;
         int stage_smem;
+        int nfilt_pad;            // SE3 filter rows (multiple of 4)
+        const float4 *filt;       // (o.x, o.y, o.z, |o|^2 - W) per obstacle, see se3_valid_fast
+        float filt_amax;          // bound on |o_c| and sqrt(W) over the rows
         int _pad;
     };
 
@@ -53,11 +56,15 @@ namespace omplcu
         }
 
     private:
+        void build_se3_filter(const double *robot, const double *sph, const double *box);
         int device_;
+        int sms_ = 148;
         CheckerDesc desc_;
         cudaStream_t stream_ = nullptr;
         std::mutex mu_;
         DevBuf<double> params_;
+        DevBuf<float4> filt_;
+        DevBuf<unsigned long long> ctr_;
         size_t smem_bytes_ = 0;
         // scratch
         DevBuf<uint32_t> nd_;
@@ -68,6 +75,8 @@ namespace omplcu
         DevBuf<uint8_t> st_v_;
         long launches_ = 0;
         long last_states_ = 0;
+        long last_evaluated_ = 0;
+        long last_group_ = 0;
     };
 
     // batched space math (host buffers) used by the parity tests and adapters
