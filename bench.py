@@ -37,6 +37,8 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
+N_SEGMENTS = 1_000_000
+MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
 UNIT = "queries/s"
 
@@ -126,6 +128,20 @@ def cpu_sample_size(kind, cores):
     return per * cores
 
 
+def cpu_motion_baseline(a, b, robot, sph, box, cores, m):
+    """DiscreteMotionValidator::checkMotion(s1, s2, lastValid) on the host cores (oracle port, pthreads)."""
+    from oracle import oracle_py as orc
+
+    osp, ochk = orc.space_se3(-1.0, 1.0), orc.checker_se3(robot, sph, box)
+    t0 = time.perf_counter()
+    ov, ot = orc.check_motions(osp, ochk, a[:m], b[:m], last_valid=True, nthreads=cores)
+    return time.perf_counter() - t0, ov, ot
+
+
+MOTION_CPU_WHAT = ("oracle restatement of DiscreteMotionValidator::checkMotion(s1,s2,lastValid) + SE3 obstacle "
+                   "predicate (bisection order, early exit)")
+
+
 def run_reference_arm(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -133,26 +149,46 @@ def run_reference_arm(args):
     pts, qs_all = make_inputs()
     cores = host_threads()
     kind, what, build_s, run = build_cpu_reference(pts)
-    per_step = max(cores * (256 if kind == "reference" else 32), 64)
-    qs = np.random.default_rng(7).random((per_step * (args.steps + args.warmup), DIM))
+    # a bounded sample of the SAME 64K queries per step (about 2 s of GNAT on 16 cores)
+    per_step = min(max(cores * (2048 if kind == "reference" else 128), 64), N_QUERIES)
+    nblocks = N_QUERIES // per_step
+
+    def block(i):
+        j = i % nblocks
+        return qs_all[j * per_step:(j + 1) * per_step]
+
     for w in range(args.warmup):
-        run(qs[w * per_step:(w + 1) * per_step], cores)
+        run(block(w), cores)
     t = 0.0
     for s in range(args.warmup, args.warmup + args.steps):
-        t += run(qs[s * per_step:(s + 1) * per_step], cores)
+        t += run(block(s), cores)
     value = per_step * args.steps / t
-    sample = f"{per_step} queries/step x {args.steps} steps vs 1M states, {cores} threads, {what}"
-    print(json.dumps({
+    sample = (f"{per_step} of the 65536 queries per step x {args.steps} steps vs the same 1M states, {cores} threads, "
+              f"{what}")
+    out = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "RealVectorStateSpace(7), 1M states, k=10 (bounded query sample per step)",
-                   "n_states": N_STATES, "k": K, "queries_per_step": per_step},
+        "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
+                   "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
+                   "queries_per_step": per_step},
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
                          "build_s": build_s},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-    }))
+    }
+    if not args.no_motion:
+        from ompl_b200 import workloads
+
+        m = min(N_SEGMENTS, 12000 * cores)
+        s1, s2 = workloads.m3_segments(N_SEGMENTS)
+        sph, box = workloads.se3_obstacles()
+        secs, _, _ = cpu_motion_baseline(s1, s2, workloads.se3_robot(), sph, box, cores, m)
+        out["motion"] = {"metric": MOTION_METRIC, "value": m / secs, "unit": "segments/s",
+                         "cpu_baseline": {"value": m / secs, "unit": "segments/s", "cores": cores, "kind": "port",
+                                          "sample": f"first {m} of the 1M segments, {cores} threads, "
+                                                    + MOTION_CPU_WHAT}}
+    print(json.dumps(out))
 
 
 # ---------------------------------------------------------------------------
@@ -276,6 +312,8 @@ def run_gpu_arm(args):
     res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
     assert (res_ids == h_ids).all(), "device and host entry points disagree"
 
+    motion = None if args.no_motion else motion_block(args, torch, dist, dev, local, rank, world, timed)
+
     if rank == 0:
         t_step = dev_ms / args.steps
         value = N_QUERIES / (t_step * 1e-3)
@@ -322,6 +360,8 @@ def run_gpu_arm(args):
             "roofline": roofline,
             "exact_fallback_queries": int(fallbacks),
         }
+        if motion is not None:
+            out["motion"] = motion
         if world == 1 and not args.no_cpu:
             cores = host_threads()
             kind, what, build_s, run = build_cpu_reference(pts)
@@ -335,6 +375,96 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+# ---------------------------------------------------------------------------
+# second half of BASELINE.json's metric: motion checks/sec (workload M3)
+# ---------------------------------------------------------------------------
+def motion_block(args, torch, dist, dev, local, rank, world, timed):
+    """1M SE3 segments against 500 spheres + 500 boxes at resolution 0.01, split by
+    segment over the ranks (no collective on the data path).  Returns the "motion"
+    object of the JSON line (rank 0) or None."""
+    import ompl_b200 as ob
+    from ompl_b200 import workloads
+    from ompl_b200._lib import check, lib
+
+    L = lib()
+    s1, s2 = workloads.m3_segments(N_SEGMENTS)
+    sph, box = workloads.se3_obstacles()
+    robot = workloads.se3_robot()
+    lo, hi = N_SEGMENTS * rank // world, N_SEGMENTS * (rank + 1) // world
+    n = hi - lo
+    a, b = np.ascontiguousarray(s1[lo:hi]), np.ascontiguousarray(s2[lo:hi])
+    sp = ob.SE3StateSpace(-1.0, 1.0, device=local)
+    chk = ob.SE3ObstacleValidityChecker(robot, sph, box, device=local)
+    da, db = torch.from_numpy(a).to(dev), torch.from_numpy(b).to(dev)
+    dv = torch.empty(n, dtype=torch.uint8, device=dev)
+    dt = torch.empty(n, dtype=torch.float64, device=dev)
+    sptr = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    hv = np.empty(n, dtype=np.uint8)
+    ht = np.empty(n, dtype=np.float64)
+    for arr in (a, b, hv, ht):
+        torch.cuda.cudart().cudaHostRegister(arr.ctypes.data, arr.nbytes, 0)
+
+    def step_device():
+        check(L.omplcu_check_motions_device(chk.handle, sp.handle, da.data_ptr(), db.data_ptr(), n, dv.data_ptr(),
+                                            dt.data_ptr(), None, sptr))
+
+    def step_e2e():
+        check(L.omplcu_check_motions(chk.handle, sp.handle, a.ctypes.data, b.ctypes.data, n, hv.ctypes.data,
+                                     ht.ctypes.data, None))
+
+    l0 = chk.stat("launches")
+    dev_ms, _, _ = timed(step_device, args.steps, args.warmup)
+    launches = (chk.stat("launches") - l0) * args.steps // (args.steps + args.warmup)
+    _, e2e_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
+    assert (dv.cpu().numpy() == hv).all() and (dt.cpu().numpy() == ht).all(), "device and host entry points disagree"
+    tot = torch.tensor([chk.stat("last_states"), chk.stat("last_states_evaluated"), int(hv.sum())],
+                       dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot)
+    if rank != 0:
+        return None
+    states, evaluated, nvalid = (int(x) for x in tot.tolist())
+    t_step = dev_ms / args.steps
+    nobs = len(sph) + len(box)
+    ffma, ffma2 = C.c_double(), C.c_double()
+    check(L.omplcu_measure_fp32_peak(local, C.byref(ffma), C.byref(ffma2)))
+    # SURVEY.md 8(d): 8 flops per (robot sphere, obstacle sphere) test, 14 per box test, every state of every segment
+    alg = float(states) * len(robot) * (8.0 * len(sph) + 14.0 * len(box))
+    # what the kernel issues: 3 FP32 FMAs per (evaluated state, obstacle bounding sphere)
+    exe = float(evaluated) * nobs * 6.0
+    out = {
+        "metric": MOTION_METRIC,
+        "value": N_SEGMENTS / (t_step * 1e-3), "unit": "segments/s", "ms_per_step": t_step, "scaling": "strong",
+        "dtype": "f32 bounding-sphere filter + f64 exact predicate",
+        "config": {"workload": "M3: SE3 [-1,1]^3, uniform endpoints, 500 spheres + 500 boxes, 4-sphere robot",
+                   "n_segments": N_SEGMENTS, "states_in_segments": states, "states_evaluated": evaluated,
+                   "valid_segments": nvalid, "lanes_per_segment": chk.stat("last_group"),
+                   "sharding": f"segments split over {world} rank(s), no collective" if world > 1 else "single GPU"},
+        "e2e": {"value": N_SEGMENTS / (e2e_ms / args.steps * 1e-3), "unit": "segments/s",
+                "h2d_bytes_per_step": int(a.nbytes + b.nbytes), "d2h_bytes_per_step": int(hv.nbytes + ht.nbytes)},
+        "gpu_launches": int(launches),
+        "roofline": {
+            "bound": "fp32", "kernel": "motion_group_kernel<SE3,8,32>", "peak": max(ffma.value, ffma2.value),
+            "unit": "TFLOP/s",
+            "achieved": exe / (t_step * 1e-3) / 1e12,
+            "frac": exe / (t_step * 1e-3) / 1e12 / max(ffma.value, ffma2.value),
+            "achieved_algorithmic": alg / (t_step * 1e-3) / 1e12,
+            "note": "achieved = issued filter flops (evaluated states x obstacles x 3 FMA) over the whole step; "
+                    "achieved_algorithmic = SURVEY 8(d) brute-force count (all states x all robot/obstacle pairs), "
+                    "which the bounding-sphere filter and the early exit avoid, so it can exceed the pipe peak",
+        },
+    }
+    if world == 1 and not args.no_cpu:
+        cores = host_threads()
+        m = min(N_SEGMENTS, 12000 * cores)
+        secs, ov, ot = cpu_motion_baseline(a, b, robot, sph, box, cores, m)
+        ok = bool((ov == hv[:m].astype(bool)).all() and (ot[~ov] == ht[:m][~ov]).all())
+        out["cpu_baseline"] = {"value": m / secs, "unit": "segments/s", "cores": cores, "kind": "port",
+                               "sample": f"first {m} of the 1M segments, {cores} threads, " + MOTION_CPU_WHAT,
+                               "matches_gpu": ok}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -342,7 +472,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scan-ctas", type=int, default=0, help="tuning: cap resident scan CTAs per SM")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg (profiling runs)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
+    ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference_arm(args)

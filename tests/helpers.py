@@ -8,8 +8,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 GOLDEN = os.path.join(HERE, "golden")
 
 
-def rng(seed):
-    return np.random.default_rng(seed)
+from ompl_b200.workloads import (m3_segments, random_quaternions, rng, se3_obstacles,  # noqa: E402,F401
+                                 se3_robot, se3_states)
 
 
 def uniform_points(seed, n, d, low=0.0, high=1.0):
@@ -27,45 +27,9 @@ def with_duplicates(pts, seed, frac=0.01):
     return pts
 
 
-def random_quaternions(seed, n):
-    """Uniform unit quaternions (Shoemake), stored x,y,z,w like SO3StateSpace."""
-    r = rng(seed)
-    u1, u2, u3 = r.random(n), r.random(n), r.random(n)
-    q = np.stack(
-        [
-            np.sqrt(1 - u1) * np.sin(2 * np.pi * u2),
-            np.sqrt(1 - u1) * np.cos(2 * np.pi * u2),
-            np.sqrt(u1) * np.sin(2 * np.pi * u3),
-            np.sqrt(u1) * np.cos(2 * np.pi * u3),
-        ],
-        axis=1,
-    )
-    return q / np.linalg.norm(q, axis=1, keepdims=True)
-
-
-def se3_states(seed, n, low=-1.0, high=1.0):
-    pos = rng(seed).uniform(low, high, size=(n, 3))
-    return np.hstack([pos, random_quaternions(seed + 17, n)])
-
-
 def se2_states(seed, n, low=0.0, high=1.0):
     r = rng(seed)
     return np.hstack([r.uniform(low, high, size=(n, 2)), r.uniform(-np.pi, np.pi, size=(n, 1))])
-
-
-def se3_obstacles(seed=7, nsph=500, nbox=500, low=-1.0, high=1.0, rmin=0.02, rmax=0.08):
-    """BASELINE config 4 / SURVEY 8d M3: spheres + axis-aligned boxes."""
-    r = rng(seed)
-    sph = np.hstack([r.uniform(low, high, size=(nsph, 3)), r.uniform(rmin, rmax, size=(nsph, 1))])
-    box = np.hstack([r.uniform(low, high, size=(nbox, 3)), r.uniform(rmin, rmax, size=(nbox, 3))])
-    return sph, box
-
-
-def se3_robot():
-    """4 body-fixed spheres (ox, oy, oz, r)."""
-    return np.array(
-        [[0.0, 0.0, 0.0, 0.03], [0.05, 0.0, 0.0, 0.02], [-0.05, 0.0, 0.0, 0.02], [0.0, 0.04, 0.02, 0.015]]
-    )
 
 
 def hypercube_valid_states(seed, n, d, edge=0.1):
