@@ -208,63 +208,79 @@ namespace omplcu
         // world) go through the exact FP64 expressions of se3_valid for that obstacle.
         // The body rotation maps offset o to (1-s) o + s R o with s = |q|^2, so
         // |c_i - p| <= (|1-s| + s)|o_i|; states with |s - 1| > 2e-4 skip the filter.
+        // robot sphere i in the world frame (the expressions of se3_valid, same order)
         template <typename PS>
-        __device__ __forceinline__ bool se3_pair_hits(const CheckerDesc &c, int j, PS st)
+        __device__ __forceinline__ void se3_robot_centre(const CheckerDesc &c, int i, PS st, double &cx, double &cy,
+                                                         double &cz, double &rr)
         {
             const double px = st[0], py = st[1], pz = st[2];
             const double qx = st[3], qy = st[4], qz = st[5], qw = st[6];
-            for (int i = 0; i < c.nrobot; ++i)
-            {
-                const double ox = c.robot[4 * i + 0], oy = c.robot[4 * i + 1], oz = c.robot[4 * i + 2];
-                const double rr = c.robot[4 * i + 3];
-                const double tx = dmul(2.0, dsub(dmul(qy, oz), dmul(qz, oy)));
-                const double ty = dmul(2.0, dsub(dmul(qz, ox), dmul(qx, oz)));
-                const double tz = dmul(2.0, dsub(dmul(qx, oy), dmul(qy, ox)));
-                const double cx = dadd(px, dadd(dadd(ox, dmul(qw, tx)), dsub(dmul(qy, tz), dmul(qz, ty))));
-                const double cy = dadd(py, dadd(dadd(oy, dmul(qw, ty)), dsub(dmul(qz, tx), dmul(qx, tz))));
-                const double cz = dadd(pz, dadd(dadd(oz, dmul(qw, tz)), dsub(dmul(qx, ty), dmul(qy, tx))));
-                if (j < c.nsph)
-                {
-                    const double *sp = c.sph + 4 * j;
-                    const double dx = dsub(sp[0], cx);
-                    const double dy = dsub(sp[1], cy);
-                    const double dz = dsub(sp[2], cz);
-                    const double R = dadd(sp[3], rr);
-                    if (dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz)) < dmul(R, R))
-                        return true;
-                }
-                else
-                {
-                    const double *bx = c.box + 6 * (j - c.nsph);
-                    double ex = dsub(fabs(dsub(cx, bx[0])), bx[3]);
-                    double ey = dsub(fabs(dsub(cy, bx[1])), bx[4]);
-                    double ez = dsub(fabs(dsub(cz, bx[2])), bx[5]);
-                    if (ex < 0.0)
-                        ex = 0.0;
-                    if (ey < 0.0)
-                        ey = 0.0;
-                    if (ez < 0.0)
-                        ez = 0.0;
-                    if (dadd(dadd(dmul(ex, ex), dmul(ey, ey)), dmul(ez, ez)) < dmul(rr, rr))
-                        return true;
-                }
-            }
-            return false;
+            const double ox = c.robot[4 * i + 0], oy = c.robot[4 * i + 1], oz = c.robot[4 * i + 2];
+            rr = c.robot[4 * i + 3];
+            const double tx = dmul(2.0, dsub(dmul(qy, oz), dmul(qz, oy)));
+            const double ty = dmul(2.0, dsub(dmul(qz, ox), dmul(qx, oz)));
+            const double tz = dmul(2.0, dsub(dmul(qx, oy), dmul(qy, ox)));
+            cx = dadd(px, dadd(dadd(ox, dmul(qw, tx)), dsub(dmul(qy, tz), dmul(qz, ty))));
+            cy = dadd(py, dadd(dadd(oy, dmul(qw, ty)), dsub(dmul(qz, tx), dmul(qx, tz))));
+            cz = dadd(pz, dadd(dadd(oz, dmul(qw, tz)), dsub(dmul(qx, ty), dmul(qy, tx))));
         }
 
-        template <typename PS>
-        __device__ __forceinline__ bool se3_valid_fast(const CheckerDesc &c, const float4 *F, PS st)
+        // exact test of one robot sphere against obstacle j (spheres first, then boxes)
+        __device__ __forceinline__ bool se3_obstacle_hits(const CheckerDesc &c, int j, double cx, double cy, double cz,
+                                                          double rr)
         {
-            const float px = (float)st[0], py = (float)st[1], pz = (float)st[2];
+            if (j < c.nsph)
+            {
+                const double *sp = c.sph + 4 * j;
+                const double dx = dsub(sp[0], cx);
+                const double dy = dsub(sp[1], cy);
+                const double dz = dsub(sp[2], cz);
+                const double R = dadd(sp[3], rr);
+                return dadd(dadd(dmul(dx, dx), dmul(dy, dy)), dmul(dz, dz)) < dmul(R, R);
+            }
+            const double *bx = c.box + 6 * (j - c.nsph);
+            double ex = dsub(fabs(dsub(cx, bx[0])), bx[3]);
+            double ey = dsub(fabs(dsub(cy, bx[1])), bx[4]);
+            double ez = dsub(fabs(dsub(cz, bx[2])), bx[5]);
+            if (ex < 0.0)
+                ex = 0.0;
+            if (ey < 0.0)
+                ey = 0.0;
+            if (ez < 0.0)
+                ez = 0.0;
+            return dadd(dadd(dmul(ex, ex), dmul(ey, ey)), dmul(ez, ez)) < dmul(rr, rr);
+        }
+
+        constexpr int SURV_CAP = 12;  // survivors kept per lane before the exact pass
+
+        // F: filter rows in shared memory; surv_base: a [SURV_CAP][blockDim.x] u16 array in shared
+        // memory (one column per thread) followed by one float4 of scratch per thread.  Survivors are only recorded while the rows stream by and
+        // are examined afterwards, all lanes of the warp together: the FP64 work of one lane
+        // does not stall the other 31 in the middle of the filter loop.
+        template <typename PS>
+        __device__ __forceinline__ bool se3_valid_fast(const CheckerDesc &c, const float4 *F,
+                                                       unsigned short *surv_base, PS st)
+        {
+            float px = (float)st[0], py = (float)st[1], pz = (float)st[2];
             const float qx = (float)st[3], qy = (float)st[4], qz = (float)st[5], qw = (float)st[6];
             const float s = qx * qx + qy * qy + qz * qz + qw * qw;
             if (!(fabsf(s - 1.0f) <= 2e-4f))
                 return se3_valid(c, c.robot, c.sph, c.box, st);
             const float A = fmaxf(c.filt_amax, fmaxf(fabsf(px), fmaxf(fabsf(py), fabsf(pz)))) * 1.0001f;
             const float pn = px * px + py * py + pz * pz;
-            const float tau = A * A * 1.52587890625e-05f - pn;
-            const float mx = -2.0f * px, my = -2.0f * py, mz = -2.0f * pz;
+            // The four loop constants take a round trip through shared memory: ptxas otherwise
+            // re-derives them from the FP64 state in every iteration of the filter loop.
+            volatile float4 *scr = reinterpret_cast<volatile float4 *>(surv_base + SURV_CAP * blockDim.x) + threadIdx.x;
+            scr->x = -2.0f * px;
+            scr->y = -2.0f * py;
+            scr->z = -2.0f * pz;
+            scr->w = A * A * 1.52587890625e-05f - pn;
+            const float mx = scr->x, my = scr->y, mz = scr->z, tau = scr->w;
+            unsigned short *surv = surv_base + threadIdx.x;
             const int nf = c.nfilt_pad;
+            const int stride = blockDim.x;
+            int ns = 0;
+            bool hit = false;
 #pragma unroll 2
             for (int j = 0; j < nf; j += 4)
             {
@@ -275,37 +291,74 @@ namespace omplcu
                 const float s3 = fmaf(mz, o3.z, fmaf(my, o3.y, fmaf(mx, o3.x, o3.w)));
                 if ((s0 <= tau) | (s1 <= tau) | (s2 <= tau) | (s3 <= tau))
                 {
-                    if (s0 <= tau && se3_pair_hits(c, j, st))
-                        return false;
-                    if (s1 <= tau && se3_pair_hits(c, j + 1, st))
-                        return false;
-                    if (s2 <= tau && se3_pair_hits(c, j + 2, st))
-                        return false;
-                    if (s3 <= tau && se3_pair_hits(c, j + 3, st))
-                        return false;
+                    unsigned m = (s0 <= tau ? 1u : 0u) | (s1 <= tau ? 2u : 0u) | (s2 <= tau ? 4u : 0u) |
+                                 (s3 <= tau ? 8u : 0u);
+                    while (m)
+                    {
+                        const int jj = j + __ffs(m) - 1;
+                        m &= m - 1;
+                        if (ns < SURV_CAP)
+                            surv[(ns++) * stride] = (unsigned short)jj;
+                        else if (!hit)
+                        {
+                            // list full (dense clutter): examine this one right away
+                            for (int i = 0; i < c.nrobot && !hit; ++i)
+                            {
+                                double cx, cy, cz, rr;
+                                se3_robot_centre(c, i, st, cx, cy, cz, rr);
+                                hit = se3_obstacle_hits(c, jj, cx, cy, cz, rr);
+                            }
+                        }
+                    }
                 }
+            }
+            if (hit)
+                return false;
+            if (ns == 0)
+                return true;
+            for (int i = 0; i < c.nrobot; ++i)
+            {
+                double cx, cy, cz, rr;
+                se3_robot_centre(c, i, st, cx, cy, cz, rr);
+                for (int k = 0; k < ns; ++k)
+                    if (se3_obstacle_hits(c, (int)surv[k * stride], cx, cy, cz, rr))
+                        return false;
             }
             return true;
         }
 
-        template <int KIND, typename PS>
-        __device__ __forceinline__ bool state_valid_f(const CheckerDesc &c, const float4 *F, PS s)
-        {
-            if (KIND == OMPLCU_CHK_SE3)
-                return se3_valid_fast(c, F, s);
-            return state_valid<KIND>(c, c.robot, c.sph, c.box, s);
-        }
-
-        // copy the SE3 filter rows into shared memory (all threads participate)
+        // Shared-memory layout of the SE3 kernels: filter rows, then the survivor lists.
         template <int KIND>
-        __device__ __forceinline__ const float4 *stage_filter(const CheckerDesc &c, float4 *smem)
+        struct Staged
         {
+            const float4 *F;
+            unsigned short *surv;
+        };
+
+        template <int KIND>
+        __device__ __forceinline__ Staged<KIND> stage_filter(const CheckerDesc &c, float4 *smem)
+        {
+            Staged<KIND> r{nullptr, nullptr};
             if (KIND != OMPLCU_CHK_SE3 || !c.stage_smem)
-                return c.filt;
+                return r;
             for (int i = threadIdx.x; i < c.nfilt_pad; i += blockDim.x)
                 smem[i] = c.filt[i];
             __syncthreads();
-            return smem;
+            r.F = smem;
+            r.surv = reinterpret_cast<unsigned short *>(smem + c.nfilt_pad);
+            return r;
+        }
+
+        template <int KIND, typename PS>
+        __device__ __forceinline__ bool state_valid_f(const CheckerDesc &c, const Staged<KIND> &sm, PS s)
+        {
+            if (KIND == OMPLCU_CHK_SE3)
+            {
+                if (c.stage_smem)
+                    return se3_valid_fast(c, sm.F, sm.surv, s);
+                return se3_valid(c, c.robot, c.sph, c.box, s);  // world too large for shared memory
+            }
+            return state_valid<KIND>(c, c.robot, c.sph, c.box, s);
         }
 
         template <int KIND, int MAXS>
@@ -313,13 +366,13 @@ namespace omplcu
                                                                    size_t n, uint8_t *valid)
         {
             extern __shared__ float4 smem_filt[];
-            const float4 *F = stage_filter<KIND>(c, smem_filt);
+            const Staged<KIND> sm = stage_filter<KIND>(c, smem_filt);
             for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += gridDim.x * (size_t)blockDim.x)
             {
                 double st[MAXS];
                 for (int d = 0; d < stride && d < MAXS; ++d)
                     st[d] = states[i * stride + d];
-                valid[i] = state_valid_f<KIND>(c, F, st) ? 1 : 0;
+                valid[i] = state_valid_f<KIND>(c, sm, st) ? 1 : 0;
             }
         }
 
@@ -343,7 +396,7 @@ namespace omplcu
                                                                    unsigned *code, unsigned long long *ctr)
         {
             extern __shared__ float4 smem_filt[];
-            const float4 *F = stage_filter<KIND>(c, smem_filt);
+            const Staged<KIND> sm = stage_filter<KIND>(c, smem_filt);
             constexpr unsigned FULL = 0xffffffffu;
             const unsigned lane = threadIdx.x & 31u, gl = lane % G, gbase = lane - gl;
             const unsigned gmask = (G == 32) ? FULL : (((1u << G) - 1u) << gbase);
@@ -391,7 +444,7 @@ namespace omplcu
                         const double t = ddiv((double)(m + 1), (double)ndv);
                         space_interpolate(sp, a, b, t, st);
                     }
-                    bad = !state_valid_f<KIND>(c, F, st);
+                    bad = !state_valid_f<KIND>(c, sm, st);
                     evaluated++;
                 }
                 const unsigned hit = __ballot_sync(FULL, bad) & gmask;
@@ -553,9 +606,11 @@ namespace omplcu
         desc_.filt = filt_.p;
         desc_.nfilt_pad = pad;
         desc_.filt_amax = (float)(amax * (1.0 + 1e-6));
-        if ((size_t)pad * sizeof(float4) <= 64 * 1024)
+        // filter rows + [SURV_CAP][128] u16 survivor lists + one float4 of scratch per thread
+        const size_t need = (size_t)pad * sizeof(float4) + SURV_CAP * 128 * sizeof(unsigned short) + 128 * sizeof(float4);
+        if (need <= 200 * 1024)
         {
-            smem_bytes_ = (size_t)pad * sizeof(float4);
+            smem_bytes_ = need;
             desc_.stage_smem = 1;
         }
     }
