@@ -126,6 +126,100 @@ def test_se3_states(gpu):
         assert (c2.isValidBatch(s[:5000]) == orc.check_states(o2, s[:5000], nthreads=8)).all()
 
 
+def _grazing_states(robot, sph, box, seed, n):
+    """States whose robot spheres sit within a few ulps .. 1e-6 of an obstacle surface:
+    the FP32 filter must hand every one of them to the exact test."""
+    r = helpers.rng(seed)
+    q = helpers.random_quaternions(seed + 1, n)
+    x, y, z, w = q.T
+    out = np.empty((n, 7))
+    for i in range(n):
+        k = r.integers(0, len(robot))
+        o, rr = robot[k, :3], robot[k, 3]
+        qv = np.array([x[i], y[i], z[i]])
+        t = 2.0 * np.cross(qv, o)
+        rot = o + w[i] * t + np.cross(qv, t)
+        d = r.normal(size=3)
+        d /= np.linalg.norm(d)
+        eps = r.choice([0.0, 1e-15, -1e-15, 1e-12, -1e-12, 1e-9, -1e-9, 1e-6, -1e-6])
+        if r.random() < 0.5 and len(sph):
+            j = r.integers(0, len(sph))
+            c = sph[j, :3] + d * (sph[j, 3] + rr + eps)
+        else:
+            j = r.integers(0, len(box))
+            face = r.integers(0, 3)
+            c = box[j, :3] + r.uniform(-1, 1, 3) * box[j, 3:]
+            c[face] = box[j, face] + r.choice([-1, 1]) * (box[j, 3 + face] + rr + eps)
+        out[i, :3] = c - rot
+        out[i, 3:] = q[i]
+    return out
+
+
+def test_se3_filter_grazing_contacts(gpu):
+    sph, box = helpers.se3_obstacles()
+    robot = helpers.se3_robot()
+    chk, ochk = ob.SE3ObstacleValidityChecker(robot, sph, box), orc.checker_se3(robot, sph, box)
+    s = _grazing_states(robot, sph, box, 11, 20000)
+    v = chk.isValidBatch(s)
+    assert (v == orc.check_states(ochk, s, nthreads=8)).all()
+    assert 0.1 < v.mean() < 0.9  # the sample really straddles the surfaces
+
+
+@pytest.mark.parametrize("offset,scale", [(1000.0, 1.0), (0.0, 1e-3), (0.0, 250.0), (-3e4, 10.0)])
+def test_se3_filter_far_from_origin_and_scaled(gpu, offset, scale):
+    """FP32 resolution shrinks with |coordinate|: the margin must follow (more survivors, same booleans)."""
+    sph, box = helpers.se3_obstacles(nsph=200, nbox=200)
+    robot = helpers.se3_robot()
+    sph, box, robot = sph * scale, box * scale, robot * scale
+    sph[:, :3] += offset
+    box[:, :3] += offset
+    chk, ochk = ob.SE3ObstacleValidityChecker(robot, sph, box), orc.checker_se3(robot, sph, box)
+    s = helpers.se3_states(5, 20000)
+    s[:, :3] = s[:, :3] * scale + offset
+    g = _grazing_states(robot, sph, box, 12, 5000)
+    s = np.vstack([s, g])
+    v = chk.isValidBatch(s)
+    assert (v == orc.check_states(ochk, s, nthreads=8)).all() and 0 < v.sum() < len(v)
+
+
+def test_se3_filter_non_unit_quaternions_and_clutter(gpu):
+    robot = helpers.se3_robot()
+    # 300 obstacles piled on one spot: the per-lane survivor list (12 entries) overflows
+    r = helpers.rng(21)
+    sph = np.hstack([r.normal(0, 0.01, (150, 3)) + 0.3, r.uniform(0.02, 0.05, (150, 1))])
+    box = np.hstack([r.normal(0, 0.01, (150, 3)) + 0.3, r.uniform(0.02, 0.05, (150, 3))])
+    chk, ochk = ob.SE3ObstacleValidityChecker(robot, sph, box), orc.checker_se3(robot, sph, box)
+    s = helpers.se3_states(6, 20000)
+    s[:, :3] = 0.3 + helpers.rng(22).normal(0, 0.08, (20000, 3))  # around the pile, in and out
+    s[::3, 3:] *= helpers.rng(23).uniform(0.2, 3.0, (len(s[::3]), 1))  # |q| != 1: the filter steps aside
+    s[5, 3:] = 0.0
+    v = chk.isValidBatch(s)
+    assert (v == orc.check_states(ochk, s, nthreads=8)).all() and 0 < v.sum() < len(v)
+    # the same world through the motion validator (short segments around the pile)
+    sp, osp = _spaces("se3")
+    a = s[1::3][:3000].copy()
+    b = a.copy()
+    b[:, :3] += helpers.rng(24).normal(0, 0.05, (len(a), 3))
+    mv = ob.BatchedDiscreteMotionValidator(sp, chk)
+    gv, gt = mv.checkMotionBatch(a, b, last_valid=True)[:2]
+    ov, ot = orc.check_motions(osp, ochk, a, b, last_valid=True, nthreads=8)
+    assert (gv == ov).all() and (gt[~ov] == ot[~ov]).all() and 0 < ov.sum() < len(ov)
+
+
+@pytest.mark.parametrize("step", [0.0005, 0.003, 0.01, 0.05])
+def test_motion_lane_group_sizes(gpu, step):
+    """Mean states per segment ~1.5 .. 130: every lane-group width (4, 8, 16, 32) gives the same answers."""
+    sp, osp = ob.RealVectorStateSpace(2), orc.space_rv(2)
+    circ = np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1], [0.8, 0.2, 0.15]])
+    chk, ochk = ob.Circles2DValidityChecker(circ), orc.checker_circles(circ)
+    r = helpers.rng(31)
+    a = r.uniform(0, 1, (6000, 2))
+    b = a + r.normal(0, step * 10, a.shape)
+    b[::7] = r.uniform(0, 1, (len(b[::7]), 2))  # a few long ones in every batch
+    _motion_parity(sp, osp, chk, ochk, a, b)
+    assert chk.stat("last_group") in (4, 8, 16, 32)
+
+
 def test_allvalid_and_single_state(gpu):
     chk = ob.AllValidStateValidityChecker()
     assert chk.isValidBatch(np.zeros((5, 3))).all()
