@@ -335,7 +335,10 @@ def run_gpu_arm(args):
         scan_bytes = 4.0 * 8 * (hi - lo) * (N_QUERIES / 512.0)  # every query tile streams the filter copy (L2-resident)
         roofline = {
             "bound": "fp32", "kernel": "knn_scan_kernel<7,4,12>", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-            "frac": ach / peak if peak else None, "traffic": None,
+            "frac": ach / peak if peak else None,
+            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+            # (profiles/r1_scan_v2_ncu_summary.csv); algorithmic: 32 MB filter copy + 1.8 MB queries + lists
+            "traffic": 34.5e6 if world == 1 else None, "traffic_unit": "bytes/launch",
             "peak_source": "FP32 FMA pipe measured live on this GPU (omplcu_measure_fp32_peak: FFMA "
                            f"{ffma.value:.1f}, FFMA2 {ffma2.value:.1f} TFLOP/s); MEASURED_PEAKS.json has no FP32 figure",
             "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * DIM,
