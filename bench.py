@@ -214,8 +214,10 @@ def run_gpu_arm(args):
     dev = torch.device("cuda", local)
     L = lib()
 
+    from ompl_b200 import sharding
+
     pts, qs = make_inputs()
-    lo, hi = N_STATES * rank // world, N_STATES * (rank + 1) // world
+    lo, hi = sharding.shard_range(N_STATES, rank, world)
     sp = ob.RealVectorStateSpace(DIM, device=local)
     nn = ob.NearestNeighborsCUDA(sp)
     nn.set_id_base(lo)
@@ -228,8 +230,7 @@ def run_gpu_arm(args):
     d_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
     d_d = torch.empty((N_QUERIES, K), dtype=torch.float64, device=dev)
     if world > 1:
-        g_ids = torch.empty((world, N_QUERIES, K), dtype=torch.int64, device=dev)
-        g_d = torch.empty((world, N_QUERIES, K), dtype=torch.float64, device=dev)
+        g_ids, g_d = sharding.alloc_gather_buffers(world, N_QUERIES, K, dev)
         m_ids, m_d = torch.empty_like(d_ids), torch.empty_like(d_d)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream()
@@ -238,8 +239,7 @@ def run_gpu_arm(args):
     def step_device():
         check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), N_QUERIES, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
         if world > 1:
-            dist.all_gather_into_tensor(g_ids, d_ids)
-            dist.all_gather_into_tensor(g_d, d_d)
+            sharding.all_gather_lists(d_ids, d_d, g_ids, g_d)
             check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
                                              m_d.data_ptr(), m_ids.data_ptr(), sptr))
 
@@ -258,8 +258,7 @@ def run_gpu_arm(args):
             # sharded roadmap: merge needs the other shards' lists; exchange on the device
             d_ids.copy_(torch.from_numpy(h_ids.view(np.int64)), non_blocking=True)
             d_d.copy_(torch.from_numpy(h_d), non_blocking=True)
-            dist.all_gather_into_tensor(g_ids, d_ids)
-            dist.all_gather_into_tensor(g_d, d_d)
+            sharding.all_gather_lists(d_ids, d_d, g_ids, g_d)
             check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
                                              m_d.data_ptr(), m_ids.data_ptr(), sptr))
             h_ids.view(np.int64)[:] = m_ids.cpu().numpy()
@@ -393,7 +392,9 @@ def motion_block(args, torch, dist, dev, local, rank, world, timed):
     s1, s2 = workloads.m3_segments(N_SEGMENTS)
     sph, box = workloads.se3_obstacles()
     robot = workloads.se3_robot()
-    lo, hi = N_SEGMENTS * rank // world, N_SEGMENTS * (rank + 1) // world
+    from ompl_b200 import sharding
+
+    lo, hi = sharding.shard_range(N_SEGMENTS, rank, world)
     n = hi - lo
     a, b = np.ascontiguousarray(s1[lo:hi]), np.ascontiguousarray(s2[lo:hi])
     sp = ob.SE3StateSpace(-1.0, 1.0, device=local)

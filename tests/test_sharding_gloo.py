@@ -1,0 +1,108 @@
+"""world_size-2 gloo test of the sharded-roadmap plumbing (ompl_b200/sharding.py).
+
+No GPU here, so each rank's local top-k comes from the oracle (tests may use it); what is
+under test is the product's host-side logic: shard ranges, global id bases, the all-gather
+layout handed to the merge, and that merging per-shard lists by (distance, id) reproduces
+the single-index answer bit for bit -- including ties that straddle shards."""
+import os
+import socket
+import subprocess
+import sys
+import textwrap
+
+import numpy as np
+import pytest
+
+from ompl_b200 import sharding
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shard_ranges_tile_the_index_space():
+    for n in (0, 1, 7, 1000, 1_000_003):
+        for world in (1, 2, 3, 8):
+            r = [sharding.shard_range(n, k, world) for k in range(world)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+            assert max(hi - lo for lo, hi in r) - min(hi - lo for lo, hi in r) <= 1
+    with pytest.raises(ValueError):
+        sharding.shard_range(10, 2, 2)
+
+
+WORKER = textwrap.dedent("""
+    import os, sys
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "tests"))
+    import helpers
+    from ompl_b200 import sharding
+    from oracle import oracle_py as orc
+
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    n, nq, k, d = 5000, 64, 10, 7
+    pts = helpers.with_duplicates(helpers.uniform_points(1, n, d), 5, frac=0.05)   # ties across shards
+    qs = np.vstack([helpers.uniform_points(2, nq - 8, d), pts[:8]])                # and exact hits
+    lo, hi = sharding.shard_range(n, rank, world)
+    sp = orc.space_rv(d)
+    ids, dd = orc.knn(sp, pts[lo:hi], qs, k)
+    ids = ids.astype(np.int64) + lo                                                # set_id_base(lo)
+    g_ids, g_d = sharding.alloc_gather_buffers(world, nq, k, "cpu")
+    sharding.all_gather_lists(torch.from_numpy(ids), torch.from_numpy(dd), g_ids, g_d)
+    # merge by (distance, id): what merge_topk_kernel does on the device
+    cat_i = g_ids.numpy().transpose(1, 0, 2).reshape(nq, world * k)
+    cat_d = g_d.numpy().transpose(1, 0, 2).reshape(nq, world * k)
+    order = np.lexsort((cat_i, cat_d), axis=1)[:, :k]
+    m_i, m_d = np.take_along_axis(cat_i, order, 1), np.take_along_axis(cat_d, order, 1)
+    w_i, w_d = orc.knn(sp, pts, qs, k)
+    ok = bool((m_i == w_i.astype(np.int64)).all() and (m_d == w_d).all())
+    # every rank holds the same gathered buffers
+    chk = torch.tensor([float(g_d.sum()), float(g_ids.sum())], dtype=torch.float64)
+    all_chk = [torch.zeros_like(chk) for _ in range(world)]
+    dist.all_gather(all_chk, chk)
+    same = all(bool((c == all_chk[0]).all()) for c in all_chk)
+    # motion batches: split by segment, results concatenated in rank order equal the unsplit run
+    a, b = helpers.se2_states(3, 400), helpers.se2_states(4, 400)
+    circ = np.array([[0.5, 0.5, 0.2], [0.2, 0.8, 0.1]])
+    osp, ochk = orc.space_se2(), orc.checker_circles(circ)
+    slo, shi = sharding.shard_range(len(a), rank, world)
+    v, t = orc.check_motions(osp, ochk, a[slo:shi], b[slo:shi], last_valid=True)
+    parts = [None] * world
+    dist.all_gather_object(parts, (slo, v, t))
+    parts.sort(key=lambda p: p[0])
+    fv, ft = orc.check_motions(osp, ochk, a, b, last_valid=True)
+    mot = bool((np.concatenate([p[1] for p in parts]) == fv).all() and (np.concatenate([p[2] for p in parts]) == ft).all())
+    print(f"RANK{{rank}} merge_ok={{ok}} same={{same}} motion_ok={{mot}}", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if ok and same and mot else 1)
+""")
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def test_world_size_2_merge_equals_single_index(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER.format(root=ROOT))
+    port = _free_port()
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="2", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), OMP_NUM_THREADS="1")
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            p.kill()
+            out, _ = p.communicate()
+        outs.append(out)
+    for rank, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0, f"rank {rank} failed:\n{out[-2000:]}"
+        assert f"RANK{rank} merge_ok=True same=True motion_ok=True" in out
