@@ -225,6 +225,8 @@ def run_gpu_arm(args):
     nn.set_option("profile", 1)
     if args.scan_ctas:
         nn.set_option("scan_ctas_per_sm", args.scan_ctas)
+    if args.no_sample_thr:
+        nn.set_option("sample_thresholds", 0)
 
     d_q = torch.from_numpy(qs).to(dev)
     d_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
@@ -476,6 +478,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scan-ctas", type=int, default=0, help="tuning: cap resident scan CTAs per SM")
+    ap.add_argument("--no-sample-thr", action="store_true", help="tuning: disable the threshold pre-pass")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
     ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")
     args = ap.parse_args()

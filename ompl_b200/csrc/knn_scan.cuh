@@ -54,6 +54,7 @@ namespace omplcu
         unsigned long long total_units;  // qtiles * units
         uint32_t qpad;
         uint32_t smax;
+        const float *init_thr;  // [qpad] starting bound per query, or nullptr
     };
 
     // ---- PTX helpers: mbarrier + TMA bulk copy (cp.async.bulk) ----
@@ -167,7 +168,7 @@ namespace omplcu
     {
         static_assert(RQ % 2 == 0, "queries are processed as packed pairs");
         static_assert(L <= 64, "slot tags are 6 bits");
-        static_assert(SCAN_PT % SCAN_GP == 0, "tile must hold whole groups");
+        static_assert(SCAN_PT % (2 * SCAN_GP) == 0, "tile must hold whole pairs of groups");
         constexpr int ROWF = scan_rowf(D);
         constexpr int RW = ROWF / 4;           // float4 per filter row
         constexpr int LS = scan_ls(L);
@@ -224,6 +225,8 @@ namespace omplcu
             {
                 const size_t q = (size_t)t * QT + j * SCAN_THREADS + tid;
                 P.cand_thr[(size_t)seg * P.qpad + q] = thr[j];
+                if (P.cand_ids == nullptr)  // threshold pre-pass: only the bound is wanted
+                    continue;
                 const uint32_t *li = lids + list_of(j);
                 for (int i = 0; i < L; ++i)
                     P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = li[i];
@@ -271,14 +274,25 @@ namespace omplcu
                 {
                     float *lv = lvals + list_of(j);
                     uint32_t *li = lids + list_of(j);
+                    // Starting bound T of this query (threshold pre-pass over a sample of the
+                    // points, nn.cu): at least L points have a scan value below T, so values
+                    // >= T can never be among the L smallest.  The list starts full of
+                    // "virtual" entries worth T (id SLOT_NONE); real points displace them.
+                    const float T = P.init_thr ? P.init_thr[(size_t)t * QT + j * SCAN_THREADS + tid] : 3.0e38f;
+                    const bool bounded = T < 1.0e38f;
+                    float m = __int_as_float(0xff800000);
                     for (int i = 0; i < LS; ++i)
                     {
-                        // real slots: empty marker (filled from slot L-1 downwards);
+                        // real slots: empty marker (filled from slot L-1 downwards) or T;
                         // padding slots: never the maximum
-                        lv[i] = i < L ? __uint_as_float(EMPTY_BITS | (uint32_t)i) : __int_as_float(0xff800000);
+                        float v = __int_as_float(0xff800000);
+                        if (i < L)
+                            v = bounded ? tag_up(T, (uint32_t)i) : __uint_as_float(EMPTY_BITS | (uint32_t)i);
+                        lv[i] = v;
                         li[i] = SLOT_NONE;
+                        m = fmaxf(m, v);
                     }
-                    thr[j] = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
+                    thr[j] = m;
                 }
             }
 
@@ -294,48 +308,36 @@ namespace omplcu
             // this one is computed, and one predicate decides whether any
             // (point, query) of the group beats its query's threshold.  Only then
             // (rare after the first few tiles) the group is replayed in point order.
-            float4 nx[SCAN_GP][RW];
-#pragma unroll
-            for (int p = 0; p < SCAN_GP; ++p)
-#pragma unroll
-                for (int w = 0; w < RW; ++w)
-                    nx[p][w] = tp[p * RW + w];
-#pragma unroll 1
-            for (int i = 0; i < SCAN_PT; i += SCAN_GP)
-            {
-                float pv[SCAN_GP][ROWF];
+            // Two register buffers of SCAN_GP rows each, used in turn (no copies between them).
+            auto load_group = [&](float4 (&buf)[SCAN_GP][RW], int i) {
 #pragma unroll
                 for (int p = 0; p < SCAN_GP; ++p)
 #pragma unroll
                     for (int w = 0; w < RW; ++w)
-                    {
-                        pv[p][4 * w + 0] = nx[p][w].x;
-                        pv[p][4 * w + 1] = nx[p][w].y;
-                        pv[p][4 * w + 2] = nx[p][w].z;
-                        pv[p][4 * w + 3] = nx[p][w].w;
-                    }
-                {
-                    // wraps to the first group on the last iteration (harmless re-read)
-                    const int in = (i + SCAN_GP) & (SCAN_PT - 1);
-#pragma unroll
-                    for (int p = 0; p < SCAN_GP; ++p)
-#pragma unroll
-                        for (int w = 0; w < RW; ++w)
-                            nx[p][w] = tp[(in + p) * RW + w];
-                }
+                        buf[p][w] = tp[(i + p) * RW + w];
+            };
+            auto coord = [](const float4 &f, int c) { return c == 0 ? f.x : (c == 1 ? f.y : (c == 2 ? f.z : f.w)); };
+            auto process = [&](const float4 (&buf)[SCAN_GP][RW], int i) {
                 float2 acc[SCAN_GP][RQ / 2];
 #pragma unroll
                 for (int p = 0; p < SCAN_GP; ++p)
+                {
+                    const float pn = coord(buf[p][D / 4], D % 4);
 #pragma unroll
                     for (int jj = 0; jj < RQ / 2; ++jj)
-                        acc[p][jj] = make_float2(pv[p][D], pv[p][D]);
+                        acc[p][jj] = make_float2(pn, pn);
+                }
+                // (ptxas schedules these freely; source order does not reach the SASS)
 #pragma unroll
                 for (int c = 0; c < D; ++c)
 #pragma unroll
-                    for (int p = 0; p < SCAN_GP; ++p)
+                    for (int jj = 0; jj < RQ / 2; ++jj)
 #pragma unroll
-                        for (int jj = 0; jj < RQ / 2; ++jj)
-                            acc[p][jj] = ffma2(qq[jj][c], make_float2(pv[p][c], pv[p][c]), acc[p][jj]);
+                        for (int p = 0; p < SCAN_GP; ++p)
+                        {
+                            const float x = coord(buf[p][c / 4], c % 4);
+                            acc[p][jj] = ffma2(qq[jj][c], make_float2(x, x), acc[p][jj]);
+                        }
                 // per-query minimum over the group: one compare per query decides the group
                 float gm[RQ];
 #pragma unroll
@@ -371,6 +373,17 @@ namespace omplcu
                             }
                         }
                 }
+            };
+            float4 bufa[SCAN_GP][RW], bufb[SCAN_GP][RW];
+            load_group(bufa, 0);
+#pragma unroll 1
+            for (int i = 0; i < SCAN_PT; i += 2 * SCAN_GP)
+            {
+                load_group(bufb, i + SCAN_GP);
+                process(bufa, i);
+                // wraps to the first group on the last iteration (harmless re-read)
+                load_group(bufa, (i + 2 * SCAN_GP) & (SCAN_PT - 1));
+                process(bufb, i + SCAN_GP);
             }
             // Warps run the ring independently (no block barrier): the last warp to
             // finish a stage refills it.  Every lane's reads of the stage are complete

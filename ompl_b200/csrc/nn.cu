@@ -212,6 +212,105 @@ namespace omplcu
             }
         }
 
+        // compact copy of every step-th filter row (the sample thr_sample_kernel reads)
+        __global__ void sample_gather_kernel(const float4 *filt, int rw, uint32_t step, uint32_t nsample, float4 *out)
+        {
+            const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+            if (i < nsample * (uint32_t)rw)
+                out[i] = filt[(size_t)(i / rw) * step * rw + (i % rw)];
+        }
+
+        // Starting bound per query for the scan lists.  One warp serves SQ queries; lane l
+        // evaluates the scan value (same FMA order as knn_scan_kernel, so bit-identical) of
+        // sample rows l, l+32, ... and keeps two running minima over alternating rows:
+        // 64 minima of 64 disjoint groups, i.e. of 64 distinct points.  T = the L-th
+        // smallest of them, so at least L points have a scan value <= T.
+        constexpr int SQ = 8;
+        template <int RW>
+        __global__ void __launch_bounds__(128) thr_sample_kernel(const float4 *sample, int D, uint32_t nsample,
+                                                                 const float *qp, uint32_t qpad, uint32_t L,
+                                                                 float *out)
+        {
+            __shared__ float sq[4][16][SQ];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const uint32_t q0 = (blockIdx.x * 4u + w) * SQ;
+            if (q0 >= qpad)
+                return;
+            for (int i = lane; i < SQ * D; i += 32)
+                sq[w][i / SQ][i % SQ] = qp[(size_t)(i / SQ) * qpad + q0 + i % SQ];
+            __syncwarp();
+            const float inf = __int_as_float(0x7f800000);
+            float m0[SQ], m1[SQ];
+#pragma unroll
+            for (int j = 0; j < SQ; ++j)
+                m0[j] = m1[j] = inf;
+            for (uint32_t i = lane; i < nsample; i += 64)
+            {
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                {
+                    const uint32_t r = i + 32u * h;
+                    float x[4 * RW];
+#pragma unroll
+                    for (int v = 0; v < RW; ++v)
+                    {
+                        const float4 f = r < nsample ? sample[(size_t)r * RW + v] : make_float4(inf, inf, inf, inf);
+                        x[4 * v + 0] = f.x;
+                        x[4 * v + 1] = f.y;
+                        x[4 * v + 2] = f.z;
+                        x[4 * v + 3] = f.w;
+                    }
+                    float sv[SQ];
+                    // row layout: D coordinates, then the squared norm (+inf for dead rows)
+                    const float pn = r < nsample ? reinterpret_cast<const float *>(sample)[(size_t)r * 4 * RW + D] : inf;
+#pragma unroll
+                    for (int j = 0; j < SQ; ++j)
+                        sv[j] = pn;
+#pragma unroll
+                    for (int c = 0; c < 4 * RW - 1; ++c)
+                        if (c < D)
+                        {
+#pragma unroll
+                            for (int j = 0; j < SQ; ++j)
+                                sv[j] = fmaf(sq[w][c][j], x[c], sv[j]);
+                        }
+#pragma unroll
+                    for (int j = 0; j < SQ; ++j)
+                        if (h)
+                            m1[j] = fminf(m1[j], sv[j]);
+                        else
+                            m0[j] = fminf(m0[j], sv[j]);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < SQ; ++j)
+            {
+                // rank of each of the 64 minima (ties by position); the one of rank L-1 is T
+                uint32_t r0 = 0, r1 = 0;
+                for (int o = 0; o < 32; ++o)
+                {
+                    const float a0 = __shfl_sync(0xffffffffu, m0[j], o);
+                    const float a1 = __shfl_sync(0xffffffffu, m1[j], o);
+                    r0 += (a0 < m0[j] || (a0 == m0[j] && o < lane)) ? 1u : 0u;
+                    r0 += (a1 < m0[j]) ? 1u : 0u;
+                    r1 += (a0 < m1[j] || a0 == m1[j]) ? 1u : 0u;
+                    r1 += (a1 < m1[j] || (a1 == m1[j] && o < lane)) ? 1u : 0u;
+                }
+                float T = inf;
+                if (r0 == L - 1)
+                    T = m0[j];
+                if (r1 == L - 1)
+                    T = m1[j];
+                T = fminf(T, __shfl_xor_sync(0xffffffffu, T, 16));
+                T = fminf(T, __shfl_xor_sync(0xffffffffu, T, 8));
+                T = fminf(T, __shfl_xor_sync(0xffffffffu, T, 4));
+                T = fminf(T, __shfl_xor_sync(0xffffffffu, T, 2));
+                T = fminf(T, __shfl_xor_sync(0xffffffffu, T, 1));
+                if (lane == 0)
+                    out[q0 + j] = T;  // +inf (no bound) if fewer than L live sample points
+            }
+        }
+
         // ---- exact path ----
         // keys[b][slot] = exact distance(point slot, query sel[b]) (+inf for dead slots)
         __global__ void dist_rows_kernel(SpaceDesc sp, const double *pts, const uint8_t *alive, size_t nslots,
@@ -591,6 +690,8 @@ namespace omplcu
         std::lock_guard<std::mutex> lk(mu_);
         if (!strcmp(key, "force_exact"))
             force_exact_ = v != 0;
+        else if (!strcmp(key, "sample_thresholds"))
+            sample_thr_ = v != 0;
         else if (!strcmp(key, "scan_ctas_per_sm"))
             scan_ctas_per_sm_ = (int)v;  // 0 = as many as fit
         else if (!strcmp(key, "profile"))
@@ -748,14 +849,41 @@ namespace omplcu
         ScanParams P;
         P.filt = filt_.p;
         P.qp = qp_.p;
+        P.qpad = qpad;
+        P.init_thr = nullptr;
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev0_, s));
+        // Starting bounds (knn_scan.cuh): a strided sample of the points gives every query a
+        // value T with at least L sample points below it; the full pass starts its lists at T
+        // and skips most of the early insertions.  Self-verifying: the re-rank's band check
+        // does not care where a list's threshold came from.
+        const uint32_t nsample = 4096;
+        if (sample_thr_ && nslots_ >= 16 * (size_t)nsample && L <= 64)
+        {
+            const int rw = rowf_ / 4;
+            sample_thr_buf_.reserve(qpad + (size_t)nsample * rowf_);
+            float4 *rows = reinterpret_cast<float4 *>(sample_thr_buf_.p + qpad);  // qpad is a multiple of 256
+            const uint32_t step = (uint32_t)(nslots_ / nsample);
+            sample_gather_kernel<<<nblk((size_t)nsample * rw, 256), 256, 0, s>>>(
+                reinterpret_cast<const float4 *>(filt_.p), rw, step, nsample, rows);
+            const unsigned grid = nblk(qpad / SQ, 4);
+            if (rw == 1)
+                thr_sample_kernel<1><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
+            else if (rw == 2)
+                thr_sample_kernel<2><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
+            else if (rw == 3)
+                thr_sample_kernel<3><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
+            else
+                thr_sample_kernel<4><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
+            CUDA_CHECK(cudaGetLastError());
+            launches_ += 2;
+            P.init_thr = sample_thr_buf_.p;
+        }
         P.cand_thr = cand_vals_.p;
         P.cand_ids = cand_ids_.p;
         P.units = U;
         P.total_units = TU;
-        P.qpad = qpad;
         P.smax = smax;
-        if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev0_, s));
         scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
         launches_++;
         CUDA_CHECK(cudaGetLastError());

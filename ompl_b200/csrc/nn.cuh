@@ -87,7 +87,7 @@ namespace omplcu
         // query scratch
         DevBuf<double> q_stage_, out_d_;
         DevBuf<uint64_t> out_i_;
-        DevBuf<float> qp_, cand_vals_;
+        DevBuf<float> qp_, cand_vals_, sample_thr_buf_;
         DevBuf<double> qaux_;
         DevBuf<uint32_t> cand_ids_, ovf_list_;
         DevBuf<unsigned> counters_;
@@ -97,6 +97,7 @@ namespace omplcu
         DevBuf<unsigned char> cub_tmp_;
 
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
+        bool sample_thr_ = true;
         bool force_exact_ = false, profile_ = false;
         cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
         long last_scan_ns_ = 0, scan_ns_total_ = 0, scan_count_ = 0;
