@@ -277,37 +277,37 @@ namespace omplcu
             scr->w = A * A * 1.52587890625e-05f - pn;
             const float mx = scr->x, my = scr->y, mz = scr->z, tau = scr->w;
             unsigned short *surv = surv_base + threadIdx.x;
-            const int nf = c.nfilt_pad;
             const int stride = blockDim.x;
+            // Broad phase: a uniform grid over the obstacles' bounding spheres.  Cell lists are
+            // built on the host with slack for the FP32 cell index; a state outside the grid is
+            // farther from every obstacle than its sphere reaches.
+            const float fx = (px - c.grid_x0) * c.grid_inv_h;
+            const float fy = (py - c.grid_y0) * c.grid_inv_h;
+            const float fz = (pz - c.grid_z0) * c.grid_inv_h;
+            if (!(fx >= 0.f && fy >= 0.f && fz >= 0.f && fx < (float)c.grid_nx && fy < (float)c.grid_ny &&
+                  fz < (float)c.grid_nz))
+                return true;
+            const int cell = ((int)fz * c.grid_ny + (int)fy) * c.grid_nx + (int)fx;
+            const uint32_t kb = __ldg(c.cell_start + cell), ke = __ldg(c.cell_start + cell + 1);
             int ns = 0;
             bool hit = false;
-#pragma unroll 2
-            for (int j = 0; j < nf; j += 4)
+            for (uint32_t k = kb; k < ke; ++k)
             {
-                const float4 o0 = F[j], o1 = F[j + 1], o2 = F[j + 2], o3 = F[j + 3];
-                const float s0 = fmaf(mz, o0.z, fmaf(my, o0.y, fmaf(mx, o0.x, o0.w)));
-                const float s1 = fmaf(mz, o1.z, fmaf(my, o1.y, fmaf(mx, o1.x, o1.w)));
-                const float s2 = fmaf(mz, o2.z, fmaf(my, o2.y, fmaf(mx, o2.x, o2.w)));
-                const float s3 = fmaf(mz, o3.z, fmaf(my, o3.y, fmaf(mx, o3.x, o3.w)));
-                if ((s0 <= tau) | (s1 <= tau) | (s2 <= tau) | (s3 <= tau))
+                const int jj = (int)__ldg(c.cell_items + k);
+                const float4 o = F[jj];
+                const float sv = fmaf(mz, o.z, fmaf(my, o.y, fmaf(mx, o.x, o.w)));
+                if (sv <= tau)
                 {
-                    unsigned m = (s0 <= tau ? 1u : 0u) | (s1 <= tau ? 2u : 0u) | (s2 <= tau ? 4u : 0u) |
-                                 (s3 <= tau ? 8u : 0u);
-                    while (m)
+                    if (ns < SURV_CAP)
+                        surv[(ns++) * stride] = (unsigned short)jj;
+                    else if (!hit)
                     {
-                        const int jj = j + __ffs(m) - 1;
-                        m &= m - 1;
-                        if (ns < SURV_CAP)
-                            surv[(ns++) * stride] = (unsigned short)jj;
-                        else if (!hit)
+                        // list full (dense clutter): examine this one right away
+                        for (int i = 0; i < c.nrobot && !hit; ++i)
                         {
-                            // list full (dense clutter): examine this one right away
-                            for (int i = 0; i < c.nrobot && !hit; ++i)
-                            {
-                                double cx, cy, cz, rr;
-                                se3_robot_centre(c, i, st, cx, cy, cz, rr);
-                                hit = se3_obstacle_hits(c, jj, cx, cy, cz, rr);
-                            }
+                            double cx, cy, cz, rr;
+                            se3_robot_centre(c, i, st, cx, cy, cz, rr);
+                            hit = se3_obstacle_hits(c, jj, cx, cy, cz, rr);
                         }
                     }
                 }
@@ -576,6 +576,7 @@ namespace omplcu
         const int nf = desc_.nsph + desc_.nbox;
         const int pad = (nf + 3) / 4 * 4;
         std::vector<float> rows(4 * (size_t)std::max(pad, 4));
+        std::vector<double> centre(3 * (size_t)std::max(nf, 1)), reach(std::max(nf, 1));
         double amax = 0.0;
         for (int j = 0; j < pad; ++j)
         {
@@ -597,6 +598,9 @@ namespace omplcu
             r[1] = (float)o[1];
             r[2] = (float)o[2];
             r[3] = (float)(o[0] * o[0] + o[1] * o[1] + o[2] * o[2] - w);
+            for (int a = 0; a < 3; ++a)
+                centre[3 * (size_t)j + a] = o[a];
+            reach[j] = std::sqrt(w);
             for (double v : {std::fabs(o[0]), std::fabs(o[1]), std::fabs(o[2]), std::sqrt(w)})
                 amax = std::max(amax, v);
         }
@@ -606,13 +610,110 @@ namespace omplcu
         desc_.filt = filt_.p;
         desc_.nfilt_pad = pad;
         desc_.filt_amax = (float)(amax * (1.0 + 1e-6));
+        build_se3_grid(centre, reach, nf);
         // filter rows + [SURV_CAP][128] u16 survivor lists + one float4 of scratch per thread
         const size_t need = (size_t)pad * sizeof(float4) + SURV_CAP * 128 * sizeof(unsigned short) + 128 * sizeof(float4);
-        if (need <= 200 * 1024)
+        if (need <= 200 * 1024 && nf <= 65535)
         {
             smem_bytes_ = need;
             desc_.stage_smem = 1;
         }
+    }
+
+    // Uniform grid over the bounding spheres (centre o_j, radius sqrt(W_j) = rho_j + rho_rob).
+    // Cell (ix,iy,iz) lists every obstacle whose sphere comes within `slack` of the cell's
+    // box; the slack covers the FP32 evaluation of the cell index on the device (error
+    // below 2^-21 * A in length units, A = largest coordinate).
+    void Checker::build_se3_grid(const std::vector<double> &centre, const std::vector<double> &R, int nf)
+    {
+        double lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0}, meanR = 0.0, amax = desc_.filt_amax;
+        for (int j = 0; j < nf; ++j)
+        {
+            const double *r = centre.data() + 3 * (size_t)j;
+            meanR += R[j] / nf;
+            for (int a = 0; a < 3; ++a)
+            {
+                lo[a] = j ? std::min(lo[a], r[a] - R[j]) : r[a] - R[j];
+                hi[a] = j ? std::max(hi[a], r[a] + R[j]) : r[a] + R[j];
+            }
+        }
+        double ext = 0.0;
+        for (int a = 0; a < 3; ++a)
+            ext = std::max(ext, hi[a] - lo[a]);
+        double h = std::max({1.5 * meanR, ext / 48.0, 1e-30});
+        std::vector<uint32_t> start;
+        std::vector<uint16_t> items;
+        int n[3] = {1, 1, 1};
+        double slack = 0.0;
+        for (int attempt = 0; attempt < 8; ++attempt, h *= 2.0)
+        {
+            slack = 1e-3 * h + amax * 9.5367431640625e-07;  // 2^-20 * A
+            for (int a = 0; a < 3; ++a)
+                n[a] = std::max(1, (int)std::ceil((hi[a] - lo[a] + 2.0 * slack) / h));
+            const size_t ncell = (size_t)n[0] * n[1] * n[2];
+            std::vector<std::vector<uint16_t>> cells(ncell);
+            size_t total = 0;
+            for (int j = 0; j < nf; ++j)
+            {
+                const double *r = centre.data() + 3 * (size_t)j;
+                int c0[3], c1[3];
+                for (int a = 0; a < 3; ++a)
+                {
+                    c0[a] = std::max(0, (int)std::floor((r[a] - R[j] - slack - (lo[a] - slack)) / h));
+                    c1[a] = std::min(n[a] - 1, (int)std::floor((r[a] + R[j] + slack - (lo[a] - slack)) / h));
+                }
+                for (int iz = c0[2]; iz <= c1[2]; ++iz)
+                    for (int iy = c0[1]; iy <= c1[1]; ++iy)
+                        for (int ix = c0[0]; ix <= c1[0]; ++ix)
+                        {
+                            // squared distance from the sphere centre to the cell's box
+                            const int ic[3] = {ix, iy, iz};
+                            double d2 = 0.0;
+                            for (int a = 0; a < 3; ++a)
+                            {
+                                const double b0 = lo[a] - slack + ic[a] * h, b1 = b0 + h;
+                                const double e = std::max({b0 - r[a], r[a] - b1, 0.0});
+                                d2 += e * e;
+                            }
+                            if (d2 <= (R[j] + slack) * (R[j] + slack))
+                            {
+                                cells[((size_t)iz * n[1] + iy) * n[0] + ix].push_back((uint16_t)j);
+                                ++total;
+                            }
+                        }
+            }
+            if (total > (size_t)8 << 20 && attempt < 7)
+                continue;  // too fine for this world: coarsen
+            start.assign(ncell + 1, 0);
+            items.clear();
+            items.reserve(total);
+            for (size_t cidx = 0; cidx < ncell; ++cidx)
+            {
+                start[cidx] = (uint32_t)items.size();
+                items.insert(items.end(), cells[cidx].begin(), cells[cidx].end());
+            }
+            start[ncell] = (uint32_t)items.size();
+            break;
+        }
+        cell_start_.reserve(start.size());
+        cell_items_.reserve(std::max<size_t>(items.size(), 1));
+        CUDA_CHECK(cudaMemcpyAsync(cell_start_.p, start.data(), start.size() * sizeof(uint32_t),
+                                   cudaMemcpyHostToDevice, stream_));
+        if (!items.empty())
+            CUDA_CHECK(cudaMemcpyAsync(cell_items_.p, items.data(), items.size() * sizeof(uint16_t),
+                                       cudaMemcpyHostToDevice, stream_));
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+        desc_.cell_start = cell_start_.p;
+        desc_.cell_items = cell_items_.p;
+        desc_.grid_x0 = (float)(lo[0] - slack);
+        desc_.grid_y0 = (float)(lo[1] - slack);
+        desc_.grid_z0 = (float)(lo[2] - slack);
+        desc_.grid_inv_h = (float)(1.0 / h);
+        desc_.grid_nx = n[0];
+        desc_.grid_ny = n[1];
+        desc_.grid_nz = n[2];
+        grid_cells_ = (long)start.size() - 1;
+        grid_items_ = (long)items.size();
     }
 
     Checker::~Checker()
@@ -635,6 +736,10 @@ namespace omplcu
             return last_evaluated_;
         if (!strcmp(key, "last_group"))
             return last_group_;
+        if (!strcmp(key, "grid_cells"))
+            return grid_cells_;
+        if (!strcmp(key, "grid_items"))
+            return grid_items_;
         throw Error(OMPLCU_ERR_INVALID, std::string("unknown stat ") + key);
     }
 

@@ -2,6 +2,7 @@
 #pragma once
 #include <atomic>
 #include <mutex>
+#include <vector>
 
 #include "common.cuh"
 
@@ -34,6 +35,11 @@ namespace omplcu
         const float4 *filt;       // (o.x, o.y, o.z, |o|^2 - W) per obstacle, see se3_valid_fast
         float filt_amax;          // bound on |o_c| and sqrt(W) over the rows
         int _pad;
+        // broad-phase grid over the bounding spheres (validity.cu, build_se3_grid)
+        float grid_x0, grid_y0, grid_z0, grid_inv_h;
+        int grid_nx, grid_ny, grid_nz, _pad2;
+        const uint32_t *cell_start;  // [ncell + 1]
+        const uint16_t *cell_items;  // obstacle rows per cell
     };
 
     class Checker
@@ -57,6 +63,7 @@ namespace omplcu
 
     private:
         void build_se3_filter(const double *robot, const double *sph, const double *box);
+        void build_se3_grid(const std::vector<double> &centre, const std::vector<double> &reach, int nf);
         int device_;
         int sms_ = 148;
         CheckerDesc desc_;
@@ -64,6 +71,9 @@ namespace omplcu
         std::mutex mu_;
         DevBuf<double> params_;
         DevBuf<float4> filt_;
+        DevBuf<uint32_t> cell_start_;
+        DevBuf<uint16_t> cell_items_;
+        long grid_cells_ = 0, grid_items_ = 0;
         DevBuf<unsigned long long> ctr_;
         size_t smem_bytes_ = 0;
         // scratch

@@ -45,7 +45,8 @@ for want_t in (False, True):
     ms = min(ts[1:])
     print(f"n={n} mode={mode} last_valid={want_t}: {ms:.2f} ms  {n / ms * 1e3 / 1e6:.2f} M segments/s  "
           f"states in segments {chk.stat('last_states')}  evaluated {chk.stat('last_states_evaluated')}  "
-          f"group {chk.stat('last_group')}  valid {int(dv.sum())}")
+          f"group {chk.stat('last_group')}  grid {chk.stat('grid_cells')} cells / {chk.stat('grid_items')} items  "
+          f"valid {int(dv.sum())}")
 m = min(n, 20000)
 osp, ochk = orc.space_se3(-1.0, 1.0), orc.checker_se3(robot, sph, box)
 t0 = time.perf_counter()
