@@ -232,6 +232,48 @@ namespace omplcu
         }
     }
 
+    // SO3StateSpace::interpolate split in two: the part that depends only on the end
+    // points (theta, 1/sin(theta), sign of the dot product) and the part that depends
+    // on t.  Same operations in the same order as so3_interpolate, so the states are
+    // bit-identical; the motion kernel computes the first part once per segment.
+    struct So3Seg
+    {
+        double theta, d;
+        bool neg;
+    };
+    template <typename PA, typename PB>
+    __device__ __forceinline__ So3Seg so3_prepare(PA from, PB to)
+    {
+        So3Seg g;
+        g.theta = so3_arc_length(from, to);
+        g.d = 0.0;
+        g.neg = false;
+        if (g.theta > kDblEps)
+        {
+            g.d = ddiv(1.0, omplcu_sin(g.theta));
+            g.neg = quat_dot(from, to) < 0;
+        }
+        return g;
+    }
+    template <typename PA, typename PB, typename PO>
+    __device__ __forceinline__ void so3_interpolate_prepared(const So3Seg &g, PA from, PB to, double t, PO out)
+    {
+        if (g.theta > kDblEps)
+        {
+            double s0 = omplcu_sin(dmul(dsub(1.0, t), g.theta));
+            double s1 = omplcu_sin(dmul(t, g.theta));
+            if (g.neg)
+                s1 = -s1;
+            for (int i = 0; i < 4; ++i)
+                out[i] = dmul(dadd(dmul(from[i], s0), dmul(to[i], s1)), g.d);
+        }
+        else
+        {
+            for (int i = 0; i < 4; ++i)
+                out[i] = from[i];
+        }
+    }
+
     // KinematicChainSpace::distance, demos/KinematicChain.h:105-121
     template <typename PA, typename PB>
     __device__ __forceinline__ double chain_distance(PA a, PB b, int d, double linkLength)
@@ -298,6 +340,50 @@ namespace omplcu
                 out[off] = so2_interpolate(from[off], to[off], t);
             else if (cc.type == OMPLCU_SO3)
                 so3_interpolate(from + off, to + off, t, out + off);
+            else
+                for (int i = 0; i < cc.dim; ++i)
+                    out[off + i] = so2_interpolate(from[off + i], to[off + i], t);
+            off += cc.dim;
+        }
+    }
+
+    // The same with the SO(3) components' per-segment constants supplied by the caller
+    // (prep[k] belongs to the k-th SO(3) component, k < MAX_SO3_PREP; further ones are
+    // computed in place).
+    constexpr int MAX_SO3_PREP = 2;
+    template <typename PA, typename PB>
+    __device__ __forceinline__ void space_prepare(const SpaceDesc &sp, PA from, PB to, So3Seg (&prep)[MAX_SO3_PREP])
+    {
+        int off = 0, k = 0;
+        for (int c = 0; c < sp.ncomp; ++c)
+        {
+            if (sp.comp[c].type == OMPLCU_SO3 && k < MAX_SO3_PREP)
+                prep[k++] = so3_prepare(from + off, to + off);
+            off += sp.comp[c].dim;
+        }
+    }
+    template <typename PA, typename PB, typename PO>
+    __device__ __forceinline__ void space_interpolate_prepared(const SpaceDesc &sp, const So3Seg (&prep)[MAX_SO3_PREP],
+                                                               PA from, PB to, double t, PO out)
+    {
+        int off = 0, k = 0;
+        for (int c = 0; c < sp.ncomp; ++c)
+        {
+            const omplcu_component &cc = sp.comp[c];
+            if (cc.type == OMPLCU_RV)
+            {
+                for (int i = 0; i < cc.dim; ++i)
+                    out[off + i] = dadd(from[off + i], dmul(dsub(to[off + i], from[off + i]), t));
+            }
+            else if (cc.type == OMPLCU_SO2)
+                out[off] = so2_interpolate(from[off], to[off], t);
+            else if (cc.type == OMPLCU_SO3)
+            {
+                if (k < MAX_SO3_PREP)
+                    so3_interpolate_prepared(prep[k++], from + off, to + off, t, out + off);
+                else
+                    so3_interpolate(from + off, to + off, t, out + off);
+            }
             else
                 for (int i = 0; i < cc.dim; ++i)
                     out[off + i] = so2_interpolate(from[off + i], to[off + i], t);

@@ -316,13 +316,60 @@ namespace omplcu
                 return false;
             if (ns == 0)
                 return true;
+            // Narrow phase, FP32 first: the robot sphere centre and the survivor's distance
+            // test in FP32 differ from the FP64 reference expressions by less than
+            // 476 u A^2 in the squared distance (centre: 64 u A per coordinate, 25 roundings
+            // on magnitudes <= 4 rho_rob plus the roundings of p, q, o; difference and
+            // squares: 3 u A more; threshold: 4 u T).  Outside a band of 2^-15 A^2 = 512 u A^2
+            // around the threshold the FP32 answer IS the FP64 answer; inside it, the FP64
+            // expressions decide.
+            const float m2 = A * A * 3.0517578125e-05f;
             for (int i = 0; i < c.nrobot; ++i)
             {
-                double cx, cy, cz, rr;
-                se3_robot_centre(c, i, st, cx, cy, cz, rr);
+                const float4 ro = __ldg(c.robot32 + i);
+                const float tx = 2.0f * (qy * ro.z - qz * ro.y);
+                const float ty = 2.0f * (qz * ro.x - qx * ro.z);
+                const float tz = 2.0f * (qx * ro.y - qy * ro.x);
+                const float cxf = px + (ro.x + qw * tx + (qy * tz - qz * ty));
+                const float cyf = py + (ro.y + qw * ty + (qz * tx - qx * tz));
+                const float czf = pz + (ro.z + qw * tz + (qx * ty - qy * tx));
+                unsigned amb = 0;
                 for (int k = 0; k < ns; ++k)
-                    if (se3_obstacle_hits(c, (int)surv[k * stride], cx, cy, cz, rr))
-                        return false;
+                {
+                    const int j = (int)surv[k * stride];
+                    float D, T;
+                    if (j < c.nsph)
+                    {
+                        const float4 o = __ldg(c.sph32 + j);
+                        const float dx = o.x - cxf, dy = o.y - cyf, dz = o.z - czf;
+                        const float R = o.w + ro.w;
+                        D = dx * dx + dy * dy + dz * dz;
+                        T = R * R;
+                    }
+                    else
+                    {
+                        const float4 b0 = __ldg(c.box32 + 2 * (j - c.nsph));
+                        const float4 b1 = __ldg(c.box32 + 2 * (j - c.nsph) + 1);
+                        const float ex = fmaxf(fabsf(cxf - b0.x) - b0.w, 0.f);
+                        const float ey = fmaxf(fabsf(cyf - b0.y) - b1.x, 0.f);
+                        const float ez = fmaxf(fabsf(czf - b0.z) - b1.y, 0.f);
+                        D = ex * ex + ey * ey + ez * ez;
+                        T = ro.w * ro.w;
+                    }
+                    if (D < T - m2)
+                        return false;  // certain hit
+                    if (!(D > T + m2))
+                        amb |= 1u << k;  // too close to call in FP32 (or NaN)
+                }
+                if (amb)
+                {
+                    double cx, cy, cz, rr;
+                    se3_robot_centre(c, i, st, cx, cy, cz, rr);
+                    for (int k = 0; k < ns; ++k)
+                        if ((amb >> k) & 1u)
+                            if (se3_obstacle_hits(c, (int)surv[k * stride], cx, cy, cz, rr))
+                                return false;
+                }
             }
             return true;
         }
@@ -402,6 +449,7 @@ namespace omplcu
             const unsigned gmask = (G == 32) ? FULL : (((1u << G) - 1u) << gbase);
             size_t seg = 0;
             unsigned cnt = 0, base = 0, ndv = 0;
+            So3Seg prep[MAX_SO3_PREP] = {};
             unsigned long long evaluated = 0;
             bool need = true, done = false;
             while (true)
@@ -422,6 +470,8 @@ namespace omplcu
                         cnt = (ndv >= 2 ? ndv - 1 : 0u) + 1u;
                         base = 0;
                         need = false;
+                        if (cnt > 1)  // acos, 1/sin(theta): once per segment, not once per state
+                            space_prepare(sp, s1 + seg * sp.stride, s2 + seg * sp.stride, prep);
                     }
                 }
                 if (__all_sync(FULL, done))
@@ -442,7 +492,7 @@ namespace omplcu
                     {
                         // t = (double)j / (double)nd, DiscreteMotionValidator.cpp:63,121
                         const double t = ddiv((double)(m + 1), (double)ndv);
-                        space_interpolate(sp, a, b, t, st);
+                        space_interpolate_prepared(sp, prep, a, b, t, st);
                     }
                     bad = !state_valid_f<KIND>(c, sm, st);
                     evaluated++;
@@ -611,6 +661,29 @@ namespace omplcu
         desc_.nfilt_pad = pad;
         desc_.filt_amax = (float)(amax * (1.0 + 1e-6));
         build_se3_grid(centre, reach, nf);
+        {
+            // FP32 copies of the robot and the obstacles for the narrow phase
+            std::vector<float> n32(4 * (size_t)(desc_.nrobot + desc_.nsph + 2 * desc_.nbox) + 4, 0.f);
+            float *q = n32.data();
+            for (int i = 0; i < 4 * desc_.nrobot; ++i)
+                *q++ = (float)robot[i];
+            for (int i = 0; i < 4 * desc_.nsph; ++i)
+                *q++ = (float)sph[i];
+            for (int j = 0; j < desc_.nbox; ++j)
+            {
+                const double *b = box + 6 * j;
+                const float v[8] = {(float)b[0], (float)b[1], (float)b[2], (float)b[3], (float)b[4], (float)b[5], 0.f, 0.f};
+                for (float x : v)
+                    *q++ = x;
+            }
+            narrow32_.reserve(n32.size() / 4);
+            CUDA_CHECK(cudaMemcpyAsync(narrow32_.p, n32.data(), n32.size() * sizeof(float), cudaMemcpyHostToDevice,
+                                       stream_));
+            CUDA_CHECK(cudaStreamSynchronize(stream_));
+            desc_.robot32 = narrow32_.p;
+            desc_.sph32 = narrow32_.p + desc_.nrobot;
+            desc_.box32 = narrow32_.p + desc_.nrobot + desc_.nsph;
+        }
         // filter rows + [SURV_CAP][128] u16 survivor lists + one float4 of scratch per thread
         const size_t need = (size_t)pad * sizeof(float4) + SURV_CAP * 128 * sizeof(unsigned short) + 128 * sizeof(float4);
         if (need <= 200 * 1024 && nf <= 65535)

@@ -40,6 +40,7 @@ namespace omplcu
         int grid_nx, grid_ny, grid_nz, _pad2;
         const uint32_t *cell_start;  // [ncell + 1]
         const uint16_t *cell_items;  // obstacle rows per cell
+        const float4 *robot32, *sph32, *box32;  // FP32 copies for the narrow phase (box: 2 float4 each)
     };
 
     class Checker
@@ -70,7 +71,7 @@ namespace omplcu
         cudaStream_t stream_ = nullptr;
         std::mutex mu_;
         DevBuf<double> params_;
-        DevBuf<float4> filt_;
+        DevBuf<float4> filt_, narrow32_;
         DevBuf<uint32_t> cell_start_;
         DevBuf<uint16_t> cell_items_;
         long grid_cells_ = 0, grid_items_ = 0;
