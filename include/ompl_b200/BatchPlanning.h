@@ -1,0 +1,203 @@
+/* BatchPlanning.h -- batch-submit call sites for sampling-based planners.
+ *
+ * The reference planners call the hot path one element at a time:
+ *   FMT*   sampleFree          one isValid per sample          geometric/planners/fmt/src/FMT.cpp:212-240
+ *          saveNeighborhood    one nearestK / nearestR per node                          FMT.cpp:169-191
+ *          expandTreeFromNode  one checkMotion per candidate edge                        FMT.cpp:498-575
+ *   PRM    addMilestone        connectionStrategy_(m) then one checkMotion per neighbour
+ *                                                      geometric/planners/prm/src/PRM.cpp:562-596
+ *          KStrategy           nn->nearestK(m, k, neighbors)   geometric/planners/prm/ConnectionStrategy.h:77-81
+ *
+ * The functions below are those loops with the per-element calls replaced by ONE batch call on
+ * the adapters of OmplBridge.h.  They hold no planner state (graphs, trees and queues stay the
+ * planner's); each states the exact sequential loop it is equivalent to, and
+ * tests/cpp/test_adapters.cpp runs that loop with the reference's own NearestNeighborsLinear and
+ * DiscreteMotionValidator beside it.
+ */
+#ifndef OMPL_B200_BATCH_PLANNING_H
+#define OMPL_B200_BATCH_PLANNING_H
+
+#include <algorithm>
+#include <cstdint>
+#include <functional>
+#include <utility>
+#include <vector>
+
+#include "ompl_b200/OmplBridge.h"
+
+namespace ompl
+{
+    namespace b200
+    {
+        /** FMT::sampleFree (FMT.cpp:212-240) for a batch: `draw(state)` is called exactly as the
+            sequential loop would call sampler_->sampleUniform, `chunk` states at a time, one
+            isValidBatch per chunk; valid states are kept IN DRAWING ORDER until `wanted` are found.
+            Returns the number of draws up to and including the last accepted one -- the
+            `sampleAttempts` of the reference loop -- so accepted set, order and attempt count are
+            those of the sequential loop run on the same random stream.  Unused states of the last
+            chunk are freed; `maxAttempts` bounds the loop (the reference uses the termination
+            condition). */
+        inline std::size_t sampleFreeBatch(const base::SpaceInformationPtr &si,
+                                           const base::BatchedStateValidityChecker &svc,
+                                           const std::function<void(base::State *)> &draw, std::size_t wanted,
+                                           std::vector<base::State *> &accepted, std::size_t chunk = 65536,
+                                           std::size_t maxAttempts = ~std::size_t(0))
+        {
+            std::size_t attempts = 0, attemptsAtLastAccept = 0;
+            std::vector<base::State *> cand;
+            std::vector<std::uint8_t> ok;
+            while (accepted.size() < wanted && attempts < maxAttempts)
+            {
+                const std::size_t n = std::min(chunk, maxAttempts - attempts);
+                cand.resize(n);
+                ok.resize(n);
+                for (auto &s : cand)
+                {
+                    s = si->allocState();
+                    draw(s);
+                }
+                svc.isValidBatch(cand.data(), n, ok.data());
+                for (std::size_t i = 0; i < n; ++i)
+                {
+                    if (accepted.size() < wanted)
+                    {
+                        ++attempts;
+                        if (ok[i] != 0)
+                        {
+                            accepted.push_back(cand[i]);
+                            attemptsAtLastAccept = attempts;
+                            continue;
+                        }
+                    }
+                    si->freeState(cand[i]);
+                }
+            }
+            return accepted.size() == wanted ? attemptsAtLastAccept : attempts;
+        }
+
+        /** FMT::saveNeighborhood (FMT.cpp:169-191) for all nodes at once.  neighborhoods[i] is what the
+            reference stores for nodes[i]: nearestK(m, k) (or nearestR(m, r) when k == 0) WITHOUT its
+            first element, which is m itself.  One batch query instead of nodes.size() queries. */
+        template <typename _T>
+        void saveNeighborhoodsBatch(const NearestNeighborsCUDA<_T> &nn, const std::vector<_T> &nodes, std::size_t k,
+                                    double r, std::vector<std::vector<_T>> &neighborhoods)
+        {
+            if (k != 0)
+                nn.nearestKBatch(nodes, k, neighborhoods);
+            else
+                nn.nearestRBatch(nodes, std::vector<double>(nodes.size(), r), neighborhoods);
+            for (auto &nbh : neighborhoods)
+                if (!nbh.empty())
+                    nbh.erase(nbh.begin());
+        }
+
+        /** One candidate edge of a roadmap / tree. */
+        template <typename _T>
+        struct CandidateEdge
+        {
+            _T from, to;
+            bool valid{false};
+        };
+
+        /** PRM::addMilestone (PRM.cpp:562-596) for a BATCH of new milestones.
+
+            Batch semantics (stated, because the sequential planner connects milestone i to the
+            milestones that existed before i): all milestones of the batch are added to `nn` first;
+            every one is then connected to its k nearest among the roadmap INCLUDING the whole batch,
+            itself excluded -- i.e. the loop
+                for m in batch: nn.add(m)
+                for m in batch: for n in nearestK(m, k + 1) minus m: edge(n, m) iff checkMotion(n, m)
+            which is sPRM / PRM* construction order.  `state(x)` maps an element to its State.
+            Edges come out grouped by milestone, neighbours in nearestK order; checkMotion(n, m) keeps
+            the reference's argument order (neighbour first).  Two batch calls replace
+            batch.size() * (1 + k) single calls. */
+        template <typename _T>
+        void connectMilestonesBatch(NearestNeighborsCUDA<_T> &nn, const base::BatchedDiscreteMotionValidator &mv,
+                                    const std::function<const base::State *(const _T &)> &state,
+                                    const std::vector<_T> &batch, std::size_t k,
+                                    std::vector<CandidateEdge<_T>> &edges)
+        {
+            edges.clear();
+            if (batch.empty() || k == 0)
+                return;
+            nn.add(batch);
+            std::vector<std::vector<_T>> nbh;
+            nn.nearestKBatch(batch, k + 1, nbh);
+            std::vector<const base::State *> s1, s2;
+            for (std::size_t i = 0; i < batch.size(); ++i)
+            {
+                std::size_t taken = 0;
+                for (const _T &n : nbh[i])
+                {
+                    if (n == batch[i] || taken == k)
+                        continue;
+                    ++taken;
+                    edges.push_back(CandidateEdge<_T>{n, batch[i], false});
+                    s1.push_back(state(n));
+                    s2.push_back(state(batch[i]));
+                }
+            }
+            std::vector<std::uint8_t> ok(edges.size());
+            mv.checkMotionBatch(s1.data(), s2.data(), edges.size(), ok.data(), nullptr);
+            for (std::size_t e = 0; e < edges.size(); ++e)
+                edges[e].valid = ok[e] != 0;
+        }
+
+        /** The lazy edge checks of FMT::expandTreeFromNode (FMT.cpp:559-573) and BITstar::checkEdge
+            (informedtrees/src/BITstar.cpp:799-817) for a wavefront: every (from, to) pair in one
+            call.  flags[i] = checkMotion(from_i, to_i). */
+        inline void checkEdgesBatch(const base::BatchedDiscreteMotionValidator &mv,
+                                    const std::vector<std::pair<const base::State *, const base::State *>> &pairs,
+                                    std::vector<std::uint8_t> &flags)
+        {
+            std::vector<const base::State *> s1(pairs.size()), s2(pairs.size());
+            for (std::size_t i = 0; i < pairs.size(); ++i)
+            {
+                s1[i] = pairs[i].first;
+                s2[i] = pairs[i].second;
+            }
+            flags.resize(pairs.size());
+            mv.checkMotionBatch(s1.data(), s2.data(), pairs.size(), flags.data(), nullptr);
+        }
+
+        /** SpaceInformation::checkMotion(states, count, firstInvalidStateIndex)
+            (base/src/SpaceInformation.cpp:274-285) with one isValidBatch. */
+        inline bool checkStatesBatch(const base::BatchedStateValidityChecker &svc,
+                                     const std::vector<base::State *> &states, unsigned int count,
+                                     unsigned int &firstInvalidStateIndex)
+        {
+            std::vector<std::uint8_t> ok(count);
+            svc.isValidBatch(states.data(), count, ok.data());
+            for (unsigned int i = 0; i < count; ++i)
+                if (ok[i] == 0)
+                {
+                    firstInvalidStateIndex = i;
+                    return false;
+                }
+            return true;
+        }
+
+        /** PathGeometric::check (geometric/src/PathGeometric.cpp:159-180): the first state, then every
+            consecutive pair of the path through the motion validator, in one call. */
+        inline bool checkPathBatch(const base::BatchedStateValidityChecker &svc,
+                                   const base::BatchedDiscreteMotionValidator &mv,
+                                   const std::vector<base::State *> &path)
+        {
+            if (path.empty())
+                return true;
+            if (!svc.isValid(path[0]))
+                return false;
+            if (path.size() < 2)
+                return true;
+            std::vector<const base::State *> s1(path.begin(), path.end() - 1), s2(path.begin() + 1, path.end());
+            std::vector<std::uint8_t> ok(s1.size());
+            mv.checkMotionBatch(s1.data(), s2.data(), s1.size(), ok.data(), nullptr);
+            for (auto f : ok)
+                if (f == 0)
+                    return false;
+            return true;
+        }
+    }  // namespace b200
+}  // namespace ompl
+
+#endif

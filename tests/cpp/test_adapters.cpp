@@ -10,6 +10,8 @@
 //   2. BatchedDiscreteMotionValidator vs DiscreteMotionValidator on SE2 with a circle
 //      world: both checkMotion overloads, counters, batch entry point.
 //   3. BatchedStateValidityChecker::isValidBatch vs the CPU predicate.
+//   4. BatchPlanning.h (FMT* / PRM batch call sites) vs the sequential loops of FMT.cpp:169-240 and
+//      PRM.cpp:562-596 run with the reference's NearestNeighborsLinear and DiscreteMotionValidator.
 #include <cmath>
 #include <cstdio>
 #include <random>
@@ -19,6 +21,7 @@
 #include "ompl/base/spaces/SE2StateSpace.h"
 #include "ompl/base/spaces/SE3StateSpace.h"
 #include "ompl/datastructures/NearestNeighborsLinear.h"
+#include "ompl_b200/BatchPlanning.h"
 #include "ompl_b200/OmplBridge.h"
 
 namespace ob = ompl::base;
@@ -255,6 +258,168 @@ static void motionTest()
     std::printf("validity adapters (SE2 circles): %u of %u motions valid\n", nv, n);
 }
 
+static void batchPlanningTest()
+{
+    auto space = std::make_shared<ob::SE2StateSpace>();
+    ob::RealVectorBounds bounds(2);
+    bounds.setLow(0);
+    bounds.setHigh(1);
+    space->setBounds(bounds);
+    space->setup();
+    Circles circ{{0.5, 0.5, 0.2, 0.2, 0.8, 0.1, 0.8, 0.2, 0.15, 0.15, 0.3, 0.08}};
+    auto siRef = std::make_shared<ob::SpaceInformation>(space);
+    siRef->setStateValidityChecker(std::make_shared<CpuCircleChecker>(siRef.get(), &circ));
+    ob::DiscreteMotionValidator ref(siRef.get());
+    auto si = std::make_shared<ob::SpaceInformation>(space);
+    auto handle = ompl::b200::CheckerHandle::circles2D(circ.c);
+    auto svc = std::make_shared<ob::BatchedStateValidityChecker>(si, handle);
+    si->setStateValidityChecker(svc);
+    ob::BatchedDiscreteMotionValidator mv(si, handle);
+
+    // ---- FMT::sampleFree: same random stream, sequential vs batched ----
+    const std::size_t wanted = 500;
+    auto drawWith = [&space](std::mt19937_64 &g) {
+        return [&space, &g](ob::State *s) {
+            std::uniform_real_distribution<double> u(0, 1), a(-M_PI, M_PI);
+            std::vector<double> r = {u(g), u(g), a(g)};
+            space->copyFromReals(s, r);
+        };
+    };
+    std::mt19937_64 g1(99), g2(99);
+    std::vector<ob::State *> seq;
+    std::size_t seqAttempts = 0;
+    {
+        auto draw = drawWith(g1);
+        ob::State *s = space->allocState();
+        while (seq.size() < wanted)
+        {
+            draw(s);
+            ++seqAttempts;
+            if (siRef->isValid(s))
+            {
+                seq.push_back(s);
+                s = space->allocState();
+            }
+        }
+        space->freeState(s);
+    }
+    std::vector<ob::State *> acc;
+    const std::size_t attempts = ompl::b200::sampleFreeBatch(si, *svc, drawWith(g2), wanted, acc, 192);
+    CHECK(acc.size() == wanted && attempts == seqAttempts && attempts > wanted);
+    for (std::size_t i = 0; i < wanted && i < acc.size(); ++i)
+        CHECK(space->equalStates(acc[i], seq[i]));
+
+    // ---- FMT::saveNeighborhood for every node ----
+    auto dist = [&space](ob::State *const &a, ob::State *const &b) { return space->distance(a, b); };
+    ompl::NearestNeighborsLinear<ob::State *> lin;
+    lin.setDistanceFunction(dist);
+    ompl::NearestNeighborsCUDA<ob::State *> nn;
+    ompl::b200::bind<ob::State *>(nn, space, [](ob::State *const &s) { return (const ob::State *)s; });
+    const std::size_t roadmap = 300;
+    std::vector<ob::State *> first(acc.begin(), acc.begin() + roadmap), rest(acc.begin() + roadmap, acc.end());
+    lin.add(first);
+    nn.add(first);
+    std::vector<std::vector<ob::State *>> nbhK, nbhR;
+    ompl::b200::saveNeighborhoodsBatch<ob::State *>(nn, first, 8, 0.0, nbhK);
+    ompl::b200::saveNeighborhoodsBatch<ob::State *>(nn, first, 0, 0.25, nbhR);
+    std::vector<ob::State *> want;
+    for (std::size_t i = 0; i < roadmap; ++i)
+    {
+        lin.nearestK(first[i], 8, want);
+        want.erase(want.begin());  // FMT.cpp:181-183
+        CHECK(nbhK[i] == want);
+        lin.nearestR(first[i], 0.25, want);
+        want.erase(want.begin());
+        CHECK(nbhR[i] == want);
+    }
+
+    // ---- PRM::addMilestone for a batch (semantics stated in BatchPlanning.h) ----
+    const std::size_t k = 6;
+    std::vector<ompl::b200::CandidateEdge<ob::State *>> edges;
+    ompl::b200::connectMilestonesBatch<ob::State *>(
+        nn, mv, [](ob::State *const &s) { return (const ob::State *)s; }, rest, k, edges);
+    lin.add(rest);
+    CHECK(nn.size() == lin.size());
+    std::size_t e = 0, nvalid = 0;
+    for (ob::State *m : rest)
+    {
+        lin.nearestK(m, k + 1, want);
+        std::size_t taken = 0;
+        for (ob::State *n : want)
+        {
+            if (n == m || taken == k)
+                continue;
+            ++taken;
+            CHECK(e < edges.size() && edges[e].from == n && edges[e].to == m);
+            const bool ok = ref.checkMotion(n, m);  // PRM.cpp:582
+            if (e < edges.size())
+                CHECK(edges[e].valid == ok);
+            nvalid += ok;
+            ++e;
+        }
+    }
+    CHECK(e == edges.size() && nvalid > 0 && nvalid < e);
+
+    // ---- lazy edge wavefront, explicit state sequence, path check ----
+    std::vector<std::pair<const ob::State *, const ob::State *>> pairs;
+    for (std::size_t i = 0; i + 7 < acc.size(); i += 3)
+        pairs.emplace_back(acc[i], acc[i + 7]);
+    std::vector<std::uint8_t> flags;
+    ompl::b200::checkEdgesBatch(mv, pairs, flags);
+    for (std::size_t i = 0; i < pairs.size(); ++i)
+        CHECK((flags[i] != 0) == ref.checkMotion(pairs[i].first, pairs[i].second));
+
+    std::vector<ob::State *> mixed(acc.begin(), acc.begin() + 40);
+    ob::State *bad = space->allocState();
+    std::vector<double> inside = {0.5, 0.5, 0.0};
+    space->copyFromReals(bad, inside);
+    mixed.insert(mixed.begin() + 17, bad);
+    unsigned int firstBad = 1000, firstBadRef = 2000;
+    CHECK(!ompl::b200::checkStatesBatch(*svc, mixed, (unsigned int)mixed.size(), firstBad));
+    // the loop of SpaceInformation::checkMotion(states, count, firstInvalid), SpaceInformation.cpp:274-285
+    // (SpaceInformation.cpp itself is not part of oracle/_ref: it needs the sampler / planner tree)
+    for (unsigned int i = 0; i < mixed.size(); ++i)
+        if (!siRef->isValid(mixed[i]))
+        {
+            firstBadRef = i;
+            break;
+        }
+    CHECK(firstBad == 17 && firstBadRef == 17);
+    CHECK(ompl::b200::checkStatesBatch(*svc, mixed, 17, firstBad));
+
+    std::vector<ob::State *> pathOk, pathBad(acc.begin(), acc.begin() + 30);
+    for (int i = 0; i < 20; ++i)
+    {
+        ob::State *s = space->allocState();
+        std::vector<double> r = {0.02 + 0.002 * i, 0.02, 0.1 * i};
+        space->copyFromReals(s, r);
+        pathOk.push_back(s);
+    }
+    auto refPath = [&](const std::vector<ob::State *> &p) {  // PathGeometric.cpp:159-180
+        if (p.empty())
+            return true;
+        if (!siRef->isValid(p[0]))
+            return false;
+        for (std::size_t j = 0; j + 1 < p.size(); ++j)
+            if (!ref.checkMotion(p[j], p[j + 1]))
+                return false;
+        return true;
+    };
+    CHECK(ompl::b200::checkPathBatch(*svc, mv, pathOk) == refPath(pathOk) && refPath(pathOk));
+    CHECK(ompl::b200::checkPathBatch(*svc, mv, pathBad) == refPath(pathBad) && !refPath(pathBad));
+    CHECK(ompl::b200::checkPathBatch(*svc, mv, {}) && !ompl::b200::checkPathBatch(*svc, mv, {bad}));
+
+    for (auto *s : pathOk)
+        space->freeState(s);
+    space->freeState(bad);
+    for (auto *s : seq)
+        space->freeState(s);
+    for (auto *s : acc)
+        space->freeState(s);
+    std::printf("batch planning call sites: %zu samples in %zu attempts, %zu candidate edges (%zu valid)\n", wanted,
+                attempts, edges.size(), nvalid);
+}
+
 int main()
 {
     int ndev = 0;
@@ -285,6 +450,7 @@ int main()
         }, "RealVector(7)");
     }
     motionTest();
+    batchPlanningTest();
     std::printf(failures ? "FAILED (%d)\n" : "all adapter tests passed\n", failures);
     return failures ? 1 : 0;
 }
