@@ -242,10 +242,9 @@ def run_gpu_arm(args):
         nn.set_option("sample_thresholds", 0)
 
     d_q = torch.from_numpy(qs).to(dev)
-    d_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
-    d_d = torch.empty((N_QUERIES, K), dtype=torch.float64, device=dev)
+    packed = sharding.PackedLists(world, N_QUERIES, K, dev)  # ids + distances in one buffer: one all-gather
+    d_ids, d_d = packed.ids, packed.dists
     if world > 1:
-        g_ids, g_d = sharding.alloc_gather_buffers(world, N_QUERIES, K, dev)
         m_ids, m_d = torch.empty_like(d_ids), torch.empty_like(d_d)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream()
@@ -254,9 +253,10 @@ def run_gpu_arm(args):
     def step_device():
         check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), N_QUERIES, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
         if world > 1:
-            sharding.all_gather_lists(d_ids, d_d, g_ids, g_d)
-            check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
-                                             m_d.data_ptr(), m_ids.data_ptr(), sptr))
+            packed.all_gather()
+            check(L.omplcu_merge_topk_strided_device(local, packed.gathered_dists().data_ptr(),
+                                                     packed.gathered_ids().data_ptr(), world, packed.part_stride,
+                                                     N_QUERIES, K, m_d.data_ptr(), m_ids.data_ptr(), sptr))
 
     h_ids = np.empty((N_QUERIES, K), dtype=np.uint64)
     h_d = np.empty((N_QUERIES, K), dtype=np.float64)
@@ -273,9 +273,10 @@ def run_gpu_arm(args):
             # sharded roadmap: merge needs the other shards' lists; exchange on the device
             d_ids.copy_(torch.from_numpy(h_ids.view(np.int64)), non_blocking=True)
             d_d.copy_(torch.from_numpy(h_d), non_blocking=True)
-            sharding.all_gather_lists(d_ids, d_d, g_ids, g_d)
-            check(L.omplcu_merge_topk_device(local, g_d.data_ptr(), g_ids.data_ptr(), world, N_QUERIES, K,
-                                             m_d.data_ptr(), m_ids.data_ptr(), sptr))
+            packed.all_gather()
+            check(L.omplcu_merge_topk_strided_device(local, packed.gathered_dists().data_ptr(),
+                                                     packed.gathered_ids().data_ptr(), world, packed.part_stride,
+                                                     N_QUERIES, K, m_d.data_ptr(), m_ids.data_ptr(), sptr))
             h_ids.view(np.int64)[:] = m_ids.cpu().numpy()
             h_d[:] = m_d.cpu().numpy()
 

@@ -124,6 +124,11 @@ int omplcu_nn_knn_device(omplcu_nn_t nn, const double *d_queries, size_t nq, siz
  * (distance, id).  Device pointers. */
 int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq,
                              size_t k, double *d_out_dists, uint64_t *d_out_ids, void *stream);
+/* The same with `part_stride` elements between consecutive parts (>= nq * k): lets a rank keep its ids and
+ * distances in ONE buffer ([ids | dists], both 8 bytes wide) so that a single all-gather moves both. */
+int omplcu_merge_topk_strided_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts,
+                                     size_t part_stride, size_t nq, size_t k, double *d_out_dists,
+                                     uint64_t *d_out_ids, void *stream);
 /* Tuning / introspection.  key: "force_exact" (0/1), "last_fallbacks" (read),
  * "last_path" (read: 1 fast scan, 2 exact sort), "launches" (read: kernels
  * launched by this handle so far). */

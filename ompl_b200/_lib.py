@@ -58,6 +58,7 @@ SIGNATURES = {
     "omplcu_nn_radius": [_vp, _pd, _sz, _pd, C.POINTER(_vp), C.POINTER(_vp), _pd],
     "omplcu_nn_knn_device": [_vp, _pd, _sz, _sz, _pd, _pd, _vp],
     "omplcu_merge_topk_device": [_i, _pd, _pd, _i, _sz, _sz, _pd, _pd, _vp],
+    "omplcu_merge_topk_strided_device": [_i, _pd, _pd, _i, _sz, _sz, _sz, _pd, _pd, _vp],
     "omplcu_nn_set_option": [_vp, C.c_char_p, C.c_long],
     "omplcu_nn_get_stat": [_vp, C.c_char_p, C.POINTER(C.c_long)],
     "omplcu_checker_create_allvalid": [_i, C.POINTER(_vp)],

@@ -305,7 +305,18 @@ int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *
 {
     return guarded([&] {
         need_gpu(device);
-        merge_topk_device(device, d_dists, d_ids, nparts, nq, k, d_out_dists, d_out_ids, (cudaStream_t)stream);
+        merge_topk_device(device, d_dists, d_ids, nparts, nq * k, nq, k, d_out_dists, d_out_ids, (cudaStream_t)stream);
+    });
+}
+
+int omplcu_merge_topk_strided_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts,
+                                     size_t part_stride, size_t nq, size_t k, double *d_out_dists,
+                                     uint64_t *d_out_ids, void *stream)
+{
+    return guarded([&] {
+        need_gpu(device);
+        merge_topk_device(device, d_dists, d_ids, nparts, part_stride, nq, k, d_out_dists, d_out_ids,
+                          (cudaStream_t)stream);
     });
 }
 

@@ -220,25 +220,27 @@ namespace omplcu
                 out[i] = filt[(size_t)(i / rw) * step * rw + (i % rw)];
         }
 
-        // Starting bound per query for the scan lists.  One warp serves SQ queries; lane l
+        // Starting bound per query for the scan lists.  One warp serves SQ queries (held in registers); lane l
         // evaluates the scan value (same FMA order as knn_scan_kernel, so bit-identical) of
         // sample rows l, l+32, ... and keeps two running minima over alternating rows:
         // 64 minima of 64 disjoint groups, i.e. of 64 distinct points.  T = the L-th
         // smallest of them, so at least L points have a scan value <= T.
-        constexpr int SQ = 8;
-        template <int RW>
-        __global__ void __launch_bounds__(128) thr_sample_kernel(const float4 *sample, int D, uint32_t nsample,
+        template <int D, int SQ>
+        __global__ void __launch_bounds__(128) thr_sample_kernel(const float4 *sample, uint32_t nsample,
                                                                  const float *qp, uint32_t qpad, uint32_t L,
                                                                  float *out)
         {
-            __shared__ float sq[4][16][SQ];
+            constexpr int RW = scan_rowf(D) / 4;
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
             const uint32_t q0 = (blockIdx.x * 4u + w) * SQ;
             if (q0 >= qpad)
                 return;
-            for (int i = lane; i < SQ * D; i += 32)
-                sq[w][i / SQ][i % SQ] = qp[(size_t)(i / SQ) * qpad + q0 + i % SQ];
-            __syncwarp();
+            float qv[D][SQ];
+#pragma unroll
+            for (int c = 0; c < D; ++c)
+#pragma unroll
+                for (int j = 0; j < SQ; ++j)
+                    qv[c][j] = qp[(size_t)c * qpad + q0 + j];
             const float inf = __int_as_float(0x7f800000);
             float m0[SQ], m1[SQ];
 #pragma unroll
@@ -260,20 +262,19 @@ namespace omplcu
                         x[4 * v + 2] = f.z;
                         x[4 * v + 3] = f.w;
                     }
-                    float sv[SQ];
                     // row layout: D coordinates, then the squared norm (+inf for dead rows)
-                    const float pn = r < nsample ? reinterpret_cast<const float *>(sample)[(size_t)r * 4 * RW + D] : inf;
+                    float sv[SQ];
 #pragma unroll
                     for (int j = 0; j < SQ; ++j)
-                        sv[j] = pn;
+                        sv[j] = x[D];
+                    if (r < nsample)
+                    {
 #pragma unroll
-                    for (int c = 0; c < 4 * RW - 1; ++c)
-                        if (c < D)
-                        {
+                        for (int c = 0; c < D; ++c)
 #pragma unroll
                             for (int j = 0; j < SQ; ++j)
-                                sv[j] = fmaf(sq[w][c][j], x[c], sv[j]);
-                        }
+                                sv[j] = fmaf(qv[c][j], x[c], sv[j]);
+                    }
 #pragma unroll
                     for (int j = 0; j < SQ; ++j)
                         if (h)
@@ -395,8 +396,8 @@ namespace omplcu
 
         // ---- merge of per-shard partial results (one warp per query) ----
         __global__ void __launch_bounds__(128) merge_topk_kernel(const double *dists, const uint64_t *ids, int nparts,
-                                                                 size_t nq, uint32_t k, double *out_d,
-                                                                 uint64_t *out_i)
+                                                                 size_t part_stride, size_t nq, uint32_t k,
+                                                                 double *out_d, uint64_t *out_i)
         {
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
             const size_t qi = blockIdx.x * 4ull + w;
@@ -412,7 +413,7 @@ namespace omplcu
             __syncwarp();
             for (uint32_t c = lane; c < n; c += 32)
             {
-                const size_t oc = ((size_t)(c / k) * nq + qi) * k + (c % k);
+                const size_t oc = (size_t)(c / k) * part_stride + qi * k + (c % k);
                 const uint64_t id = ids[oc];
                 if (id == OMPLCU_ID_NONE)
                     continue;
@@ -420,7 +421,7 @@ namespace omplcu
                 uint32_t rank = 0;
                 for (uint32_t o = 0; o < n; ++o)
                 {
-                    const size_t oo = ((size_t)(o / k) * nq + qi) * k + (o % k);
+                    const size_t oo = (size_t)(o / k) * part_stride + qi * k + (o % k);
                     const uint64_t io = ids[oo];
                     const double ko = dists[oo];
                     rank += (io != OMPLCU_ID_NONE && (ko < key || (ko == key && io < id))) ? 1u : 0u;
@@ -801,6 +802,48 @@ namespace omplcu
         }
     }  // namespace
 
+    namespace
+    {
+        template <int D>
+        void launch_thr_sample_d(const float4 *rows, uint32_t nsample, const float *qp, uint32_t qpad, uint32_t L,
+                                 float *out, cudaStream_t s)
+        {
+            constexpr int SQ = D <= 8 ? 8 : 4;
+            thr_sample_kernel<D, SQ><<<nblk(qpad / SQ, 4), 128, 0, s>>>(rows, nsample, qp, qpad, L, out);
+        }
+
+        void launch_thr_sample(int D, const float4 *rows, uint32_t nsample, const float *qp, uint32_t qpad, uint32_t L,
+                               float *out, cudaStream_t s)
+        {
+            switch (D)
+            {
+#define OMPLCU_THR_CASE(d)                                            \
+    case d:                                                           \
+        launch_thr_sample_d<d>(rows, nsample, qp, qpad, L, out, s);   \
+        break;
+                OMPLCU_THR_CASE(1)
+                OMPLCU_THR_CASE(2)
+                OMPLCU_THR_CASE(3)
+                OMPLCU_THR_CASE(4)
+                OMPLCU_THR_CASE(5)
+                OMPLCU_THR_CASE(6)
+                OMPLCU_THR_CASE(7)
+                OMPLCU_THR_CASE(8)
+                OMPLCU_THR_CASE(9)
+                OMPLCU_THR_CASE(10)
+                OMPLCU_THR_CASE(11)
+                OMPLCU_THR_CASE(12)
+                OMPLCU_THR_CASE(13)
+                OMPLCU_THR_CASE(14)
+                OMPLCU_THR_CASE(15)
+                OMPLCU_THR_CASE(16)
+#undef OMPLCU_THR_CASE
+                default:
+                    throw Error(OMPLCU_ERR_INTERNAL, "threshold sample: unsupported dimension");
+            }
+        }
+    }  // namespace
+
     // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
     void NNIndex::knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
                            double *d_dists, cudaStream_t s)
@@ -866,15 +909,7 @@ namespace omplcu
             const uint32_t step = (uint32_t)(nslots_ / nsample);
             sample_gather_kernel<<<nblk((size_t)nsample * rw, 256), 256, 0, s>>>(
                 reinterpret_cast<const float4 *>(filt_.p), rw, step, nsample, rows);
-            const unsigned grid = nblk(qpad / SQ, 4);
-            if (rw == 1)
-                thr_sample_kernel<1><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
-            else if (rw == 2)
-                thr_sample_kernel<2><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
-            else if (rw == 3)
-                thr_sample_kernel<3><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
-            else
-                thr_sample_kernel<4><<<grid, 128, 0, s>>>(rows, D_, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p);
+            launch_thr_sample(D_, rows, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p, s);
             CUDA_CHECK(cudaGetLastError());
             launches_ += 2;
             P.init_thr = sample_thr_buf_.p;
@@ -1142,15 +1177,16 @@ namespace omplcu
         }
     }
 
-    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq, size_t k,
-                           double *d_out_dists, uint64_t *d_out_ids, cudaStream_t s)
+    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t part_stride,
+                           size_t nq, size_t k, double *d_out_dists, uint64_t *d_out_ids, cudaStream_t s)
     {
         DeviceGuard g(device);
         REQUIRE(nparts >= 1 && d_dists && d_ids && d_out_dists && d_out_ids, "omplcu_merge_topk: bad arguments");
+        REQUIRE(part_stride >= nq * k, "omplcu_merge_topk: part stride smaller than one part");
         if (nq == 0 || k == 0)
             return;
-        merge_topk_kernel<<<nblk(nq, 4), 128, 0, s>>>(d_dists, d_ids, nparts, nq, (uint32_t)k, d_out_dists,
-                                                      d_out_ids);
+        merge_topk_kernel<<<nblk(nq, 4), 128, 0, s>>>(d_dists, d_ids, nparts, part_stride, nq, (uint32_t)k,
+                                                      d_out_dists, d_out_ids);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaStreamSynchronize(s));
     }

@@ -104,6 +104,7 @@ namespace omplcu
         long last_fallbacks_ = 0, last_path_ = 0, launches_ = 0;
     };
 
-    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq, size_t k,
+    void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t part_stride,
+                           size_t nq, size_t k,
                            double *d_out_dists, uint64_t *d_out_ids, cudaStream_t s);
 }  // namespace omplcu

@@ -35,3 +35,35 @@ def all_gather_lists(ids, dists, g_ids, g_dists, group=None):
     # concatenation along dim 0 is the one layout every backend accepts: [world*nq, k] is the same memory
     dist.all_gather_into_tensor(g_ids.view(-1, g_ids.shape[-1]), ids.contiguous(), group=group)
     dist.all_gather_into_tensor(g_dists.view(-1, g_dists.shape[-1]), dists.contiguous(), group=group)
+
+
+class PackedLists:
+    """ids and distances of one rank in ONE [2, nq, k] int64 buffer (row 0: ids, row 1: the float64
+    distances' bits), so that a single all-gather moves both; `gathered` is [world, 2, nq, k].
+    omplcu_merge_topk_strided_device reads it in place with part_stride = 2 * nq * k."""
+
+    def __init__(self, world, nq, k, device):
+        self.world, self.nq, self.k = world, nq, k
+        self.local = torch.empty((2, nq, k), dtype=torch.int64, device=device)
+        self.gathered = torch.empty((world, 2, nq, k), dtype=torch.int64, device=device)
+
+    @property
+    def ids(self):
+        return self.local[0]
+
+    @property
+    def dists(self):
+        return self.local[1].view(torch.float64)
+
+    @property
+    def part_stride(self):
+        return 2 * self.nq * self.k
+
+    def gathered_ids(self):
+        return self.gathered[:, 0]
+
+    def gathered_dists(self):
+        return self.gathered[:, 1].view(torch.float64)
+
+    def all_gather(self, group=None):
+        dist.all_gather_into_tensor(self.gathered.view(-1, self.k), self.local.view(-1, self.k), group=group)

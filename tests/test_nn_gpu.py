@@ -331,3 +331,12 @@ def test_merge_topk_equals_single_index(gpu):
     check(lib().omplcu_merge_topk_device(0, pd.data_ptr(), pi.data_ptr(), parts, nq, k, od.data_ptr(), oi.data_ptr(),
                                          None))
     assert (oi.cpu().numpy().astype(np.uint64) == wi).all() and (od.cpu().numpy() == wd).all()
+    # the packed layout bench.py all-gathers: [part][ids | dists][nq][k], merged in place with a stride
+    packed = torch.empty((parts, 2, nq, k), dtype=torch.int64, device="cuda")
+    packed[:, 0] = pi
+    packed[:, 1] = pd.view(torch.int64)
+    od.zero_()
+    oi.zero_()
+    check(lib().omplcu_merge_topk_strided_device(0, packed[0, 1].data_ptr(), packed[0, 0].data_ptr(), parts,
+                                                 2 * nq * k, nq, k, od.data_ptr(), oi.data_ptr(), None))
+    assert (oi.cpu().numpy().astype(np.uint64) == wi).all() and (od.cpu().numpy() == wd).all()

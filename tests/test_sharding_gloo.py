@@ -57,6 +57,13 @@ WORKER = textwrap.dedent("""
     m_i, m_d = np.take_along_axis(cat_i, order, 1), np.take_along_axis(cat_d, order, 1)
     w_i, w_d = orc.knn(sp, pts, qs, k)
     ok = bool((m_i == w_i.astype(np.int64)).all() and (m_d == w_d).all())
+    # the packed variant bench.py uses: one buffer, one all-gather
+    pk = sharding.PackedLists(world, nq, k, "cpu")
+    pk.ids.copy_(torch.from_numpy(ids))
+    pk.dists.copy_(torch.from_numpy(dd))
+    pk.all_gather()
+    ok = ok and bool((pk.gathered_ids() == g_ids).all() and (pk.gathered_dists() == g_d).all())
+    ok = ok and pk.part_stride == 2 * nq * k
     # every rank holds the same gathered buffers
     chk = torch.tensor([float(g_d.sum()), float(g_ids.sum())], dtype=torch.float64)
     all_chk = [torch.zeros_like(chk) for _ in range(world)]
