@@ -395,15 +395,28 @@ namespace omplcu
         }
 
         // ---- merge of per-shard partial results (one warp per query) ----
+        // The nparts * k candidates of a query are staged in shared memory once; every lane then
+        // ranks its candidates against all of them by (distance, id) with broadcast reads.
         __global__ void __launch_bounds__(128) merge_topk_kernel(const double *dists, const uint64_t *ids, int nparts,
                                                                  size_t part_stride, size_t nq, uint32_t k,
                                                                  double *out_d, uint64_t *out_i)
         {
+            extern __shared__ __align__(16) unsigned char merge_smem[];
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
             const size_t qi = blockIdx.x * 4ull + w;
             if (qi >= nq)
                 return;
             const uint32_t n = (uint32_t)nparts * k;
+            double *sk = reinterpret_cast<double *>(merge_smem) + (size_t)w * 2 * n;
+            uint64_t *si = reinterpret_cast<uint64_t *>(sk + n);
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const size_t oc = (size_t)(c / k) * part_stride + qi * k + (c % k);
+                const uint64_t id = ids[oc];
+                si[c] = id;
+                // absent entries sort after everything real
+                sk[c] = id == OMPLCU_ID_NONE ? __longlong_as_double(0x7ff8000000000000ll) : dists[oc];
+            }
             // pre-fill (fewer than k valid entries overall)
             for (uint32_t r = lane; r < k; r += 32)
             {
@@ -413,18 +426,15 @@ namespace omplcu
             __syncwarp();
             for (uint32_t c = lane; c < n; c += 32)
             {
-                const size_t oc = (size_t)(c / k) * part_stride + qi * k + (c % k);
-                const uint64_t id = ids[oc];
+                const uint64_t id = si[c];
                 if (id == OMPLCU_ID_NONE)
                     continue;
-                const double key = dists[oc];
+                const double key = sk[c];
                 uint32_t rank = 0;
                 for (uint32_t o = 0; o < n; ++o)
                 {
-                    const size_t oo = (size_t)(o / k) * part_stride + qi * k + (o % k);
-                    const uint64_t io = ids[oo];
-                    const double ko = dists[oo];
-                    rank += (io != OMPLCU_ID_NONE && (ko < key || (ko == key && io < id))) ? 1u : 0u;
+                    const double ko = sk[o];  // NaN (absent) compares false both ways
+                    rank += (ko < key || (ko == key && si[o] < id)) ? 1u : 0u;
                 }
                 if (rank < k)
                 {
@@ -1185,8 +1195,12 @@ namespace omplcu
         REQUIRE(part_stride >= nq * k, "omplcu_merge_topk: part stride smaller than one part");
         if (nq == 0 || k == 0)
             return;
-        merge_topk_kernel<<<nblk(nq, 4), 128, 0, s>>>(d_dists, d_ids, nparts, part_stride, nq, (uint32_t)k,
-                                                      d_out_dists, d_out_ids);
+        const size_t smem = 4 * (size_t)nparts * k * 16;
+        REQUIRE(smem <= 200 * 1024, "omplcu_merge_topk: nparts * k too large (limit 3200 candidates per query)");
+        if (smem > 48 * 1024)
+            CUDA_CHECK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<<<nblk(nq, 4), 128, smem, s>>>(d_dists, d_ids, nparts, part_stride, nq, (uint32_t)k,
+                                                         d_out_dists, d_out_ids);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaStreamSynchronize(s));
     }
