@@ -17,12 +17,14 @@
 #include <cub/cub.cuh>
 
 #include "knn_scan.cuh"
+#include "knn_scan_hd.cuh"
 
 namespace omplcu
 {
     namespace
     {
-        constexpr int KNN_MAX_FAST_DIM = 16;
+        constexpr int KNN_MAX_FAST_DIM = 128;  // 1..16: knn_scan.cuh, 17..128: knn_scan_hd.cuh
+        constexpr int KNN_MAX_REG_DIM = 16;
         constexpr size_t EXACT_PAIR_BUDGET = (size_t)1 << 25;
 
         __device__ __forceinline__ float inff()
@@ -854,19 +856,50 @@ namespace omplcu
         }
     }  // namespace
 
+    namespace
+    {
+        // action 0: report resident CTAs per SM; action 1: launch
+        template <int L>
+        void hd_action(int action, int D, int rowf, const ScanParams *P, unsigned grid, cudaStream_t s, int *occ)
+        {
+            const size_t smem = hd_smem_bytes(D, L);
+            CUDA_CHECK(cudaFuncSetAttribute(knn_scan_hd_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)smem));
+            if (action == 0)
+                CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(occ, knn_scan_hd_kernel<L>, HD_THREADS, smem));
+            else
+                knn_scan_hd_kernel<L><<<grid, HD_THREADS, smem, s>>>(*P, D, rowf);
+        }
+
+        void hd_any(int cfg, int action, int D, int rowf, const ScanParams *P, unsigned grid, cudaStream_t s, int *occ)
+        {
+            if (cfg == 0)
+                hd_action<12>(action, D, rowf, P, grid, s, occ);
+            else if (cfg == 1)
+                hd_action<16>(action, D, rowf, P, grid, s, occ);
+            else
+                hd_action<42>(action, D, rowf, P, grid, s, occ);
+        }
+    }  // namespace
+
     // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
     void NNIndex::knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
                            double *d_dists, cudaStream_t s)
     {
         const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
         const int RQ = cfg == 2 ? 2 : 4, L = cfg == 0 ? 12 : (cfg == 1 ? 16 : 42);
-        const size_t QT = (size_t)SCAN_THREADS * RQ;
+        const bool hd = D_ > KNN_MAX_REG_DIM;  // register-tiled kernel of knn_scan_hd.cuh
+        const size_t QT = hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
+        const size_t PT = hd ? (size_t)HD_PT : (size_t)SCAN_PT;
         const size_t qtiles = (nq + QT - 1) / QT;
         const uint32_t qpad = (uint32_t)(qtiles * QT);
-        const unsigned long long U = (nslots_ + SCAN_PT - 1) / SCAN_PT;
+        const unsigned long long U = (nslots_ + PT - 1) / PT;
         const unsigned long long TU = qtiles * U;
         int resident = 1;  // CTAs per SM: one persistent CTA per resident slot
-        scan_any(cfg, D_, 0, nullptr, 0, s, &resident);
+        if (hd)
+            hd_any(cfg, 0, D_, rowf_, nullptr, 0, s, &resident);
+        else
+            scan_any(cfg, D_, 0, nullptr, 0, s, &resident);
         resident = std::max(resident, 1);
         if (scan_ctas_per_sm_ > 0)
             resident = std::min(resident, scan_ctas_per_sm_);
@@ -911,7 +944,7 @@ namespace omplcu
         // and skips most of the early insertions.  Self-verifying: the re-rank's band check
         // does not care where a list's threshold came from.
         const uint32_t nsample = 4096;
-        if (sample_thr_ && nslots_ >= 16 * (size_t)nsample && L <= 64)
+        if (sample_thr_ && !hd && nslots_ >= 16 * (size_t)nsample && L <= 64)
         {
             const int rw = rowf_ / 4;
             sample_thr_buf_.reserve(qpad + (size_t)nsample * rowf_);
@@ -929,7 +962,10 @@ namespace omplcu
         P.units = U;
         P.total_units = TU;
         P.smax = smax;
-        scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
+        if (hd)
+            hd_any(cfg, 1, D_, rowf_, &P, (unsigned)G, s, nullptr);
+        else
+            scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         if (profile_)

@@ -139,15 +139,16 @@ def m4(n=100_000):
         emit(workload=f"M4 chain nearestR(r={rad}), {links} links", n_states=n, n_queries=len(q),
              queries_per_s=len(q) / t, ms=t * 1e3, mean_neighbours=float(offs[-1]) / len(q),
              parity_query_ids_equal=bool(list(got) == list(want[0])), neighbours_of_query_3=len(want[0]))
-    # plain L2 at d = 100 (SURVEY: "separately, plain L2 at d = 100"): exact path, no tensor-core variant yet
+    # plain L2 at d = 100 (SURVEY: "separately, plain L2 at d = 100"): register-tiled FP32 scan (knn_scan_hd.cuh)
     d = 100
-    pts, qs = helpers.uniform_points(4, n, d), helpers.uniform_points(5, 4096, d)
+    pts, qs = helpers.uniform_points(4, n, d), helpers.uniform_points(5, 65536, d)
     nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
     nn.add_rows(pts)
     t, (ids, dd) = timed(lambda: nn.nearestKBatch(qs, 10), reps=1)
     oi, od = orc.knn(orc.space_rv(d), pts, qs[:16], 10, nthreads=CORES)
-    emit(workload="M4 plain L2, d=100, k=10 (exact path)", n_states=n, n_queries=len(qs), queries_per_s=len(qs) / t,
-         ms=t * 1e3, ids_equal=bool((ids[:16] == oi).all()), dists_equal=bool((dd[:16] == od).all()))
+    emit(workload="M4 plain L2, d=100, k=10 (high-dimensional scan)", n_states=n, n_queries=len(qs), queries_per_s=len(qs) / t,
+         ms=t * 1e3, fallbacks=nn.stat("last_fallbacks"), scan_path=nn.stat("last_path") == 1,
+         ids_equal=bool((ids[:16] == oi).all()), dists_equal=bool((dd[:16] == od).all()))
 
 
 if __name__ == "__main__":

@@ -55,6 +55,43 @@ def test_scan_path_dims_and_k(gpu, d, k):
     assert nn.stat("last_path") == 1
 
 
+@pytest.mark.parametrize("d", [17, 31, 64, 100, 128])
+@pytest.mark.parametrize("k", [1, 10, 36])
+def test_high_dimensional_scan_path(gpu, d, k):
+    """17 <= d <= 128: the register-tiled scan of knn_scan_hd.cuh feeds the same exact re-rank."""
+    n, nq = 20000 + d, 333  # neither a multiple of the tile sizes
+    pts, qs = helpers.uniform_points(d, n, d), helpers.uniform_points(200 + d, nq, d)
+    qs[:40] = pts[:40]  # exact hits
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts[:15000])
+    nn.add_rows(pts[15000:])  # two appends: filter rows are extended, not rebuilt
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), qs, k)
+    assert nn.stat("last_path") == 1
+    assert nn.stat("last_fallbacks") <= nq // 10
+
+
+def test_high_dimensional_scan_ties_removal_and_scales(gpu):
+    d = 100
+    r = helpers.rng(12)
+    pts = helpers.with_duplicates(r.random((12000, d)), 3, frac=0.2)
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    qs = np.vstack([pts[:200], r.random((200, d))])
+    ids, dd = _check_knn(nn, orc.space_rv(d), pts, np.arange(len(pts)), qs, 10)
+    ties = dd[:, 1:] == dd[:, :-1]
+    assert ties.any() and (ids[:, 1:][ties] > ids[:, :-1][ties]).all()
+    # tombstones: removed points never come back
+    for i in range(0, 2000, 2):
+        assert nn.remove_id(i)
+    live = np.setdiff1d(np.arange(len(pts)), np.arange(0, 2000, 2))
+    _check_knn(nn, orc.space_rv(d), pts[live], live, qs[:128], 10)
+    # far from the origin with a tiny spread: the band check must send what it cannot prove to the exact path
+    far = 1e5 + r.random((8000, d)) * 1e-4
+    nn2 = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn2.add_rows(far)
+    _check_knn(nn2, orc.space_rv(d), far, np.arange(len(far)), far[:64] + 1e-9, 10)
+
+
 @pytest.mark.parametrize("seed", [1, 2, 3])
 def test_scan_path_rv7_seeds(gpu, seed):
     n, nq = 200000, 2048
@@ -135,7 +172,7 @@ def test_full_size_sampled_against_oracle(gpu):
 
 
 # ---------------------------------------------------------------- exact path: every space, any k
-@pytest.mark.parametrize("space", ["so2", "so3", "se2", "se3", "chain", "rv40"])
+@pytest.mark.parametrize("space", ["so2", "so3", "se2", "se3", "chain", "rv40_forced"])
 def test_exact_path_spaces(gpu, space):
     n, nq, k = 1500, 200, 12
     if space == "so2":
@@ -151,10 +188,13 @@ def test_exact_path_spaces(gpu, space):
         sp, osp = ob.KinematicChainSpace(10, 0.1), orc.space_chain(10, 0.1)
         pts = helpers.rng(1).uniform(-np.pi, np.pi, (n, 10))
     else:
+        # every RealVector dimension up to the stride limit has a scan kernel now: force the sort path
         sp, osp, pts = ob.RealVectorStateSpace(40), orc.space_rv(40), helpers.uniform_points(1, n, 40)
     qs = np.vstack([pts[: nq // 2], pts[::-1][: nq // 2] * 0.999])
     nn = ob.NearestNeighborsCUDA(sp)
     nn.add_rows(pts)
+    if space == "rv40_forced":
+        nn.set_option("force_exact", 1)
     ids, d = nn.nearestKBatch(qs, k)
     oi, od = orc.knn(osp, pts, qs, k, nthreads=8)
     if space in ("so3", "se3", "chain"):
