@@ -26,6 +26,7 @@ namespace omplcu
         constexpr int KNN_MAX_FAST_DIM = 128;  // 1..16: knn_scan.cuh, 17..128: knn_scan_hd.cuh
         constexpr int KNN_MAX_REG_DIM = 16;
         constexpr size_t EXACT_PAIR_BUDGET = (size_t)1 << 25;
+        constexpr size_t RADIUS_PAIR_BUDGET = (size_t)1 << 27;  // 8 B per pair: 1 GB of distances per batch
 
         __device__ __forceinline__ float inff()
         {
@@ -316,9 +317,50 @@ namespace omplcu
 
         // ---- exact path ----
         // keys[b][slot] = exact distance(point slot, query sel[b]) (+inf for dead slots)
-        __global__ void dist_rows_kernel(SpaceDesc sp, const double *pts, const uint8_t *alive, size_t nslots,
-                                         const double *q, const uint32_t *sel, size_t b0, size_t nb, double *keys,
-                                         uint32_t *vals)
+        // Distance between slot `slot` and query `qi` for the exact-path kernels.  For the kinematic
+        // chain metric (demos/KinematicChain.h:105-121) the cos / sin of the cumulative joint angles
+        // depend on one state only, so they are tabulated per state (chain_trig_kernel) and the
+        // per-pair work is the reference's running sums on tabulated values: same operations on the
+        // same operands in the same order, hence the same bits, without 4 * links libm calls per pair.
+        struct PairMetric
+        {
+            SpaceDesc sp;
+            const double *pts, *q;
+            const double *ptrig, *qtrig;  // [slot][2*links] and [query][2*links], or nullptr
+            __device__ __forceinline__ double operator()(size_t slot, size_t qi) const
+            {
+                if (ptrig == nullptr)
+                    return space_distance(sp, pts + slot * sp.stride, q + qi * sp.stride);
+                const int d = sp.comp[0].dim;
+                const double *a = ptrig + slot * 2 * d, *b = qtrig + qi * 2 * d;
+                double dx = 0., dy = 0., dist = 0.;
+                for (int i = 0; i < d; ++i)
+                {
+                    dx = dadd(dx, dsub(a[2 * i], b[2 * i]));
+                    dy = dadd(dy, dsub(a[2 * i + 1], b[2 * i + 1]));
+                    dist = dadd(dist, dsqrt(dadd(dmul(dx, dx), dmul(dy, dy))));
+                }
+                return dmul(dist, sp.comp[0].param);
+            }
+        };
+
+        // out[row][2i] = cos(theta_i), out[row][2i+1] = sin(theta_i), theta_i = s_0 + ... + s_i
+        __global__ void chain_trig_kernel(const double *rows, size_t n, int d, double *out)
+        {
+            size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (r >= n)
+                return;
+            double theta = 0.;
+            for (int i = 0; i < d; ++i)
+            {
+                theta = dadd(theta, rows[r * d + i]);
+                out[r * 2 * d + 2 * i] = omplcu_cos(theta);
+                out[r * 2 * d + 2 * i + 1] = omplcu_sin(theta);
+            }
+        }
+
+        __global__ void dist_rows_kernel(PairMetric pm, const uint8_t *alive, size_t nslots, const uint32_t *sel,
+                                         size_t b0, size_t nb, double *keys, uint32_t *vals)
         {
             size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
             if (i >= nb * nslots)
@@ -327,7 +369,7 @@ namespace omplcu
             size_t qi = sel ? sel[b0 + b] : (b0 + b);
             double d = __longlong_as_double(0x7ff0000000000000ll);
             if (alive[slot])
-                d = space_distance(sp, pts + slot * sp.stride, q + qi * sp.stride);
+                d = pm(slot, qi);
             keys[i] = d;
             vals[i] = (uint32_t)slot;
         }
@@ -346,6 +388,107 @@ namespace omplcu
                 out_dists[qi * kstride + r] = keys[b * nslots + r];
         }
 
+        // ---- exact path, large k: distance bound from a sample, collect, sort only what passed ----
+        // sd[b][j] = exact distance from query b to every step-th slot (dead slots: +inf)
+        __global__ void sample_dist_kernel(PairMetric pm, const uint8_t *alive, size_t step, uint32_t m,
+                                           const uint32_t *sel, size_t b0, size_t nb, double *sd)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * m)
+                return;
+            const size_t b = i / m, slot = (i % m) * step;
+            const size_t qi = sel ? sel[b0 + b] : (b0 + b);
+            double d = __longlong_as_double(0x7ff0000000000000ll);
+            if (alive[slot])
+                d = pm(slot, qi);
+            sd[i] = d;
+        }
+
+        // bound[b] = the R-th smallest (1-based) of the m sample distances of query b: at least R sample
+        // points lie within it.  One warp per query; distances are >= 0 (or +inf), so their bit patterns
+        // order like unsigned integers and the value is found by bisection on the bits.
+        __global__ void __launch_bounds__(128) rank_select_kernel(const double *sd, uint32_t m, size_t nb, uint32_t R,
+                                                                  double *bound)
+        {
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const unsigned long long *v = reinterpret_cast<const unsigned long long *>(sd) + b * m;
+            unsigned long long lo = 0, hi = 0x7ff0000000000000ull;  // answer in [lo, hi]
+            while (lo < hi)
+            {
+                const unsigned long long mid = lo + ((hi - lo) >> 1);
+                unsigned c = 0;
+                for (uint32_t j = lane; j < m; j += 32)
+                    c += v[j] <= mid ? 1u : 0u;
+                c = __reduce_add_sync(0xffffffffu, c);
+                if (c >= R)
+                    hi = mid;
+                else
+                    lo = mid + 1;
+            }
+            if (lane == 0)
+                bound[b] = __longlong_as_double((long long)lo);
+        }
+
+        // every live slot within bound[b] of query b is appended to the query's segment [b*cap, b*cap+cap)
+        __global__ void collect_kernel(PairMetric pm, const uint8_t *alive, size_t nslots, const uint32_t *sel,
+                                       size_t b0, size_t nb, const double *bound, uint32_t cap, double *keys,
+                                       uint32_t *vals, uint32_t *cnt)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * nslots)
+                return;
+            const size_t b = i / nslots, slot = i % nslots;
+            if (!alive[slot])
+                return;
+            const size_t qi = sel ? sel[b0 + b] : (b0 + b);
+            const double d = pm(slot, qi);
+            if (d <= bound[b])
+            {
+                const uint32_t pos = atomicAdd(&cnt[b], 1u);
+                if (pos < cap)
+                {
+                    keys[b * cap + pos] = d;
+                    vals[b * cap + pos] = (uint32_t)slot;
+                }
+            }
+        }
+
+        __global__ void collect_segments_kernel(const uint32_t *cnt, uint32_t cap, size_t nb, int *beg, int *end)
+        {
+            size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (b >= nb)
+                return;
+            beg[b] = (int)(b * cap);
+            end[b] = (int)(b * cap + min(cnt[b], cap));
+        }
+
+        // first kk of every sorted segment; segments that overflowed or came up short are queued for
+        // the full sort (redo holds query indices)
+        __global__ void collect_emit_kernel(const double *keys, const uint32_t *vals, const uint32_t *cnt,
+                                            uint32_t cap, const uint64_t *slot_ids, const uint32_t *sel, size_t b0,
+                                            size_t nb, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
+                                            double *out_dists, uint32_t *redo, unsigned *redo_count)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * kk)
+                return;
+            const size_t b = i / kk, r = i % kk;
+            const size_t qi = sel ? sel[b0 + b] : (b0 + b);
+            const uint32_t c = cnt[b];
+            if (c > cap || c < kk)
+            {
+                if (r == 0)
+                    redo[atomicAdd(redo_count, 1u)] = (uint32_t)qi;
+                return;
+            }
+            out_ids[qi * kstride + r] = slot_ids[vals[b * cap + r]];
+            if (out_dists)
+                out_dists[qi * kstride + r] = keys[b * cap + r];
+        }
+
         // pad columns [kk, kstride) with OMPLCU_ID_NONE / +inf
         __global__ void pad_rows_kernel(uint64_t *ids, double *dists, size_t nq, uint32_t kk, uint32_t kstride)
         {
@@ -359,41 +502,49 @@ namespace omplcu
                 dists[qi * kstride + r] = __longlong_as_double(0x7ff0000000000000ll);
         }
 
-        // radius: count of sorted keys <= r per row (binary search), then gather
-        __global__ void radius_count_kernel(const double *keys, size_t nslots, const double *radii, size_t b0,
-                                            size_t nb, size_t nlive_cap, uint32_t *counts)
+        // radius: exact distance of every (query, slot) pair; pairs within the radius are counted per
+        // query as they are written (dead slots carry +inf and never count)
+        __global__ void radius_dist_kernel(PairMetric pm, const uint8_t *alive, size_t nslots, size_t b0, size_t nb,
+                                           const double *radii, double *keys, uint32_t *counts)
         {
-            size_t b = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-            if (b >= nb)
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * nslots)
                 return;
-            const double r = radii[b0 + b];
-            const double *row = keys + b * nslots;
-            size_t lo = 0, hi = nlive_cap;  // dead slots (+inf keys) sort last and are never counted
-            while (lo < hi)
-            {
-                size_t mid = (lo + hi) / 2;
-                if (row[mid] <= r)
-                    lo = mid + 1;
-                else
-                    hi = mid;
-            }
-            counts[b] = (uint32_t)lo;
+            const size_t b = i / nslots, slot = i % nslots;
+            double d = __longlong_as_double(0x7ff0000000000000ll);
+            if (alive[slot])
+                d = pm(slot, b0 + b);
+            keys[i] = d;
+            if (d <= radii[b0 + b] && d < __longlong_as_double(0x7ff0000000000000ll))
+                atomicAdd(&counts[b], 1u);
         }
 
-        __global__ void radius_gather_kernel(const double *keys, const uint32_t *vals, size_t nslots,
-                                             const uint64_t *slot_ids, const uint32_t *counts,
-                                             const unsigned long long *offs, size_t nb, uint64_t *out_ids,
-                                             double *out_dists)
+        // the counted pairs, copied into the query's segment (any order: the sort by slot follows)
+        __global__ void radius_compact_kernel(const double *keys, size_t nslots, size_t b0, size_t nb,
+                                              const double *radii, const unsigned long long *offs, uint32_t *fill,
+                                              double *out_keys, uint32_t *out_vals)
         {
-            size_t b = blockIdx.y;
-            if (b >= nb)
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nb * nslots)
                 return;
-            for (size_t r = blockIdx.x * (size_t)blockDim.x + threadIdx.x; r < counts[b];
-                 r += (size_t)gridDim.x * blockDim.x)
+            const size_t b = i / nslots, slot = i % nslots;
+            const double d = keys[i];
+            if (d <= radii[b0 + b] && d < __longlong_as_double(0x7ff0000000000000ll))
             {
-                out_ids[offs[b] + r] = slot_ids[vals[b * nslots + r]];
-                out_dists[offs[b] + r] = keys[b * nslots + r];
+                const unsigned long long p = offs[b] + atomicAdd(&fill[b], 1u);
+                out_keys[p] = d;
+                out_vals[p] = (uint32_t)slot;
             }
+        }
+
+        __global__ void radius_emit_kernel(const double *keys, const uint32_t *vals, const uint64_t *slot_ids,
+                                           size_t tot, uint64_t *out_ids, double *out_dists)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= tot)
+                return;
+            out_ids[i] = slot_ids[vals[i]];
+            out_dists[i] = keys[i];
         }
 
         // ---- merge of per-shard partial results (one warp per query) ----
@@ -632,6 +783,7 @@ namespace omplcu
         }
         const size_t old_slots = nslots_;
         nslots_ = live.size();
+        trig_rows_ = 0;  // slots moved: the chain trig table is rebuilt on the next query
         h_ids_.swap(nids);
         h_alive_.assign(nslots_, 1);
         if (fast_space_)
@@ -666,6 +818,7 @@ namespace omplcu
         }
         have_center_ = false;
         nslots_ = nlive_ = 0;
+        trig_rows_ = 0;
         h_ids_.clear();
         h_alive_.clear();
         // ids keep increasing across clear() so stale ids can never alias new points
@@ -705,6 +858,8 @@ namespace omplcu
             force_exact_ = v != 0;
         else if (!strcmp(key, "sample_thresholds"))
             sample_thr_ = v != 0;
+        else if (!strcmp(key, "collect"))
+            collect_ = v != 0;
         else if (!strcmp(key, "scan_ctas_per_sm"))
             scan_ctas_per_sm_ = (int)v;  // 0 = as many as fit
         else if (!strcmp(key, "profile"))
@@ -737,6 +892,8 @@ namespace omplcu
             return (long)nslots_;
         if (!strcmp(key, "fast_space"))
             return fast_space_ ? 1 : 0;
+        if (!strcmp(key, "last_collect_redo"))
+            return last_collect_redo_;
         throw Error(OMPLCU_ERR_INVALID, std::string("unknown stat ") + key);
     }
 
@@ -993,8 +1150,116 @@ namespace omplcu
             knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }
 
+    // Large index (>= 32K slots), any k and any metric (FMT*'s k ~ 2100 of 100K; SE3 / chain kNN): sorting
+    // every slot per query is the cost of the full path.  Here an exact distance bound per query comes from a strided sample (the R-th
+    // smallest of m sample distances, R chosen 4 sigma above k*m/n), only slots within the bound are
+    // kept (the same exact FP64 distances, any metric), and only those are sorted: by slot, then
+    // stably by distance, so ties stay in insertion order.  A query whose bound caught fewer than k
+    // or more than `cap` slots goes to the full sort.  Returns false if the sample cannot help.
+    // Chain metric only: bring the per-slot trig table up to date and tabulate the queries.
+    // Returns true if the exact-path kernels should use the tables.
+    bool NNIndex::prepare_chain_tables(const double *d_q, size_t nq, cudaStream_t s)
+    {
+        if (sp_.compound || sp_.ncomp != 1 || sp_.comp[0].type != OMPLCU_CHAIN)
+            return false;
+        const int d = sp_.comp[0].dim;
+        trig_.reserve(std::max<size_t>(nslots_, 1) * 2 * d, true, s);
+        if (trig_rows_ < nslots_)
+        {
+            chain_trig_kernel<<<nblk(nslots_ - trig_rows_, 128), 128, 0, s>>>(pts64_.p + trig_rows_ * d,
+                                                                               nslots_ - trig_rows_, d,
+                                                                               trig_.p + trig_rows_ * 2 * d);
+            trig_rows_ = nslots_;
+            launches_++;
+        }
+        qtrig_.reserve(std::max<size_t>(nq, 1) * 2 * d);
+        chain_trig_kernel<<<nblk(nq, 128), 128, 0, s>>>(d_q, nq, d, qtrig_.p);
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+        return true;
+    }
+
+    bool NNIndex::knn_exact_collect(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                                    uint64_t *d_ids, double *d_dists, cudaStream_t s)
+    {
+        const uint32_t m = 1024;
+        if (!collect_ || nslots_ < 32 * (size_t)m || nlive_ == 0 || nslots_ >= ((size_t)1 << 31))
+            return false;
+        const double mean = (double)kk / (double)nlive_ * m;
+        const uint32_t R = (uint32_t)std::ceil(mean + 4.0 * std::sqrt(mean) + 6.0);
+        if (R > m / 4)
+            return false;
+        const size_t step = nslots_ / m;
+        const uint32_t cap = (uint32_t)(1.6 * (double)R / m * (double)nslots_) + 256;
+        if (cap < kk)
+            return false;
+        const size_t budget = (size_t)1 << 26;
+        const size_t nb_max = std::max<size_t>(1, std::min(nsel, budget / cap));
+        ex_keys_.reserve(nb_max * cap);
+        ex_keys2_.reserve(nb_max * cap);
+        ex_vals_.reserve(nb_max * cap);
+        ex_vals2_.reserve(nb_max * cap);
+        ex_offs_.reserve(2 * nb_max + 2);
+        col_sd_.reserve(nb_max * m);
+        col_bound_.reserve(nb_max);
+        col_cnt_.reserve(nb_max);
+        col_redo_.reserve(nsel);
+        CUDA_CHECK(cudaMemsetAsync(counters_.p + 1, 0, sizeof(unsigned), s));
+        const bool tables = prepare_chain_tables(d_q, exact_nq_, s);
+        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
+        int *beg = ex_offs_.p, *end = ex_offs_.p + nb_max + 1;
+        for (size_t b0 = 0; b0 < nsel; b0 += nb_max)
+        {
+            const size_t nb = std::min(nb_max, nsel - b0);
+            const size_t items = nb * cap;
+            REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
+            CUDA_CHECK(cudaMemsetAsync(col_cnt_.p, 0, nb * sizeof(uint32_t), s));
+            sample_dist_kernel<<<nblk(nb * m, 256), 256, 0, s>>>(pm, alive_.p, step, m, d_sel, b0, nb, col_sd_.p);
+            rank_select_kernel<<<nblk(nb, 4), 128, 0, s>>>(col_sd_.p, m, nb, R, col_bound_.p);
+            collect_kernel<<<nblk(nb * nslots_, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, col_bound_.p,
+                                                                   cap, ex_keys_.p, ex_vals_.p, col_cnt_.p);
+            collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(col_cnt_.p, cap, nb, beg, end);
+            CUDA_CHECK(cudaGetLastError());
+            size_t tmp = 0, tmp2 = 0;
+            // pass 1: by slot (payload: distance); pass 2: stable by distance (payload: slot)
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_vals_.p, ex_vals2_.p, ex_keys_.p,
+                                                                ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, ex_keys2_.p, ex_keys_.p, ex_vals2_.p,
+                                                                ex_vals_.p, (int)items, (int)nb, beg, end, 0, 64, s));
+            cub_tmp_.reserve(std::max(tmp, tmp2));
+            tmp = tmp2 = cub_tmp_.cap;
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_vals_.p, ex_vals2_.p, ex_keys_.p,
+                                                                ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp2, ex_keys2_.p, ex_keys_.p,
+                                                                ex_vals2_.p, ex_vals_.p, (int)items, (int)nb, beg, end,
+                                                                0, 64, s));
+            collect_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(ex_keys_.p, ex_vals_.p, col_cnt_.p, cap, ids_.p,
+                                                                   d_sel, b0, nb, (uint32_t)kk, (uint32_t)kstride,
+                                                                   d_ids, d_dists, col_redo_.p, counters_.p + 1);
+            CUDA_CHECK(cudaGetLastError());
+            launches_ += 16;
+        }
+        unsigned nredo = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&nredo, counters_.p + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        last_collect_redo_ = nredo;
+        if (nredo)
+            knn_exact_sort(d_q, col_redo_.p, nredo, kk, kstride, d_ids, d_dists, s);
+        return true;
+    }
+
     void NNIndex::knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                             uint64_t *d_ids, double *d_dists, cudaStream_t s)
+    {
+        if (nsel == 0 || nslots_ == 0)
+            return;
+        if (knn_exact_collect(d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s))
+            return;
+        knn_exact_sort(d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s);
+    }
+
+    void NNIndex::knn_exact_sort(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                                 uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         if (nsel == 0 || nslots_ == 0)
             return;
@@ -1010,13 +1275,15 @@ namespace omplcu
             offs[b] = (int)(b * nslots_);
         CUDA_CHECK(cudaMemcpyAsync(ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
+        const bool tables = prepare_chain_tables(d_q, exact_nq_, s);
+        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
         for (size_t b0 = 0; b0 < nsel; b0 += nb_max)
         {
             const size_t nb = std::min(nb_max, nsel - b0);
             const size_t items = nb * nslots_;
             REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
-            dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(sp_, pts64_.p, alive_.p, nslots_, d_q, d_sel, b0, nb,
-                                                              ex_keys_.p, ex_vals_.p);
+            dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, ex_keys_.p,
+                                                              ex_vals_.p);
             launches_++;
             CUDA_CHECK(cudaGetLastError());
             size_t tmp = 0;
@@ -1058,6 +1325,7 @@ namespace omplcu
         REQUIRE(k < ((size_t)1 << 31), "omplcu_nn_knn: k too large");
         const size_t kk = std::min(k, nlive_);
         last_fallbacks_ = 0;
+        exact_nq_ = nq;
         if (kk > 0)
         {
             if (fast_eligible(kk))
@@ -1114,8 +1382,10 @@ namespace omplcu
                 counts[i] = (uint32_t)kk;
     }
 
-    // NearestNeighborsLinear::nearestR (NearestNeighborsLinear.h:135-142): all
-    // elements with distance <= radius (inclusive), sorted; via the exact path.
+    // NearestNeighborsLinear::nearestR (NearestNeighborsLinear.h:135-142): all elements with
+    // distance <= radius (inclusive), sorted by (distance, insertion order).  Exact FP64 distances
+    // for every (query, slot) pair; the pairs within the radius are counted while the distances are
+    // written, copied out per query, and only they are sorted (by slot, then stably by distance).
     void NNIndex::radius_host(const double *q, size_t nq, const double *radii, uint64_t **ids, double **dists,
                               uint64_t *offsets)
     {
@@ -1131,96 +1401,99 @@ namespace omplcu
         DeviceGuard g(device_);
         cudaStream_t s = stream_;
         const size_t st = (size_t)sp_.stride;
-        std::vector<uint64_t> all_ids;
-        std::vector<double> all_d;
+        size_t total = 0;  // neighbours found so far (all batches), kept on the device in rad_ids_/rad_d_
         if (nslots_ > 0 && nlive_ > 0)
         {
             REQUIRE(nslots_ < ((size_t)1 << 31), "radius: too many slots");
             q_stage_.reserve(nq * st);
-            DevBuf<double> d_r;
-            d_r.reserve(nq);
+            rad_r_.reserve(nq);
             CUDA_CHECK(cudaMemcpyAsync(q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, s));
-            CUDA_CHECK(cudaMemcpyAsync(d_r.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
-            size_t nb_max = std::max<size_t>(1, std::min(nq, EXACT_PAIR_BUDGET / nslots_));
+            CUDA_CHECK(cudaMemcpyAsync(rad_r_.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
+            const size_t nb_max = std::max<size_t>(1, std::min(nq, RADIUS_PAIR_BUDGET / nslots_));
             ex_keys_.reserve(nb_max * nslots_);
-            ex_keys2_.reserve(nb_max * nslots_);
-            ex_vals_.reserve(nb_max * nslots_);
-            ex_vals2_.reserve(nb_max * nslots_);
+            col_cnt_.reserve(2 * nb_max);
+            rad_off_.reserve(nb_max);
             ex_offs_.reserve(nb_max + 1);
-            DevBuf<uint32_t> d_cnt;
-            DevBuf<unsigned long long> d_off;
-            d_cnt.reserve(nb_max);
-            d_off.reserve(nb_max);
-            std::vector<int> offs(nb_max + 1);
-            for (size_t b = 0; b <= nb_max; ++b)
-                offs[b] = (int)(b * nslots_);
-            CUDA_CHECK(
-                cudaMemcpyAsync(ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
             std::vector<uint32_t> cnt(nb_max);
             std::vector<unsigned long long> boff(nb_max);
+            std::vector<int> seg(nb_max + 1);
+            const bool tables = prepare_chain_tables(q_stage_.p, nq, s);
+            const PairMetric pm{sp_, pts64_.p, q_stage_.p, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
             for (size_t b0 = 0; b0 < nq; b0 += nb_max)
             {
                 const size_t nb = std::min(nb_max, nq - b0);
                 const size_t items = nb * nslots_;
-                dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(sp_, pts64_.p, alive_.p, nslots_, q_stage_.p,
-                                                                  nullptr, b0, nb, ex_keys_.p, ex_vals_.p);
-                size_t tmp = 0;
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
-                                                                    ex_vals2_.p, (int)items, (int)nb, ex_offs_.p,
-                                                                    ex_offs_.p + 1, 0, 64, s));
-                cub_tmp_.reserve(tmp);
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p,
-                                                                    ex_vals_.p, ex_vals2_.p, (int)items, (int)nb,
-                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
-                radius_count_kernel<<<nblk(nb, 128), 128, 0, s>>>(ex_keys2_.p, nslots_, d_r.p, b0, nb, nlive_,
-                                                                  d_cnt.p);
-                launches_ += 10;
-                CUDA_CHECK(cudaMemcpyAsync(cnt.data(), d_cnt.p, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+                uint32_t *d_cnt = col_cnt_.p, *d_fill = col_cnt_.p + nb_max;
+                CUDA_CHECK(cudaMemsetAsync(col_cnt_.p, 0, 2 * nb_max * sizeof(uint32_t), s));
+                radius_dist_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, b0, nb, rad_r_.p, ex_keys_.p,
+                                                                    d_cnt);
+                launches_++;
+                CUDA_CHECK(cudaGetLastError());
+                CUDA_CHECK(cudaMemcpyAsync(cnt.data(), d_cnt, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
                 CUDA_CHECK(cudaStreamSynchronize(s));
                 unsigned long long tot = 0;
                 for (size_t b = 0; b < nb; ++b)
                 {
                     boff[b] = tot;
+                    seg[b] = (int)tot;
                     tot += cnt[b];
                     offsets[b0 + b + 1] = offsets[b0 + b] + cnt[b];
                 }
-                if (tot)
-                {
-                    DevBuf<uint64_t> d_oi;
-                    DevBuf<double> d_od;
-                    d_oi.reserve(tot);
-                    d_od.reserve(tot);
-                    CUDA_CHECK(cudaMemcpyAsync(d_off.p, boff.data(), nb * sizeof(unsigned long long),
-                                               cudaMemcpyHostToDevice, s));
-                    dim3 grid(std::max<unsigned>(1, std::min<unsigned>(64, nblk(nlive_, 256))), (unsigned)nb);
-                    radius_gather_kernel<<<grid, 256, 0, s>>>(ex_keys2_.p, ex_vals2_.p, nslots_, ids_.p, d_cnt.p,
-                                                              d_off.p, nb, d_oi.p, d_od.p);
-                    launches_++;
-                    CUDA_CHECK(cudaGetLastError());
-                    const size_t base = all_ids.size();
-                    all_ids.resize(base + tot);
-                    all_d.resize(base + tot);
-                    CUDA_CHECK(cudaMemcpyAsync(all_ids.data() + base, d_oi.p, tot * sizeof(uint64_t),
-                                               cudaMemcpyDeviceToHost, s));
-                    CUDA_CHECK(cudaMemcpyAsync(all_d.data() + base, d_od.p, tot * sizeof(double),
-                                               cudaMemcpyDeviceToHost, s));
-                    CUDA_CHECK(cudaStreamSynchronize(s));
-                }
+                seg[nb] = (int)tot;
+                if (tot == 0)
+                    continue;
+                REQUIRE(tot < ((unsigned long long)1 << 31), "radius: too many neighbours in one batch");
+                ex_keys2_.reserve(tot);
+                ex_keys3_.reserve(tot);
+                ex_vals_.reserve(tot);
+                ex_vals2_.reserve(tot);
+                rad_ids_.reserve(total + tot, true, s);
+                rad_d_.reserve(total + tot, true, s);
+                CUDA_CHECK(cudaMemcpyAsync(rad_off_.p, boff.data(), nb * sizeof(unsigned long long),
+                                           cudaMemcpyHostToDevice, s));
+                CUDA_CHECK(cudaMemcpyAsync(ex_offs_.p, seg.data(), (nb + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+                radius_compact_kernel<<<nblk(items, 256), 256, 0, s>>>(ex_keys_.p, nslots_, b0, nb, rad_r_.p, rad_off_.p,
+                                                                       d_fill, ex_keys2_.p, ex_vals_.p);
+                // by slot (payload distance), then stably by distance (payload slot)
+                size_t tmp = 0, tmp2 = 0;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_vals_.p, ex_vals2_.p, ex_keys2_.p,
+                                                                    ex_keys3_.p, (int)tot, (int)nb, ex_offs_.p,
+                                                                    ex_offs_.p + 1, 0, 32, s));
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, ex_keys3_.p, ex_keys2_.p,
+                                                                    ex_vals2_.p, ex_vals_.p, (int)tot, (int)nb,
+                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
+                cub_tmp_.reserve(std::max(tmp, tmp2));
+                tmp = tmp2 = cub_tmp_.cap;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_vals_.p, ex_vals2_.p,
+                                                                    ex_keys2_.p, ex_keys3_.p, (int)tot, (int)nb,
+                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 32, s));
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp2, ex_keys3_.p, ex_keys2_.p,
+                                                                    ex_vals2_.p, ex_vals_.p, (int)tot, (int)nb,
+                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
+                radius_emit_kernel<<<nblk(tot, 256), 256, 0, s>>>(ex_keys2_.p, ex_vals_.p, ids_.p, tot,
+                                                                  rad_ids_.p + total, rad_d_.p + total);
+                launches_ += 18;
+                CUDA_CHECK(cudaGetLastError());
+                total += tot;
             }
         }
         else
             for (size_t i = 0; i < nq; ++i)
                 offsets[i + 1] = 0;
-        const size_t tot = all_ids.size();
-        *ids = (uint64_t *)malloc(std::max<size_t>(tot, 1) * sizeof(uint64_t));
+        *ids = (uint64_t *)malloc(std::max<size_t>(total, 1) * sizeof(uint64_t));
         REQUIRE(*ids != nullptr, "omplcu_nn_radius: out of host memory");
-        memcpy(*ids, all_ids.data(), tot * sizeof(uint64_t));
         if (dists)
         {
-            *dists = (double *)malloc(std::max<size_t>(tot, 1) * sizeof(double));
+            *dists = (double *)malloc(std::max<size_t>(total, 1) * sizeof(double));
             REQUIRE(*dists != nullptr, "omplcu_nn_radius: out of host memory");
-            memcpy(*dists, all_d.data(), tot * sizeof(double));
         }
+        if (total)
+        {
+            CUDA_CHECK(cudaMemcpyAsync(*ids, rad_ids_.p, total * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+            if (dists)
+                CUDA_CHECK(cudaMemcpyAsync(*dists, rad_d_.p, total * sizeof(double), cudaMemcpyDeviceToHost, s));
+        }
+        CUDA_CHECK(cudaStreamSynchronize(s));
     }
 
     void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t part_stride,

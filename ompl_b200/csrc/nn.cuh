@@ -58,6 +58,11 @@ namespace omplcu
         void knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                       cudaStream_t s);
         // exact sort path over the selected queries (d_sel == nullptr: all nq)
+        bool prepare_chain_tables(const double *d_q, size_t nq, cudaStream_t s);
+        bool knn_exact_collect(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                               uint64_t *d_ids, double *d_dists, cudaStream_t s);
+        void knn_exact_sort(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+                            uint64_t *d_ids, double *d_dists, cudaStream_t s);
         void knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                        uint64_t *d_ids, double *d_dists, cudaStream_t s);
 
@@ -94,6 +99,13 @@ namespace omplcu
         DevBuf<double> ex_keys_, ex_keys2_;
         DevBuf<uint32_t> ex_vals_, ex_vals2_;
         DevBuf<int> ex_offs_;
+        DevBuf<double> col_sd_, col_bound_, trig_, qtrig_, rad_r_, rad_d_, ex_keys3_;
+        DevBuf<uint64_t> rad_ids_;
+        DevBuf<unsigned long long> rad_off_;
+        size_t trig_rows_ = 0, exact_nq_ = 0;
+        DevBuf<uint32_t> col_cnt_, col_redo_;
+        bool collect_ = true;
+        long last_collect_redo_ = 0;
         DevBuf<unsigned char> cub_tmp_;
 
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;

@@ -208,6 +208,55 @@ def test_exact_path_spaces(gpu, space):
     assert nn.stat("last_path") == 2
 
 
+def test_exact_collect_path_large_index(gpu):
+    """>= 32K slots: the exact path bounds each query from a sample, collects and sorts only what passed."""
+    n = 40000
+    # SE3 (acos metric), k = 10
+    sp, osp, pts = ob.SE3StateSpace(), orc.space_se3(), helpers.se3_states(3, n, 0, 1)
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.add_rows(pts)
+    qs = np.vstack([pts[:100], helpers.se3_states(4, 100, 0, 1)])
+    ids, d = nn.nearestKBatch(qs, 10)
+    oi, od = orc.knn(osp, pts, qs, 10, nthreads=8)
+    assert nn.stat("last_path") == 2 and (ids == oi).all() and np.allclose(d, od, rtol=4e-16, atol=1e-15)
+    nn.set_option("collect", 0)
+    ids2, d2 = nn.nearestKBatch(qs, 10)
+    assert (ids2 == ids).all() and (d2 == d).all()  # identical to the full sort, bit for bit
+    # RealVector(8), FMT*-sized k, 30% duplicates (ties across the bound), tombstones
+    pts = helpers.with_duplicates(helpers.uniform_points(5, n, 8), 6, frac=0.3)
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(8))
+    nn.add_rows(pts)
+    for i in range(0, 3000, 3):
+        nn.remove_id(i)
+    live = np.setdiff1d(np.arange(n), np.arange(0, 3000, 3))
+    qs = np.vstack([pts[3000:3064], helpers.uniform_points(7, 64, 8)])
+    ids, d = nn.nearestKBatch(qs, 2100)
+    oi, od = orc.knn(orc.space_rv(8), pts[live], qs, 2100, nthreads=8)
+    assert nn.stat("last_path") == 2
+    assert (ids == live.astype(np.uint64)[oi.astype(np.int64)]).all() and (d == od).all()
+    ties = d[:, 1:] == d[:, :-1]
+    assert ties.any() and (ids[:, 1:][ties] > ids[:, :-1][ties]).all()
+
+
+def test_exact_collect_redo_when_the_sample_misleads(gpu):
+    """A dense cluster the strided sample never sees: the bound catches far more than `cap` slots for queries
+    inside it, and those queries must come back through the full sort with the same answers."""
+    n = 65536
+    r = helpers.rng(17)
+    pts = np.column_stack([r.random((n, 2)) * 100.0, r.uniform(-3.0, 3.0, n)])  # SE2: x, y, theta
+    step = n // 1024
+    hidden = np.array([i for i in range(n) if i % step != 0][:30000])
+    # 30000 states in a 1e-3 box, none of them on the sample stride
+    pts[hidden] = np.column_stack([50.0 + r.random((len(hidden), 2)) * 1e-3, r.random(len(hidden)) * 1e-3])
+    nn = ob.NearestNeighborsCUDA(ob.SE2StateSpace(0.0, 100.0))
+    nn.add_rows(pts)
+    qs = np.vstack([pts[hidden[:32]], np.column_stack([r.random((32, 2)) * 100.0, r.uniform(-3.0, 3.0, 32)])])
+    ids, dd = nn.nearestKBatch(qs, 50)
+    oi, od = orc.knn(orc.space_se2(0.0, 100.0), pts, qs, 50, nthreads=8)
+    assert nn.stat("last_path") == 2 and nn.stat("last_collect_redo") >= 1
+    assert (ids == oi).all() and (dd == od).all()
+
+
 def test_large_k_uses_exact_path(gpu):
     n = 20000
     pts = helpers.uniform_points(2, n, 8)
