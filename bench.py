@@ -149,8 +149,9 @@ def run_reference_arm(args):
     pts, qs_all = make_inputs()
     cores = host_threads()
     kind, what, build_s, run = build_cpu_reference(pts)
-    # a bounded sample of the SAME 64K queries per step (about 2 s of GNAT on 16 cores)
-    per_step = min(max(cores * (2048 if kind == "reference" else 128), 64), N_QUERIES)
+    # a bounded sample of the SAME 64K queries per step: all of them for GNAT on >= 16 cores (about 3.5 s
+    # per step), a slice for fewer cores or for the Linear port
+    per_step = min(max(cores * (4096 if kind == "reference" else 128), 64), N_QUERIES)
     nblocks = N_QUERIES // per_step
 
     def block(i):
