@@ -797,6 +797,8 @@ namespace omplcu
             cudaStreamSynchronize(stream_);
             cudaStreamDestroy(stream_);
         }
+        if (copy_stream_)
+            cudaStreamDestroy(copy_stream_);
     }
 
     long Checker::get_stat(const char *key) const
@@ -1026,20 +1028,47 @@ namespace omplcu
             st_t_.reserve(n);
         if (last_state)
             st_ls_.reserve(n * st);
-        CUDA_CHECK(cudaMemcpyAsync(st_a_.p, s1, n * st * sizeof(double), cudaMemcpyHostToDevice, stream_));
-        CUDA_CHECK(cudaMemcpyAsync(st_b_.p, s2, n * st * sizeof(double), cudaMemcpyHostToDevice, stream_));
-        if (last_state)  // rows of valid segments stay as the caller initialised them: send them over first
-            CUDA_CHECK(
-                cudaMemcpyAsync(st_ls_.p, last_state, n * st * sizeof(double), cudaMemcpyHostToDevice, stream_));
-        check_motions_device(sp, st_a_.p, st_b_.p, n, st_v_.p, last_t ? st_t_.p : nullptr,
-                             last_state ? st_ls_.p : nullptr, stream_);
-        CUDA_CHECK(cudaMemcpyAsync(valid, st_v_.p, n, cudaMemcpyDeviceToHost, stream_));
-        if (last_t)
-            CUDA_CHECK(cudaMemcpyAsync(last_t, st_t_.p, n * sizeof(double), cudaMemcpyDeviceToHost, stream_));
-        if (last_state)
-            CUDA_CHECK(
-                cudaMemcpyAsync(last_state, st_ls_.p, n * st * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+        // Large batches are cut into chunks: all host->device copies are queued on a second stream up
+        // front (one event per chunk), so chunk c+1 crosses PCIe while chunk c is being checked.
+        const size_t CH = (size_t)1 << 18;
+        const size_t nch = (n + CH - 1) / CH;
+        if (copy_stream_ == nullptr)
+            CUDA_CHECK(cudaStreamCreateWithFlags(&copy_stream_, cudaStreamNonBlocking));
+        std::vector<cudaEvent_t> ev(nch);
+        for (size_t c = 0; c < nch; ++c)
+        {
+            const size_t o = c * CH, cn = std::min(CH, n - o);
+            CUDA_CHECK(cudaEventCreateWithFlags(&ev[c], cudaEventDisableTiming));
+            CUDA_CHECK(cudaMemcpyAsync(st_a_.p + o * st, s1 + o * st, cn * st * sizeof(double), cudaMemcpyHostToDevice,
+                                       copy_stream_));
+            CUDA_CHECK(cudaMemcpyAsync(st_b_.p + o * st, s2 + o * st, cn * st * sizeof(double), cudaMemcpyHostToDevice,
+                                       copy_stream_));
+            if (last_state)  // rows of valid segments stay as the caller initialised them: send them over first
+                CUDA_CHECK(cudaMemcpyAsync(st_ls_.p + o * st, last_state + o * st, cn * st * sizeof(double),
+                                           cudaMemcpyHostToDevice, copy_stream_));
+            CUDA_CHECK(cudaEventRecord(ev[c], copy_stream_));
+        }
+        long tot_states = 0, tot_eval = 0;
+        for (size_t c = 0; c < nch; ++c)
+        {
+            const size_t o = c * CH, cn = std::min(CH, n - o);
+            CUDA_CHECK(cudaStreamWaitEvent(stream_, ev[c], 0));
+            check_motions_device(sp, st_a_.p + o * st, st_b_.p + o * st, cn, st_v_.p + o,
+                                 last_t ? st_t_.p + o : nullptr, last_state ? st_ls_.p + o * st : nullptr, stream_);
+            tot_states += last_states_;
+            tot_eval += last_evaluated_;
+            CUDA_CHECK(cudaMemcpyAsync(valid + o, st_v_.p + o, cn, cudaMemcpyDeviceToHost, stream_));
+            if (last_t)
+                CUDA_CHECK(cudaMemcpyAsync(last_t + o, st_t_.p + o, cn * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+            if (last_state)
+                CUDA_CHECK(cudaMemcpyAsync(last_state + o * st, st_ls_.p + o * st, cn * st * sizeof(double),
+                                           cudaMemcpyDeviceToHost, stream_));
+        }
         CUDA_CHECK(cudaStreamSynchronize(stream_));
+        last_states_ = tot_states;  // statistics of the whole call, not of its last chunk
+        last_evaluated_ = tot_eval;
+        for (auto &e : ev)
+            cudaEventDestroy(e);
     }
 
     // ---- batched space math ----

@@ -68,7 +68,7 @@ namespace omplcu
         int device_;
         int sms_ = 148;
         CheckerDesc desc_;
-        cudaStream_t stream_ = nullptr;
+        cudaStream_t stream_ = nullptr, copy_stream_ = nullptr;
         std::mutex mu_;
         DevBuf<double> params_;
         DevBuf<float4> filt_, narrow32_;
