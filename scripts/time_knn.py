@@ -1,5 +1,5 @@
 #!/usr/bin/env python
-"""Device-resident kNN timing for one index size (shard-size experiments): python scripts/time_knn.py N [Q] [k]"""
+"""Device-resident kNN timing for one index size (shard-size experiments): python scripts/time_knn.py N [Q] [k] [d]"""
 import ctypes as C
 import os
 import sys
@@ -15,7 +15,7 @@ from ompl_b200._lib import check, lib  # noqa: E402
 n = int(sys.argv[1]) if len(sys.argv) > 1 else 125_000
 nq = int(sys.argv[2]) if len(sys.argv) > 2 else 65536
 k = int(sys.argv[3]) if len(sys.argv) > 3 else 10
-d = 7
+d = int(sys.argv[4]) if len(sys.argv) > 4 else 7
 r = np.random.default_rng(1)
 pts, qs = r.random((n, d)), r.random((nq, d))
 L = lib()
@@ -38,4 +38,4 @@ for sample in (1, 0):
         e1.synchronize()
         ts.append(e0.elapsed_time(e1))
     print(f"n={n} q={nq} k={k} sample_thr={sample}: call {min(ts[1:]):.3f} ms  scan {nn.stat('last_scan_ns') / 1e6:.3f} ms  "
-          f"fallbacks {nn.stat('last_fallbacks')}  ideal scan at 63 TFLOP/s(3d) {3 * d * n * nq / 63e12 * 1e3:.3f} ms")
+          f"fallbacks {nn.stat('last_fallbacks')}  3d-flop rate {3 * d * n * nq / max(nn.stat("last_scan_ns"), 1) / 1e3:.1f} TFLOP/s; ideal at 63 TFLOP/s {3 * d * n * nq / 63e12 * 1e3:.3f} ms")
