@@ -29,6 +29,7 @@
 #include "validity.cuh"
 
 #include <algorithm>
+#include <cstdlib>
 #include <limits>
 #include <vector>
 
@@ -955,9 +956,15 @@ namespace omplcu
         CUDA_CHECK(cudaMemcpyAsync(&total, offs_.p, sizeof(total), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaMemsetAsync(ctr_.p, 0, 2 * sizeof(unsigned long long), s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        // lanes per segment: the power of two nearest below 1.5 x the mean state count
+        // Lanes per segment.  Measured on M3 (nd ~ 72): 32 lanes 2.46 ms, 16 lanes 1.64, 8 lanes 1.25,
+        // 4 lanes 1.16 (uniform end points: most segments fail within their first few states, and a
+        // pass evaluates all its lanes); PRM-like short edges: 2.55 / 2.38 / 2.33 / 2.52.  Narrow
+        // groups waste fewer evaluations after the first failure and in the last pass of a segment,
+        // and fewer lanes repeat the per-segment setup; 8 is the best all-rounder.
         const double mean = (double)total / (double)n;
-        const int group = mean >= 24.0 ? 32 : mean >= 12.0 ? 16 : mean >= 6.0 ? 8 : 4;
+        int group = mean >= 6.0 ? 8 : 4;
+        if (const char *e = getenv("OMPLCU_MOTION_GROUP"))  // tuning experiments only
+            group = atoi(e);
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
