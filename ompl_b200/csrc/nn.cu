@@ -18,6 +18,7 @@
 
 #include "knn_scan.cuh"
 #include "knn_scan_hd.cuh"
+#include "knn_scan_tc.cuh"
 
 namespace omplcu
 {
@@ -140,7 +141,7 @@ namespace omplcu
             const float *cand_thr, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
             const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
             const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
-            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count)
+            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units)
         {
             __shared__ double s_key[4][MAXC];
             __shared__ uint32_t s_slot[4][MAXC];
@@ -195,7 +196,7 @@ namespace omplcu
             const double delta = (double)(D + 4) * 1.1102230246251565e-16;
             const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
             const double A = dk * (1.0 + delta) + rho + 1e-150;
-            const double e1 = (double)(D + 3) * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+            const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
             const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
             bool bad = !(tau64 == tau64) || !(tau64 < 1e37);  // NaN / overflow -> redo exactly
             for (uint32_t s = lane; s < smax; s += 32)
@@ -725,6 +726,7 @@ namespace omplcu
         nslots_ += n;
         nlive_ += n;
         next_seq_ += n;
+        mut_version_++;
         return first_id;
     }
 
@@ -738,6 +740,7 @@ namespace omplcu
         const size_t slot = it - h_ids_.begin();
         h_alive_[slot] = 0;
         nlive_--;
+        mut_version_++;
         mark_dead_kernel<<<1, 1, 0, stream_>>>(alive_.p, fast_space_ ? filt_.p : nullptr, rowf_, D_, slot);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
@@ -818,6 +821,7 @@ namespace omplcu
         }
         have_center_ = false;
         nslots_ = nlive_ = 0;
+        mut_version_++;
         trig_rows_ = 0;
         h_ids_.clear();
         h_alive_.clear();
@@ -862,6 +866,15 @@ namespace omplcu
             collect_ = v != 0;
         else if (!strcmp(key, "scan_ctas_per_sm"))
             scan_ctas_per_sm_ = (int)v;  // 0 = as many as fit
+        else if (!strcmp(key, "tc_scan"))
+            tc_mode_ = (int)v;  // -1 auto, 0 never, 1 whenever the space is eligible
+        else if (!strcmp(key, "tc_variant"))
+        {
+            tc_variant_ = (int)v;
+            tc_version_ = 0;
+        }
+        else if (!strcmp(key, "tc_scan_values_out"))
+            tc_dbg_ = reinterpret_cast<float *>(v);  // diagnostics: device buffer [qpad][units * 128] floats, 0 = off
         else if (!strcmp(key, "profile"))
         {
             // time the scan kernel with CUDA events on the launching stream
@@ -880,6 +893,8 @@ namespace omplcu
             return last_fallbacks_;
         if (!strcmp(key, "last_path"))
             return last_path_;
+        if (!strcmp(key, "last_tc"))
+            return last_tc_;
         if (!strcmp(key, "launches"))
             return launches_;
         if (!strcmp(key, "last_scan_ns"))
@@ -1044,16 +1059,29 @@ namespace omplcu
                            double *d_dists, cudaStream_t s)
     {
         const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
-        const int RQ = cfg == 2 ? 2 : 4, L = cfg == 0 ? 12 : (cfg == 1 ? 16 : 42);
+        const int RQ = cfg == 2 ? 2 : 4;
         const bool hd = D_ > KNN_MAX_REG_DIM;  // register-tiled kernel of knn_scan_hd.cuh
-        const size_t QT = hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
-        const size_t PT = hd ? (size_t)HD_PT : (size_t)SCAN_PT;
+        // tensor cores for the dense-contraction case (knn_scan_tc.cuh): d >= 64 and a real batch.
+        // Its scan values carry a wider error band than the FP32 kernels', so its lists keep more
+        // spare entries (16 / 24 / 48 instead of 12 / 16 / 42): the band check then compares the
+        // k-th exact distance with the (k + 6)-th scan value or later, and fall-backs stay rare.
+        const int tc_nkc = tc_kpad(D_) / TC_KC;
+        const int tc_L = cfg == 0 ? 16 : (cfg == 1 ? 24 : 48);
+        const int tc_stages = tc_pick_stages(tc_nkc, tc_L);
+        const bool tc = hd && D_ >= TC_MIN_DIM && D_ <= TC_MAX_DIM && tc_stages > 0 &&
+                        (tc_mode_ == 1 || (tc_mode_ < 0 && nq >= 1024));
+        last_tc_ = tc ? 1 : 0;
+        const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));
+        const size_t QT = tc ? (size_t)TC_QT : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
+        const size_t PT = tc ? (size_t)TC_PT : hd ? (size_t)HD_PT : (size_t)SCAN_PT;
         const size_t qtiles = (nq + QT - 1) / QT;
         const uint32_t qpad = (uint32_t)(qtiles * QT);
         const unsigned long long U = (nslots_ + PT - 1) / PT;
         const unsigned long long TU = qtiles * U;
         int resident = 1;  // CTAs per SM: one persistent CTA per resident slot
-        if (hd)
+        if (tc)
+            resident = 1;  // all of shared memory and all 512 TMEM columns
+        else if (hd)
             hd_any(cfg, 0, D_, rowf_, nullptr, 0, s, &resident);
         else
             scan_any(cfg, D_, 0, nullptr, 0, s, &resident);
@@ -1119,7 +1147,37 @@ namespace omplcu
         P.units = U;
         P.total_units = TU;
         P.smax = smax;
-        if (hd)
+        if (tc)
+        {
+            const uint32_t lbo = (tc_variant_ & 1) ? 128u : 2048u, sbo = (tc_variant_ & 1) ? 1024u : 128u;
+            if (tc_version_ != mut_version_)
+            {
+                tc_pimg_.reserve((size_t)U * tc_nkc * TC_CHUNK_ELEMS);
+                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, lbo, sbo, tc_pimg_.p, s);
+                tc_version_ = mut_version_;
+                launches_++;
+            }
+            tc_qimg_.reserve(qtiles * tc_nkc * TC_CHUNK_ELEMS);
+            tc_build_query_image(qp_.p, qpad, D_, lbo, sbo, tc_qimg_.p, s);
+            launches_++;
+            TcScanParams T;
+            T.pimg = tc_pimg_.p;
+            T.qimg = tc_qimg_.p;
+            T.cand_thr = cand_vals_.p;
+            T.cand_ids = cand_ids_.p;
+            T.units = U;
+            T.total_units = TU;
+            T.qpad = qpad;
+            T.smax = smax;
+            T.nkc = tc_nkc;
+            T.nstages = tc_stages;
+            T.lbo = lbo;
+            T.sbo = sbo;
+            T.swap_desc = (tc_variant_ >> 1) & 7;  // bit 0 swaps the descriptor fields, bits 1-2 cut the selection short (diagnostics)
+            T.dbg = tc_dbg_;
+            tc_launch_scan(L, T, (unsigned)G, s);
+        }
+        else if (hd)
             hd_any(cfg, 1, D_, rowf_, &P, (unsigned)G, s, nullptr);
         else
             scan_any(cfg, D_, 1, &P, (unsigned)G, s, nullptr);
@@ -1131,7 +1189,8 @@ namespace omplcu
         knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(cand_vals_.p, cand_ids_.p, smax, (uint32_t)L, qpad,
                                                           pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
                                                           (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists,
-                                                          ovf_list_.p, counters_.p);
+                                                          ovf_list_.p, counters_.p,
+                                                          tc ? tc_err_units(D_) : (double)(D_ + 3));
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         unsigned novf = 0;

@@ -108,6 +108,15 @@ namespace omplcu
         long last_collect_redo_ = 0;
         DevBuf<unsigned char> cub_tmp_;
 
+        // tensor-core scan (knn_scan_tc.cuh): BF16 split-operand images of the filter copy, rebuilt
+        // lazily when the point set changed since the last tensor-core query
+        DevBuf<uint16_t> tc_pimg_, tc_qimg_;
+        unsigned long mut_version_ = 1, tc_version_ = 0;
+        int tc_mode_ = -1;        // -1 auto (d >= 64 and >= 1024 queries), 0 off, 1 whenever eligible
+        int tc_variant_ = 0;      // image layout / descriptor variants (diagnostics)
+        float *tc_dbg_ = nullptr; // device buffer for raw scan values (diagnostics), caller-owned
+        long last_tc_ = 0;
+
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
         bool force_exact_ = false, profile_ = false;
