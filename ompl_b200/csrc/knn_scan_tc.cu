@@ -25,16 +25,20 @@ namespace omplcu
 {
     namespace
     {
-        constexpr int TC_THREADS = 192;
+        constexpr int TC_THREADS = 320;  // TMA warp, MMA warp, 8 selection warps (two per TMEM lane quadrant)
         constexpr int TC_ACC = 4;  // accumulator buffers (4 x 128 = all 512 TMEM columns)
         constexpr int TC_MAX_STAGES = 8;
 
         // ---------------- operand images ----------------
-        // BF16 element offset of (row, k) inside one 128-row image block
-        __host__ __device__ inline size_t tc_img_off(int row, int k, uint32_t lbo, uint32_t sbo)
+        // Within a 128-row block the image is [chunk][column group j][row group g][row r][8 BF16]:
+        // an 8-row x 16-byte core matrix is 128 contiguous bytes, row groups follow each other
+        // (stride byte offset 128), K-adjacent core matrices are 2048 bytes apart (leading byte offset).
+        constexpr uint32_t TC_LBO = 2048, TC_SBO = 128;
+
+        __host__ __device__ inline size_t tc_img_off(int row, int k, int kw)
         {
-            const int kc = k / TC_KC, kk = k % TC_KC, j = kk >> 3, e = kk & 7;
-            return (size_t)kc * TC_CHUNK_ELEMS + (size_t)j * (lbo / 2) + (size_t)(row >> 3) * (sbo / 2) +
+            const int cw = kw * 8, kc = k / cw, j = (k % cw) >> 3, e = k & 7;
+            return (size_t)kc * cw * TC_PT + (size_t)j * (TC_LBO / 2) + (size_t)(row >> 3) * (TC_SBO / 2) +
                    (size_t)(row & 7) * 8 + e;
         }
 
@@ -46,7 +50,7 @@ namespace omplcu
         {
             return __bfloat162float(__float2bfloat16_rn(x));
         }
-        // x = p[0] + p[1] + p[2] (+ residual <= 2^-26 |x|; zero for every FP32 x in range)
+        // x = p[0] + p[1] + p[2] exactly (three BF16 pieces hold the 24 bits of an FP32 value)
         __device__ __forceinline__ void bf16_split3(float x, float p[3])
         {
             if (!(fabsf(x) < 3.0e38f))
@@ -61,7 +65,7 @@ namespace omplcu
             p[2] = bf16_val(r1 - p[1]);
         }
 
-        // role of column k for a point row (B operand) / a query row (A operand)
+        // role of column k for a point row (B operand)
         __device__ __forceinline__ float tc_point_elem(const float *row, int D, int k)
         {
             if (k < 3 * D)
@@ -80,16 +84,15 @@ namespace omplcu
             return 0.f;
         }
 
-        // one thread writes 8 consecutive K elements (16 bytes) of one row
-        __global__ void tc_point_image_kernel(const float *filt, int rowf, int D, int Kp, size_t rows, uint32_t lbo,
-                                              uint32_t sbo, uint16_t *out)
+        // one thread writes 8 consecutive K elements (16 bytes) of one row; consecutive threads take
+        // consecutive rows of the same column group, so a warp writes 512 contiguous bytes
+        __global__ void tc_point_image_kernel(const float *filt, int rowf, int D, TcShape sh, size_t rows,
+                                              uint16_t *out)
         {
             const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-            const int groups = Kp / 8;
+            const int groups = sh.kpad() / 8;
             if (i >= rows * groups)
                 return;
-            // consecutive threads take consecutive rows of the same K group: 16-byte stores that
-            // are contiguous across the 8 rows of a core matrix
             const size_t tile = i / ((size_t)TC_PT * groups);
             const size_t rem = i % ((size_t)TC_PT * groups);
             const int grp = (int)(rem / TC_PT), r = (int)(rem % TC_PT);
@@ -98,16 +101,15 @@ namespace omplcu
 #pragma unroll
             for (int e = 0; e < 8; ++e)
                 v[e] = bf16_bits(tc_point_elem(row, D, grp * 8 + e));
-            uint16_t *dst = out + tile * (size_t)(Kp / TC_KC) * TC_CHUNK_ELEMS + tc_img_off(r, grp * 8, lbo, sbo);
+            uint16_t *dst = out + tile * (size_t)sh.nkc * sh.chunk_elems() + tc_img_off(r, grp * 8, sh.kw);
             *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(v);
         }
 
         // qp is [c][qpad] = -2 * qt_c (query_prep_kernel in nn.cu); padded queries are zero rows
-        __global__ void tc_query_image_kernel(const float *qp, uint32_t qpad, int D, int Kp, uint32_t lbo,
-                                              uint32_t sbo, uint16_t *out)
+        __global__ void tc_query_image_kernel(const float *qp, uint32_t qpad, int D, TcShape sh, uint16_t *out)
         {
             const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
-            const int groups = Kp / 8;
+            const int groups = sh.kpad() / 8;
             if (i >= (size_t)qpad * groups)
                 return;
             const size_t tile = i / ((size_t)TC_QT * groups);
@@ -131,7 +133,7 @@ namespace omplcu
                     x = 1.f;
                 v[e] = bf16_bits(x);
             }
-            uint16_t *dst = out + tile * (size_t)(Kp / TC_KC) * TC_CHUNK_ELEMS + tc_img_off(r, grp * 8, lbo, sbo);
+            uint16_t *dst = out + tile * (size_t)sh.nkc * sh.chunk_elems() + tc_img_off(r, grp * 8, sh.kw);
             *reinterpret_cast<uint4 *>(dst) = *reinterpret_cast<const uint4 *>(v);
         }
 
@@ -195,10 +197,11 @@ namespace omplcu
         {
             return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
         }
-        // 32 consecutive columns of this thread's TMEM lane
-        __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float v[32])
+        // 32 consecutive columns of this thread's TMEM lane.  The load is asynchronous: the registers
+        // are valid after tmem_ld_wait, which takes them as operands so that no use can be scheduled
+        // ahead of it.
+        __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32])
         {
-            uint32_t r[32];
             asm volatile(
                 "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
                 "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -210,10 +213,17 @@ namespace omplcu
                   "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
                 : "r"(taddr)
                 : "memory");
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-            for (int i = 0; i < 32; ++i)
-                v[i] = __uint_as_float(r[i]);
+        }
+        __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[32])
+        {
+            asm volatile("tcgen05.wait::ld.sync.aligned;"
+                         : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]),
+                           "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]),
+                           "+r"(r[14]), "+r"(r[15]), "+r"(r[16]), "+r"(r[17]), "+r"(r[18]), "+r"(r[19]),
+                           "+r"(r[20]), "+r"(r[21]), "+r"(r[22]), "+r"(r[23]), "+r"(r[24]), "+r"(r[25]),
+                           "+r"(r[26]), "+r"(r[27]), "+r"(r[28]), "+r"(r[29]), "+r"(r[30]), "+r"(r[31])
+                         :
+                         : "memory");
         }
 
         // ---------------- the scan ----------------
@@ -225,22 +235,72 @@ namespace omplcu
             uint32_t tmem_base;
         };
 
+        // diagnostics (DBG instantiation only): raw scan values of one 32-column step
+        __device__ __noinline__ void tc_dump(const TcScanParams &P, const uint32_t (&v)[32], size_t q, uint32_t col0)
+        {
+            float *d = P.dbg + q * (P.units * TC_PT) + col0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                d[i] = __uint_as_float(v[i]);
+        }
+
+        // The slow path of the selection, out of line so that the hot loop stays small in the
+        // instruction cache: visit the values of this thread's staged 32-column chunk that beat the
+        // threshold, in column order, and put each into the list (it replaces the current maximum).
         template <int L>
+        __device__ __noinline__ float tc_select_hits(float thr, const float *scr_q, float *lvq, uint32_t *liq,
+                                                     uint32_t id0)
+        {
+            uint32_t mask = 0;
+#pragma unroll
+            for (int i = 0; i < 32; ++i)
+                mask |= scr_q[i * TC_QT] < thr ? 1u << i : 0u;
+            while (mask)
+            {
+                const int i = __ffs(mask) - 1;
+                mask &= mask - 1;
+                const float x = scr_q[i * TC_QT];
+                if (x < thr)
+                {
+                    const uint32_t slot = __float_as_uint(thr) & TAG_MASK;
+                    lvq[slot] = tag_up(x, slot);
+                    liq[slot * TC_QT] = id0 + i;
+                    float4 a = *reinterpret_cast<const float4 *>(lvq);
+                    float m0 = fmaxf(a.x, a.y), m1 = fmaxf(a.z, a.w);
+#pragma unroll
+                    for (int k = 1; k < L / 4; ++k)
+                    {
+                        a = *reinterpret_cast<const float4 *>(lvq + 4 * k);
+                        m0 = fmaxf(m0, fmaxf(a.x, a.y));
+                        m1 = fmaxf(m1, fmaxf(a.z, a.w));
+                    }
+                    thr = fmaxf(m0, m1);
+                }
+            }
+            return thr;
+        }
+
+        // Work: the (query super-tile x point tile) rectangle, linearised (super-tile major) and cut
+        // into gridDim.x equal pieces as in knn_scan.cuh.  A super-tile is NA query tiles of 128; per
+        // point tile the CTA runs NA "jobs" (one accumulator each, job j -> TMEM buffer j % 4).
+        template <int L, int NA, bool DBG>
         __global__ void __launch_bounds__(TC_THREADS, 1) knn_scan_tc_kernel(const TcScanParams P)
         {
             extern __shared__ __align__(1024) uint8_t tc_smem[];
-            const int nkc = P.nkc, nst = P.nstages;
-            uint8_t *sA = tc_smem;                                  // [nkc][16 KB]
-            uint8_t *sB = sA + (size_t)nkc * TC_CHUNK_ELEMS * 2;    // [nst][16 KB]
-            float *lv = reinterpret_cast<float *>(sB + (size_t)nst * TC_CHUNK_ELEMS * 2);  // [128][L + 4]
-            uint32_t *li = reinterpret_cast<uint32_t *>(lv + (L + 4) * TC_QT);             // [L][128]
-            float *scr = reinterpret_cast<float *>(li + L * TC_QT);                        // [32][128] slow-path staging
-            TcSmem *S = reinterpret_cast<TcSmem *>(scr + 32 * TC_QT);
+            constexpr int LS = L + 4;
+            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw;
+            const uint32_t chunk_bytes = (uint32_t)kw * 2048u;
+            const uint32_t a_tile_bytes = (uint32_t)nkc * chunk_bytes;
+            uint8_t *sA = tc_smem;                                    // [NA][nkc][chunk]
+            uint8_t *sB = sA + (size_t)NA * a_tile_bytes;             // [nst][chunk]
+            float *lv = reinterpret_cast<float *>(sB + (size_t)nst * chunk_bytes);  // [NA][128][LS]
+            uint32_t *li = reinterpret_cast<uint32_t *>(lv + NA * TC_QT * LS);      // [NA][L][128]
+            float *scr = reinterpret_cast<float *>(li + NA * L * TC_QT);            // [32][128] slow-path staging, [NA][128] thresholds
+            TcSmem *S = reinterpret_cast<TcSmem *>(scr + (32 * (NA >= 2 ? 2 : 1) + NA) * TC_QT);
 
             const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
             const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
             const unsigned long long u0 = TU * g / G, u1 = TU * (g + 1) / G;
-            constexpr uint32_t CHUNK_BYTES = TC_CHUNK_ELEMS * 2;
 
             if (tid == 0)
             {
@@ -271,26 +331,30 @@ namespace omplcu
                 {
                     int st = 0;
                     uint32_t ph = 0, aph = 0;
-                    unsigned long long cur = ~0ull;
-                    for (unsigned long long u = u0; u < u1; ++u)
+                    unsigned long long cur = ~0ull, t = 0, pt = 0;
+                    for (unsigned long long u = u0; u < u1; ++u, ++pt)
                     {
-                        const unsigned long long t = u / U, pt = u % U;
+                        if (u == u0 || pt == U)
+                        {
+                            t = u / U;
+                            pt = u % U;
+                        }
                         if (t != cur)
                         {
-                            mbar_wait(&S->a_empty, aph ^ 1);  // the MMAs of the previous tile are done with sA
-                            mbar_expect_tx(&S->a_full, (uint32_t)nkc * CHUNK_BYTES);
-                            tma_bulk_g2s(sA, P.qimg + (size_t)t * nkc * TC_CHUNK_ELEMS, (uint32_t)nkc * CHUNK_BYTES,
+                            mbar_wait(&S->a_empty, aph ^ 1);  // the MMAs of the previous super-tile are done with sA
+                            mbar_expect_tx(&S->a_full, NA * a_tile_bytes);
+                            tma_bulk_g2s(sA, P.qimg + (size_t)t * NA * (a_tile_bytes / 2), NA * a_tile_bytes,
                                          &S->a_full);
                             aph ^= 1;
                             cur = t;
                         }
-                        const uint16_t *src = P.pimg + (size_t)pt * nkc * TC_CHUNK_ELEMS;
+                        const uint16_t *src = P.pimg + (size_t)pt * (a_tile_bytes / 2);
                         for (int kc = 0; kc < nkc; ++kc)
                         {
                             mbar_wait(&S->empty[st], ph ^ 1);
-                            mbar_expect_tx(&S->full[st], CHUNK_BYTES);
-                            tma_bulk_g2s(sB + (size_t)st * CHUNK_BYTES, src + (size_t)kc * TC_CHUNK_ELEMS, CHUNK_BYTES,
-                                         &S->full[st]);
+                            mbar_expect_tx(&S->full[st], chunk_bytes);
+                            tma_bulk_g2s(sB + (size_t)st * chunk_bytes, src + (size_t)kc * (chunk_bytes / 2),
+                                         chunk_bytes, &S->full[st]);
                             if (++st == nst)
                             {
                                 st = 0;
@@ -305,15 +369,19 @@ namespace omplcu
                 if (lane == 0)
                 {
                     constexpr uint32_t idesc = umma_idesc_bf16(TC_QT, TC_PT);
-                    const uint32_t dl = (P.swap_desc & 1) ? P.sbo : P.lbo, ds = (P.swap_desc & 1) ? P.lbo : P.sbo;
-                    const uint32_t kstep = 2 * P.lbo;  // one MMA covers K = 16 = two 16-byte column groups
-                    const uint32_t a0 = smem_u32(sA), b0 = smem_u32(sB);
-                    int st = 0, buf = 0;
-                    uint32_t ph = 0, aph = 0, bph = 0;
-                    unsigned long long cur = ~0ull;
-                    for (unsigned long long u = u0; u < u1; ++u)
+                    const uint32_t dl = (P.diag & 1) ? TC_SBO : TC_LBO, ds = (P.diag & 1) ? TC_LBO : TC_SBO;
+                    const uint32_t a0 = smem_u32(sA) & 0x3FFFFu, b0 = smem_u32(sB) & 0x3FFFFu;
+                    const uint64_t desc0 = umma_desc(0, dl, ds);  // one MMA covers K = 16 = two column groups
+                    int st = 0;
+                    uint32_t ph = 0, aph = 0;
+                    unsigned long long cur = ~0ull, job = 0, t = 0, pt = 0;  // job = (unit - u0) * NA + tile
+                    for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
                     {
-                        const unsigned long long t = u / U;
+                        if (u == u0 || pt == U)
+                        {
+                            t = u / U;
+                            pt = u % U;
+                        }
                         if (t != cur)
                         {
                             if (cur != ~0ull)
@@ -322,19 +390,33 @@ namespace omplcu
                             aph ^= 1;
                             cur = t;
                         }
-                        mbar_wait(&S->t_empty[buf], bph ^ 1);
-                        tc_fence_after();
-                        const uint32_t dcol = tmem + (uint32_t)buf * TC_PT;
                         for (int kc = 0; kc < nkc; ++kc)
                         {
                             mbar_wait(&S->full[st], ph);
                             tc_fence_after();
 #pragma unroll
-                            for (int s = 0; s < TC_KC / 16; ++s)
+                            for (int a = 0; a < NA; ++a)
                             {
-                                const uint64_t ad = umma_desc(a0 + (uint32_t)kc * CHUNK_BYTES + s * kstep, dl, ds);
-                                const uint64_t bd = umma_desc(b0 + (uint32_t)st * CHUNK_BYTES + s * kstep, dl, ds);
-                                umma_bf16(dcol, ad, bd, idesc, (kc | s) ? 1u : 0u);
+                                const unsigned long long j = job + a;
+                                const int buf = (int)(j & (TC_ACC - 1));
+                                if (kc == 0)
+                                {
+                                    mbar_wait(&S->t_empty[buf], (uint32_t)((j / TC_ACC) & 1) ^ 1);
+                                    tc_fence_after();
+                                }
+                                const uint32_t dcol = tmem + (uint32_t)buf * TC_PT;
+                                // descriptors differ in the start address only (low word, units of 16 bytes)
+                                const uint64_t ad = desc0 + ((a0 + (uint32_t)a * a_tile_bytes + (uint32_t)kc * chunk_bytes) >> 4);
+                                const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
+                                umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
+                                umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
+                                if (kw == 8)
+                                {
+                                    umma_bf16(dcol, ad + 2 * (2 * TC_LBO >> 4), bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
+                                    umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
+                                }
+                                if (kc == nkc - 1)
+                                    umma_commit(&S->t_full[buf]);
                             }
                             umma_commit(&S->empty[st]);
                             if (++st == nst)
@@ -343,123 +425,116 @@ namespace omplcu
                                 ph ^= 1;
                             }
                         }
-                        umma_commit(&S->t_full[buf]);
-                        if (++buf == TC_ACC)
-                        {
-                            buf = 0;
-                            bph ^= 1;
-                        }
                     }
                 }
             }
-            else
+            else if (((warp - 2) >> 2) < (NA >= 2 ? 2 : 1))
             {
-                // selection: this thread's TMEM lane is its query.  The query's list lives in shared
-                // memory, LS = L + 4 floats apart (conflict-free LDS.128 across lanes); values carry
-                // their list slot in the low mantissa bits (knn_scan.cuh: tag_up), so the running
-                // maximum `thr` names the entry to overwrite and ONE max-tree over the list yields the
-                // next threshold and the next victim.
-                const int wq = warp & 3, qrow = wq * 32 + lane;
-                constexpr int LS = L + 4;
-                float *lvq = lv + qrow * LS;
-                float thr;
+                // selection: this thread's TMEM lane is its query (one per resident tile).  A query's
+                // list lives in shared memory, LS = L + 4 floats apart (conflict-free LDS.128 across
+                // lanes); values carry their list slot in the low mantissa bits (knn_scan.cuh: tag_up),
+                // so the running maximum names the entry to overwrite and ONE max-tree over the list
+                // yields the next threshold and the next victim.  The hot loop is kept to two copies of
+                // the 32-column step (the two register buffers of the TMEM load pipeline) so that it
+                // stays resident in the instruction cache; thresholds of the NA tiles sit in shared memory.
+                // Two warps share a lane quadrant; with NA >= 2 they take alternate tiles (a query belongs
+                // to one warp only), with NA = 1 the second warp of a quadrant has nothing to do.
+                const int wq = warp & 3, qrow = wq * 32 + lane, half = (warp - 2) >> 2;
+                constexpr int WSPLIT = NA >= 2 ? 2 : 1;
+                float *thr_s = scr + 32 * TC_QT * WSPLIT;  // [NA][128]
+                scr += half * 32 * TC_QT;
                 auto reset = [&]() {
-#pragma unroll
-                    for (int i = 0; i < L; ++i)
+                    for (int a = half; a < NA; a += WSPLIT)
                     {
-                        lvq[i] = __uint_as_float(EMPTY_BITS | (uint32_t)i);
-                        li[i * TC_QT + qrow] = SLOT_NONE;
+                        for (int i = 0; i < L; ++i)
+                        {
+                            lv[(a * TC_QT + qrow) * LS + i] = __uint_as_float(EMPTY_BITS | (uint32_t)i);
+                            li[(a * L + i) * TC_QT + qrow] = SLOT_NONE;
+                        }
+                        thr_s[a * TC_QT + qrow] = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
                     }
-                    thr = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
                 };
                 auto flush = [&](unsigned long long t) {
                     const unsigned long long x = t * U;
                     const unsigned long long gfirst = ((x + 1) * G + TU - 1) / TU - 1;
                     const unsigned seg = (unsigned)(g - gfirst);
-                    const size_t q = (size_t)t * TC_QT + qrow;
-                    P.cand_thr[(size_t)seg * P.qpad + q] = thr;
-#pragma unroll
-                    for (int i = 0; i < L; ++i)
-                        P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = li[i * TC_QT + qrow];
-                };
-                auto insert = [&](float v, uint32_t id) {
-                    const uint32_t slot = __float_as_uint(thr) & TAG_MASK;
-                    lvq[slot] = tag_up(v, slot);
-                    li[slot * TC_QT + qrow] = id;
-                    float4 a = *reinterpret_cast<const float4 *>(lvq);
-                    float m0 = fmaxf(a.x, a.y), m1 = fmaxf(a.z, a.w);
-#pragma unroll
-                    for (int i = 1; i < L / 4; ++i)
+                    for (int a = half; a < NA; a += WSPLIT)
                     {
-                        a = *reinterpret_cast<const float4 *>(lvq + 4 * i);
-                        m0 = fmaxf(m0, fmaxf(a.x, a.y));
-                        m1 = fmaxf(m1, fmaxf(a.z, a.w));
+                        const size_t q = ((size_t)t * NA + a) * TC_QT + qrow;
+                        P.cand_thr[(size_t)seg * P.qpad + q] = thr_s[a * TC_QT + qrow];
+                        for (int i = 0; i < L; ++i)
+                            P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = li[(a * L + i) * TC_QT + qrow];
                     }
-                    thr = fmaxf(m0, m1);
                 };
-                int buf = 0;
-                uint32_t bph = 0;
-                unsigned long long cur = ~0ull;
-                for (unsigned long long u = u0; u < u1; ++u)
-                {
-                    const unsigned long long t = u / U, pt = u % U;
-                    if (t != cur)
+                // one 32-column step: min-tree against the threshold; the rare hit stages the values in
+                // shared memory and calls the out-of-line routine
+                auto step = [&](uint32_t(&v)[32], float th, int a, uint32_t id0) -> float {
+                    float m0 = fminf(__uint_as_float(v[0]), __uint_as_float(v[1]));
+                    float m1 = fminf(__uint_as_float(v[2]), __uint_as_float(v[3]));
+#pragma unroll
+                    for (int i = 4; i < 32; i += 4)
                     {
+                        m0 = fminf(m0, fminf(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
+                        m1 = fminf(m1, fminf(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])));
+                    }
+                    if (fminf(m0, m1) < th && !(P.diag & 4))
+                    {
+#pragma unroll
+                        for (int i = 0; i < 32; ++i)
+                            scr[i * TC_QT + qrow] = __uint_as_float(v[i]);
+                        th = tc_select_hits<L>(th, scr + qrow, lv + (a * TC_QT + qrow) * LS, li + a * L * TC_QT + qrow,
+                                               id0);
+                    }
+                    return th;
+                };
+                unsigned long long cur = ~0ull, job = 0, t = 0, pt = 0;
+                for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
+                {
+                    if (u == u0 || pt == U)
+                    {
+                        t = u / U;  // once per super-tile: no 64-bit division in the unit loop
+                        pt = u % U;
                         if (cur != ~0ull)
                             flush(cur);
                         reset();
                         cur = t;
                     }
-                    mbar_wait(&S->t_full[buf], bph);
-                    tc_fence_after();
-                    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
                     const uint32_t slot0 = (uint32_t)(pt * TC_PT);
 #pragma unroll 1
-                    for (int c4 = 0; c4 < TC_PT / 32; ++c4)
+                    for (int a = half; a < NA; a += WSPLIT)
                     {
-                        float v[32];
-                        if (P.swap_desc & 2)
-                            break;  // diagnostics: no selection at all
-                        __syncwarp();
-                        tmem_ld32(taddr + c4 * 32, v);
-                        if (P.dbg)
+                        const unsigned long long j = job + a;
+                        const int buf = (int)(j & (TC_ACC - 1));
+                        mbar_wait(&S->t_full[buf], (uint32_t)((j / TC_ACC) & 1));
+                        tc_fence_after();
+                        const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
+                        if (!(P.diag & 2))
                         {
-                            float *d = P.dbg + ((size_t)t * TC_QT + qrow) * (U * TC_PT) + slot0 + c4 * 32;
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
-                                d[i] = v[i];
-                        }
-                        float m = v[0];
-#pragma unroll
-                        for (int i = 1; i < 32; ++i)
-                            m = fminf(m, v[i]);
-                        // Rare after the first few thousand points of a segment.  The values go through
-                        // shared memory so that the loop can index them; it visits the hits only.
-                        if (m < thr && !(P.swap_desc & 4))
-                        {
-                            uint32_t mask = 0;
-#pragma unroll
-                            for (int i = 0; i < 32; ++i)
+                            uint32_t ra[32], rb[32];
+                            float th = thr_s[a * TC_QT + qrow];
+                            __syncwarp();
+                            tmem_ld32_issue(taddr, ra);
+#pragma unroll 1
+                            for (int c = 0; c < TC_PT / 32; c += 2)
                             {
-                                scr[i * TC_QT + qrow] = v[i];
-                                mask |= v[i] < thr ? 1u << i : 0u;
+                                __syncwarp();
+                                tmem_ld_wait(ra);
+                                tmem_ld32_issue(taddr + (c + 1) * 32, rb);  // in flight during the tree below
+                                if (DBG)
+                                    tc_dump(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * 32);
+                                th = step(ra, th, a, slot0 + c * 32);
+                                __syncwarp();
+                                tmem_ld_wait(rb);
+                                if (c + 2 < TC_PT / 32)
+                                    tmem_ld32_issue(taddr + (c + 2) * 32, ra);
+                                if (DBG)
+                                    tc_dump(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * 32);
+                                th = step(rb, th, a, slot0 + (c + 1) * 32);
                             }
-                            while (mask)
-                            {
-                                const int i = __ffs(mask) - 1;
-                                mask &= mask - 1;
-                                const float x = scr[i * TC_QT + qrow];
-                                if (x < thr)
-                                    insert(x, slot0 + c4 * 32 + i);
-                            }
+                            thr_s[a * TC_QT + qrow] = th;
                         }
-                    }
-                    tc_fence_before();
-                    mbar_arrive(&S->t_empty[buf]);
-                    if (++buf == TC_ACC)
-                    {
-                        buf = 0;
-                        bph ^= 1;
+                        tc_fence_before();
+                        mbar_arrive(&S->t_empty[buf]);
                     }
                 }
                 if (cur != ~0ull)
@@ -476,57 +551,74 @@ namespace omplcu
         }
     }  // namespace
 
-    size_t tc_smem_bytes(int nkc, int nstages, int L)
+    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L)
     {
-        return (size_t)(nkc + nstages) * TC_CHUNK_ELEMS * 2 + (size_t)(2 * L + 4) * TC_QT * 4 + 32 * TC_QT * 4 + sizeof(TcSmem) + 64;
+        const size_t chunk = (size_t)sh.kw * 2048;
+        return (size_t)sh.na * sh.nkc * chunk + (size_t)nstages * chunk + (size_t)sh.na * TC_QT * (2 * L + 4) * 4 +
+               (32 * (sh.na >= 2 ? 2 : 1) + sh.na) * TC_QT * 4 + sizeof(TcSmem) + 64;
     }
 
-    int tc_pick_stages(int nkc, int L)
+    int tc_pick_stages(const TcShape &sh, int L)
     {
-        for (int st = 6; st >= 3; --st)
-            if (tc_smem_bytes(nkc, st, L) <= 227 * 1024)
+        for (int st = TC_MAX_STAGES; st >= 3; --st)
+            if (tc_smem_bytes(sh, st, L) <= 227 * 1024)
                 return st;
         return 0;
     }
 
-    void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint32_t lbo, uint32_t sbo,
-                              uint16_t *out, cudaStream_t s)
+    void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint16_t *out, cudaStream_t s)
     {
-        const int Kp = tc_kpad(D);
-        const size_t rows = units * TC_PT, n = rows * (Kp / 8);
+        const TcShape sh = tc_shape(D);
+        const size_t rows = units * TC_PT, n = rows * (sh.kpad() / 8);
         if (n)
-            tc_point_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(filt, rowf, D, Kp, rows, lbo, sbo, out);
+            tc_point_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(filt, rowf, D, sh, rows, out);
     }
 
-    void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint32_t lbo, uint32_t sbo, uint16_t *out,
-                              cudaStream_t s)
+    void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint16_t *out, cudaStream_t s)
     {
-        const int Kp = tc_kpad(D);
-        const size_t n = (size_t)qpad * (Kp / 8);
+        const TcShape sh = tc_shape(D);
+        const size_t n = (size_t)qpad * (sh.kpad() / 8);
         if (n)
-            tc_query_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(qp, qpad, D, Kp, lbo, sbo, out);
+            tc_query_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(qp, qpad, D, sh, out);
     }
 
     namespace
     {
-        template <int L>
+        template <int L, int NA>
         void tc_launch(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
-            const size_t smem = tc_smem_bytes(P.nkc, P.nstages, L);
-            CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)smem));
-            knn_scan_tc_kernel<L><<<grid, TC_THREADS, smem, s>>>(P);
+            const size_t smem = tc_smem_bytes(P.sh, P.nstages, L);
+            if (P.dbg)
+            {
+                CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, NA, true>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                knn_scan_tc_kernel<L, NA, true><<<grid, TC_THREADS, smem, s>>>(P);
+                return;
+            }
+            CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, NA, false>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            knn_scan_tc_kernel<L, NA, false><<<grid, TC_THREADS, smem, s>>>(P);
+        }
+        template <int L>
+        void tc_launch_na(const TcScanParams &P, unsigned grid, cudaStream_t s)
+        {
+            if (P.sh.na == 4)
+                tc_launch<L, 4>(P, grid, s);
+            else if (P.sh.na == 2)
+                tc_launch<L, 2>(P, grid, s);
+            else
+                tc_launch<L, 1>(P, grid, s);
         }
     }  // namespace
 
     void tc_launch_scan(int L, const TcScanParams &P, unsigned grid, cudaStream_t s)
     {
         if (L == 16)
-            tc_launch<16>(P, grid, s);
+            tc_launch_na<16>(P, grid, s);
         else if (L == 24)
-            tc_launch<24>(P, grid, s);
+            tc_launch_na<24>(P, grid, s);
         else if (L == 48)
-            tc_launch<48>(P, grid, s);
+            tc_launch_na<48>(P, grid, s);
         else
             throw Error(OMPLCU_ERR_INTERNAL, "tensor-core scan: unsupported list length");
     }

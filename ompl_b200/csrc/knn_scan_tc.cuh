@@ -20,15 +20,33 @@
 
 namespace omplcu
 {
-    constexpr int TC_QT = 128;          // queries per tile  (UMMA M)
+    constexpr int TC_QT = 128;          // queries per A tile (UMMA M); a CTA keeps 1, 2 or 4 tiles resident
     constexpr int TC_PT = 128;          // points per tile   (UMMA N)
-    constexpr int TC_KC = 64;           // BF16 elements of K per shared-memory chunk (128 B per row)
-    constexpr int TC_CHUNK_ELEMS = TC_PT * TC_KC;        // 8192 BF16 = 16 KB: one operand chunk
-    constexpr int TC_MIN_DIM = 64, TC_MAX_DIM = 128;
+    constexpr int TC_MIN_DIM = 64, TC_MAX_DIM = 128;  // "auto" range; any d in 1..128 can be forced
 
-    __host__ __device__ constexpr int tc_kpad(int D)
+    // K = 3 d + 3, padded to a whole number of chunks.  A chunk is kw 16-byte column groups
+    // (kw = 4: 32 BF16, 8 KB per 128 rows; kw = 8: 64 BF16, 16 KB), whichever pads less.
+    struct TcShape
     {
-        return (3 * D + 3 + TC_KC - 1) / TC_KC * TC_KC;
+        int kw, nkc, na;  // column groups per chunk, chunks, resident query tiles
+        __host__ __device__ int kpad() const
+        {
+            return nkc * kw * 8;
+        }
+        __host__ __device__ size_t chunk_elems() const
+        {
+            return (size_t)kw * 8 * TC_PT;
+        }
+    };
+    inline TcShape tc_shape(int D)
+    {
+        const int k32 = (3 * D + 3 + 31) / 32;
+        TcShape s;
+        s.kw = (k32 % 2 == 0) ? 8 : 4;
+        s.nkc = (k32 % 2 == 0) ? k32 / 2 : k32;
+        const size_t a_bytes = (size_t)k32 * 32 * TC_QT * 2;
+        s.na = a_bytes <= 16384 ? 4 : (a_bytes <= 40960 ? 2 : 1);  // d <= 20: 4 tiles, d <= 52: 2, else 1
+        return s;
     }
 
     // Scan-value error bound in units of u = 2^-24 times (pmax2 + 2 |qt| pmax), see DESIGN.md 3.5:
@@ -36,33 +54,31 @@ namespace omplcu
     //   192    split: dropped b2 b2 products and the two eps terms, 3 * 2^-18 = 192 u
     //   32/MMA accumulation: every tcgen05.mma (K = 16) is allowed 2^-19 of the largest partial sum
     //   x 1.02 partial sums of split operands exceed |q||p| by at most 2^-7
-    __host__ __device__ constexpr double tc_err_units(int D)
+    inline double tc_err_units(int D)
     {
-        return 1.02 * (3.0 + 192.0 + 32.0 * (tc_kpad(D) / 16));
+        return 1.02 * (3.0 + 192.0 + 32.0 * (tc_shape(D).kpad() / 16));
     }
 
     struct TcScanParams
     {
-        const uint16_t *pimg;   // [units][nkc][TC_CHUNK_ELEMS] BF16, UMMA core-matrix order
-        const uint16_t *qimg;   // [qtiles][nkc][TC_CHUNK_ELEMS]
+        const uint16_t *pimg;   // [units][nkc][chunk] BF16, UMMA core-matrix order
+        const uint16_t *qimg;   // [qtiles][nkc][chunk]; a CTA loads na consecutive tiles at once
         float *cand_thr;        // [smax][qpad]
         uint32_t *cand_ids;     // [smax*L][qpad]
-        unsigned long long units, total_units;
+        unsigned long long units, total_units;  // point tiles; (query super-tiles) x units
         uint32_t qpad, smax;
-        int nkc, nstages;
-        uint32_t lbo, sbo;      // byte strides of the image: K-adjacent core matrices / 8-row groups
-        int swap_desc;          // debugging: exchange the two descriptor fields
+        TcShape sh;
+        int nstages;
+        int diag;               // diagnostics: 1 swap descriptor fields, 2 no selection, 4 no insertion
         float *dbg;             // [qpad][units*TC_PT] raw scan values, or nullptr
     };
 
-    size_t tc_smem_bytes(int nkc, int nstages, int L);
-    int tc_pick_stages(int nkc, int L);  // 0: does not fit
+    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L);
+    int tc_pick_stages(const TcShape &sh, int L);  // 0: does not fit
 
     // images
-    void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint32_t lbo, uint32_t sbo,
-                              uint16_t *out, cudaStream_t s);
-    void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint32_t lbo, uint32_t sbo, uint16_t *out,
-                              cudaStream_t s);
+    void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint16_t *out, cudaStream_t s);
+    void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint16_t *out, cudaStream_t s);
     // L in {16, 24, 48}
     void tc_launch_scan(int L, const TcScanParams &P, unsigned grid, cudaStream_t s);
 }  // namespace omplcu

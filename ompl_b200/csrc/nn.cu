@@ -162,7 +162,7 @@ namespace omplcu
                 s_slot[w][c] = slot;
             }
             if (lane == 0)
-                s_dk[w] = 0.0;
+                s_dk[w] = -1.0;  // stays negative if the lists hold fewer than kk candidates
             __syncwarp();
             for (uint32_t c = lane; c < n; c += 32)
             {
@@ -198,7 +198,7 @@ namespace omplcu
             const double A = dk * (1.0 + delta) + rho + 1e-150;
             const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
             const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
-            bool bad = !(tau64 == tau64) || !(tau64 < 1e37);  // NaN / overflow -> redo exactly
+            bool bad = !(tau64 == tau64) || !(tau64 < 1e37) || dk < 0.0;  // NaN / overflow / too few -> redo exactly
             for (uint32_t s = lane; s < smax; s += 32)
             {
                 // final threshold of the segment's list; an EMPTY marker (> 1e38) means
@@ -1065,14 +1065,19 @@ namespace omplcu
         // Its scan values carry a wider error band than the FP32 kernels', so its lists keep more
         // spare entries (16 / 24 / 48 instead of 12 / 16 / 42): the band check then compares the
         // k-th exact distance with the (k + 6)-th scan value or later, and fall-backs stay rare.
-        const int tc_nkc = tc_kpad(D_) / TC_KC;
+        TcShape tc_sh = tc_shape(D_);
         const int tc_L = cfg == 0 ? 16 : (cfg == 1 ? 24 : 48);
-        const int tc_stages = tc_pick_stages(tc_nkc, tc_L);
-        const bool tc = hd && D_ >= TC_MIN_DIM && D_ <= TC_MAX_DIM && tc_stages > 0 &&
-                        (tc_mode_ == 1 || (tc_mode_ < 0 && nq >= 1024));
+        int tc_stages = tc_pick_stages(tc_sh, tc_L);
+        while (tc_stages == 0 && tc_sh.na > 1)
+        {
+            tc_sh.na /= 2;  // long lists: fewer resident query tiles
+            tc_stages = tc_pick_stages(tc_sh, tc_L);
+        }
+        const bool tc_auto = D_ >= TC_MIN_DIM && nq >= 1024;
+        const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
         last_tc_ = tc ? 1 : 0;
         const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));
-        const size_t QT = tc ? (size_t)TC_QT : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
+        const size_t QT = tc ? (size_t)TC_QT * tc_sh.na : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
         const size_t PT = tc ? (size_t)TC_PT : hd ? (size_t)HD_PT : (size_t)SCAN_PT;
         const size_t qtiles = (nq + QT - 1) / QT;
         const uint32_t qpad = (uint32_t)(qtiles * QT);
@@ -1129,7 +1134,7 @@ namespace omplcu
         // and skips most of the early insertions.  Self-verifying: the re-rank's band check
         // does not care where a list's threshold came from.
         const uint32_t nsample = 4096;
-        if (sample_thr_ && !hd && nslots_ >= 16 * (size_t)nsample && L <= 64)
+        if (sample_thr_ && !hd && !tc && nslots_ >= 16 * (size_t)nsample && L <= 64)
         {
             const int rw = rowf_ / 4;
             sample_thr_buf_.reserve(qpad + (size_t)nsample * rowf_);
@@ -1149,16 +1154,15 @@ namespace omplcu
         P.smax = smax;
         if (tc)
         {
-            const uint32_t lbo = (tc_variant_ & 1) ? 128u : 2048u, sbo = (tc_variant_ & 1) ? 1024u : 128u;
             if (tc_version_ != mut_version_)
             {
-                tc_pimg_.reserve((size_t)U * tc_nkc * TC_CHUNK_ELEMS);
-                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, lbo, sbo, tc_pimg_.p, s);
+                tc_pimg_.reserve((size_t)U * tc_sh.nkc * tc_sh.chunk_elems());
+                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
                 tc_version_ = mut_version_;
                 launches_++;
             }
-            tc_qimg_.reserve(qtiles * tc_nkc * TC_CHUNK_ELEMS);
-            tc_build_query_image(qp_.p, qpad, D_, lbo, sbo, tc_qimg_.p, s);
+            tc_qimg_.reserve((size_t)(qpad / TC_QT) * tc_sh.nkc * tc_sh.chunk_elems());
+            tc_build_query_image(qp_.p, qpad, D_, tc_qimg_.p, s);
             launches_++;
             TcScanParams T;
             T.pimg = tc_pimg_.p;
@@ -1169,11 +1173,9 @@ namespace omplcu
             T.total_units = TU;
             T.qpad = qpad;
             T.smax = smax;
-            T.nkc = tc_nkc;
+            T.sh = tc_sh;
             T.nstages = tc_stages;
-            T.lbo = lbo;
-            T.sbo = sbo;
-            T.swap_desc = (tc_variant_ >> 1) & 7;  // bit 0 swaps the descriptor fields, bits 1-2 cut the selection short (diagnostics)
+            T.diag = tc_variant_;
             T.dbg = tc_dbg_;
             tc_launch_scan(L, T, (unsigned)G, s);
         }

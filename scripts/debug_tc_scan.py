@@ -1,7 +1,7 @@
 """Diagnostics for the tensor-core scan (knn_scan_tc.cu): dump the raw scan values of a small
 problem through the `tc_scan_values_out` option and compare them with an FP64 evaluation of
     s = |p - c|^2 - 2 (q - c).(p - c)
-for each image layout / descriptor variant; then check the neighbour sets against the oracle.
+then check the neighbour sets against the oracle.
 Run on the GPU box:  python scripts/debug_tc_scan.py [variant ...]
 """
 import os
@@ -52,5 +52,6 @@ def run(variant, d=100, n=1000, nq=256, k=10):
 
 
 if __name__ == "__main__":
-    for v in [int(a) for a in sys.argv[1:]] or [0]:
-        run(v)
+    # usage: debug_tc_scan.py [d ...]   (variant 1 swaps the descriptor fields and must fail)
+    for d in [int(a) for a in sys.argv[1:]] or [100]:
+        run(0, d=d)
