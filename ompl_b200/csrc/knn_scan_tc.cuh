@@ -7,7 +7,7 @@
 //        s ~= pn + sum_c (-2 qt_c) * pt_c ,     pn = fl32(|pt|^2)
 // and per (segment, query) the L smallest s with their slots.  Here s comes out of
 // tcgen05.mma (BF16 operands, FP32 accumulators in TMEM) on split operands:
-//        x = b1(x) + b2(x) + eps,   b1 = bf16(x), b2 = bf16(x - b1),  |eps| <= 2^-17 |x|
+//        x = b1(x) + b2(x) + eps,   b1 = bf16(x), b2 = bf16(x - b1),  |eps| <= 2^-16 |x|
 //        s_tc = sum_c [ b1(q_c) b1(p_c) + b1(q_c) b2(p_c) + b2(q_c) b1(p_c) ] + n1 + n2 + n3
 // with q_c = -2 qt_c and n1 + n2 + n3 = pn exactly (three BF16 pieces hold 24 bits).  That
 // is ONE GEMM with K = 3 d + 3: the A row of a query is [b1(q) | b1(q) | b2(q) | 1 1 1],
@@ -22,7 +22,8 @@ namespace omplcu
 {
     constexpr int TC_QT = 128;          // queries per A tile (UMMA M); a CTA keeps 1, 2 or 4 tiles resident
     constexpr int TC_PT = 128;          // points per tile   (UMMA N)
-    constexpr int TC_MIN_DIM = 64, TC_MAX_DIM = 128;  // "auto" range; any d in 1..128 can be forced
+    constexpr int TC_MAX_DIM = 128;
+    constexpr int TC_MIN_BATCH = 32;    // "auto": batches of at least this many queries; single queries stay on the FP32 scans
 
     // K = 3 d + 3, padded to a whole number of chunks.  A chunk is kw 16-byte column groups
     // (kw = 4: 32 BF16, 8 KB per 128 rows; kw = 8: 64 BF16, 16 KB), whichever pads less.
@@ -51,12 +52,16 @@ namespace omplcu
 
     // Scan-value error bound in units of u = 2^-24 times (pmax2 + 2 |qt| pmax), see DESIGN.md 3.5:
     //   3      pn as stored (rounding of the FP32 norm, as in the FP32 kernels)
-    //   192    split: dropped b2 b2 products and the two eps terms, 3 * 2^-18 = 192 u
+    //   768    split: BF16 keeps 8 significant bits, so x = b1 + b2 + eps with |b2| <= 2^-8 |x| and
+    //          |eps| <= 2^-16 |x|; the dropped b2 b2 product and the two eps terms are each
+    //          <= 2^-16 |q_c||p_c|, summed over c <= 3 * 2^-16 |q||p| = 768 u (Cauchy-Schwarz)
     //   32/MMA accumulation: every tcgen05.mma (K = 16) is allowed 2^-19 of the largest partial sum
-    //   x 1.02 partial sums of split operands exceed |q||p| by at most 2^-7
+    //          (products of BF16 values are exact in FP32; the accumulator rounding is not documented,
+    //          the allowance is 16 ulp per instruction and the tests measure the real figure)
+    //   x 1.02 second-order terms of the above
     inline double tc_err_units(int D)
     {
-        return 1.02 * (3.0 + 192.0 + 32.0 * (tc_shape(D).kpad() / 16));
+        return 1.02 * (3.0 + 768.0 + 32.0 * (tc_shape(D).kpad() / 16));
     }
 
     struct TcScanParams

@@ -13,6 +13,7 @@
 
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include <cub/cub.cuh>
 
@@ -624,6 +625,8 @@ namespace omplcu
             pmax2_.reserve(1);
             CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
         }
+        if (const char *e = getenv("OMPLCU_TC_SCAN"))
+            tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
         counters_.reserve(4);
         CUDA_CHECK(cudaEventCreate(&ev0_));
         CUDA_CHECK(cudaEventCreate(&ev1_));
@@ -1073,7 +1076,7 @@ namespace omplcu
             tc_sh.na /= 2;  // long lists: fewer resident query tiles
             tc_stages = tc_pick_stages(tc_sh, tc_L);
         }
-        const bool tc_auto = D_ >= TC_MIN_DIM && nq >= 1024;
+        const bool tc_auto = nq >= TC_MIN_BATCH;  // measured faster than the FP32 scans at every batched size
         const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
         last_tc_ = tc ? 1 : 0;
         const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));

@@ -17,6 +17,15 @@ from oracle import oracle_py as orc
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["fp32-scan", "tensor-core-scan"])
+def scan_kernel(request, monkeypatch):
+    """Every test of this module runs twice: once with the filter scan on the FP32 pipe
+    (knn_scan.cuh / knn_scan_hd.cuh) and once on the tensor cores (knn_scan_tc.cu, forced even for
+    single queries).  OMPLCU_TC_SCAN is the default of the `tc_scan` option for new handles."""
+    monkeypatch.setenv("OMPLCU_TC_SCAN", "0" if request.param == "fp32-scan" else "1")
+    return request.param
+
+
 def _check_knn(nn, osp, pts_live, live_ids, qs, k, nthreads=8):
     ids, d = nn.nearestKBatch(qs, k)
     oi, od = orc.knn(osp, pts_live, qs, k, nthreads=nthreads)
@@ -429,3 +438,87 @@ def test_merge_topk_equals_single_index(gpu):
     check(lib().omplcu_merge_topk_strided_device(0, packed[0, 1].data_ptr(), packed[0, 0].data_ptr(), parts,
                                                  2 * nq * k, nq, k, od.data_ptr(), oi.data_ptr(), None))
     assert (oi.cpu().numpy().astype(np.uint64) == wi).all() and (od.cpu().numpy() == wd).all()
+
+
+# ---------------------------------------------------------------- tensor-core scan (knn_scan_tc.cu)
+def _tc_err_units(d):
+    k32 = (3 * d + 3 + 31) // 32
+    return 1.02 * (3.0 + 768.0 + 32.0 * (k32 * 32 // 16))
+
+
+@pytest.mark.parametrize("d", [1, 7, 9, 10, 20, 21, 33, 52, 53, 64, 100, 128])
+def test_tensor_core_scan_values_within_the_stated_error_bound(gpu, scan_kernel, d):
+    """Raw scan values (tcgen05.mma on BF16 split operands) against an FP64 evaluation of
+    s = |pt|^2 - 2 qt.pt on the FP32-rounded operands: the band check of the re-rank assumes
+    |s_tc - s| <= tc_err_units(d) * 2^-24 * (pmax2 + 2 |qt| pmax) (knn_scan_tc.cuh).  The measured
+    error must stay below half of that bound; every operand-image shape is covered
+    (chunks of 32 / 64 columns, 1 / 2 / 4 resident query tiles)."""
+    if scan_kernel != "tensor-core-scan":
+        pytest.skip("tensor-core scan only")
+    import torch
+
+    n, nq, k = 1500, 300, 10
+    r = np.random.default_rng(d)
+    pts, qs = r.uniform(-np.pi, np.pi, (n, d)), r.uniform(-np.pi, np.pi, (nq, d))
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    units, qpad = (n + 127) // 128, (nq + 511) // 512 * 512
+    buf = torch.full((qpad, units * 128), float("nan"), dtype=torch.float32, device="cuda")
+    nn.set_option("tc_scan_values_out", buf.data_ptr())
+    ids, dist = nn.nearestKBatch(qs, k)
+    nn.set_option("tc_scan_values_out", 0)
+    torch.cuda.synchronize()
+    assert nn.stat("last_tc") == 1
+    got = buf.cpu().numpy().astype(np.float64)[:nq, :n]
+    c = pts.mean(axis=0)
+    pt = (pts - c).astype(np.float32).astype(np.float64)
+    qt = (qs - c).astype(np.float32).astype(np.float64)
+    pn = (pt * pt).sum(1).astype(np.float32).astype(np.float64)  # the norm as stored
+    want = pn[None, :] - 2.0 * qt @ pt.T
+    pmax2, qn = pn.max(), np.sqrt((qt * qt).sum(1))
+    bound = _tc_err_units(d) * 2.0**-24 * (pmax2 + 2.0 * qn * np.sqrt(pmax2))
+    err = np.abs(got - want)
+    assert np.isfinite(got).all()
+    assert (err <= 0.5 * bound[:, None]).all(), f"max error {np.max(err / bound[:, None]):.3f} of the bound"
+    oi, od = orc.knn(orc.space_rv(d), pts, qs, k, nthreads=8)
+    assert (ids == oi).all() and (dist == od).all()
+
+
+def test_tensor_core_scan_is_the_batched_default(gpu, monkeypatch):
+    monkeypatch.delenv("OMPLCU_TC_SCAN", raising=False)
+    d, n = 7, 20000
+    pts = helpers.uniform_points(1, n, d)
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
+    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(3, 5, d), 10)
+    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 0  # single queries: FP32 scan
+    nn.set_option("tc_scan", 0)
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
+    assert nn.stat("last_tc") == 0
+
+
+@pytest.mark.parametrize("d", [7, 40, 100])
+def test_tensor_core_images_follow_add_and_remove(gpu, scan_kernel, d):
+    """The BF16 operand image is rebuilt lazily after every mutation: interleave add / remove /
+    query and compare each answer with the oracle on the live set."""
+    r = np.random.default_rng(7 + d)
+    pts = r.uniform(-1.0, 1.0, (6000, d))
+    qs = r.uniform(-1.0, 1.0, (130, d))
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts[:2500])
+    live = list(range(2500))
+    _check_knn(nn, orc.space_rv(d), pts[live], live, qs, 10)
+    for i in r.choice(2500, 400, replace=False):
+        assert nn.remove_id(int(i))
+        live.remove(int(i))
+    _check_knn(nn, orc.space_rv(d), pts[live], live, qs, 10)
+    nn.add_rows(pts[2500:])
+    live += list(range(2500, 6000))
+    _check_knn(nn, orc.space_rv(d), pts[live], live, qs, 14)
+    for i in r.choice(live, 3500, replace=False):  # crosses the compaction threshold
+        assert nn.remove_id(int(i))
+        live.remove(int(i))
+    _check_knn(nn, orc.space_rv(d), pts[live], live, qs, 36)
+    assert nn.stat("last_path") == 1
