@@ -25,7 +25,11 @@ namespace omplcu
 {
     namespace
     {
-        constexpr int TC_THREADS = 320;  // TMA warp, MMA warp, 8 selection warps (two per TMEM lane quadrant)
+        // threads per CTA: TMA warp, MMA warp, four selection warps per resident query tile
+        __host__ __device__ constexpr int tc_threads(int NA)
+        {
+            return 64 + 128 * NA;
+        }
         constexpr int TC_ACC = 4;  // accumulator buffers (4 x 128 = all 512 TMEM columns)
         constexpr int TC_MAX_STAGES = 8;
 
@@ -235,31 +239,61 @@ namespace omplcu
             uint32_t tmem_base;
         };
 
-        // diagnostics (DBG instantiation only): raw scan values of one 32-column step
-        __device__ __noinline__ void tc_dump(const TcScanParams &P, const uint32_t (&v)[32], size_t q, uint32_t col0)
+        __device__ __forceinline__ void tmem_ld16_issue(uint32_t taddr, uint32_t (&r)[16])
+        {
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+                         "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                         : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]),
+                           "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]),
+                           "=r"(r[14]), "=r"(r[15])
+                         : "r"(taddr)
+                         : "memory");
+        }
+        __device__ __forceinline__ void tmem_ld_wait(uint32_t (&r)[16])
+        {
+            asm volatile("tcgen05.wait::ld.sync.aligned;"
+                         : "+r"(r[0]), "+r"(r[1]), "+r"(r[2]), "+r"(r[3]), "+r"(r[4]), "+r"(r[5]), "+r"(r[6]),
+                           "+r"(r[7]), "+r"(r[8]), "+r"(r[9]), "+r"(r[10]), "+r"(r[11]), "+r"(r[12]), "+r"(r[13]),
+                           "+r"(r[14]), "+r"(r[15])
+                         :
+                         : "memory");
+        }
+        __device__ __forceinline__ void tmem_ld_issue(uint32_t taddr, uint32_t (&r)[32])
+        {
+            tmem_ld32_issue(taddr, r);
+        }
+        __device__ __forceinline__ void tmem_ld_issue(uint32_t taddr, uint32_t (&r)[16])
+        {
+            tmem_ld16_issue(taddr, r);
+        }
+
+        // diagnostics (DBG instantiation only): raw scan values of one W-column step
+        template <int W>
+        __device__ __noinline__ void tc_dump(const TcScanParams &P, const uint32_t (&v)[W], size_t q, uint32_t col0)
         {
             float *d = P.dbg + q * (P.units * TC_PT) + col0;
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
+            for (int i = 0; i < W; ++i)
                 d[i] = __uint_as_float(v[i]);
         }
 
         // The slow path of the selection, out of line so that the hot loop stays small in the
-        // instruction cache: visit the values of this thread's staged 32-column chunk that beat the
+        // instruction cache: visit the values of this thread's staged W-column step that beat the
         // threshold, in column order, and put each into the list (it replaces the current maximum).
-        template <int L>
+        // scr_q: the thread's column of the warp's [W][32] staging block.
+        template <int L, int W>
         __device__ __noinline__ float tc_select_hits(float thr, const float *scr_q, float *lvq, uint32_t *liq,
                                                      uint32_t id0)
         {
             uint32_t mask = 0;
 #pragma unroll
-            for (int i = 0; i < 32; ++i)
-                mask |= scr_q[i * TC_QT] < thr ? 1u << i : 0u;
+            for (int i = 0; i < W; ++i)
+                mask |= scr_q[i * 32] < thr ? 1u << i : 0u;
             while (mask)
             {
                 const int i = __ffs(mask) - 1;
                 mask &= mask - 1;
-                const float x = scr_q[i * TC_QT];
+                const float x = scr_q[i * 32];
                 if (x < thr)
                 {
                     const uint32_t slot = __float_as_uint(thr) & TAG_MASK;
@@ -284,7 +318,7 @@ namespace omplcu
         // into gridDim.x equal pieces as in knn_scan.cuh.  A super-tile is NA query tiles of 128; per
         // point tile the CTA runs NA "jobs" (one accumulator each, job j -> TMEM buffer j % 4).
         template <int L, int NA, bool DBG>
-        __global__ void __launch_bounds__(TC_THREADS, 1) knn_scan_tc_kernel(const TcScanParams P)
+        __global__ void __launch_bounds__(tc_threads(NA), 1) knn_scan_tc_kernel(const TcScanParams P)
         {
             extern __shared__ __align__(1024) uint8_t tc_smem[];
             constexpr int LS = L + 4;
@@ -295,8 +329,9 @@ namespace omplcu
             uint8_t *sB = sA + (size_t)NA * a_tile_bytes;             // [nst][chunk]
             float *lv = reinterpret_cast<float *>(sB + (size_t)nst * chunk_bytes);  // [NA][128][LS]
             uint32_t *li = reinterpret_cast<uint32_t *>(lv + NA * TC_QT * LS);      // [NA][L][128]
-            float *scr = reinterpret_cast<float *>(li + NA * L * TC_QT);            // [32][128] slow-path staging, [NA][128] thresholds
-            TcSmem *S = reinterpret_cast<TcSmem *>(scr + (32 * (NA >= 2 ? 2 : 1) + NA) * TC_QT);
+            float *scr = reinterpret_cast<float *>(li + NA * L * TC_QT);            // [4 NA warps][W][32] slow-path staging
+            constexpr int W = NA == 4 ? 16 : 32;  // columns per selection step (register budget at 576 threads)
+            TcSmem *S = reinterpret_cast<TcSmem *>(scr + 4 * NA * W * 32);
 
             const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
             const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
@@ -428,66 +463,57 @@ namespace omplcu
                     }
                 }
             }
-            else if (((warp - 2) >> 2) < (NA >= 2 ? 2 : 1))
+            else
             {
-                // selection: this thread's TMEM lane is its query (one per resident tile).  A query's
-                // list lives in shared memory, LS = L + 4 floats apart (conflict-free LDS.128 across
-                // lanes); values carry their list slot in the low mantissa bits (knn_scan.cuh: tag_up),
-                // so the running maximum names the entry to overwrite and ONE max-tree over the list
-                // yields the next threshold and the next victim.  The hot loop is kept to two copies of
-                // the 32-column step (the two register buffers of the TMEM load pipeline) so that it
-                // stays resident in the instruction cache; thresholds of the NA tiles sit in shared memory.
-                // Two warps share a lane quadrant; with NA >= 2 they take alternate tiles (a query belongs
-                // to one warp only), with NA = 1 the second warp of a quadrant has nothing to do.
-                const int wq = warp & 3, qrow = wq * 32 + lane, half = (warp - 2) >> 2;
-                constexpr int WSPLIT = NA >= 2 ? 2 : 1;
-                float *thr_s = scr + 32 * TC_QT * WSPLIT;  // [NA][128]
-                scr += half * 32 * TC_QT;
+                // selection: warp (a, wq) owns TMEM lane quadrant wq of the accumulators of resident
+                // tile a; a thread's lane is its query.  The query's list lives in shared memory,
+                // LS = L + 4 floats apart (conflict-free LDS.128 across lanes); values carry their list
+                // slot in the low mantissa bits (knn_scan.cuh: tag_up), so the running maximum `thr`
+                // names the entry to overwrite and ONE max-tree over the list yields the next threshold
+                // and the next victim.  The hot loop is two copies of the W-column step (the two register
+                // buffers of the TMEM load pipeline) and stays resident in the instruction cache.
+                const int a = (warp - 2) >> 2, wq = warp & 3, qrow = wq * 32 + lane;
+                float *lvq = lv + (a * TC_QT + qrow) * LS;
+                uint32_t *liq = li + a * L * TC_QT + qrow;
+                float *scr_q = scr + (warp - 2) * W * 32 + lane;
+                float thr = 0.f;
                 auto reset = [&]() {
-                    for (int a = half; a < NA; a += WSPLIT)
+                    for (int i = 0; i < L; ++i)
                     {
-                        for (int i = 0; i < L; ++i)
-                        {
-                            lv[(a * TC_QT + qrow) * LS + i] = __uint_as_float(EMPTY_BITS | (uint32_t)i);
-                            li[(a * L + i) * TC_QT + qrow] = SLOT_NONE;
-                        }
-                        thr_s[a * TC_QT + qrow] = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
+                        lvq[i] = __uint_as_float(EMPTY_BITS | (uint32_t)i);
+                        liq[i * TC_QT] = SLOT_NONE;
                     }
+                    thr = __uint_as_float(EMPTY_BITS | (uint32_t)(L - 1));
                 };
                 auto flush = [&](unsigned long long t) {
                     const unsigned long long x = t * U;
                     const unsigned long long gfirst = ((x + 1) * G + TU - 1) / TU - 1;
                     const unsigned seg = (unsigned)(g - gfirst);
-                    for (int a = half; a < NA; a += WSPLIT)
-                    {
-                        const size_t q = ((size_t)t * NA + a) * TC_QT + qrow;
-                        P.cand_thr[(size_t)seg * P.qpad + q] = thr_s[a * TC_QT + qrow];
-                        for (int i = 0; i < L; ++i)
-                            P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = li[(a * L + i) * TC_QT + qrow];
-                    }
+                    const size_t q = ((size_t)t * NA + a) * TC_QT + qrow;
+                    P.cand_thr[(size_t)seg * P.qpad + q] = thr;
+                    for (int i = 0; i < L; ++i)
+                        P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = liq[i * TC_QT];
                 };
-                // one 32-column step: min-tree against the threshold; the rare hit stages the values in
+                // one W-column step: min-tree against the threshold; the rare hit stages the values in
                 // shared memory and calls the out-of-line routine
-                auto step = [&](uint32_t(&v)[32], float th, int a, uint32_t id0) -> float {
+                auto step = [&](uint32_t(&v)[W], uint32_t id0) {
                     float m0 = fminf(__uint_as_float(v[0]), __uint_as_float(v[1]));
                     float m1 = fminf(__uint_as_float(v[2]), __uint_as_float(v[3]));
 #pragma unroll
-                    for (int i = 4; i < 32; i += 4)
+                    for (int i = 4; i < W; i += 4)
                     {
                         m0 = fminf(m0, fminf(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
                         m1 = fminf(m1, fminf(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])));
                     }
-                    if (fminf(m0, m1) < th && !(P.diag & 4))
+                    if (fminf(m0, m1) < thr && !(P.diag & 4))
                     {
 #pragma unroll
-                        for (int i = 0; i < 32; ++i)
-                            scr[i * TC_QT + qrow] = __uint_as_float(v[i]);
-                        th = tc_select_hits<L>(th, scr + qrow, lv + (a * TC_QT + qrow) * LS, li + a * L * TC_QT + qrow,
-                                               id0);
+                        for (int i = 0; i < W; ++i)
+                            scr_q[i * 32] = __uint_as_float(v[i]);
+                        thr = tc_select_hits<L, W>(thr, scr_q, lvq, liq, id0);
                     }
-                    return th;
                 };
-                unsigned long long cur = ~0ull, job = 0, t = 0, pt = 0;
+                unsigned long long cur = ~0ull, job = a, t = 0, pt = 0;
                 for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
                 {
                     if (u == u0 || pt == U)
@@ -500,42 +526,35 @@ namespace omplcu
                         cur = t;
                     }
                     const uint32_t slot0 = (uint32_t)(pt * TC_PT);
-#pragma unroll 1
-                    for (int a = half; a < NA; a += WSPLIT)
+                    const int buf = (int)(job & (TC_ACC - 1));
+                    mbar_wait(&S->t_full[buf], (uint32_t)((job / TC_ACC) & 1));
+                    tc_fence_after();
+                    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
+                    if (!(P.diag & 2))
                     {
-                        const unsigned long long j = job + a;
-                        const int buf = (int)(j & (TC_ACC - 1));
-                        mbar_wait(&S->t_full[buf], (uint32_t)((j / TC_ACC) & 1));
-                        tc_fence_after();
-                        const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
-                        if (!(P.diag & 2))
-                        {
-                            uint32_t ra[32], rb[32];
-                            float th = thr_s[a * TC_QT + qrow];
-                            __syncwarp();
-                            tmem_ld32_issue(taddr, ra);
+                        uint32_t ra[W], rb[W];
+                        __syncwarp();
+                        tmem_ld_issue(taddr, ra);
 #pragma unroll 1
-                            for (int c = 0; c < TC_PT / 32; c += 2)
-                            {
-                                __syncwarp();
-                                tmem_ld_wait(ra);
-                                tmem_ld32_issue(taddr + (c + 1) * 32, rb);  // in flight during the tree below
-                                if (DBG)
-                                    tc_dump(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * 32);
-                                th = step(ra, th, a, slot0 + c * 32);
-                                __syncwarp();
-                                tmem_ld_wait(rb);
-                                if (c + 2 < TC_PT / 32)
-                                    tmem_ld32_issue(taddr + (c + 2) * 32, ra);
-                                if (DBG)
-                                    tc_dump(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * 32);
-                                th = step(rb, th, a, slot0 + (c + 1) * 32);
-                            }
-                            thr_s[a * TC_QT + qrow] = th;
+                        for (int c = 0; c < TC_PT / W; c += 2)
+                        {
+                            __syncwarp();
+                            tmem_ld_wait(ra);
+                            tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
+                            if (DBG)
+                                tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
+                            step(ra, slot0 + c * W);
+                            __syncwarp();
+                            tmem_ld_wait(rb);
+                            if (c + 2 < TC_PT / W)
+                                tmem_ld_issue(taddr + (c + 2) * W, ra);
+                            if (DBG)
+                                tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
+                            step(rb, slot0 + (c + 1) * W);
                         }
-                        tc_fence_before();
-                        mbar_arrive(&S->t_empty[buf]);
                     }
+                    tc_fence_before();
+                    mbar_arrive(&S->t_empty[buf]);
                 }
                 if (cur != ~0ull)
                     flush(cur);
@@ -555,7 +574,7 @@ namespace omplcu
     {
         const size_t chunk = (size_t)sh.kw * 2048;
         return (size_t)sh.na * sh.nkc * chunk + (size_t)nstages * chunk + (size_t)sh.na * TC_QT * (2 * L + 4) * 4 +
-               (32 * (sh.na >= 2 ? 2 : 1) + sh.na) * TC_QT * 4 + sizeof(TcSmem) + 64;
+               (size_t)4 * sh.na * (sh.na == 4 ? 16 : 32) * 32 * 4 + sizeof(TcSmem) + 64;
     }
 
     int tc_pick_stages(const TcShape &sh, int L)
@@ -592,12 +611,12 @@ namespace omplcu
             {
                 CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, NA, true>,
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-                knn_scan_tc_kernel<L, NA, true><<<grid, TC_THREADS, smem, s>>>(P);
+                knn_scan_tc_kernel<L, NA, true><<<grid, tc_threads(NA), smem, s>>>(P);
                 return;
             }
             CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, NA, false>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            knn_scan_tc_kernel<L, NA, false><<<grid, TC_THREADS, smem, s>>>(P);
+            knn_scan_tc_kernel<L, NA, false><<<grid, tc_threads(NA), smem, s>>>(P);
         }
         template <int L>
         void tc_launch_na(const TcScanParams &P, unsigned grid, cudaStream_t s)

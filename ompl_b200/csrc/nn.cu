@@ -871,6 +871,8 @@ namespace omplcu
             scan_ctas_per_sm_ = (int)v;  // 0 = as many as fit
         else if (!strcmp(key, "tc_scan"))
             tc_mode_ = (int)v;  // -1 auto, 0 never, 1 whenever the space is eligible
+        else if (!strcmp(key, "tc_tiles"))
+            tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
         else if (!strcmp(key, "tc_variant"))
         {
             tc_variant_ = (int)v;
@@ -1069,6 +1071,8 @@ namespace omplcu
         // spare entries (16 / 24 / 48 instead of 12 / 16 / 42): the band check then compares the
         // k-th exact distance with the (k + 6)-th scan value or later, and fall-backs stay rare.
         TcShape tc_sh = tc_shape(D_);
+        if (tc_na_ > 0 && tc_na_ < tc_sh.na)
+            tc_sh.na = tc_na_;
         const int tc_L = cfg == 0 ? 16 : (cfg == 1 ? 24 : 48);
         int tc_stages = tc_pick_stages(tc_sh, tc_L);
         while (tc_stages == 0 && tc_sh.na > 1)

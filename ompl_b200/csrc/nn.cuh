@@ -113,6 +113,7 @@ namespace omplcu
         DevBuf<uint16_t> tc_pimg_, tc_qimg_;
         unsigned long mut_version_ = 1, tc_version_ = 0;
         int tc_mode_ = -1;        // -1 auto (d >= 64 and >= 1024 queries), 0 off, 1 whenever eligible
+        int tc_na_ = 0;
         int tc_variant_ = 0;      // image layout / descriptor variants (diagnostics)
         float *tc_dbg_ = nullptr; // device buffer for raw scan values (diagnostics), caller-owned
         long last_tc_ = 0;
