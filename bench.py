@@ -10,8 +10,12 @@ step     one batched nearestK over the whole query batch
   e2e        through the host-pointer C-ABI call omplcu_nn_knn (what the C++
              adapter NearestNeighborsCUDA::nearestKBatch calls): H2D of the
              queries and D2H of ids + distances inside the timed region
-  roofline   the scan kernel (knn_scan_kernel), FP32-pipe bound; its duration
-             is measured live with CUDA events on the launching stream
+  roofline   the dominant kernel: the tensor-core filter scan (knn_scan_tc_kernel:
+             tcgen05.mma on BF16 split operands, selection straight from TMEM); its
+             duration is measured live with CUDA events on the launching stream and
+             put against the measured dense BF16 peak (MEASURED_PEAKS.json).
+             roofline_fp32_scan: the same step with the FP32-pipe scan kernel
+             (knn_scan_kernel, option tc_scan = 0) against the FP32 FMA peak
   cpu_baseline / --impl reference
              the reference's own NearestNeighborsGNAT (oracle/_ref, compiled
              from the reference headers) on all host threads; falls back to the
@@ -40,6 +44,7 @@ N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
 N_SEGMENTS = 1_000_000
 MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
+TC_TRAFFIC = None  # bytes per launch of the tensor-core scan from the ncu capture (set when profiled)
 UNIT = "queries/s"
 
 
@@ -241,6 +246,8 @@ def run_gpu_arm(args):
         nn.set_option("scan_ctas_per_sm", args.scan_ctas)
     if args.no_sample_thr:
         nn.set_option("sample_thresholds", 0)
+    if args.fp32_scan:
+        nn.set_option("tc_scan", 0)
 
     d_q = torch.from_numpy(qs).to(dev)
     packed = sharding.PackedLists(world, N_QUERIES, K, dev)  # ids + distances in one buffer: one all-gather
@@ -322,11 +329,21 @@ def run_gpu_arm(args):
     launches_timed = launches * args.steps // (args.steps + args.warmup)
     scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
     fallbacks = nn.stat("last_fallbacks")
+    used_tc = nn.stat("last_tc") == 1
     _, e2e_wall_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
 
     # sanity: device-resident and host-pointer results agree (same code path underneath)
     res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
     assert (res_ids == h_ids).all(), "device and host entry points disagree"
+
+    # the same step on the FP32-pipe scan kernel (the round-1 default), for the second roofline
+    fp32_leg = None
+    if used_tc:
+        nn.set_option("tc_scan", 0)
+        nn.set_option("profile", 1)
+        f_ms, _, _ = timed(step_device, max(args.steps // 2, 2), 3)
+        fp32_leg = (f_ms / max(args.steps // 2, 2), nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1))
+        nn.set_option("tc_scan", -1)
 
     motion = None if args.no_motion else motion_block(args, torch, dist, dev, local, rank, world, timed)
 
@@ -334,39 +351,73 @@ def run_gpu_arm(args):
         t_step = dev_ms / args.steps
         value = N_QUERIES / (t_step * 1e-3)
         e2e_val = N_QUERIES / (e2e_wall_ms / args.steps * 1e-3)
-        # roofline of the dominant kernel (the scan), FP32 pipe
+        # rooflines of the dominant kernel (the filter scan)
         ffma, ffma2 = C.c_double(), C.c_double()
         check(L.omplcu_measure_fp32_peak(local, C.byref(ffma), C.byref(ffma2)))
-        peak = max(ffma.value, ffma2.value)
+        fp32_peak = max(ffma.value, ffma2.value)
         pairs = float(N_QUERIES) * (hi - lo)
         alg_flops = 3.0 * DIM * pairs           # sub, mul, add per dimension
-        exe_flops = 2.0 * DIM * pairs           # what the kernel issues: DIM FMAs per pair
-        ach = alg_flops / (scan_ns * 1e-9) / 1e12
         peaks = {}
         try:
             peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
         except OSError:
             pass
         hbm_peak = peaks.get("hbm_gbs", 6650.0)
-        scan_bytes = 4.0 * 8 * (hi - lo) * (N_QUERIES / 512.0)  # every query tile streams the filter copy (L2-resident)
-        roofline = {
-            "bound": "fp32", "kernel": "knn_scan_kernel<7,4,12>", "achieved": ach, "peak": peak, "unit": "TFLOP/s",
-            "frac": ach / peak if peak else None,
-            # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
-            # (profiles/r1_scan_v3_ncu_summary.csv); algorithmic: 32 MB filter copy + 1.8 MB queries + lists
-            "traffic": 34.9e6 if world == 1 else None, "traffic_unit": "bytes/launch",
-            "peak_source": "FP32 FMA pipe measured live on this GPU (omplcu_measure_fp32_peak: FFMA "
-                           f"{ffma.value:.1f}, FFMA2 {ffma2.value:.1f} TFLOP/s); MEASURED_PEAKS.json has no FP32 figure",
-            "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * DIM,
-            "frac_executed": exe_flops / (scan_ns * 1e-9) / 1e12 / peak if peak else None,
-            "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
-            "hbm_view": {"l2_stream_gbs": scan_bytes / (scan_ns * 1e-9) / 1e9, "hbm_peak_gbs": hbm_peak,
-                         "note": "filter copy (32 MB) is L2-resident; HBM is not the bound for batched queries"},
-        }
+        fp32_src = ("FP32 FMA pipe measured live on this GPU (omplcu_measure_fp32_peak: FFMA "
+                    f"{ffma.value:.1f}, FFMA2 {ffma2.value:.1f} TFLOP/s); MEASURED_PEAKS.json has no FP32 figure")
+
+        def fp32_roofline(kernel_ns, step_ms):
+            exe = 2.0 * DIM * pairs             # what the kernel issues: DIM FMAs per pair
+            a = alg_flops / (kernel_ns * 1e-9) / 1e12
+            scan_bytes = 4.0 * 8 * (hi - lo) * (N_QUERIES / 512.0)  # every query tile streams the filter copy
+            return {
+                "bound": "fp32", "kernel": "knn_scan_kernel<7,4,12>", "achieved": a, "peak": fp32_peak,
+                "unit": "TFLOP/s", "frac": a / fp32_peak if fp32_peak else None,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+                # (profiles/r1_scan_v3_ncu_summary.csv); algorithmic: 32 MB filter copy + 1.8 MB queries + lists
+                "traffic": 34.9e6 if world == 1 else None, "traffic_unit": "bytes/launch",
+                "peak_source": fp32_src, "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * DIM,
+                "frac_executed": exe / (kernel_ns * 1e-9) / 1e12 / fp32_peak if fp32_peak else None,
+                "kernel_ms": kernel_ns * 1e-6, "kernel_share_of_step": kernel_ns * 1e-6 / step_ms,
+                "hbm_view": {"l2_stream_gbs": scan_bytes / (kernel_ns * 1e-9) / 1e9, "hbm_peak_gbs": hbm_peak,
+                             "note": "filter copy (32 MB) is L2-resident; HBM is not the bound for batched queries"},
+            }
+
+        roofline_fp32 = None
+        if used_tc:
+            kpad = (3 * DIM + 3 + 31) // 32 * 32
+            tpeak = peaks.get("bf16_tflops", 2250.0)
+            ach = alg_flops / (scan_ns * 1e-9) / 1e12
+            exe = 2.0 * kpad * pairs            # MMA flops issued: K = 3d + 3 padded to 32
+            roofline = {
+                "bound": "tensor", "kernel": "knn_scan_tc_kernel<16,4> (+ query image kernel)", "achieved": ach,
+                "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
+                # (profiles/r1_scan_tc_ncu_summary.csv); algorithmic: 64 MB operand image + queries + lists
+                "traffic": TC_TRAFFIC if world == 1 else None, "traffic_unit": "bytes/launch",
+                "peak_source": "MEASURED_PEAKS.json bf16_tflops (dense BF16 cuBLAS, burst: the kernel is timed alone)"
+                if "bf16_tflops" in peaks else "fallback 2250 TFLOP/s (B200_PROFILING.md): MEASURED_PEAKS.json absent",
+                "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * kpad,
+                "frac_executed": exe / (scan_ns * 1e-9) / 1e12 / tpeak,
+                "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
+                "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
+                "note": "K = 32 per accumulator: the kernel is bound by the MMA -> TMEM -> selection hand-over "
+                        "(TMEM capacity / round-trip latency), not by the tensor pipe (ncu: tensor pipe ~17 % "
+                        "busy) and not by HBM; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which "
+                        "bounded the round-1 FP32 scan (roofline_fp32_scan)",
+            }
+            if fp32_leg:
+                roofline_fp32 = fp32_roofline(fp32_leg[1], fp32_leg[0])
+                roofline_fp32["ms_per_step"] = fp32_leg[0]
+                roofline_fp32["queries_per_s"] = N_QUERIES / (fp32_leg[0] * 1e-3)
+        else:
+            roofline = fp32_roofline(scan_ns, t_step)
         out = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_step, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32 filter + f64 exact re-rank", "data": "synthetic",
+            "vs_baseline": None,
+            "dtype": "bf16x2 split filter on tensor cores (f32 accumulate) + f64 exact re-rank" if used_tc
+            else "f32 filter + f64 exact re-rank", "data": "synthetic",
             "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
                        "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
                        "sharding": f"states split by insertion index over {world} rank(s); NCCL all-gather + merge"
@@ -379,6 +430,8 @@ def run_gpu_arm(args):
             "roofline": roofline,
             "exact_fallback_queries": int(fallbacks),
         }
+        if roofline_fp32 is not None:
+            out["roofline_fp32_scan"] = roofline_fp32
         if motion is not None:
             out["motion"] = motion
         if world == 1 and not args.no_cpu:
@@ -501,6 +554,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scan-ctas", type=int, default=0, help="tuning: cap resident scan CTAs per SM")
     ap.add_argument("--no-sample-thr", action="store_true", help="tuning: disable the threshold pre-pass")
+    ap.add_argument("--fp32-scan", action="store_true", help="use the FP32-pipe scan kernel instead of the tensor-core scan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
     ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")
     args = ap.parse_args()
