@@ -67,3 +67,63 @@ class PackedLists:
 
     def all_gather(self, group=None):
         dist.all_gather_into_tensor(self.gathered.view(-1, self.k), self.local.view(-1, self.k), group=group)
+
+
+# ----------------------------------------------------------------------
+# radius queries over a sharded roadmap (all-gather of counts, then of padded lists)
+# ----------------------------------------------------------------------
+def all_gather_radius(ids, dists, offsets, device="cpu", group=None):
+    """Merge per-shard nearestR results into the answer of the whole roadmap, on every rank.
+
+    ids / dists / offsets: this rank's NearestNeighborsCUDA.nearestRBatch output for ALL queries against
+    its shard (numpy; ids are global insertion indices via set_id_base, each query's slice sorted by
+    (distance, id), offsets = CSR boundaries, length nq + 1).  Two exchanges, as the lists are ragged:
+    the per-query counts of every rank, then every rank's lists padded to the longest rank total, ids
+    and the distances' bits packed in ONE int64 buffer.  `device` is where the exchanged tensors live
+    ("cpu" for gloo, a CUDA device for NCCL).  Returns (ids, dists, offsets) of the merged result; the
+    order (distance, id) is total and ids are insertion indices, so it equals the single-index answer
+    (NearestNeighborsLinear::nearestR, NearestNeighborsLinear.h:135-142, with ties by insertion index).
+    """
+    import numpy as np
+
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    ids = np.ascontiguousarray(ids, dtype=np.uint64)
+    dists = np.ascontiguousarray(dists, dtype=np.float64)
+    offsets = np.ascontiguousarray(offsets, dtype=np.int64)
+    nq = len(offsets) - 1
+    if nq < 0 or len(ids) != offsets[-1] or len(dists) != offsets[-1]:
+        raise ValueError("ids / dists / offsets do not describe one CSR result")
+    if world == 1:
+        return ids, dists, offsets
+    counts = torch.from_numpy(np.diff(offsets)).to(device)
+    g_counts = torch.empty((world, nq), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(g_counts.view(-1), counts, group=group)
+    g_counts = g_counts.cpu().numpy()
+    totals = g_counts.sum(axis=1)
+    pad = int(totals.max())
+    merged_off = np.concatenate([[0], np.cumsum(g_counts.sum(axis=0))]).astype(np.int64)
+    if pad == 0:
+        return np.empty(0, np.uint64), np.empty(0, np.float64), merged_off
+    local = np.zeros((2, pad), dtype=np.int64)
+    local[0, : len(ids)] = ids.view(np.int64)
+    local[1, : len(dists)] = dists.view(np.int64)
+    g = torch.empty((world, 2, pad), dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(g.view(world * 2, pad), torch.from_numpy(local).to(device), group=group)
+    g = g.cpu().numpy()
+    parts = [(g[r, 0, : totals[r]].view(np.uint64), g[r, 1, : totals[r]].view(np.float64), g_counts[r])
+             for r in range(world)]
+    return merge_radius_parts(parts)
+
+
+def merge_radius_parts(parts):
+    """parts: per shard (ids, dists, counts per query).  Returns the merged (ids, dists, offsets): per query
+    the union of the shards' neighbours ordered by (distance, id)."""
+    import numpy as np
+
+    nq = len(parts[0][2])
+    qidx = np.concatenate([np.repeat(np.arange(nq), np.asarray(c, dtype=np.int64)) for _, _, c in parts])
+    all_ids = np.concatenate([np.asarray(i, dtype=np.uint64) for i, _, _ in parts])
+    all_d = np.concatenate([np.asarray(d, dtype=np.float64) for _, d, _ in parts])
+    order = np.lexsort((all_ids, all_d, qidx))  # last key is the primary one
+    total = np.sum([np.asarray(c, dtype=np.int64) for _, _, c in parts], axis=0)
+    return all_ids[order], all_d[order], np.concatenate([[0], np.cumsum(total)]).astype(np.int64)

@@ -522,3 +522,28 @@ def test_tensor_core_images_follow_add_and_remove(gpu, scan_kernel, d):
         live.remove(int(i))
     _check_knn(nn, orc.space_rv(d), pts[live], live, qs, 36)
     assert nn.stat("last_path") == 1
+
+
+def test_sharded_radius_merge_equals_single_index(gpu):
+    """SURVEY 8(e), radius row: two shards with global id bases, nearestRBatch on each, merged by
+    (distance, id) (sharding.merge_radius_parts, the function all_gather_radius applies after the two
+    exchanges) == the single index holding everything, including duplicates that straddle the shards."""
+    from ompl_b200 import sharding
+
+    d, n, nq = 7, 6000, 96
+    pts = helpers.with_duplicates(helpers.uniform_points(11, n, d), 12, frac=0.05)
+    qs = np.vstack([helpers.uniform_points(13, nq - 6, d), pts[:6]])
+    radii = np.where(np.arange(nq) % 4 == 0, 0.0, 0.5)
+    whole = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    whole.add_rows(pts)
+    w_i, w_d, w_o = whole.nearestRBatch(qs, radii)
+    parts = []
+    for r in range(2):
+        lo, hi = sharding.shard_range(n, r, 2)
+        nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+        nn.set_id_base(lo)
+        nn.add_rows(pts[lo:hi])
+        i, x, o = nn.nearestRBatch(qs, radii)
+        parts.append((i, x, np.diff(o)))
+    m_i, m_d, m_o = sharding.merge_radius_parts(parts)
+    assert (m_o == w_o).all() and (m_i == w_i).all() and (m_d == w_d).all() and m_o[-1] > 1000

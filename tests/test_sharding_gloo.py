@@ -80,9 +80,22 @@ WORKER = textwrap.dedent("""
     parts.sort(key=lambda p: p[0])
     fv, ft = orc.check_motions(osp, ochk, a, b, last_valid=True)
     mot = bool((np.concatenate([p[1] for p in parts]) == fv).all() and (np.concatenate([p[2] for p in parts]) == ft).all())
-    print(f"RANK{{rank}} merge_ok={{ok}} same={{same}} motion_ok={{mot}}", flush=True)
+    # radius queries over the sharded roadmap: counts, then padded lists, merged by (distance, id)
+    def csr(points, base, radii):
+        ii, dd, off = [], [], [0]
+        for qv, r in zip(qs, radii):
+            i, x = orc.radius(sp, points, qv, r)
+            ii.append(i.astype(np.uint64) + np.uint64(base)); dd.append(x); off.append(off[-1] + len(i))
+        return np.concatenate(ii), np.concatenate(dd), np.array(off)
+    radii = np.where(np.arange(nq) % 5 == 0, 0.0, 0.45)     # some queries find nothing (or only exact hits)
+    r_i, r_d, r_o = sharding.all_gather_radius(*csr(pts[lo:hi], lo, radii))
+    w_i, w_d, w_o = csr(pts, 0, radii)
+    rad = bool((r_o == w_o).all() and (r_i == w_i).all() and (r_d == w_d).all() and r_o[-1] > 1000)
+    e_i, e_d, e_o = sharding.all_gather_radius(np.empty(0, np.uint64), np.empty(0), np.zeros(nq + 1, np.int64))
+    rad = rad and len(e_i) == 0 and (e_o == 0).all()
+    print(f"RANK{{rank}} merge_ok={{ok}} same={{same}} motion_ok={{mot}} radius_ok={{rad}}", flush=True)
     dist.destroy_process_group()
-    sys.exit(0 if ok and same and mot else 1)
+    sys.exit(0 if ok and same and mot and rad else 1)
 """)
 
 
@@ -112,4 +125,4 @@ def test_world_size_2_merge_equals_single_index(tmp_path):
         outs.append(out)
     for rank, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, f"rank {rank} failed:\n{out[-2000:]}"
-        assert f"RANK{rank} merge_ok=True same=True motion_ok=True" in out
+        assert f"RANK{rank} merge_ok=True same=True motion_ok=True radius_ok=True" in out
