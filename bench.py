@@ -236,7 +236,15 @@ def run_gpu_arm(args):
     from ompl_b200 import sharding
 
     pts, qs = make_inputs()
-    lo, hi = sharding.shard_range(N_STATES, rank, world)
+    # N > 1: S state shards x R query blocks (sharding.grid_shape); rank = s * R + r
+    S_SH, R_QB = (1, 1) if args.shard == "single" else sharding.grid_shape(world, N_STATES)
+    if args.shard == "states":
+        S_SH, R_QB = world, 1
+    sh_s, sh_r = divmod(rank, R_QB)
+    lo, hi = sharding.shard_range(N_STATES, sh_s, S_SH)
+    assert N_QUERIES % R_QB == 0
+    NQB = N_QUERIES // R_QB           # queries answered by this rank
+    qlo = sh_r * NQB
     sp = ob.RealVectorStateSpace(DIM, device=local)
     nn = ob.NearestNeighborsCUDA(sp)
     nn.set_id_base(lo)
@@ -249,44 +257,53 @@ def run_gpu_arm(args):
     if args.fp32_scan:
         nn.set_option("tc_scan", 0)
 
+    qs_all = qs
+    qs = np.ascontiguousarray(qs_all[qlo:qlo + NQB])
     d_q = torch.from_numpy(qs).to(dev)
-    packed = sharding.PackedLists(world, N_QUERIES, K, dev)  # ids + distances in one buffer: one all-gather
+    packed = sharding.PackedLists(world, NQB, K, dev)  # ids + distances in one buffer: one all-gather
     d_ids, d_d = packed.ids, packed.dists
     if world > 1:
-        m_ids, m_d = torch.empty_like(d_ids), torch.empty_like(d_d)
+        m_ids = torch.empty((N_QUERIES, K), dtype=torch.int64, device=dev)
+        m_d = torch.empty((N_QUERIES, K), dtype=torch.float64, device=dev)
+
+    def merge_blocks():
+        # block r: the S lists of ranks s * R + r, part_stride = R rank buffers apart
+        g_i, g_d = packed.gathered_ids(), packed.gathered_dists()
+        for r in range(R_QB):
+            check(L.omplcu_merge_topk_strided_device(local, g_d[r].data_ptr(), g_i[r].data_ptr(), S_SH,
+                                                     R_QB * packed.part_stride, NQB, K,
+                                                     m_d[r * NQB:].data_ptr(), m_ids[r * NQB:].data_ptr(), sptr))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream()
     sptr = C.c_void_p(stream.cuda_stream)
 
     def step_device():
-        check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), N_QUERIES, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
+        check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), NQB, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
         if world > 1:
             packed.all_gather()
-            check(L.omplcu_merge_topk_strided_device(local, packed.gathered_dists().data_ptr(),
-                                                     packed.gathered_ids().data_ptr(), world, packed.part_stride,
-                                                     N_QUERIES, K, m_d.data_ptr(), m_ids.data_ptr(), sptr))
+            merge_blocks()
 
-    h_ids = np.empty((N_QUERIES, K), dtype=np.uint64)
-    h_d = np.empty((N_QUERIES, K), dtype=np.float64)
-    h_cnt = np.empty(N_QUERIES, dtype=np.uint32)
+    h_ids = np.empty((NQB, K), dtype=np.uint64)
+    h_d = np.empty((NQB, K), dtype=np.float64)
+    h_cnt = np.empty(NQB, dtype=np.uint32)
+    h_all_ids = np.empty((N_QUERIES, K), dtype=np.uint64) if world > 1 else h_ids
+    h_all_d = np.empty((N_QUERIES, K), dtype=np.float64) if world > 1 else h_d
     pin = lambda a: torch.cuda.cudart().cudaHostRegister(a.ctypes.data, a.nbytes, 0)  # noqa: E731
     for a in (qs, h_ids, h_d):
         pin(a)
 
     def step_e2e():
         # host buffers in, host buffers out: the reference-facing call
-        check(L.omplcu_nn_knn(nn.handle, qs.ctypes.data, N_QUERIES, K, h_ids.ctypes.data, h_d.ctypes.data,
+        check(L.omplcu_nn_knn(nn.handle, qs.ctypes.data, NQB, K, h_ids.ctypes.data, h_d.ctypes.data,
                               h_cnt.ctypes.data))
         if world > 1:
             # sharded roadmap: merge needs the other shards' lists; exchange on the device
             d_ids.copy_(torch.from_numpy(h_ids.view(np.int64)), non_blocking=True)
             d_d.copy_(torch.from_numpy(h_d), non_blocking=True)
             packed.all_gather()
-            check(L.omplcu_merge_topk_strided_device(local, packed.gathered_dists().data_ptr(),
-                                                     packed.gathered_ids().data_ptr(), world, packed.part_stride,
-                                                     N_QUERIES, K, m_d.data_ptr(), m_ids.data_ptr(), sptr))
-            h_ids.view(np.int64)[:] = m_ids.cpu().numpy()
-            h_d[:] = m_d.cpu().numpy()
+            merge_blocks()
+            h_all_ids.view(np.int64)[:] = m_ids.cpu().numpy()
+            h_all_d[:] = m_d.cpu().numpy()
 
     def barrier():
         if world > 1:
@@ -325,7 +342,7 @@ def run_gpu_arm(args):
     nn.set_option("profile", 1)
     sampler = ClockSampler(local) if rank == 0 else None
     dev_ms, _, clocks = timed(step_device, args.steps, args.warmup, sampler)
-    launches = nn.stat("launches") - l0 + (args.steps + args.warmup) * (1 if world > 1 else 0)
+    launches = nn.stat("launches") - l0 + (args.steps + args.warmup) * (R_QB if world > 1 else 0)
     launches_timed = launches * args.steps // (args.steps + args.warmup)
     scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
     fallbacks = nn.stat("last_fallbacks")
@@ -334,7 +351,7 @@ def run_gpu_arm(args):
 
     # sanity: device-resident and host-pointer results agree (same code path underneath)
     res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
-    assert (res_ids == h_ids).all(), "device and host entry points disagree"
+    assert (res_ids == h_all_ids).all(), "device and host entry points disagree"
 
     # the same step on the FP32-pipe scan kernel (the round-1 default), for the second roofline
     fp32_leg = None
@@ -355,7 +372,7 @@ def run_gpu_arm(args):
         ffma, ffma2 = C.c_double(), C.c_double()
         check(L.omplcu_measure_fp32_peak(local, C.byref(ffma), C.byref(ffma2)))
         fp32_peak = max(ffma.value, ffma2.value)
-        pairs = float(N_QUERIES) * (hi - lo)
+        pairs = float(NQB) * (hi - lo)
         alg_flops = 3.0 * DIM * pairs           # sub, mul, add per dimension
         peaks = {}
         try:
@@ -369,7 +386,7 @@ def run_gpu_arm(args):
         def fp32_roofline(kernel_ns, step_ms):
             exe = 2.0 * DIM * pairs             # what the kernel issues: DIM FMAs per pair
             a = alg_flops / (kernel_ns * 1e-9) / 1e12
-            scan_bytes = 4.0 * 8 * (hi - lo) * (N_QUERIES / 512.0)  # every query tile streams the filter copy
+            scan_bytes = 4.0 * 8 * (hi - lo) * (NQB / 512.0)  # every query tile streams the filter copy
             return {
                 "bound": "fp32", "kernel": "knn_scan_kernel<7,4,12>", "achieved": a, "peak": fp32_peak,
                 "unit": "TFLOP/s", "frac": a / fp32_peak if fp32_peak else None,
@@ -420,12 +437,13 @@ def run_gpu_arm(args):
             else "f32 filter + f64 exact re-rank", "data": "synthetic",
             "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
                        "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
-                       "sharding": f"states split by insertion index over {world} rank(s); NCCL all-gather + merge"
+                       "sharding": f"{S_SH} state shard(s) by insertion index x {R_QB} query block(s) over {world} ranks; "
+                                   "one NCCL all-gather of the packed (distance, id) lists + merge by (distance, id)"
                        if world > 1 else "single GPU",
                        "l2": "flushed between timed iterations (256 MB write)"},
             "clocks": clocks,
-            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes),
-                    "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes)},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes) * world,
+                    "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes) * world},
             "gpu_launches": int(launches_timed),
             "roofline": roofline,
             "exact_fallback_queries": int(fallbacks),
@@ -554,6 +572,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--scan-ctas", type=int, default=0, help="tuning: cap resident scan CTAs per SM")
     ap.add_argument("--no-sample-thr", action="store_true", help="tuning: disable the threshold pre-pass")
+    ap.add_argument("--shard", default="grid", choices=["grid", "states", "single"],
+                    help="N > 1: 'grid' = state shards x query blocks (sharding.grid_shape), 'states' = N state shards")
     ap.add_argument("--fp32-scan", action="store_true", help="use the FP32-pipe scan kernel instead of the tensor-core scan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
     ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")

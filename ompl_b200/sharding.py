@@ -20,6 +20,21 @@ def shard_range(n, rank, world):
     return n * rank // world, n * (rank + 1) // world
 
 
+def grid_shape(world, n_states, min_shard=500_000):
+    """(S, R) with S * R = world: the roadmap is cut into S state shards and the query batch into R blocks;
+    rank = s * R + r holds shard s and answers block r.  S is the largest divisor of `world` that keeps
+    n_states / S >= min_shard, but at least 2 once there are 2 ranks (the roadmap IS sharded): below
+    ~500K states per shard the scan's fixed cost per (query, shard) list outweighs the shorter stream,
+    so further ranks are better spent on disjoint query blocks.  One all-gather still
+    moves every rank's lists; block r is merged from the S ranks s * R + r."""
+    best = 1
+    for s in range(1, world + 1):
+        if world % s == 0 and (n_states // s >= min_shard or s <= 2):
+            best = s
+    best = min(best, world)
+    return best, world // best
+
+
 def alloc_gather_buffers(world, nq, k, device):
     """[world, nq, k] int64 ids and float64 distances, the layout merge_topk expects (parts-major)."""
     return (torch.empty((world, nq, k), dtype=torch.int64, device=device),

@@ -29,6 +29,20 @@ def test_shard_ranges_tile_the_index_space():
         sharding.shard_range(10, 2, 2)
 
 
+def test_grid_shape_covers_every_rank_once():
+    for world in (1, 2, 4, 8):
+        for n in (100_000, 1_000_000, 4_000_000, 16_000_000):
+            S, R = sharding.grid_shape(world, n)
+            assert S * R == world and S >= min(world, 2)
+            assert S == world or n // (2 * S) < 500_000 or world % (2 * S)   # no finer cut would keep 500K per shard
+            seen = set()
+            for rank in range(world):
+                s, r = divmod(rank, R)
+                seen.add((sharding.shard_range(n, s, S), sharding.shard_range(65536, r, R)))
+            assert len(seen) == world
+    assert sharding.grid_shape(8, 1_000_000) == (2, 4) and sharding.grid_shape(8, 16_000_000) == (8, 1)
+
+
 WORKER = textwrap.dedent("""
     import os, sys
     import numpy as np
