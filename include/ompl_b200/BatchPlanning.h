@@ -160,6 +160,75 @@ namespace ompl
             mv.checkMotionBatch(s1.data(), s2.data(), pairs.size(), flags.data(), nullptr);
         }
 
+        /** BIT*: the sampling loop of ImplicitGraph::updateSamples
+            (geometric/planners/informedtrees/bitstar/src/ImplicitGraph.cpp:965-993)
+
+                for (tries = 0; tries < factor * numRequired && numSamples < numRequired; ++tries)
+                    draw a state; if isValid: keep it, ++numSamples
+
+            with isValid replaced by isValidBatch over chunks of the same random stream.  States are accepted
+            in drawing order, so the kept states and the returned number of tries (= state collision checks)
+            equal the sequential loop's.  `draw` fills one state; `accepted` receives the kept states (owned by
+            the caller, allocated with si->allocState()); the caller adds them to the sample structure with
+            one add(vector) (addToSamples, :996). */
+        inline std::size_t updateSamplesBatch(const base::SpaceInformationPtr &si,
+                                              const base::BatchedStateValidityChecker &svc,
+                                              const std::function<void(base::State *)> &draw, std::size_t numHave,
+                                              std::size_t numRequired, std::size_t allowedFailedFactor,
+                                              std::vector<base::State *> &accepted, std::size_t chunk = 16384)
+        {
+            const std::size_t limit = allowedFailedFactor * numRequired;
+            std::size_t tries = 0;
+            while (tries < limit && numHave < numRequired)
+            {
+                const std::size_t n = std::min(chunk, limit - tries);
+                std::vector<base::State *> cand(n);
+                for (auto &s : cand)
+                {
+                    s = si->allocState();
+                    draw(s);
+                }
+                std::vector<std::uint8_t> ok(n);
+                svc.isValidBatch(cand.data(), n, ok.data());
+                std::size_t used = n;
+                for (std::size_t i = 0; i < n; ++i)
+                {
+                    if (numHave < numRequired && ok[i] != 0)
+                    {
+                        accepted.push_back(cand[i]);
+                        cand[i] = nullptr;
+                        if (++numHave == numRequired)
+                            used = i + 1;
+                    }
+                }
+                for (auto *s : cand)
+                    if (s != nullptr)
+                        si->freeState(s);
+                tries += used;
+            }
+            return tries;
+        }
+
+        /** BIT*: ImplicitGraph::nearestSamples (ImplicitGraph.cpp:303-321) for every vertex about to be
+            expanded: nearestK(vertex, k) if k != 0, else nearestR(vertex, r), in one batched call. */
+        template <typename _T>
+        void nearestSamplesBatch(const NearestNeighborsCUDA<_T> &samples, const std::vector<_T> &vertices,
+                                 std::size_t k, double r, std::vector<std::vector<_T>> &neighbourSamples)
+        {
+            if (k != 0)
+                samples.nearestKBatch(vertices, k, neighbourSamples);
+            else
+                samples.nearestRBatch(vertices, std::vector<double>(vertices.size(), r), neighbourSamples);
+        }
+
+        /** BIT*: the samples_->remove(sample) calls of ImplicitGraph::pruneSamples as one bulk removal
+            (tombstones on the device; compaction when more than half of the slots are dead). */
+        template <typename _T>
+        std::size_t pruneSamplesBatch(NearestNeighborsCUDA<_T> &samples, const std::vector<_T> &pruned)
+        {
+            return samples.removeBatch(pruned);
+        }
+
         /** SpaceInformation::checkMotion(states, count, firstInvalidStateIndex)
             (base/src/SpaceInformation.cpp:274-285) with one isValidBatch. */
         inline bool checkStatesBatch(const base::BatchedStateValidityChecker &svc,

@@ -218,6 +218,30 @@ namespace ompl
             return true;
         }
 
+        /** Bulk remove (BIT* prunes samples in batches: ImplicitGraph.cpp, pruneSamples): for every element
+            the most recently added equal one, as remove(); one device call.  Returns how many were removed. */
+        std::size_t removeBatch(const std::vector<_T> &data)
+        {
+            std::vector<std::uint64_t> ids;
+            ids.reserve(data.size());
+            for (const _T &d : data)
+            {
+                auto range = idsOf_.equal_range(d);
+                if (range.first == range.second)
+                    continue;
+                auto best = range.first;
+                for (auto it = range.first; it != range.second; ++it)
+                    if (it->second > best->second)
+                        best = it;
+                ids.push_back(best->second);
+                elems_.erase(best->second);
+                idsOf_.erase(best);
+            }
+            std::size_t removed = 0;
+            b200::check(omplcu_nn_remove_batch(nn_, ids.data(), ids.size(), &removed));
+            return removed;
+        }
+
         _T nearest(const _T &data) const override
         {
             if (size() == 0)

@@ -100,6 +100,9 @@ int omplcu_nn_destroy(omplcu_nn_t nn);
 int omplcu_nn_set_id_base(omplcu_nn_t nn, uint64_t id_base);
 int omplcu_nn_add(omplcu_nn_t nn, const double *rows, size_t n, uint64_t *first_id);
 int omplcu_nn_remove(omplcu_nn_t nn, uint64_t id);
+/* n removals in one call (BIT* prunes samples in bulk: ImplicitGraph.cpp, pruneSamples): ids that are
+ * not present are skipped, *removed (may be NULL) receives how many were. */
+int omplcu_nn_remove_batch(omplcu_nn_t nn, const uint64_t *ids, size_t n, size_t *removed);
 int omplcu_nn_clear(omplcu_nn_t nn);
 int omplcu_nn_size(omplcu_nn_t nn, size_t *n);
 int omplcu_nn_list(omplcu_nn_t nn, uint64_t *ids, size_t cap, size_t *n);

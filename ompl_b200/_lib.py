@@ -50,6 +50,7 @@ SIGNATURES = {
     "omplcu_nn_set_id_base": [_vp, _u64],
     "omplcu_nn_add": [_vp, _pd, _sz, C.POINTER(_u64)],
     "omplcu_nn_remove": [_vp, _u64],
+    "omplcu_nn_remove_batch": [_vp, _pd, _sz, C.POINTER(_sz)],
     "omplcu_nn_clear": [_vp],
     "omplcu_nn_size": [_vp, C.POINTER(_sz)],
     "omplcu_nn_list": [_vp, _pd, _sz, C.POINTER(_sz)],

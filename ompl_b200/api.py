@@ -341,6 +341,19 @@ class NearestNeighborsCUDA:
                 ids.remove(int(i))
         return True
 
+    def remove_ids(self, ids):
+        """Bulk removal by id (one kernel, one synchronisation); returns how many were present."""
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        n = C.c_size_t()
+        check(lib().omplcu_nn_remove_batch(self._h, _ptr(ids), len(ids), C.byref(n)))
+        for i in ids.tolist():
+            e = self._elem.pop(i, None)
+            if e is not None:
+                lst = self._ids_of.get(self._key(e), [])
+                if i in lst:
+                    lst.remove(i)
+        return n.value
+
     def size(self):
         n = C.c_size_t()
         check(lib().omplcu_nn_size(self._h, C.byref(n)))

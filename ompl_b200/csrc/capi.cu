@@ -241,6 +241,16 @@ int omplcu_nn_remove(omplcu_nn_t nn, uint64_t id)
     });
 }
 
+int omplcu_nn_remove_batch(omplcu_nn_t nn, const uint64_t *ids, size_t n, size_t *removed)
+{
+    return guarded([&] {
+        REQUIRE(nn && (ids || n == 0), "omplcu_nn_remove_batch: NULL argument");
+        const size_t r = nn->impl->remove_batch(ids, n);
+        if (removed)
+            *removed = r;
+    });
+}
+
 int omplcu_nn_clear(omplcu_nn_t nn)
 {
     return guarded([&] {

@@ -83,6 +83,17 @@ namespace omplcu
                 filt[slot * rowf + D] = inff();
         }
 
+        __global__ void mark_dead_batch_kernel(uint8_t *alive, float *filt, int rowf, int D, const uint32_t *slots,
+                                               size_t n)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= n)
+                return;
+            alive[slots[i]] = 0;
+            if (filt)
+                filt[(size_t)slots[i] * rowf + D] = inff();
+        }
+
         __global__ void fill_ids_kernel(uint64_t *ids, uint8_t *alive, size_t first, size_t n, uint64_t id0)
         {
             size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
@@ -751,6 +762,43 @@ namespace omplcu
         if (dead > 1024 && dead > nlive_)
             compact();
         CUDA_CHECK(cudaStreamSynchronize(stream_));
+    }
+
+    // Bulk removal: one kernel marks every slot, one synchronisation.  Absent ids are skipped.
+    size_t NNIndex::remove_batch(const uint64_t *ids, size_t n)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        std::vector<uint32_t> slots;
+        slots.reserve(n);
+        for (size_t i = 0; i < n; ++i)
+        {
+            auto it = std::lower_bound(h_ids_.begin(), h_ids_.end(), ids[i]);
+            if (it == h_ids_.end() || *it != ids[i] || !h_alive_[it - h_ids_.begin()])
+                continue;
+            h_alive_[it - h_ids_.begin()] = 0;
+            slots.push_back((uint32_t)(it - h_ids_.begin()));
+        }
+        if (slots.empty())
+            return 0;
+        nlive_ -= slots.size();
+        mut_version_++;
+        DevBuf<uint32_t> d_slots;
+        d_slots.reserve(slots.size());
+        CUDA_CHECK(cudaMemcpyAsync(d_slots.p, slots.data(), slots.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
+                                   stream_));
+        mark_dead_batch_kernel<<<nblk(slots.size(), 256), 256, 0, stream_>>>(alive_.p, fast_space_ ? filt_.p : nullptr,
+                                                                             rowf_, D_, d_slots.p, slots.size());
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaStreamSynchronize(stream_));
+        const size_t dead = nslots_ - nlive_;
+        if (dead > 1024 && dead > nlive_)
+        {
+            compact();
+            CUDA_CHECK(cudaStreamSynchronize(stream_));
+        }
+        return slots.size();
     }
 
     // Drop dead slots, keeping insertion order (so slot order stays id order).

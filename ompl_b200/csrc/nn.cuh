@@ -25,6 +25,7 @@ namespace omplcu
         void set_id_base(uint64_t base);
         uint64_t add(const double *rows, size_t n);
         void remove(uint64_t id);
+        size_t remove_batch(const uint64_t *ids, size_t n);
         void clear();
         size_t size() const
         {

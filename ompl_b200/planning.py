@@ -1,5 +1,5 @@
 """Batch-submit call sites for sampling-based planners -- the Python mirror of
-include/ompl_b200/BatchPlanning.h.  Elements are roadmap ids
+include/ompl_b200/BatchPlanning.h (FMT*, PRM, BIT*).  Elements are roadmap ids
 (insertion indices); states are rows in copyToReals order.
 
 Each function is a loop of the reference with its per-element calls replaced by one batch
@@ -105,3 +105,58 @@ def check_path_batch(checker, mv, path_rows):
     if len(path_rows) < 2:
         return True
     return bool(mv.checkMotionBatch(path_rows[:-1], path_rows[1:]).all())
+
+
+# ----------------------------------------------------------------------
+# BIT* (SURVEY 8(f) row 3): sample batches, neighbourhoods of a set of vertices, bulk pruning
+# ----------------------------------------------------------------------
+def update_samples_batch(checker, nn, draw, num_have, num_required, allowed_failed_factor=100, chunk=16384):
+    """The sampling loop of BITstar::ImplicitGraph::updateSamples,
+    geometric/planners/informedtrees/bitstar/src/ImplicitGraph.cpp:965-993, followed by addToSamples (:996):
+
+        for (tries = 0; tries < factor * numRequired && numSamples_ < numRequired; ++tries)
+            draw a state; ++numStateCollisionChecks_; if isValid: keep it, ++numSamples_
+
+    with the per-state isValid replaced by isValidBatch over chunks of the same random stream; states are
+    accepted in drawing order, so the kept set, `tries` and the collision-check count equal the
+    sequential loop's.  The kept states go into the free-sample structure with ONE bulk add.
+    Returns (rows, ids, tries)."""
+    limit = allowed_failed_factor * num_required
+    kept, tries, have = [], 0, num_have
+    while tries < limit and have < num_required:
+        n = min(chunk, limit - tries)
+        cand = np.ascontiguousarray(draw(n), dtype=np.float64)
+        idx = np.flatnonzero(checker.isValidBatch(cand))
+        if have + len(idx) >= num_required:
+            idx = idx[: num_required - have]
+            tries += int(idx[-1]) + 1
+            have = num_required
+            kept.append(cand[idx])
+            break
+        tries += len(cand)
+        have += len(idx)
+        kept.append(cand[idx])
+    rows = np.vstack(kept) if kept else np.zeros((0, nn.space.stride))
+    ids = np.zeros(0, dtype=np.uint64)
+    if len(rows):
+        first = nn.add_rows(rows)
+        ids = first + np.arange(len(rows), dtype=np.uint64)
+    return rows, ids, tries
+
+
+def nearest_samples_batch(nn, vertex_rows, k=None, r=None):
+    """BITstar::ImplicitGraph::nearestSamples (ImplicitGraph.cpp:303-321) for every vertex about to be
+    expanded: samples_->nearestK(vertex, k_) or nearestR(vertex, r_), one batched call.  Returns a list of
+    id arrays sorted by (distance, id)."""
+    if k:
+        ids, _ = nn.nearestKBatch(vertex_rows, k)
+        return [row for row in ids]
+    ids, _, offs = nn.nearestRBatch(vertex_rows, r)
+    return [ids[offs[i]:offs[i + 1]] for i in range(len(vertex_rows))]
+
+
+def prune_samples_batch(nn, ids):
+    """The removals of BITstar::ImplicitGraph::pruneSamples (samples_->remove(sample) per pruned sample,
+    ImplicitGraph.cpp, pruneSamples) as one bulk removal: tombstones on the device, compaction when more
+    than half of the slots are dead.  Returns the number removed."""
+    return nn.remove_ids(ids)

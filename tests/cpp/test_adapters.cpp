@@ -369,6 +369,66 @@ static void batchPlanningTest()
     for (std::size_t i = 0; i < pairs.size(); ++i)
         CHECK((flags[i] != 0) == ref.checkMotion(pairs[i].first, pairs[i].second));
 
+    // ---- BIT*: updateSamples loop, nearestSamples for a set of vertices, bulk prune ----
+    {
+        std::mt19937_64 h1(7), h2(7);
+        const std::size_t have = 10, required = 260, factor = 100;
+        std::vector<ob::State *> seqS;
+        std::size_t seqTries = 0, n = have;
+        {
+            auto draw = drawWith(h1);  // ImplicitGraph.cpp:965-993
+            for (; seqTries < factor * required && n < required; ++seqTries)
+            {
+                ob::State *s = space->allocState();
+                draw(s);
+                if (siRef->isValid(s))
+                {
+                    seqS.push_back(s);
+                    ++n;
+                }
+                else
+                    space->freeState(s);
+            }
+        }
+        std::vector<ob::State *> batS;
+        const std::size_t tries = ompl::b200::updateSamplesBatch(si, *svc, drawWith(h2), have, required, factor, batS, 64);
+        CHECK(tries == seqTries && batS.size() == seqS.size() && batS.size() == required - have);
+        for (std::size_t i = 0; i < batS.size() && i < seqS.size(); ++i)
+            CHECK(space->equalStates(batS[i], seqS[i]));
+
+        ompl::NearestNeighborsLinear<ob::State *> linS;
+        linS.setDistanceFunction(dist);
+        ompl::NearestNeighborsCUDA<ob::State *> samples;
+        ompl::b200::bind<ob::State *>(samples, space, [](ob::State *const &s) { return (const ob::State *)s; });
+        linS.add(batS);
+        samples.add(batS);  // addToSamples: one bulk add
+        std::vector<ob::State *> vertices(acc.begin(), acc.begin() + 40);
+        std::vector<std::vector<ob::State *>> nsK, nsR;
+        ompl::b200::nearestSamplesBatch<ob::State *>(samples, vertices, 7, 0.0, nsK);
+        ompl::b200::nearestSamplesBatch<ob::State *>(samples, vertices, 0, 0.2, nsR);
+        for (std::size_t i = 0; i < vertices.size(); ++i)
+        {
+            linS.nearestK(vertices[i], 7, want);
+            CHECK(nsK[i] == want);
+            linS.nearestR(vertices[i], 0.2, want);
+            CHECK(nsR[i] == want);
+        }
+        std::vector<ob::State *> pruned;
+        for (std::size_t i = 0; i < batS.size(); i += 3)
+            pruned.push_back(batS[i]);
+        for (ob::State *p : pruned)
+            linS.remove(p);
+        CHECK(ompl::b200::pruneSamplesBatch<ob::State *>(samples, pruned) == pruned.size());
+        CHECK(ompl::b200::pruneSamplesBatch<ob::State *>(samples, pruned) == 0);  // already gone
+        CHECK(samples.size() == linS.size());
+        ompl::b200::nearestSamplesBatch<ob::State *>(samples, vertices, 7, 0.0, nsK);
+        for (std::size_t i = 0; i < vertices.size(); ++i)
+        {
+            linS.nearestK(vertices[i], 7, want);
+            CHECK(nsK[i] == want);
+        }
+    }
+
     std::vector<ob::State *> mixed(acc.begin(), acc.begin() + 40);
     ob::State *bad = space->allocState();
     std::vector<double> inside = {0.5, 0.5, 0.0};

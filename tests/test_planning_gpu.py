@@ -117,3 +117,60 @@ def test_state_sequences_and_paths(gpu):
     bad = np.vstack([edge[:5], np.full((1, D), 0.5), edge[5:]])
     assert not planning.check_path_batch(chk, mv, bad)
     assert planning.check_path_batch(chk, mv, edge[:0]) and planning.check_path_batch(chk, mv, edge[:1])
+
+
+def test_bitstar_sample_batches_neighbourhoods_and_bulk_prune(gpu):
+    """BIT* call sites (SURVEY 8(f) row 3): ImplicitGraph::updateSamples (ImplicitGraph.cpp:965-996),
+    nearestSamples (:303-321) and the removals of pruneSamples, against the sequential loops."""
+    sp, osp, chk, ochk = _world()
+    nn = ob.NearestNeighborsCUDA(sp)
+    have, required, factor = 25, 2500, 100
+    rows, ids, tries = planning.update_samples_batch(chk, nn, _stream(9), have, required, factor, chunk=512)
+    draw = _stream(9)
+    seq, seq_tries, n = [], 0, have
+    while seq_tries < factor * required and n < required:
+        cand = draw(512)
+        ok = orc.check_states(ochk, cand, nthreads=8)
+        for c, v in zip(cand, ok):
+            if not (seq_tries < factor * required and n < required):
+                break
+            seq_tries += 1
+            if v:
+                seq.append(c)
+                n += 1
+    assert tries == seq_tries and len(rows) == required - have and (rows == np.array(seq)).all()
+    assert nn.size() == len(rows) and (ids == np.arange(len(rows), dtype=np.uint64)).all()
+    # tries exhausted before enough samples are found: the loop stops at the limit
+    nn2 = ob.NearestNeighborsCUDA(sp)
+    r2, _, t2 = planning.update_samples_batch(ob.HypercubeValidityChecker(D), nn2, lambda m: np.full((m, D), 0.5),
+                                              0, 10, 3, chunk=7)
+    assert t2 == 30 and len(r2) == 0 and nn2.size() == 0
+
+    verts = rows[:200]
+    nbk = planning.nearest_samples_batch(nn, verts, k=12)
+    oi, _ = orc.knn(osp, rows, verts, 12, nthreads=8)
+    assert all((nbk[i] == oi[i]).all() for i in range(len(verts)))
+    nbr = planning.nearest_samples_batch(nn, verts[:40], r=0.1)
+    for i in range(40):
+        want, _ = orc.radius(osp, rows, verts[i], 0.1)
+        assert (nbr[i] == want).all()
+
+    pruned = ids[::3]
+    assert planning.prune_samples_batch(nn, pruned) == len(pruned)
+    assert planning.prune_samples_batch(nn, pruned) == 0  # already gone
+    live = np.setdiff1d(ids, pruned)
+    assert nn.size() == len(live)
+    nbk = planning.nearest_samples_batch(nn, verts, k=12)
+    oi, _ = orc.knn(osp, rows[live.astype(np.int64)], verts, 12, nthreads=8)
+    assert all((nbk[i] == live[oi[i].astype(np.int64)]).all() for i in range(len(verts)))
+    # prune past the compaction threshold, then add again: ids keep increasing
+    more = live[: len(live) * 3 // 4]
+    assert planning.prune_samples_batch(nn, more) == len(more)
+    live = np.setdiff1d(live, more)
+    first = nn.add_rows(rows[:50])
+    assert first == len(rows)
+    allrows = np.vstack([rows, rows[:50]])
+    live = np.concatenate([live, first + np.arange(50, dtype=np.uint64)])
+    nbk = planning.nearest_samples_batch(nn, verts[:64], k=5)
+    oi, _ = orc.knn(osp, allrows[live.astype(np.int64)], verts[:64], 5, nthreads=8)
+    assert all((nbk[i] == live[oi[i].astype(np.int64)]).all() for i in range(64))
