@@ -132,9 +132,13 @@ int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *
 int omplcu_merge_topk_strided_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts,
                                      size_t part_stride, size_t nq, size_t k, double *d_out_dists,
                                      uint64_t *d_out_ids, void *stream);
-/* Tuning / introspection.  key: "force_exact" (0/1), "last_fallbacks" (read),
- * "last_path" (read: 1 fast scan, 2 exact sort), "launches" (read: kernels
- * launched by this handle so far). */
+/* Tuning / introspection.  Options: "force_exact" (0/1); "tc_scan" (-1 auto: tensor-core filter scan for
+ * batches of >= 32 queries, 0 never: FP32-pipe scans, 1 whenever the space is eligible; the environment
+ * variable OMPLCU_TC_SCAN sets the default for new handles); "sample_thresholds", "collect",
+ * "scan_ctas_per_sm", "tc_tiles", "profile" (tuning); "tc_scan_values_out" (diagnostics: device pointer that
+ * receives the raw scan values).  Stats: "last_fallbacks", "last_path" (1 filter scan + exact re-rank,
+ * 2 exact sort), "last_tc" (1 if the last scan ran on the tensor cores), "launches" (kernels launched by
+ * this handle so far), "last_scan_ns", "slots". */
 int omplcu_nn_set_option(omplcu_nn_t nn, const char *key, long value);
 int omplcu_nn_get_stat(omplcu_nn_t nn, const char *key, long *value);
 
