@@ -25,10 +25,10 @@ namespace omplcu
 {
     namespace
     {
-        // threads per CTA: TMA warp, MMA warp, four selection warps per resident query tile
+        // threads per CTA: TMA warp, then per resident query tile one MMA warp and four selection warps
         __host__ __device__ constexpr int tc_threads(int NA)
         {
-            return 64 + 128 * NA;
+            return 32 * (1 + NA + 4 * NA);
         }
         constexpr int TC_ACC = 4;  // accumulator buffers (4 x 128 = all 512 TMEM columns)
         constexpr int TC_MAX_STAGES = 8;
@@ -330,7 +330,7 @@ namespace omplcu
             float *lv = reinterpret_cast<float *>(sB + (size_t)nst * chunk_bytes);  // [NA][128][LS]
             uint32_t *li = reinterpret_cast<uint32_t *>(lv + NA * TC_QT * LS);      // [NA][L][128]
             float *scr = reinterpret_cast<float *>(li + NA * L * TC_QT);            // [4 NA warps][W][32] slow-path staging
-            constexpr int W = NA == 4 ? 16 : 32;  // columns per selection step (register budget at 576 threads)
+            constexpr int W = 32;  // columns per selection step
             TcSmem *S = reinterpret_cast<TcSmem *>(scr + 4 * NA * W * 32);
 
             const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -342,10 +342,10 @@ namespace omplcu
                 for (int i = 0; i < TC_MAX_STAGES; ++i)
                 {
                     mbar_init(&S->full[i], 1);
-                    mbar_init(&S->empty[i], 1);
+                    mbar_init(&S->empty[i], NA);
                 }
                 mbar_init(&S->a_full, 1);
-                mbar_init(&S->a_empty, 1);
+                mbar_init(&S->a_empty, NA);
                 for (int i = 0; i < TC_ACC; ++i)
                 {
                     mbar_init(&S->t_full[i], 1);
@@ -399,17 +399,20 @@ namespace omplcu
                     }
                 }
             }
-            else if (warp == 1)
+            else if (warp <= NA)
             {
+                // one issuer per resident tile: the four accumulator chains (MMA -> selection -> MMA) advance
+                // independently instead of queueing behind one thread's barrier waits
                 if (lane == 0)
                 {
+                    const int a = warp - 1;
                     constexpr uint32_t idesc = umma_idesc_bf16(TC_QT, TC_PT);
                     const uint32_t dl = (P.diag & 1) ? TC_SBO : TC_LBO, ds = (P.diag & 1) ? TC_LBO : TC_SBO;
-                    const uint32_t a0 = smem_u32(sA) & 0x3FFFFu, b0 = smem_u32(sB) & 0x3FFFFu;
+                    const uint32_t a0 = (smem_u32(sA) & 0x3FFFFu) + (uint32_t)a * a_tile_bytes, b0 = smem_u32(sB) & 0x3FFFFu;
                     const uint64_t desc0 = umma_desc(0, dl, ds);  // one MMA covers K = 16 = two column groups
                     int st = 0;
-                    uint32_t ph = 0, aph = 0;
-                    unsigned long long cur = ~0ull, job = 0, t = 0, pt = 0;  // job = (unit - u0) * NA + tile
+                    uint32_t ph = 0, aph = 0, job = (uint32_t)a;  // job = (unit - u0) * NA + tile
+                    unsigned long long cur = ~0ull, t = 0, pt = 0;
                     for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
                     {
                         if (u == u0 || pt == U)
@@ -425,24 +428,19 @@ namespace omplcu
                             aph ^= 1;
                             cur = t;
                         }
+                        const uint32_t buf = job & (TC_ACC - 1);
+                        const uint32_t dcol = tmem + buf * TC_PT;
                         for (int kc = 0; kc < nkc; ++kc)
                         {
                             mbar_wait(&S->full[st], ph);
+                            if (kc == 0)
+                                mbar_wait(&S->t_empty[buf], ((job / TC_ACC) & 1) ^ 1);
                             tc_fence_after();
-#pragma unroll
-                            for (int a = 0; a < NA; ++a)
+                            // descriptors differ in the start address only (low word, units of 16 bytes)
+                            const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
+                            const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
+                            if (!(P.diag & 8))  // diagnostics: barriers and commits only
                             {
-                                const unsigned long long j = job + a;
-                                const int buf = (int)(j & (TC_ACC - 1));
-                                if (kc == 0)
-                                {
-                                    mbar_wait(&S->t_empty[buf], (uint32_t)((j / TC_ACC) & 1) ^ 1);
-                                    tc_fence_after();
-                                }
-                                const uint32_t dcol = tmem + (uint32_t)buf * TC_PT;
-                                // descriptors differ in the start address only (low word, units of 16 bytes)
-                                const uint64_t ad = desc0 + ((a0 + (uint32_t)a * a_tile_bytes + (uint32_t)kc * chunk_bytes) >> 4);
-                                const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
                                 umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
                                 if (kw == 8)
@@ -450,10 +448,10 @@ namespace omplcu
                                     umma_bf16(dcol, ad + 2 * (2 * TC_LBO >> 4), bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
                                     umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
                                 }
-                                if (kc == nkc - 1)
-                                    umma_commit(&S->t_full[buf]);
                             }
-                            umma_commit(&S->empty[st]);
+                            umma_commit(&S->empty[st]);  // the stage is free once all NA issuers' MMAs have read it
+                            if (kc == nkc - 1)
+                                umma_commit(&S->t_full[buf]);
                             if (++st == nst)
                             {
                                 st = 0;
@@ -472,10 +470,10 @@ namespace omplcu
                 // names the entry to overwrite and ONE max-tree over the list yields the next threshold
                 // and the next victim.  The hot loop is two copies of the W-column step (the two register
                 // buffers of the TMEM load pipeline) and stays resident in the instruction cache.
-                const int a = (warp - 2) >> 2, wq = warp & 3, qrow = wq * 32 + lane;
+                const int a = (warp - 1 - NA) >> 2, wq = warp & 3, qrow = wq * 32 + lane;
                 float *lvq = lv + (a * TC_QT + qrow) * LS;
                 uint32_t *liq = li + a * L * TC_QT + qrow;
-                float *scr_q = scr + (warp - 2) * W * 32 + lane;
+                float *scr_q = scr + (warp - 1 - NA) * W * 32 + lane;
                 float thr = 0.f;
                 auto reset = [&]() {
                     for (int i = 0; i < L; ++i)
@@ -532,25 +530,44 @@ namespace omplcu
                     const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
                     if (!(P.diag & 2))
                     {
-                        uint32_t ra[W], rb[W];
-                        __syncwarp();
-                        tmem_ld_issue(taddr, ra);
-#pragma unroll 1
-                        for (int c = 0; c < TC_PT / W; c += 2)
+                        if constexpr (NA == 4)
                         {
+                            // 21 warps per CTA: the other warps of the scheduler hide the TMEM load latency,
+                            // one register buffer of 32 columns keeps the thread within 96 registers
+                            uint32_t ra[W];
+#pragma unroll 1
+                            for (int c = 0; c < TC_PT / W; ++c)
+                            {
+                                __syncwarp();
+                                tmem_ld_issue(taddr + c * W, ra);
+                                tmem_ld_wait(ra);
+                                if (DBG)
+                                    tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
+                                step(ra, slot0 + c * W);
+                            }
+                        }
+                        else
+                        {
+                            uint32_t ra[W], rb[W];
                             __syncwarp();
-                            tmem_ld_wait(ra);
-                            tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
-                            if (DBG)
-                                tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
-                            step(ra, slot0 + c * W);
-                            __syncwarp();
-                            tmem_ld_wait(rb);
-                            if (c + 2 < TC_PT / W)
-                                tmem_ld_issue(taddr + (c + 2) * W, ra);
-                            if (DBG)
-                                tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
-                            step(rb, slot0 + (c + 1) * W);
+                            tmem_ld_issue(taddr, ra);
+#pragma unroll 1
+                            for (int c = 0; c < TC_PT / W; c += 2)
+                            {
+                                __syncwarp();
+                                tmem_ld_wait(ra);
+                                tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
+                                if (DBG)
+                                    tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
+                                step(ra, slot0 + c * W);
+                                __syncwarp();
+                                tmem_ld_wait(rb);
+                                if (c + 2 < TC_PT / W)
+                                    tmem_ld_issue(taddr + (c + 2) * W, ra);
+                                if (DBG)
+                                    tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
+                                step(rb, slot0 + (c + 1) * W);
+                            }
                         }
                     }
                     tc_fence_before();
@@ -574,7 +591,7 @@ namespace omplcu
     {
         const size_t chunk = (size_t)sh.kw * 2048;
         return (size_t)sh.na * sh.nkc * chunk + (size_t)nstages * chunk + (size_t)sh.na * TC_QT * (2 * L + 4) * 4 +
-               (size_t)4 * sh.na * (sh.na == 4 ? 16 : 32) * 32 * 4 + sizeof(TcSmem) + 64;
+               (size_t)4 * sh.na * 32 * 32 * 4 + sizeof(TcSmem) + 64;
     }
 
     int tc_pick_stages(const TcShape &sh, int L)
