@@ -235,7 +235,7 @@ namespace omplcu
         {
             uint64_t full[TC_MAX_STAGES], empty[TC_MAX_STAGES];  // point-chunk ring: TMA <-> MMA
             uint64_t a_full, a_empty;                            // query image:     TMA <-> MMA
-            uint64_t t_full[TC_ACC], t_empty[TC_ACC];            // accumulators:    MMA <-> selection
+            uint64_t t_full[2 * TC_ACC], t_empty[2 * TC_ACC];    // accumulators:    MMA <-> selection (8 of 64 columns at NA = 4)
             uint32_t tmem_base;
         };
 
@@ -346,7 +346,7 @@ namespace omplcu
                 }
                 mbar_init(&S->a_full, 1);
                 mbar_init(&S->a_empty, NA);
-                for (int i = 0; i < TC_ACC; ++i)
+                for (int i = 0; i < 2 * TC_ACC; ++i)
                 {
                     mbar_init(&S->t_full[i], 1);
                     mbar_init(&S->t_empty[i], TC_QT);
@@ -427,6 +427,42 @@ namespace omplcu
                             mbar_wait(&S->a_full, aph);
                             aph ^= 1;
                             cur = t;
+                        }
+                        if constexpr (NA == 4)
+                        {
+                            // K fits one chunk (d <= 20).  The tile owns two 64-column accumulators and fills them
+                            // alternately with the two halves of the point tile, so that the selection of one half
+                            // overlaps the MMAs and the hand-over of the other.
+                            constexpr uint32_t idesc64 = umma_idesc_bf16(TC_QT, TC_PT / 2);
+                            mbar_wait(&S->full[st], ph);
+                            const uint64_t ad = desc0 + (a0 >> 4);
+                            const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
+#pragma unroll
+                            for (uint32_t h = 0; h < 2; ++h)
+                            {
+                                const uint32_t jt = 2 * (job >> 2) + h, b = 2 * (uint32_t)a + (jt & 1);
+                                mbar_wait(&S->t_empty[b], ((jt >> 1) & 1) ^ 1);
+                                tc_fence_after();
+                                const uint64_t bh = bd + h * ((TC_PT / 2 / 8) * TC_SBO >> 4);  // rows 64 h .. 64 h + 63
+                                if (!(P.diag & 8))
+                                {
+                                    umma_bf16(tmem + b * (TC_PT / 2), ad, bh, idesc64, 0u);
+                                    umma_bf16(tmem + b * (TC_PT / 2), ad + (2 * TC_LBO >> 4), bh + (2 * TC_LBO >> 4), idesc64, 1u);
+                                    if (kw == 8)
+                                    {
+                                        umma_bf16(tmem + b * (TC_PT / 2), ad + 2 * (2 * TC_LBO >> 4), bh + 2 * (2 * TC_LBO >> 4), idesc64, 1u);
+                                        umma_bf16(tmem + b * (TC_PT / 2), ad + 3 * (2 * TC_LBO >> 4), bh + 3 * (2 * TC_LBO >> 4), idesc64, 1u);
+                                    }
+                                }
+                                umma_commit(&S->t_full[b]);
+                            }
+                            umma_commit(&S->empty[st]);
+                            if (++st == nst)
+                            {
+                                st = 0;
+                                ph ^= 1;
+                            }
+                            continue;
                         }
                         const uint32_t buf = job & (TC_ACC - 1);
                         const uint32_t dcol = tmem + buf * TC_PT;
@@ -524,29 +560,42 @@ namespace omplcu
                         cur = t;
                     }
                     const uint32_t slot0 = (uint32_t)(pt * TC_PT);
+                    if constexpr (NA == 4)
+                    {
+                        // two 64-column half-jobs per point tile (see the issuer); 21 warps per CTA hide the
+                        // TMEM load latency, one register buffer keeps the thread within 96 registers
+#pragma unroll 1
+                        for (uint32_t h = 0; h < 2; ++h)
+                        {
+                            const uint32_t jt = 2 * (uint32_t)(job >> 2) + h, b = 2 * (uint32_t)a + (jt & 1);
+                            mbar_wait(&S->t_full[b], (jt >> 1) & 1);
+                            tc_fence_after();
+                            const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + b * (TC_PT / 2);
+                            if (!(P.diag & 2))
+                            {
+                                uint32_t ra[W];
+#pragma unroll 1
+                                for (int c = 0; c < TC_PT / 2 / W; ++c)
+                                {
+                                    __syncwarp();
+                                    tmem_ld_issue(taddr + c * W, ra);
+                                    tmem_ld_wait(ra);
+                                    if (DBG)
+                                        tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + h * (TC_PT / 2) + c * W);
+                                    step(ra, slot0 + h * (TC_PT / 2) + c * W);
+                                }
+                            }
+                            tc_fence_before();
+                            mbar_arrive(&S->t_empty[b]);
+                        }
+                        continue;
+                    }
                     const int buf = (int)(job & (TC_ACC - 1));
                     mbar_wait(&S->t_full[buf], (uint32_t)((job / TC_ACC) & 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
                     if (!(P.diag & 2))
                     {
-                        if constexpr (NA == 4)
-                        {
-                            // 21 warps per CTA: the other warps of the scheduler hide the TMEM load latency,
-                            // one register buffer of 32 columns keeps the thread within 96 registers
-                            uint32_t ra[W];
-#pragma unroll 1
-                            for (int c = 0; c < TC_PT / W; ++c)
-                            {
-                                __syncwarp();
-                                tmem_ld_issue(taddr + c * W, ra);
-                                tmem_ld_wait(ra);
-                                if (DBG)
-                                    tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
-                                step(ra, slot0 + c * W);
-                            }
-                        }
-                        else
                         {
                             uint32_t ra[W], rb[W];
                             __syncwarp();
