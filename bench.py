@@ -44,7 +44,7 @@ N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
 N_SEGMENTS = 1_000_000
 MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
-TC_TRAFFIC = 388.7e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r1_scan_tc_d7_ncu_summary.csv
+TC_TRAFFIC = 183.6e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r1_scan_tc_d7_ncu_summary.csv
 UNIT = "queries/s"
 
 
@@ -418,10 +418,11 @@ def run_gpu_arm(args):
                 "frac_executed": exe / (scan_ns * 1e-9) / 1e12 / tpeak,
                 "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                 "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
-                "note": "K = 32 per accumulator: the kernel is bound by the MMA -> TMEM -> selection hand-over "
-                        "(TMEM capacity / round-trip latency), not by the tensor pipe (ncu: tensor pipe ~17 % "
-                        "busy) and not by HBM; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which "
-                        "bounded the round-1 FP32 scan (roofline_fp32_scan)",
+                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu: 21 % busy) and neither is HBM: "
+                        "the kernel is bound by instruction issue in the selection warps (ncu: issue slots 62 % busy, "
+                        "three quarters of the instructions are list insertions while the per-query thresholds "
+                        "converge) on top of the MMA -> TMEM -> selection hand-over latency; achieved exceeds the FP32 "
+                        "FMA peak (vs_fp32_pipe_peak > 1), which bounded the round-1 FP32 scan (roofline_fp32_scan)",
             }
             if fp32_leg:
                 roofline_fp32 = fp32_roofline(fp32_leg[1], fp32_leg[0])
