@@ -1,16 +1,17 @@
 // knn_scan_tc.cu -- tensor-core filter scan (tcgen05.mma, BF16 split operands, FP32
-// accumulators in TMEM) for k-nearest queries in 64..128 dimensions.  See knn_scan_tc.cuh
-// for the contract and DESIGN.md 3.5 for the error bound and the roofline.
+// accumulators in TMEM) for batched k-nearest queries on plain RealVector spaces of 1..128
+// dimensions.  See knn_scan_tc.cuh for the contract and DESIGN.md 3.5 for the error bound,
+// the measurements and what bounds each shape.
 //
-// One persistent CTA per SM (192 threads), warp-specialised:
-//   warp 0, one lane   producer: cp.async.bulk (TMA bulk copy) of the query image (once per
-//                      query tile, stays resident) and of 16 KB point chunks into a ring
-//   warp 1, one lane   tcgen05.mma issuer: per point tile nkc x 4 MMAs (M 128 x N 128 x K 16)
-//                      into one of four 128-column TMEM accumulators; tcgen05.commit frees the
-//                      ring slot and hands the accumulator to the selection warps
-//   warps 2..5         selection: thread = TMEM lane = query; tcgen05.ld 32 columns at a time,
-//                      one FMNMX tree against the query's threshold (a register), the rare hit
-//                      goes into the query's private list in shared memory
+// One persistent CTA per SM, warp-specialised; NA = 4 / 2 / 1 resident query tiles of 128 queries:
+//   warp 0, one lane      producer: cp.async.bulk (TMA bulk copy) of the query image (once per
+//                         query super-tile, stays resident) and of 8 / 16 KB point chunks into a ring
+//   warps 1..NA, one lane tcgen05.mma issuers, one per resident tile: per point tile Kpad/16 MMAs
+//                         (M 128 x N 128 x K 16; N 64 x 2 at NA = 4) into a TMEM accumulator;
+//                         tcgen05.commit frees the ring slot and hands the accumulator over
+//   4 NA selection warps  thread = TMEM lane = query; tcgen05.ld 32 columns at a time, one FMNMX3
+//                         tree against the query's threshold (a register), the rare hit goes
+//                         into the query's private list in shared memory (out of line)
 // Operand images are written by the prep kernels in exactly the order the UMMA shared-memory
 // descriptor walks them (K-major, no swizzle: 8-row x 16-byte core matrices), so every stage is
 // ONE contiguous bulk copy and no tensor map is needed.

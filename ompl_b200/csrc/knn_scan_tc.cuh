@@ -1,7 +1,7 @@
-// knn_scan_tc.cuh -- interface of the tensor-core filter scan (knn_scan_tc.cu) for k-nearest
-// queries on plain RealVector spaces of 64..128 dimensions: the "dense contraction" case
-// of the hot path (d >= 64 plain-L2 distance matrix, a filter only, followed
-// by the exact FP64 re-rank of nn.cu).
+// knn_scan_tc.cuh -- interface of the tensor-core filter scan (knn_scan_tc.cu) for batched
+// k-nearest queries on plain RealVector spaces of 1..128 dimensions: the distance matrix as a
+// dense contraction (SURVEY 8(d) asks for it at d >= 64; measured faster at every dimension once
+// queries come in batches), a filter only, followed by the exact FP64 re-rank of nn.cu.
 //
 // Contract, as knn_scan.cuh / knn_scan_hd.cuh: per (query, point) pair a scan value
 //        s ~= pn + sum_c (-2 qt_c) * pt_c ,     pn = fl32(|pt|^2)
