@@ -240,7 +240,7 @@ def run_gpu_arm(args):
     S_SH, R_QB = (1, 1) if args.shard == "single" else sharding.grid_shape(world, N_STATES)
     if args.shard == "states":
         S_SH, R_QB = world, 1
-    sh_s, sh_r = divmod(rank, R_QB)
+    sh_s, sh_r = divmod(rank, R_QB)  # sharding.grid_coords; block r is merged from sharding.block_part_ranks(r, S, R)
     lo, hi = sharding.shard_range(N_STATES, sh_s, S_SH)
     assert N_QUERIES % R_QB == 0
     NQB = N_QUERIES // R_QB           # queries answered by this rank

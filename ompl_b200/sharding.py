@@ -35,6 +35,19 @@ def grid_shape(world, n_states, min_shard=500_000):
     return best, world // best
 
 
+def grid_coords(rank, world, n_states, min_shard=500_000):
+    """(s, r, S, R) of `rank` in the grid of grid_shape: state shard s of S, query block r of R."""
+    S, R = grid_shape(world, n_states, min_shard)
+    s, r = divmod(rank, R)
+    return s, r, S, R
+
+
+def block_part_ranks(r, S, R):
+    """The ranks whose lists make up query block r (one per state shard), in shard order.  In the
+    all-gathered buffer they are R rank-buffers apart, which is the part_stride the merge kernel gets."""
+    return [s * R + r for s in range(S)]
+
+
 def alloc_gather_buffers(world, nq, k, device):
     """[world, nq, k] int64 ids and float64 distances, the layout merge_topk expects (parts-major)."""
     return (torch.empty((world, nq, k), dtype=torch.int64, device=device),

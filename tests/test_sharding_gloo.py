@@ -140,3 +140,68 @@ def test_world_size_2_merge_equals_single_index(tmp_path):
     for rank, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0, f"rank {rank} failed:\n{out[-2000:]}"
         assert f"RANK{rank} merge_ok=True same=True motion_ok=True radius_ok=True" in out
+
+
+GRID_WORKER = textwrap.dedent("""
+    import os, sys
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, {root!r}); sys.path.insert(0, os.path.join({root!r}, "tests"))
+    import helpers
+    from ompl_b200 import sharding
+    from oracle import oracle_py as orc
+
+    dist.init_process_group("gloo")
+    rank, world = dist.get_rank(), dist.get_world_size()
+    n, nq, k, d = 4000, 64, 10, 7
+    pts = helpers.with_duplicates(helpers.uniform_points(21, n, d), 22, frac=0.05)
+    qs = np.vstack([helpers.uniform_points(23, nq - 8, d), pts[:8]])
+    # the layout bench.py uses for N > 1: S state shards x R query blocks, rank = s * R + r
+    s, r, S, R = sharding.grid_coords(rank, world, n, min_shard=n // 2)
+    assert (S, R) == (2, 2) and S * R == world
+    lo, hi = sharding.shard_range(n, s, S)
+    nqb = nq // R
+    sp = orc.space_rv(d)
+    ids, dd = orc.knn(sp, pts[lo:hi], qs[r * nqb:(r + 1) * nqb], k)
+    pk = sharding.PackedLists(world, nqb, k, "cpu")
+    pk.ids.copy_(torch.from_numpy(ids.astype(np.int64) + lo))
+    pk.dists.copy_(torch.from_numpy(dd))
+    pk.all_gather()
+    g_i, g_d = pk.gathered_ids().numpy(), pk.gathered_dists().numpy()
+    m_i = np.empty((nq, k), dtype=np.int64)
+    m_d = np.empty((nq, k), dtype=np.float64)
+    for rb in range(R):   # what omplcu_merge_topk_strided_device does per block, part_stride = R rank buffers
+        parts = sharding.block_part_ranks(rb, S, R)
+        assert parts == [rb + j * R for j in range(S)]
+        cat_i = np.concatenate([g_i[p] for p in parts], axis=1)
+        cat_d = np.concatenate([g_d[p] for p in parts], axis=1)
+        order = np.lexsort((cat_i, cat_d), axis=1)[:, :k]
+        m_i[rb * nqb:(rb + 1) * nqb] = np.take_along_axis(cat_i, order, 1)
+        m_d[rb * nqb:(rb + 1) * nqb] = np.take_along_axis(cat_d, order, 1)
+    w_i, w_d = orc.knn(sp, pts, qs, k)
+    ok = bool((m_i == w_i.astype(np.int64)).all() and (m_d == w_d).all())
+    print(f"RANK{{rank}} grid_ok={{ok}}", flush=True)
+    dist.destroy_process_group()
+    sys.exit(0 if ok else 1)
+""")
+
+
+def test_world_size_4_grid_of_state_shards_and_query_blocks(tmp_path):
+    script = tmp_path / "grid_worker.py"
+    script.write_text(GRID_WORKER.format(root=ROOT))
+    port = _free_port()
+    procs = []
+    for rank in range(4):
+        env = dict(os.environ, RANK=str(rank), WORLD_SIZE="4", LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1",
+                   MASTER_PORT=str(port), OMP_NUM_THREADS="1")
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE,
+                                      stderr=subprocess.STDOUT, text=True))
+    for rank, p in enumerate(procs):
+        try:
+            out, _ = p.communicate(timeout=240)
+        except subprocess.TimeoutExpired:
+            p.kill()
+            out, _ = p.communicate()
+        assert p.returncode == 0, f"rank {rank} failed:\n{out[-2000:]}"
+        assert f"RANK{rank} grid_ok=True" in out
