@@ -283,13 +283,9 @@ namespace omplcu
         // threshold, in column order, and put each into the list (it replaces the current maximum).
         // scr_q: the thread's column of the warp's [W][32] staging block.
         template <int L, int W>
-        __device__ __noinline__ float tc_select_hits(float thr, const float *scr_q, float *lvq, uint32_t *liq,
-                                                     uint32_t id0)
+        __device__ __noinline__ float tc_select_hits(float thr, uint32_t mask, const float *scr_q, float *lvq,
+                                                     uint32_t *liq, uint32_t id0)
         {
-            uint32_t mask = 0;
-#pragma unroll
-            for (int i = 0; i < W; ++i)
-                mask |= scr_q[i * 32] < thr ? 1u << i : 0u;
             while (mask)
             {
                 const int i = __ffs(mask) - 1;
@@ -542,10 +538,14 @@ namespace omplcu
                     }
                     if (fminf(m0, m1) < thr && !(P.diag & 4))
                     {
+                        uint32_t mask = 0;  // the columns that beat the threshold at entry
 #pragma unroll
                         for (int i = 0; i < W; ++i)
+                        {
                             scr_q[i * 32] = __uint_as_float(v[i]);
-                        thr = tc_select_hits<L, W>(thr, scr_q, lvq, liq, id0);
+                            mask |= __uint_as_float(v[i]) < thr ? 1u << i : 0u;
+                        }
+                        thr = tc_select_hits<L, W>(thr, mask, scr_q, lvq, liq, id0);
                     }
                 };
                 unsigned long long cur = ~0ull, job = a, t = 0, pt = 0;
