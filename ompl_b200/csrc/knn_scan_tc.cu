@@ -311,6 +311,26 @@ namespace omplcu
             return thr;
         }
 
+        // The common case late in a segment: exactly one column of the step beats the threshold, and its value
+        // is the step's minimum, which the caller already holds.  No staging, one insertion.
+        template <int L>
+        __device__ __noinline__ float tc_insert_one(float thr, float x, float *lvq, uint32_t *liq, uint32_t id)
+        {
+            const uint32_t slot = __float_as_uint(thr) & TAG_MASK;
+            lvq[slot] = tag_up(x, slot);
+            liq[slot * TC_QT] = id;
+            float4 a = *reinterpret_cast<const float4 *>(lvq);
+            float m0 = fmaxf(a.x, a.y), m1 = fmaxf(a.z, a.w);
+#pragma unroll
+            for (int k = 1; k < L / 4; ++k)
+            {
+                a = *reinterpret_cast<const float4 *>(lvq + 4 * k);
+                m0 = fmaxf(m0, fmaxf(a.x, a.y));
+                m1 = fmaxf(m1, fmaxf(a.z, a.w));
+            }
+            return fmaxf(m0, m1);
+        }
+
         // Work: the (query super-tile x point tile) rectangle, linearised (super-tile major) and cut
         // into gridDim.x equal pieces as in knn_scan.cuh.  A super-tile is NA query tiles of 128; per
         // point tile the CTA runs NA "jobs" (one accumulator each, job j -> TMEM buffer j % 4).
@@ -536,16 +556,22 @@ namespace omplcu
                         m0 = fminf(m0, fminf(__uint_as_float(v[i]), __uint_as_float(v[i + 1])));
                         m1 = fminf(m1, fminf(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])));
                     }
-                    if (fminf(m0, m1) < thr && !(P.diag & 4))
+                    const float mn = fminf(m0, m1);
+                    if (mn < thr && !(P.diag & 4))
                     {
                         uint32_t mask = 0;  // the columns that beat the threshold at entry
 #pragma unroll
                         for (int i = 0; i < W; ++i)
-                        {
-                            scr_q[i * 32] = __uint_as_float(v[i]);
                             mask |= __uint_as_float(v[i]) < thr ? 1u << i : 0u;
+                        if ((mask & (mask - 1)) == 0)
+                            thr = tc_insert_one<L>(thr, mn, lvq, liq, id0 + (uint32_t)__ffs(mask) - 1);
+                        else
+                        {
+#pragma unroll
+                            for (int i = 0; i < W; ++i)
+                                scr_q[i * 32] = __uint_as_float(v[i]);
+                            thr = tc_select_hits<L, W>(thr, mask, scr_q, lvq, liq, id0);
                         }
-                        thr = tc_select_hits<L, W>(thr, mask, scr_q, lvq, liq, id0);
                     }
                 };
                 unsigned long long cur = ~0ull, job = a, t = 0, pt = 0;
