@@ -44,7 +44,7 @@ N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
 N_SEGMENTS = 1_000_000
 MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
-TC_TRAFFIC = 187.3e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r1_scan_tc_d7_ncu_summary.csv
+TC_TRAFFIC = 356.8e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r1_scan_tc_d7_ncu_summary.csv
 UNIT = "queries/s"
 
 

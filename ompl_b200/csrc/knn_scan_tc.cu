@@ -559,10 +559,27 @@ namespace omplcu
                     const float mn = fminf(m0, m1);
                     if (mn < thr && !(P.diag & 4))
                     {
-                        uint32_t mask = 0;  // the columns that beat the threshold at entry
+                        // the columns that beat the threshold at entry; m0 covers columns 0,1 mod 4, m1 columns 2,3
+                        // mod 4, so usually only one of the two halves has to be looked at
+                        uint32_t mask = 0;
+                        if (m0 < thr)
+                        {
 #pragma unroll
-                        for (int i = 0; i < W; ++i)
-                            mask |= __uint_as_float(v[i]) < thr ? 1u << i : 0u;
+                            for (int i = 0; i < W; i += 4)
+                            {
+                                mask |= __uint_as_float(v[i]) < thr ? 1u << i : 0u;
+                                mask |= __uint_as_float(v[i + 1]) < thr ? 2u << i : 0u;
+                            }
+                        }
+                        if (m1 < thr)
+                        {
+#pragma unroll
+                            for (int i = 0; i < W; i += 4)
+                            {
+                                mask |= __uint_as_float(v[i + 2]) < thr ? 4u << i : 0u;
+                                mask |= __uint_as_float(v[i + 3]) < thr ? 8u << i : 0u;
+                            }
+                        }
                         if ((mask & (mask - 1)) == 0)
                             thr = tc_insert_one<L>(thr, mn, lvq, liq, id0 + (uint32_t)__ffs(mask) - 1);
                         else
