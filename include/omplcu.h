@@ -132,8 +132,8 @@ int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *
 int omplcu_merge_topk_strided_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts,
                                      size_t part_stride, size_t nq, size_t k, double *d_out_dists,
                                      uint64_t *d_out_ids, void *stream);
-/* Tuning / introspection.  Options: "force_exact" (0/1); "tc_scan" (-1 auto: tensor-core filter scan for
- * batches of >= 32 queries, 0 never: FP32-pipe scans, 1 whenever the space is eligible; the environment
+/* Tuning / introspection.  Options: "force_exact" (0/1); "tc_scan" (-1 auto and 1: tensor-core filter scan
+ * whenever the space is eligible (plain RealVector, d <= 128, k <= 40), 0 never: FP32-pipe scans; the environment
  * variable OMPLCU_TC_SCAN sets the default for new handles); "sample_thresholds", "collect",
  * "scan_ctas_per_sm", "tc_tiles", "profile" (tuning); "tc_scan_values_out" (diagnostics: device pointer that
  * receives the raw scan values).  Stats: "last_fallbacks", "last_path" (1 filter scan + exact re-rank,

@@ -484,7 +484,7 @@ def test_tensor_core_scan_values_within_the_stated_error_bound(gpu, scan_kernel,
     assert (ids == oi).all() and (dist == od).all()
 
 
-def test_tensor_core_scan_is_the_batched_default(gpu, monkeypatch):
+def test_tensor_core_scan_is_the_default(gpu, monkeypatch):
     monkeypatch.delenv("OMPLCU_TC_SCAN", raising=False)
     d, n = 7, 20000
     pts = helpers.uniform_points(1, n, d)
@@ -492,8 +492,8 @@ def test_tensor_core_scan_is_the_batched_default(gpu, monkeypatch):
     nn.add_rows(pts)
     _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
     assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1
-    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(3, 5, d), 10)
-    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 0  # single queries: FP32 scan
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(3, 1, d), 10)
+    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1  # single queries too (measured faster)
     nn.set_option("tc_scan", 0)
     _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
     assert nn.stat("last_tc") == 0
