@@ -419,9 +419,10 @@ def run_gpu_arm(args):
                 "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                 "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
                 "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu: 21 % busy) and neither is HBM: "
-                        "the kernel is bound by the MMA -> TMEM -> selection hand-over (ncu: issue slots 62 % busy, of which "
-                        "43 % mbarrier polls, 21 % min-trees over the accumulators, 25 % list insertions while the "
-                        "per-query thresholds converge) and by shared-memory operand reads; achieved exceeds the FP32 "
+                        "the kernel is bound by the MMA -> TMEM -> selection hand-over and the selection itself (ncu: issue "
+                        "slots 65 % busy: 31 % min-trees over the accumulators, 27 % list insertions while the per-query "
+                        "thresholds converge, 25 % mbarrier polls, 18 % bookkeeping; profiles/r1_scan_tc_d7_instruction_mix.txt) "
+                        "and by shared-memory operand reads; achieved exceeds the FP32 "
                         "FMA peak (vs_fp32_pipe_peak > 1), which bounded the round-1 FP32 scan (roofline_fp32_scan)",
             }
             if fp32_leg:
