@@ -48,7 +48,8 @@ TC_TRAFFIC = 356.8e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch,
 UNIT = "queries/s"
 
 
-def make_inputs(n_states=N_STATES, n_queries=N_QUERIES):
+def make_inputs(n_states=None, n_queries=N_QUERIES):
+    n_states = N_STATES if n_states is None else n_states
     pts = np.random.default_rng(1).random((n_states, DIM))
     qs = np.random.default_rng(1001).random((n_queries, DIM))
     return pts, qs
@@ -437,7 +438,8 @@ def run_gpu_arm(args):
             "vs_baseline": None,
             "dtype": "bf16x2 split filter on tensor cores (f32 accumulate) + f64 exact re-rank" if used_tc
             else "f32 filter + f64 exact re-rank", "data": "synthetic",
-            "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
+            "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), "
+                                   f"{N_STATES // 1_000_000}M states, 64K queries, k=10",
                        "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
                        "sharding": f"{S_SH} state shard(s) by insertion index x {R_QB} query block(s) over {world} ranks; "
                                    "one NCCL all-gather of the packed (distance, id) lists + merge by (distance, id)"
@@ -576,10 +578,14 @@ def main():
     ap.add_argument("--no-sample-thr", action="store_true", help="tuning: disable the threshold pre-pass")
     ap.add_argument("--shard", default="grid", choices=["grid", "states", "single"],
                     help="N > 1: 'grid' = state shards x query blocks (sharding.grid_shape), 'states' = N state shards")
+    ap.add_argument("--states", type=int, default=0, help="roadmap size for scaling studies (default: the metric's 1M)")
     ap.add_argument("--fp32-scan", action="store_true", help="use the FP32-pipe scan kernel instead of the tensor-core scan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
     ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")
     args = ap.parse_args()
+    if args.states:
+        global N_STATES
+        N_STATES = args.states  # scaling studies on larger roadmaps; the default run is BASELINE's 1M states
     if args.impl == "reference":
         run_reference_arm(args)
     else:
