@@ -91,8 +91,10 @@ namespace omplcu
 
         // one thread writes 8 consecutive K elements (16 bytes) of one row; consecutive threads take
         // consecutive rows of the same column group, so a warp writes 512 contiguous bytes
+        // Image row i is filter row i * row_step (row_step = 1: the whole set; > 1: the strided sample);
+        // rows at or beyond src_rows are dead (norm +inf).
         __global__ void tc_point_image_kernel(const float *filt, int rowf, int D, TcShape sh, size_t rows,
-                                              uint16_t *out)
+                                              size_t src_rows, size_t row_step, uint16_t *out)
         {
             const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
             const int groups = sh.kpad() / 8;
@@ -101,8 +103,17 @@ namespace omplcu
             const size_t tile = i / ((size_t)TC_PT * groups);
             const size_t rem = i % ((size_t)TC_PT * groups);
             const int grp = (int)(rem / TC_PT), r = (int)(rem % TC_PT);
-            const float *row = filt + (tile * TC_PT + r) * rowf;
+            const size_t src = (tile * TC_PT + r) * row_step;
+            const float *row = filt + src * rowf;
             uint16_t v[8];
+            if (src >= src_rows)
+            {
+                // dead row: coordinates 0, n1 = +inf
+#pragma unroll
+                for (int e = 0; e < 8; ++e)
+                    v[e] = (grp * 8 + e == 3 * D) ? (uint16_t)0x7f80u : (uint16_t)0;
+            }
+            else
 #pragma unroll
             for (int e = 0; e < 8; ++e)
                 v[e] = bf16_bits(tc_point_elem(row, D, grp * 8 + e));
@@ -544,6 +555,9 @@ namespace omplcu
                     P.cand_thr[(size_t)seg * P.qpad + q] = thr;
                     for (int i = 0; i < L; ++i)
                         P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = liq[i * TC_QT];
+                    if (P.list_vals)
+                        for (int i = 0; i < L; ++i)
+                            P.list_vals[((size_t)seg * L + i) * P.qpad + q] = lvq[i];
                 };
                 // one W-column step: min-tree against the threshold; the rare hit stages the values in
                 // shared memory and calls the out-of-line routine
@@ -678,6 +692,279 @@ namespace omplcu
                 tmem_dealloc(tmem, 512);
             }
         }
+
+        // ---------------- the threshold scan ----------------
+        // Same operand images, producer and issuer roles as knn_scan_tc_kernel, but the selection keeps no
+        // list: every query has a fixed bound tau (nn.cu: the r-th smallest scan value of a strided sample
+        // of the points, an exact distance bound, or a radius, all mapped to a scan value), and every slot
+        // whose scan value is below it is appended to the query's row of this CTA's segment -- one
+        // predicated store and one add per hit, a register counter, no shared-memory state per query, no
+        // convergence phase.  The exact epilogue (nn.cu) evaluates every kept slot in FP64 and proves
+        // that nothing dropped can matter (any point within the k-th exact distance has a scan value
+        // below tau, or the query is redone exactly).  A job is a whole 128-column accumulator
+        // (job j -> TMEM buffer j % 4), read W columns at a time through two register buffers.
+        constexpr int TC_THR_MAX_STAGES = 12;
+        struct TcThrSmem
+        {
+            uint64_t full[TC_THR_MAX_STAGES], empty[TC_THR_MAX_STAGES];
+            uint64_t a_full, a_empty;
+            uint64_t t_full[TC_ACC], t_empty[TC_ACC];
+            uint32_t tmem_base;
+        };
+
+        __device__ __forceinline__ float min8(const uint32_t *v)
+        {
+            float x = fminf(__uint_as_float(v[0]), fminf(__uint_as_float(v[1]), __uint_as_float(v[2])));
+            x = fminf(x, fminf(__uint_as_float(v[3]), __uint_as_float(v[4])));
+            x = fminf(x, fminf(__uint_as_float(v[5]), __uint_as_float(v[6])));
+            return fminf(x, __uint_as_float(v[7]));
+        }
+
+        template <int NA, int W, bool DBG>
+        __global__ void __launch_bounds__(tc_threads(NA), 1) knn_thr_scan_tc_kernel(const TcScanParams P)
+        {
+            extern __shared__ __align__(1024) uint8_t tc_smem[];
+            static_assert(W == 16 || W == 32, "columns per selection step");
+            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw;
+            const uint32_t chunk_bytes = (uint32_t)kw * 2048u;
+            const uint32_t a_tile_bytes = (uint32_t)nkc * chunk_bytes;
+            uint8_t *sA = tc_smem;                         // [NA][nkc][chunk]
+            uint8_t *sB = sA + (size_t)NA * a_tile_bytes;  // [nst][chunk]
+            TcThrSmem *S = reinterpret_cast<TcThrSmem *>(sB + (size_t)nst * chunk_bytes);
+
+            const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+            const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
+            const unsigned long long u0 = TU * g / G, u1 = TU * (g + 1) / G;
+
+            if (tid == 0)
+            {
+                for (int i = 0; i < TC_THR_MAX_STAGES; ++i)
+                {
+                    mbar_init(&S->full[i], 1);
+                    mbar_init(&S->empty[i], NA);
+                }
+                mbar_init(&S->a_full, 1);
+                mbar_init(&S->a_empty, NA);
+                for (int i = 0; i < TC_ACC; ++i)
+                {
+                    mbar_init(&S->t_full[i], 1);
+                    mbar_init(&S->t_empty[i], TC_QT);
+                }
+                mbar_fence_init();
+            }
+            if (warp == 1)
+                tmem_alloc(&S->tmem_base, 512);
+            tc_fence_before();
+            __syncthreads();
+            tc_fence_after();
+            const uint32_t tmem = S->tmem_base;
+
+            if (warp == 0)
+            {
+                if (lane == 0)
+                {
+                    int st = 0;
+                    uint32_t ph = 0, aph = 0;
+                    unsigned long long cur = ~0ull, t = 0, pt = 0;
+                    for (unsigned long long u = u0; u < u1; ++u, ++pt)
+                    {
+                        if (u == u0 || pt == U)
+                        {
+                            t = u / U;
+                            pt = u % U;
+                        }
+                        if (t != cur)
+                        {
+                            mbar_wait(&S->a_empty, aph ^ 1);
+                            mbar_expect_tx(&S->a_full, NA * a_tile_bytes);
+                            tma_bulk_g2s(sA, P.qimg + (size_t)t * NA * (a_tile_bytes / 2), NA * a_tile_bytes,
+                                         &S->a_full);
+                            aph ^= 1;
+                            cur = t;
+                        }
+                        const uint16_t *src = P.pimg + (size_t)pt * (a_tile_bytes / 2);
+                        for (int kc = 0; kc < nkc; ++kc)
+                        {
+                            mbar_wait(&S->empty[st], ph ^ 1);
+                            mbar_expect_tx(&S->full[st], chunk_bytes);
+                            tma_bulk_g2s(sB + (size_t)st * chunk_bytes, src + (size_t)kc * (chunk_bytes / 2),
+                                         chunk_bytes, &S->full[st]);
+                            if (++st == nst)
+                            {
+                                st = 0;
+                                ph ^= 1;
+                            }
+                        }
+                    }
+                }
+            }
+            else if (warp <= NA)
+            {
+                if (lane == 0)
+                {
+                    const int a = warp - 1;
+                    constexpr uint32_t idesc = umma_idesc_bf16(TC_QT, TC_PT);
+                    const uint32_t a0 = (smem_u32(sA) & 0x3FFFFu) + (uint32_t)a * a_tile_bytes, b0 = smem_u32(sB) & 0x3FFFFu;
+                    const uint64_t desc0 = umma_desc(0, TC_LBO, TC_SBO);
+                    const bool no_mma = (P.diag & 8) != 0;
+                    int st = 0;
+                    uint32_t ph = 0, aph = 0, job = (uint32_t)a;  // job = (unit - u0) * NA + tile
+                    unsigned long long cur = ~0ull, t = 0, pt = 0;
+                    for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
+                    {
+                        if (u == u0 || pt == U)
+                        {
+                            t = u / U;
+                            pt = u % U;
+                        }
+                        if (t != cur)
+                        {
+                            if (cur != ~0ull)
+                                umma_commit(&S->a_empty);
+                            mbar_wait(&S->a_full, aph);
+                            aph ^= 1;
+                            cur = t;
+                        }
+                        const uint32_t buf = job & (TC_ACC - 1);
+                        const uint32_t dcol = tmem + buf * TC_PT;
+                        for (int kc = 0; kc < nkc; ++kc)
+                        {
+                            mbar_wait(&S->full[st], ph);
+                            if (kc == 0)
+                                mbar_wait(&S->t_empty[buf], ((job / TC_ACC) & 1) ^ 1);
+                            tc_fence_after();
+                            const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
+                            const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
+                            if (!no_mma)
+                            {
+                                umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
+                                umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
+                                if (kw == 8)
+                                {
+                                    umma_bf16(dcol, ad + 2 * (2 * TC_LBO >> 4), bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
+                                    umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
+                                }
+                            }
+                            umma_commit(&S->empty[st]);
+                            if (kc == nkc - 1)
+                                umma_commit(&S->t_full[buf]);
+                            if (++st == nst)
+                            {
+                                st = 0;
+                                ph ^= 1;
+                            }
+                        }
+                    }
+                }
+            }
+            else
+            {
+                // selection: warp (a, wq) owns TMEM lane quadrant wq of the accumulators of resident tile a;
+                // a thread's lane is its query
+                const int a = (warp - 1 - NA) >> 2, wq = warp & 3, qrow = wq * 32 + lane;
+                const bool no_sel = (P.diag & 2) != 0, no_app = (P.diag & 4) != 0;
+                const uint32_t cap_w = P.cap - W;
+                float thr = 0.f;
+                uint32_t cnt = 0;
+                uint32_t *row = P.app_ids;
+                size_t qslot = 0;  // seg * qpad + q of the current (segment, query)
+                auto begin = [&](unsigned long long t) {
+                    const unsigned long long x = t * U;
+                    const unsigned long long gfirst = ((x + 1) * G + TU - 1) / TU - 1;
+                    const unsigned seg = (unsigned)(g - gfirst);
+                    const size_t q = ((size_t)t * NA + a) * TC_QT + qrow;
+                    qslot = (size_t)seg * P.qpad + q;
+                    thr = P.tau[q];
+                    cnt = 0;
+                    row = P.app_ids + qslot * P.cap;
+                };
+                // one W-column step: a min-tree against the bound; on a hit the columns below it are
+                // appended in column order.  Eight columns share a partial minimum, so a hit usually
+                // looks at one group only.
+                auto step = [&](uint32_t(&v)[W], uint32_t id0) {
+                    float p[W / 8];
+#pragma unroll
+                    for (int j = 0; j < W / 8; ++j)
+                        p[j] = min8(&v[8 * j]);
+                    float mn = fminf(p[0], p[1]);
+                    if constexpr (W == 32)
+                        mn = fminf(mn, fminf(p[2], p[3]));
+                    if (mn < thr && !no_app)
+                    {
+                        if (cnt <= cap_w)
+                        {
+#pragma unroll
+                            for (int j = 0; j < W / 8; ++j)
+                                if (p[j] < thr)
+                                {
+#pragma unroll
+                                    for (int i = 0; i < 8; ++i)
+                                        if (__uint_as_float(v[8 * j + i]) < thr)
+                                        {
+                                            row[cnt] = id0 + 8 * j + i;
+                                            ++cnt;
+                                        }
+                                }
+                        }
+                        else
+                            cnt = 0xFFFFFFFFu;  // the row is full: the count says so, the epilogue redoes the query exactly
+                    }
+                };
+                unsigned long long cur = ~0ull, job = a, t = 0, pt = 0;
+                for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
+                {
+                    if (u == u0 || pt == U)
+                    {
+                        t = u / U;  // once per super-tile: no 64-bit division in the unit loop
+                        pt = u % U;
+                        if (cur != ~0ull)
+                            P.app_cnt[qslot] = cnt;
+                        begin(t);
+                        cur = t;
+                    }
+                    const uint32_t slot0 = (uint32_t)(pt * TC_PT);
+                    const int buf = (int)(job & (TC_ACC - 1));
+                    mbar_wait(&S->t_full[buf], (uint32_t)((job / TC_ACC) & 1));
+                    tc_fence_after();
+                    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
+                    if (!no_sel)
+                    {
+                        uint32_t ra[W], rb[W];
+                        __syncwarp();
+                        tmem_ld_issue(taddr, ra);
+#pragma unroll 1
+                        for (int c = 0; c < TC_PT / W; c += 2)
+                        {
+                            __syncwarp();
+                            tmem_ld_wait(ra);
+                            tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
+                            if (DBG)
+                                tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
+                            step(ra, slot0 + c * W);
+                            __syncwarp();
+                            tmem_ld_wait(rb);
+                            if (c + 2 < TC_PT / W)
+                                tmem_ld_issue(taddr + (c + 2) * W, ra);
+                            if (DBG)
+                                tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
+                            step(rb, slot0 + (c + 1) * W);
+                        }
+                    }
+                    tc_fence_before();
+                    mbar_arrive(&S->t_empty[buf]);
+                }
+                if (cur != ~0ull)
+                    P.app_cnt[qslot] = cnt;
+            }
+            tc_fence_before();
+            __syncthreads();
+            if (warp == 1)
+            {
+                __syncwarp();
+                tc_fence_after();
+                tmem_dealloc(tmem, 512);
+            }
+        }
     }  // namespace
 
     size_t tc_smem_bytes(const TcShape &sh, int nstages, int L)
@@ -700,7 +987,17 @@ namespace omplcu
         const TcShape sh = tc_shape(D);
         const size_t rows = units * TC_PT, n = rows * (sh.kpad() / 8);
         if (n)
-            tc_point_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(filt, rowf, D, sh, rows, out);
+            tc_point_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(filt, rowf, D, sh, rows, rows, 1, out);
+    }
+
+    void tc_build_sample_image(const float *filt, int rowf, int D, size_t src_rows, size_t row_step, size_t units,
+                               uint16_t *out, cudaStream_t s)
+    {
+        const TcShape sh = tc_shape(D);
+        const size_t rows = units * TC_PT, n = rows * (sh.kpad() / 8);
+        if (n)
+            tc_point_image_kernel<<<(unsigned)((n + 255) / 256), 256, 0, s>>>(filt, rowf, D, sh, rows, src_rows,
+                                                                              row_step, out);
     }
 
     void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint16_t *out, cudaStream_t s)
@@ -740,9 +1037,56 @@ namespace omplcu
         }
     }  // namespace
 
+    size_t tc_thr_smem_bytes(const TcShape &sh, int nstages)
+    {
+        const size_t chunk = (size_t)sh.kw * 2048;
+        return (size_t)sh.na * sh.nkc * chunk + (size_t)nstages * chunk + sizeof(TcThrSmem) + 64;
+    }
+
+    int tc_thr_pick_stages(const TcShape &sh)
+    {
+        for (int st = TC_THR_MAX_STAGES; st >= 3; --st)
+            if (tc_thr_smem_bytes(sh, st) <= 227 * 1024)
+                return st;
+        return 0;
+    }
+
+    namespace
+    {
+        template <int NA, int W>
+        void tc_thr_launch(const TcScanParams &P, unsigned grid, cudaStream_t s)
+        {
+            const size_t smem = tc_thr_smem_bytes(P.sh, P.nstages);
+            if (P.dbg)
+            {
+                CUDA_CHECK(cudaFuncSetAttribute(knn_thr_scan_tc_kernel<NA, W, true>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                knn_thr_scan_tc_kernel<NA, W, true><<<grid, tc_threads(NA), smem, s>>>(P);
+                return;
+            }
+            CUDA_CHECK(cudaFuncSetAttribute(knn_thr_scan_tc_kernel<NA, W, false>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            knn_thr_scan_tc_kernel<NA, W, false><<<grid, tc_threads(NA), smem, s>>>(P);
+        }
+    }  // namespace
+
+    void tc_launch_thr_scan(const TcScanParams &P, unsigned grid, cudaStream_t s)
+    {
+        REQUIRE(P.cap >= 64 && P.cap % 32 == 0, "threshold scan: bad row capacity");
+        const bool w16 = (P.diag & 16) != 0;
+        if (P.sh.na == 4)
+            w16 ? tc_thr_launch<4, 16>(P, grid, s) : tc_thr_launch<4, 32>(P, grid, s);
+        else if (P.sh.na == 2)
+            w16 ? tc_thr_launch<2, 16>(P, grid, s) : tc_thr_launch<2, 32>(P, grid, s);
+        else
+            w16 ? tc_thr_launch<1, 16>(P, grid, s) : tc_thr_launch<1, 32>(P, grid, s);
+    }
+
     void tc_launch_scan(int L, const TcScanParams &P, unsigned grid, cudaStream_t s)
     {
-        if (L == 16)
+        if (L == 8)
+            tc_launch_na<8>(P, grid, s);
+        else if (L == 16)
             tc_launch_na<16>(P, grid, s);
         else if (L == 24)
             tc_launch_na<24>(P, grid, s);

@@ -76,6 +76,14 @@ namespace omplcu
         int nstages;
         int diag;               // diagnostics: 1 swap descriptor fields, 2 no selection, 4 no insertion
         float *dbg;             // [qpad][units*TC_PT] raw scan values, or nullptr
+        // list kernel only: the list values themselves, [smax*L][qpad] (tagged, i.e. rounded up by < 128 ulp;
+        // EMPTY markers > 1e38 where the list did not fill), or nullptr.  Read by the threshold selection.
+        float *list_vals;
+        // threshold kernel only (tc_launch_thr_scan): per-query bound and the append rows
+        const float *tau;       // [qpad]  a point is kept iff its scan value < tau[query]
+        uint32_t *app_ids;      // [smax][qpad][cap] slots kept, in scan order
+        uint32_t *app_cnt;      // [smax][qpad] how many (> cap: the row overflowed, its content is incomplete)
+        uint32_t cap;           // multiple of 32, >= 64
     };
 
     size_t tc_smem_bytes(const TcShape &sh, int nstages, int L);
@@ -84,6 +92,14 @@ namespace omplcu
     // images
     void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint16_t *out, cudaStream_t s);
     void tc_build_query_image(const float *qp, uint32_t qpad, int D, uint16_t *out, cudaStream_t s);
-    // L in {16, 24, 48}
+    // every row_step-th filter row (rows >= src_rows count as dead): the sample the thresholds come from
+    void tc_build_sample_image(const float *filt, int rowf, int D, size_t src_rows, size_t row_step, size_t units,
+                               uint16_t *out, cudaStream_t s);
+    // list scan: the L smallest scan values per (segment, query); L in {8, 16, 24, 48}
     void tc_launch_scan(int L, const TcScanParams &P, unsigned grid, cudaStream_t s);
+    // threshold scan: every slot whose scan value is below the query's bound is appended to the
+    // query's row of its segment; no lists, no shared-memory state per query
+    void tc_launch_thr_scan(const TcScanParams &P, unsigned grid, cudaStream_t s);
+    size_t tc_thr_smem_bytes(const TcShape &sh, int nstages);
+    int tc_thr_pick_stages(const TcShape &sh);
 }  // namespace omplcu

@@ -29,6 +29,7 @@ namespace omplcu
         constexpr int KNN_MAX_REG_DIM = 16;
         constexpr size_t EXACT_PAIR_BUDGET = (size_t)1 << 25;
         constexpr size_t RADIUS_PAIR_BUDGET = (size_t)1 << 27;  // 8 B per pair: 1 GB of distances per batch
+        constexpr size_t THR_MIN_SLOTS = 32768;  // below: the list scan (its warm-up is cheaper than a sample pass)
 
         __device__ __forceinline__ float inff()
         {
@@ -224,6 +225,216 @@ namespace omplcu
             if (bad && lane == 0)
             {
                 unsigned pos = atomicAdd(ovf_count, 1u);
+                ovf_list[pos] = (uint32_t)qi;
+            }
+        }
+
+        // ---- threshold path (knn_thr_scan_tc_kernel): bound selection and exact epilogue ----
+        // floats ordered as unsigned integers
+        __device__ __forceinline__ uint32_t f32_key(float x)
+        {
+            const uint32_t b = __float_as_uint(x);
+            return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+        }
+
+        // tau[q] = the r-th smallest (1-based) of the nvals list values the sample scan left for query q
+        // (vals[c][q], c < nvals; EMPTY markers > 1e38 where a list did not fill), found by bisection on
+        // the bits.  Fewer than r real values: no bound (3e38, everything is kept).  LPQ lanes serve one
+        // query: 1 when a query has a few dozen values, 32 when a lone query was cut into many segments.
+        template <int LPQ>
+        __global__ void __launch_bounds__(128) tau_select_kernel(const float *vals, uint32_t nvals, uint32_t qpad,
+                                                                 uint32_t r, float *tau)
+        {
+            const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+            const uint32_t qi = t / LPQ, l = t % LPQ;
+            if (qi >= qpad)
+                return;
+            uint32_t lo = 0, hi = 0xFFFFFFFFu;
+            while (lo < hi)
+            {
+                const uint32_t mid = lo + ((hi - lo) >> 1);
+                uint32_t c = 0;
+                for (uint32_t j = l; j < nvals; j += LPQ)
+                    c += f32_key(vals[(size_t)j * qpad + qi]) <= mid ? 1u : 0u;
+                if (LPQ > 1)
+                    c = __reduce_add_sync(0xffffffffu, c);
+                if (c >= r)
+                    hi = mid;
+                else
+                    lo = mid + 1;
+            }
+            if (l == 0)
+            {
+                const uint32_t b = (lo & 0x80000000u) ? (lo & 0x7FFFFFFFu) : ~lo;
+                const float v = __uint_as_float(b);
+                tau[qi] = (v < 1e38f) ? v : 3.0e38f;  // (NaN never enters a list)
+            }
+        }
+
+        // Exact epilogue of the threshold scan, one warp per query.  Every kept slot gets its exact
+        // distance (RealVectorStateSpace::distance, argument order (element, query) as in
+        // NearestNeighborsLinear.h:159-172); the kk smallest by (distance, slot) are written in that order.
+        // Proof obligation (the band check of knn_rerank_kernel with one list whose final threshold is
+        // tau): a point within the kk-th selected distance Dk has a scan value <= bound(Dk); the scan
+        // kept everything below tau; so tau > bound(Dk) proves the answer.  Otherwise -- or when a row
+        // overflowed, or fewer than kk slots were kept -- the query goes to the exact path.
+        // Selection: a 256-bucket histogram of the distances (monotone map) finds the bucket of the kk-th
+        // smallest, the slots up to that bucket are compacted in place and ranked among themselves.
+        template <int MAXC>
+        __global__ void __launch_bounds__(128) knn_rerank_thr_kernel(
+            const uint32_t *app_ids, const uint32_t *app_cnt, uint32_t smax, uint32_t cap, uint32_t qpad,
+            const float *tau, const double *pts, const uint64_t *slot_ids, int D, const double *q,
+            const double *qaux, const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride,
+            uint64_t *out_ids, double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units,
+            unsigned long long *kept_total)
+        {
+            extern __shared__ __align__(16) unsigned char rr_smem[];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            double *s_key = reinterpret_cast<double *>(rr_smem) + (size_t)w * MAXC;
+            uint32_t *s_slot = reinterpret_cast<uint32_t *>(reinterpret_cast<double *>(rr_smem) + 4 * MAXC) + (size_t)w * MAXC;
+            uint32_t *s_hist = reinterpret_cast<uint32_t *>(reinterpret_cast<double *>(rr_smem) + 4 * MAXC) + 4 * MAXC + w * 256;
+            const size_t qi = blockIdx.x * 4ull + w;
+            if (qi >= nq)
+                return;
+            const double *qrow = q + qi * D;
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            bool bad = false;
+            uint32_t n = 0;
+            double kmin = inf, kmax = 0.0;
+            for (uint32_t s = 0; s < smax; ++s)
+            {
+                const uint32_t c = app_cnt[(size_t)s * qpad + qi];
+                if (c > cap || n + c > MAXC)
+                {
+                    bad = true;  // the row overflowed, or more slots than the epilogue holds
+                    break;
+                }
+                const uint32_t *row = app_ids + ((size_t)s * qpad + qi) * cap;
+                for (uint32_t i = lane; i < c; i += 32)
+                {
+                    const uint32_t slot = row[i];
+                    const double key = rv_distance(pts + (size_t)slot * D, qrow, D);
+                    s_key[n + i] = key;
+                    s_slot[n + i] = slot;
+                    kmin = fmin(kmin, key);  // fmin / fmax drop a NaN: a NaN distance fails the band check below
+                    kmax = fmax(kmax, key);
+                }
+                n += c;
+            }
+            if (lane == 0 && kept_total)
+                atomicAdd(kept_total, (unsigned long long)n);
+            double dk = -1.0;
+            if (!bad && n >= kk)
+            {
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    kmin = fmin(kmin, __shfl_xor_sync(0xffffffffu, kmin, o));
+                    kmax = fmax(kmax, __shfl_xor_sync(0xffffffffu, kmax, o));
+                }
+                for (int i = lane; i < 256; i += 32)
+                    s_hist[i] = 0;
+                __syncwarp();
+                const double scale = (kmax > kmin) ? 255.0 / (kmax - kmin) : 0.0;
+                auto bucket = [&](double key) -> uint32_t {
+                    const double b = (key - kmin) * scale;  // monotone in key; NaN -> bucket 255
+                    return (b >= 0.0 && b < 255.0) ? (uint32_t)b : 255u;
+                };
+                for (uint32_t i = lane; i < n; i += 32)
+                    atomicAdd(&s_hist[bucket(s_key[i])], 1u);
+                __syncwarp();
+                // bucket of the kk-th smallest: lane l owns buckets 8 l .. 8 l + 7
+                uint32_t mine = 0;
+                for (int i = 0; i < 8; ++i)
+                    mine += s_hist[8 * lane + i];
+                uint32_t incl = mine;
+                for (int o = 1; o < 32; o <<= 1)
+                {
+                    const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                    if (lane >= o)
+                        incl += v;
+                }
+                const uint32_t first = __ffs(__ballot_sync(0xffffffffu, incl >= kk)) - 1;  // n >= kk: some lane reaches it
+                uint32_t bsel = 0;
+                if ((uint32_t)lane == first)
+                {
+                    uint32_t acc = incl - mine;
+                    for (int i = 0; i < 8; ++i)
+                    {
+                        acc += s_hist[8 * lane + i];
+                        if (acc >= kk)
+                        {
+                            bsel = 8 * lane + i;
+                            break;
+                        }
+                    }
+                }
+                bsel = __shfl_sync(0xffffffffu, bsel, first);
+                // compact the slots of buckets <= bsel in place (a write never passes the chunk being read)
+                uint32_t m = 0;
+                for (uint32_t i0 = 0; i0 < n; i0 += 32)
+                {
+                    const uint32_t i = i0 + lane;
+                    double key = 0.0;
+                    uint32_t slot = 0;
+                    bool keep = false;
+                    if (i < n)
+                    {
+                        key = s_key[i];
+                        slot = s_slot[i];
+                        keep = bucket(key) <= bsel;
+                    }
+                    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                    __syncwarp();
+                    if (keep)
+                    {
+                        const uint32_t pos = m + __popc(bal & ((1u << lane) - 1u));
+                        s_key[pos] = key;
+                        s_slot[pos] = slot;
+                    }
+                    m += __popc(bal);
+                    __syncwarp();
+                }
+                // rank by (distance, slot) among the m compacted entries (m >= kk)
+                for (uint32_t c = lane; c < m; c += 32)
+                {
+                    const double key = s_key[c];
+                    const uint32_t slot = s_slot[c];
+                    uint32_t rank = 0;
+                    for (uint32_t o = 0; o < m; ++o)
+                    {
+                        const double ko = s_key[o];
+                        const uint32_t so = s_slot[o];
+                        rank += (ko < key || (ko == key && so < slot)) ? 1u : 0u;
+                    }
+                    if (rank < kk)
+                    {
+                        out_ids[qi * kstride + rank] = slot_ids[slot];
+                        if (out_dists)
+                            out_dists[qi * kstride + rank] = key;
+                        if (rank == kk - 1)
+                            dk = key;
+                    }
+                }
+                for (int o = 16; o > 0; o >>= 1)
+                    dk = fmax(dk, __shfl_xor_sync(0xffffffffu, dk, o));
+            }
+            // ---- band check (same bound as knn_rerank_kernel) ----
+            const double u = 5.9604644775390625e-08;  // 2^-24
+            const double qn = qaux[2 * qi], qnorm = qaux[2 * qi + 1];
+            const double pmax2 = (double)__uint_as_float(*pmax2_bits) * (1.0 + 2.0 * u);
+            const double pmax = sqrt(pmax2) * (1.0 + 1e-9);
+            const double delta = (double)(D + 4) * 1.1102230246251565e-16;
+            const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
+            const double A = dk * (1.0 + delta) + rho + 1e-150;
+            const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+            const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
+            bad = bad || !(tau64 == tau64) || !(tau64 < 1e37) || dk < 0.0;  // NaN / overflow / too few -> redo exactly
+            const double tq = (double)tau[qi];
+            if (tq < 1e38 && !(tq > tau64))
+                bad = true;  // tau >= 1e38: nothing was dropped
+            if (bad && lane == 0)
+            {
+                const unsigned pos = atomicAdd(ovf_count, 1u);
                 ovf_list[pos] = (uint32_t)qi;
             }
         }
@@ -638,9 +849,14 @@ namespace omplcu
         }
         if (const char *e = getenv("OMPLCU_TC_SCAN"))
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
+        if (const char *e = getenv("OMPLCU_THR_SCAN"))
+            thr_mode_ = atoi(e);  // default for the "thr_scan" option
         counters_.reserve(4);
         CUDA_CHECK(cudaEventCreate(&ev0_));
         CUDA_CHECK(cudaEventCreate(&ev1_));
+        CUDA_CHECK(cudaEventCreate(&ev2_));
+        CUDA_CHECK(cudaEventCreate(&ev3_));
+        kept_.reserve(1);
         CUDA_CHECK(cudaStreamSynchronize(stream_));
     }
 
@@ -656,6 +872,10 @@ namespace omplcu
             cudaEventDestroy(ev0_);
         if (ev1_)
             cudaEventDestroy(ev1_);
+        if (ev2_)
+            cudaEventDestroy(ev2_);
+        if (ev3_)
+            cudaEventDestroy(ev3_);
     }
 
     void NNIndex::set_id_base(uint64_t base)
@@ -921,6 +1141,13 @@ namespace omplcu
             tc_mode_ = (int)v;  // -1 auto, 0 never, 1 whenever the space is eligible
         else if (!strcmp(key, "tc_tiles"))
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
+        else if (!strcmp(key, "thr_scan"))
+            thr_mode_ = (int)v;  // -1 auto, 0 never (list scan), 1 whenever the tensor-core scan runs
+        else if (!strcmp(key, "thr_sample_step"))
+        {
+            thr_step_ = (int)std::max<long>(1, v);
+            tc_sversion_ = 0;
+        }
         else if (!strcmp(key, "tc_variant"))
         {
             tc_variant_ = (int)v;
@@ -950,6 +1177,16 @@ namespace omplcu
             return last_tc_;
         if (!strcmp(key, "launches"))
             return launches_;
+        if (!strcmp(key, "last_thr"))
+            return last_thr_;
+        if (!strcmp(key, "last_kept"))
+            return last_kept_;
+        if (!strcmp(key, "last_rank"))
+            return last_rank_;
+        if (!strcmp(key, "last_sample_ns"))
+            return last_sample_ns_;
+        if (!strcmp(key, "last_main_ns"))
+            return last_main_ns_;
         if (!strcmp(key, "last_scan_ns"))
             return last_scan_ns_;
         if (!strcmp(key, "scan_ns_total"))
@@ -1131,6 +1368,12 @@ namespace omplcu
         const bool tc_auto = nq >= TC_MIN_BATCH;  // measured faster than the FP32 scans at every batched size
         const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
         last_tc_ = tc ? 1 : 0;
+        last_thr_ = 0;
+        if (tc && (thr_mode_ == 1 || (thr_mode_ < 0 && nslots_ >= THR_MIN_SLOTS)) && nslots_ >= 4096)
+        {
+            knn_fast_thr(d_q, nq, kk, kstride, d_ids, d_dists, s);
+            return;
+        }
         const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));
         const size_t QT = tc ? (size_t)TC_QT * tc_sh.na : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
         const size_t PT = tc ? (size_t)TC_PT : hd ? (size_t)HD_PT : (size_t)SCAN_PT;
@@ -1219,7 +1462,7 @@ namespace omplcu
             tc_qimg_.reserve((size_t)(qpad / TC_QT) * tc_sh.nkc * tc_sh.chunk_elems());
             tc_build_query_image(qp_.p, qpad, D_, tc_qimg_.p, s);
             launches_++;
-            TcScanParams T;
+            TcScanParams T{};
             T.pimg = tc_pimg_.p;
             T.qimg = tc_qimg_.p;
             T.cand_thr = cand_vals_.p;
@@ -1261,6 +1504,212 @@ namespace omplcu
             last_scan_ns_ = (long)(ms * 1e6);
             scan_ns_total_ += last_scan_ns_;
             scan_count_++;
+        }
+        if (novf)
+            knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
+    }
+
+    namespace
+    {
+        // Smallest r such that, when the bound is the r-th smallest scan value of a sample holding each
+        // point with probability p, fewer than k + 3 points of the whole set fall below it with
+        // probability < 1e-5 (the count is r + NegBin(r, p)).  Such a query is not wrong, only redone exactly.
+        uint32_t thr_pick_rank(size_t k, double p)
+        {
+            const double q = 1.0 - p;
+            for (uint32_t r = 1; r < 4096; ++r)
+            {
+                if (r >= k + 3)
+                    return r;
+                const uint32_t jmax = (uint32_t)(k + 2 - r);  // P(NegBin <= jmax)
+                double term = std::pow(p, (double)r), cdf = term;
+                for (uint32_t j = 1; j <= jmax; ++j)
+                {
+                    term *= q * (double)(j + r - 1) / (double)j;
+                    cdf += term;
+                }
+                if (cdf < 1e-5)
+                    return r;
+            }
+            return 4096;
+        }
+    }  // namespace
+
+    // Threshold path of the tensor-core scan (knn_scan_tc.cu, knn_thr_scan_tc_kernel), for an index
+    // large enough that a sample pass pays:
+    //   1. list scan (L = 8 / 16 / 24) over the sample image: every step-th point, 1/step of the pairs
+    //   2. tau_select: the r-th smallest sample value per query is the query's bound tau
+    //   3. threshold scan over all points: slots with a scan value below tau are appended (~ r * step per query)
+    //   4. exact epilogue: FP64 distance of every kept slot, k best by (distance, slot), band check
+    //      against tau; unprovable queries (row overflow, fewer than k kept, band) go to the exact path
+    // Nothing here converges, so the cost per (query, segment) is the appends, not a list warm-up:
+    // the time is linear in the points a rank owns, which is what makes a sharded roadmap scale.
+    void NNIndex::knn_fast_thr(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+                               double *d_dists, cudaStream_t s)
+    {
+        TcShape sh = tc_shape(D_);
+        if (tc_na_ > 0 && tc_na_ < sh.na)
+            sh.na = tc_na_;
+        const int stages = tc_thr_pick_stages(sh);
+        REQUIRE(stages > 0, "threshold scan: shape does not fit shared memory");
+        const size_t QT = (size_t)TC_QT * sh.na;
+        const size_t qtiles = (nq + QT - 1) / QT;
+        const uint32_t qpad = (uint32_t)(qtiles * QT);
+        auto segments = [&](size_t qtiles, unsigned long long U, unsigned long long G) {
+            const unsigned long long TU = qtiles * U;
+            uint32_t smax = 1;
+            for (size_t t = 0; t < qtiles; ++t)
+            {
+                const unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
+                const unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
+                const unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
+                smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
+            }
+            return smax;
+        };
+        // ---- sample ----
+        const size_t step = (size_t)thr_step_;
+        const size_t srows = (nslots_ + step - 1) / step;
+        const unsigned long long Us = (srows + TC_PT - 1) / TC_PT;
+        const uint32_t r = thr_pick_rank(kk, 1.0 / (double)step);
+        REQUIRE(r <= 48, "threshold scan: k too large for the sample lists");
+        const int Ls = r <= 8 ? 8 : (r <= 16 ? 16 : (r <= 24 ? 24 : 48));
+        TcShape shs = sh;
+        int stages_s = tc_pick_stages(shs, Ls);
+        while (stages_s == 0 && shs.na > 1)
+        {
+            shs.na /= 2;
+            stages_s = tc_pick_stages(shs, Ls);
+        }
+        REQUIRE(stages_s > 0, "threshold scan: sample lists do not fit shared memory");
+        const size_t qtiles_s = qpad / ((size_t)TC_QT * shs.na);  // long lists: fewer resident query tiles
+        const unsigned long long TUs = qtiles_s * Us;
+        const unsigned long long Gs = std::max<unsigned long long>(1, std::min<unsigned long long>(sm_count_, TUs));
+        const uint32_t smax_s = segments(qtiles_s, Us, Gs);
+        // ---- main ----
+        const unsigned long long U = (nslots_ + TC_PT - 1) / TC_PT, TU = qtiles * U;
+        const unsigned long long G = std::max<unsigned long long>(1, std::min<unsigned long long>(sm_count_, TU));
+        const uint32_t smax = segments(qtiles, U, G);
+        // expected kept slots per query r * step, standard deviation sqrt(r (1 - p)) * step
+        const double mean = (double)r * (double)step, sd = std::sqrt((double)r) * (double)step;
+        constexpr int MAXC = 1024;
+        uint32_t cap = (uint32_t)(mean + 6.0 * sd) + 64;
+        cap = std::min<uint32_t>(MAXC, ((cap + 31) / 32) * 32);
+        last_rank_ = r;
+
+        qp_.reserve((size_t)D_ * qpad);
+        qaux_.reserve(2 * (size_t)qpad);
+        cand_vals_.reserve((size_t)smax_s * qpad);
+        cand_ids_.reserve((size_t)smax_s * Ls * qpad);
+        list_vals_.reserve((size_t)smax_s * Ls * qpad);
+        tau_.reserve(qpad);
+        app_cnt_.reserve((size_t)smax * qpad);
+        app_ids_.reserve((size_t)smax * qpad * cap);
+        ovf_list_.reserve(nq);
+        CUDA_CHECK(cudaMemsetAsync(list_vals_.p, 0x7F, (size_t)smax_s * Ls * qpad * sizeof(float), s));  // "empty"
+        CUDA_CHECK(cudaMemsetAsync(app_cnt_.p, 0, (size_t)smax * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(counters_.p, 0, sizeof(unsigned), s));
+        CUDA_CHECK(cudaMemsetAsync(kept_.p, 0, sizeof(unsigned long long), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, qp_.p, qaux_.p, qpad);
+        launches_++;
+        if (tc_version_ != mut_version_)
+        {
+            tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
+            tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+            tc_version_ = mut_version_;
+            launches_++;
+        }
+        if (tc_sversion_ != mut_version_ || tc_sstep_ != step)
+        {
+            tc_simg_.reserve((size_t)Us * sh.nkc * sh.chunk_elems());
+            tc_build_sample_image(filt_.p, rowf_, D_, nslots_, step, (size_t)Us, tc_simg_.p, s);
+            tc_sversion_ = mut_version_;
+            tc_sstep_ = step;
+            launches_++;
+        }
+        tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
+        tc_build_query_image(qp_.p, qpad, D_, tc_qimg_.p, s);
+        launches_++;
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev0_, s));
+        TcScanParams T{};
+        T.qimg = tc_qimg_.p;
+        T.qpad = qpad;
+        T.sh = sh;
+        T.diag = tc_variant_;
+        T.dbg = nullptr;
+        // 1. sample lists
+        T.pimg = tc_simg_.p;
+        T.cand_thr = cand_vals_.p;
+        T.cand_ids = cand_ids_.p;
+        T.list_vals = list_vals_.p;
+        T.units = Us;
+        T.total_units = TUs;
+        T.smax = smax_s;
+        T.nstages = stages_s;
+        T.diag = 0;
+        T.sh = shs;
+        tc_launch_scan(Ls, T, (unsigned)Gs, s);
+        T.sh = sh;
+        // 2. bounds
+        if ((size_t)smax_s * Ls > 64)
+            tau_select_kernel<32><<<nblk((size_t)qpad * 32, 128), 128, 0, s>>>(list_vals_.p, smax_s * Ls, qpad, r, tau_.p);
+        else
+            tau_select_kernel<1><<<nblk(qpad, 128), 128, 0, s>>>(list_vals_.p, smax_s * Ls, qpad, r, tau_.p);
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev2_, s));
+        // 3. threshold scan
+        T.pimg = tc_pimg_.p;
+        T.list_vals = nullptr;
+        T.tau = tau_.p;
+        T.app_ids = app_ids_.p;
+        T.app_cnt = app_cnt_.p;
+        T.cap = cap;
+        T.units = U;
+        T.total_units = TU;
+        T.smax = smax;
+        T.nstages = stages;
+        T.diag = tc_variant_;
+        T.dbg = tc_dbg_;
+        tc_launch_thr_scan(T, (unsigned)G, s);
+        launches_ += 3;
+        CUDA_CHECK(cudaGetLastError());
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev1_, s));
+        // 4. exact epilogue
+        const size_t rr_smem = (size_t)48 * MAXC + 4096;
+        static std::once_flag rr_once[64];
+        std::call_once(rr_once[device_ & 63], [&] {
+            CUDA_CHECK(cudaFuncSetAttribute(knn_rerank_thr_kernel<MAXC>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)rr_smem));
+        });
+        knn_rerank_thr_kernel<MAXC><<<nblk(nq, 4), 128, rr_smem, s>>>(
+            app_ids_.p, app_cnt_.p, smax, cap, qpad, tau_.p, pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
+            (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, ovf_list_.p, counters_.p, tc_err_units(D_),
+            profile_ ? kept_.p : nullptr);
+        launches_++;
+        CUDA_CHECK(cudaGetLastError());
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(ev3_, s));
+        unsigned novf = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&novf, counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        last_fallbacks_ = novf;
+        last_thr_ = 1;
+        if (profile_)
+        {
+            float ms = 0.f;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev1_));
+            last_scan_ns_ = (long)(ms * 1e6);
+            scan_ns_total_ += last_scan_ns_;
+            scan_count_++;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev2_));
+            last_sample_ns_ = (long)(ms * 1e6);
+            CUDA_CHECK(cudaEventElapsedTime(&ms, ev2_, ev1_));
+            last_main_ns_ = (long)(ms * 1e6);
+            unsigned long long kept = 0;
+            CUDA_CHECK(cudaMemcpy(&kept, kept_.p, sizeof(kept), cudaMemcpyDeviceToHost));
+            last_kept_ = (long)kept;
         }
         if (novf)
             knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);

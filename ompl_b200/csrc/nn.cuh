@@ -58,6 +58,9 @@ namespace omplcu
         bool fast_eligible(size_t kk) const;
         void knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                       cudaStream_t s);
+        // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
+        void knn_fast_thr(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
+                          cudaStream_t s);
         // exact sort path over the selected queries (d_sel == nullptr: all nq)
         bool prepare_chain_tables(const double *d_q, size_t nq, cudaStream_t s);
         bool knn_exact_collect(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
@@ -118,6 +121,18 @@ namespace omplcu
         int tc_variant_ = 0;      // image layout / descriptor variants (diagnostics)
         float *tc_dbg_ = nullptr; // device buffer for raw scan values (diagnostics), caller-owned
         long last_tc_ = 0;
+        // threshold path (knn_fast_thr): sample image, bounds, append rows
+        DevBuf<uint16_t> tc_simg_;
+        unsigned long tc_sversion_ = 0;
+        size_t tc_sstep_ = 0;
+        DevBuf<float> tau_, list_vals_;
+        DevBuf<uint32_t> app_ids_, app_cnt_;
+        DevBuf<unsigned long long> kept_;
+        int thr_mode_ = 0;        // -1 auto (index of >= 32768 slots), 0 never, 1 whenever the tensor-core scan runs
+        int thr_step_ = 16;       // sample stride
+        long last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
+        cudaEvent_t ev2_ = nullptr, ev3_ = nullptr;
+        long last_sample_ns_ = 0, last_main_ns_ = 0;
 
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
