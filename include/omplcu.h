@@ -168,6 +168,22 @@ int omplcu_check_states_device(omplcu_checker_t c, int stride, const double *d_s
 int omplcu_check_motions_device(omplcu_checker_t c, omplcu_space_t sp, const double *d_s1, const double *d_s2,
                                 size_t n, uint8_t *d_valid, double *d_last_t, double *d_last_state, void *stream);
 
+/* Allocation-free variant of omplcu_check_motions_device.  It has NO counterpart in the reference; it was
+ * added for callers that cannot call cudaMalloc (code under CUDA
+ * graph capture, tight serving loops, harnesses that forbid it).  Same inputs, outputs and results as
+ * omplcu_check_motions_device, but the per-segment scratch (segment counts, first-failure codes, the work
+ * counter) lives in a file-scope static __device__ array of the library instead of the checker's growable
+ * buffers: the call performs no cudaMalloc / cudaFree and uses no allocating library routine.
+ * Limit: n <= OMPLCU_NOALLOC_MAX_SEGMENTS, larger batches return OMPLCU_ERR_INVALID (split them).  The
+ * array (2 MiB + 256 B) is held by every GPU that loads the library until the process exits.  It is
+ * shared by ALL checkers and calls on a device and keeps the last call's contents; the call clears what
+ * must start at zero itself.  Calls that overlap on one GPU (different streams or host threads) RACE on
+ * it: issue them one at a time per device.  Synchronises `stream` before returning. */
+#define OMPLCU_NOALLOC_MAX_SEGMENTS 262144
+int omplcu_check_motions_device_noalloc(omplcu_checker_t c, omplcu_space_t sp, const double *d_s1,
+                                        const double *d_s2, size_t n, uint8_t *d_valid, double *d_last_t,
+                                        double *d_last_state, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

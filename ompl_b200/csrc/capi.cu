@@ -496,4 +496,15 @@ int omplcu_check_motions_device(omplcu_checker_t c, omplcu_space_t sp, const dou
         c->impl->check_motions_device(sp->desc, d_s1, d_s2, n, d_valid, d_last_t, d_last_state, (cudaStream_t)stream);
     });
 }
+
+int omplcu_check_motions_device_noalloc(omplcu_checker_t c, omplcu_space_t sp, const double *d_s1,
+                                        const double *d_s2, size_t n, uint8_t *d_valid, double *d_last_t,
+                                        double *d_last_state, void *stream)
+{
+    return guarded([&] {
+        REQUIRE(c && sp, "checker or space is NULL");
+        c->impl->check_motions_device_noalloc(sp->desc, d_s1, d_s2, n, d_valid, d_last_t, d_last_state,
+                                              (cudaStream_t)stream);
+    });
+}
 }

@@ -576,12 +576,44 @@ namespace omplcu
     // ==================================================================
     // host side
     // ==================================================================
+    // ---- scratch of omplcu_check_motions_device_noalloc (no counterpart in the reference; added
+    // for callers that cannot call cudaMalloc) ----
+    // Layout: [0, 16) the two work counters of motion_group_kernel, [256, 256 + 4 M) segment counts,
+    // [256 + 4 M, 256 + 8 M) first-failure codes, M = OMPLCU_NOALLOC_MAX_SEGMENTS.  Every GPU that loads
+    // the library holds these 2 MiB + 256 B until exit; all checkers and calls on a device share them.
+    constexpr size_t NOALLOC_HEAD = 256;
+    constexpr size_t NOALLOC_BYTES = NOALLOC_HEAD + 8 * (size_t)OMPLCU_NOALLOC_MAX_SEGMENTS;
+    static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+    namespace
+    {
+        // In host code the array's name is a host-side stand-in, not a device address: the address a
+        // kernel may be given comes from cudaGetSymbolAddress, asked once per device with that device
+        // current (the caller holds a DeviceGuard).
+        unsigned char *noalloc_scratch_address(int device)
+        {
+            static std::mutex mu;
+            static unsigned char *addr[64] = {};
+            std::lock_guard<std::mutex> lk(mu);
+            REQUIRE(device >= 0 && device < 64, "device index out of range");
+            if (!addr[device])
+            {
+                void *p = nullptr;
+                CUDA_CHECK(cudaGetSymbolAddress(&p, g_noalloc_scratch));
+                REQUIRE(p != nullptr, "cudaGetSymbolAddress returned NULL for the no-alloc scratch");
+                addr[device] = static_cast<unsigned char *>(p);
+            }
+            return addr[device];
+        }
+    }  // namespace
+
     Checker::Checker(int device, const CheckerDesc &proto, const double *env, const double *robot, const double *sph,
                      const double *box, const double *circ)
       : device_(device), desc_(proto)
     {
         DeviceGuard g(device_);
         CUDA_CHECK(cudaStreamCreateWithFlags(&stream_, cudaStreamNonBlocking));
+        noalloc_scratch_ = noalloc_scratch_address(device_);  // set-up: the calls themselves only use the pointer
         const size_t n_env = 4 * (size_t)desc_.nenv, n_rob = 4 * (size_t)desc_.nrobot, n_sph = 4 * (size_t)desc_.nsph,
                      n_box = 6 * (size_t)desc_.nbox, n_circ = 3 * (size_t)desc_.ncirc;
         const size_t tot = n_env + n_rob + n_sph + n_box + n_circ;
@@ -997,6 +1029,63 @@ namespace omplcu
         launches_ += 4;
         last_states_ = (long)total;
         last_evaluated_ = (long)ctr_host[1];
+        last_group_ = group;
+    }
+
+    // omplcu_check_motions_device_noalloc: the same three kernels as check_motions_device on the same
+    // inputs, hence the same outputs, with the per-segment scratch in g_noalloc_scratch.  No cudaMalloc,
+    // cudaFree, CUB temporary storage or DevBuf::reserve on this path.  The lane-group width is fixed at 8
+    // (the other entry point picks 4 or 8 from the mean state count, which costs a reduction into
+    // temporary storage; the results do not depend on it).  The array keeps the previous call's contents:
+    // the work counters must start at zero and are cleared here; segment counts and codes of rows < n are
+    // overwritten by segment_count_kernel / motion_group_kernel before they are read.  Calls that overlap
+    // on one GPU race on the array.
+    void Checker::check_motions_device_noalloc(const SpaceDesc &sp, const double *d_s1, const double *d_s2, size_t n,
+                                               uint8_t *d_valid, double *d_last_t, double *d_last_state,
+                                               cudaStream_t s)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        DeviceGuard g(device_);
+        if (n == 0)
+            return;
+        REQUIRE(n <= (size_t)OMPLCU_NOALLOC_MAX_SEGMENTS,
+                "omplcu_check_motions_device_noalloc: more than OMPLCU_NOALLOC_MAX_SEGMENTS (262144) segments in one "
+                "call; split the batch or use omplcu_check_motions_device");
+        REQUIRE(d_s1 && d_s2 && d_valid, "omplcu_check_motions: NULL buffer");
+        REQUIRE(!(d_last_state && !d_last_t), "omplcu_check_motions: last_state needs last_t");
+        REQUIRE(noalloc_scratch_ != nullptr, "no-alloc scratch address missing");
+        check_stride(desc_, sp.stride);
+        unsigned long long *ctr = reinterpret_cast<unsigned long long *>(noalloc_scratch_);
+        uint32_t *nd = reinterpret_cast<uint32_t *>(noalloc_scratch_ + NOALLOC_HEAD);
+        unsigned *code = reinterpret_cast<unsigned *>(noalloc_scratch_ + NOALLOC_HEAD +
+                                                      4 * (size_t)OMPLCU_NOALLOC_MAX_SEGMENTS);
+        CUDA_CHECK(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), s));
+        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, nullptr);
+        CUDA_CHECK(cudaGetLastError());
+        const int group = 8;
+        switch (desc_.kind)
+        {
+            case OMPLCU_CHK_HYPERCUBE:
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                break;
+            case OMPLCU_CHK_CHAIN:
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                break;
+            case OMPLCU_CHK_SE3:
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                break;
+            case OMPLCU_CHK_CIRCLES:
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                break;
+            default:
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+        }
+        CUDA_CHECK(cudaGetLastError());
+        motion_finalize_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, code, d_valid, d_last_t,
+                                                            d_last_state);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        launches_ += 3;
         last_group_ = group;
     }
 

@@ -53,6 +53,9 @@ namespace omplcu
         void check_states_device(int stride, const double *d_states, size_t n, uint8_t *d_valid, cudaStream_t s);
         void check_motions_device(const SpaceDesc &sp, const double *d_s1, const double *d_s2, size_t n,
                                   uint8_t *d_valid, double *d_last_t, double *d_last_state, cudaStream_t s);
+        // allocation-free variant: scratch in the library's static __device__ array (validity.cu)
+        void check_motions_device_noalloc(const SpaceDesc &sp, const double *d_s1, const double *d_s2, size_t n,
+                                          uint8_t *d_valid, double *d_last_t, double *d_last_state, cudaStream_t s);
         void check_states_host(int stride, const double *states, size_t n, uint8_t *valid);
         void check_motions_host(const SpaceDesc &sp, const double *s1, const double *s2, size_t n, uint8_t *valid,
                                 double *last_t, double *last_state);
@@ -88,6 +91,7 @@ namespace omplcu
         long last_states_ = 0;
         long last_evaluated_ = 0;
         long last_group_ = 0;
+        unsigned char *noalloc_scratch_ = nullptr;  // device address of the static scratch array on device_
     };
 
     // batched space math (host buffers) used by the parity tests and adapters
