@@ -266,6 +266,116 @@ namespace ompl
                     return false;
             return true;
         }
+
+        /** SpaceInformation::getMotionStates (base/src/SpaceInformation.cpp:201-272) with the interpolation
+            done as ONE batched device call: the same control flow (count + 1 segments, optional end points,
+            optional allocation, never more states than `states` holds when alloc is false), the states in
+            between are interpolate(s1, s2, j / count) evaluated by omplcu_space_interpolate with the
+            reference's operations.  `space` describes si's state space (describe() or an explicit description). */
+        inline unsigned int getMotionStates(const base::SpaceInformation *si, const SpaceHandle &space,
+                                            const base::State *s1, const base::State *s2,
+                                            std::vector<base::State *> &states, unsigned int count, bool endpoints,
+                                            bool alloc, int device = 0)
+        {
+            count++;
+            if (count < 2)
+            {
+                unsigned int added = 0;
+                if (endpoints)
+                {
+                    if (alloc)
+                    {
+                        states.resize(2);
+                        states[0] = si->allocState();
+                        states[1] = si->allocState();
+                    }
+                    if (states.size() > 0)
+                    {
+                        si->copyState(states[0], s1);
+                        added++;
+                    }
+                    if (states.size() > 1)
+                    {
+                        si->copyState(states[1], s2);
+                        added++;
+                    }
+                }
+                else if (alloc)
+                    states.resize(0);
+                return added;
+            }
+            if (alloc)
+            {
+                states.resize(count + (endpoints ? 1 : -1));
+                if (endpoints)
+                    states[0] = si->allocState();
+            }
+            unsigned int added = 0;
+            if (endpoints && states.size() > 0)
+            {
+                si->copyState(states[0], s1);
+                added++;
+            }
+            // the states in between: j = 1 .. count - 1 while there is room
+            const std::size_t room = states.size() > added ? states.size() - added : 0;
+            const std::size_t m = std::min<std::size_t>(count - 1, room), st = space.stride();
+            if (m > 0)
+            {
+                std::vector<double> a, b, from(m * st), to(m * st), t(m), out(m * st);
+                gatherRows(si->getStateSpace().get(), &s1, 1, st, a);
+                gatherRows(si->getStateSpace().get(), &s2, 1, st, b);
+                for (std::size_t j = 0; j < m; ++j)
+                {
+                    std::copy(a.begin(), a.end(), from.begin() + j * st);
+                    std::copy(b.begin(), b.end(), to.begin() + j * st);
+                    t[j] = (double)(j + 1) / (double)count;
+                }
+                check(omplcu_space_interpolate(space.get(), device, from.data(), to.data(), t.data(), m, out.data()));
+                std::vector<double> row(st);
+                for (std::size_t j = 0; j < m; ++j)
+                {
+                    if (alloc)
+                        states[added] = si->allocState();
+                    row.assign(out.begin() + j * st, out.begin() + (j + 1) * st);
+                    si->getStateSpace()->copyFromReals(states[added], row);
+                    added++;
+                }
+            }
+            if (added < states.size() && endpoints)
+            {
+                if (alloc)
+                    states[added] = si->allocState();
+                si->copyState(states[added], s2);
+                added++;
+            }
+            return added;
+        }
+
+        /** StateSpace::satisfiesBounds for a batch (RealVectorStateSpace.cpp:200-208 with its DBL_EPSILON slack,
+            SO2 / SO3 / compound rules; valid-state samplers call it before isValid,
+            base/samplers/src/UniformValidStateSampler.cpp:53).  low / high: one entry per stored value in
+            copyToReals order (entries of SO2 / SO3 values are ignored). */
+        inline void satisfiesBoundsBatch(const base::StateSpace *stateSpace, const SpaceHandle &space,
+                                         const std::vector<double> &low, const std::vector<double> &high,
+                                         const base::State *const *states, std::size_t n, std::uint8_t *inBounds,
+                                         int device = 0)
+        {
+            if (low.size() != space.stride() || high.size() != space.stride())
+                throw Exception("ompl::b200::satisfiesBoundsBatch: one low / high entry per stored value");
+            std::vector<double> rows;
+            gatherRows(stateSpace, states, n, space.stride(), rows);
+            check(omplcu_space_satisfies_bounds(space.get(), device, low.data(), high.data(), rows.data(), n, inBounds));
+        }
+
+        /** StateSpace::getMaximumExtent of the described space (RealVectorStateSpace.cpp:167-176 and the
+            SO2 / SO3 / compound rules). */
+        inline double getMaximumExtent(const SpaceHandle &space, const std::vector<double> &low,
+                                       const std::vector<double> &high)
+        {
+            double e = 0.0;
+            check(omplcu_space_maximum_extent(space.get(), low.data(), high.data(), &e));
+            return e;
+        }
     }  // namespace b200
 }  // namespace ompl
 

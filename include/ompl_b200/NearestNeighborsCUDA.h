@@ -66,6 +66,16 @@ namespace ompl
                 c.param = param;
                 return c;
             }
+            /** KinematicChainSpace of demos/KinematicChain.h:88-191: a RealVectorStateSpace subclass whose
+                distance (:105-121) and interpolate (:150-176) are overridden.  Its getType() is still
+                STATE_SPACE_REAL_VECTOR, so it can only be described explicitly (OmplBridge.h: describe()
+                refuses subclasses it cannot vouch for). */
+            static SpaceDescription kinematicChain(int links, double linkLength, double lvs = 1.0, unsigned factor = 1)
+            {
+                SpaceDescription d;
+                d.components.push_back(component(OMPLCU_CHAIN, links, 1.0, lvs, factor, linkLength));
+                return d;
+            }
             /** RealVectorStateSpace(dim) with longest valid segment lvs (only used by motion checks). */
             static SpaceDescription realVector(int dim, double lvs = 1.0)
             {
@@ -146,16 +156,38 @@ namespace ompl
                 throw Exception("NearestNeighborsCUDA: setSpace() on a non-empty structure");
             omplcu_nn_destroy(nn_);
             nn_ = nullptr;
+            byId_.clear();
+            idOffset_ = kUnset;
+            idsOf_.clear();
             space_.reset(space);
-            b200::check(omplcu_nn_create(space_.get(), device_, &nn_));
+            desc_ = space;
+            haveDesc_ = true;
+            if (devices_.empty())
+                b200::check(omplcu_nn_create(space_.get(), device_, &nn_));
+            else
+                b200::check(omplcu_nn_create_sharded(space_.get(), devices_.data(), (int)devices_.size(), &nn_));
         }
         void setRowFunction(RowFunction f)
         {
             rowFun_ = std::move(f);
         }
+        /** GPU of the structure; takes effect at the next setSpace() or, if the space is known and the
+            structure is empty, at once. */
         void setDevice(int device)
         {
             device_ = device;
+            devices_.clear();
+            if (haveDesc_)
+                setSpace(b200::SpaceDescription(desc_));
+        }
+        /** Shard the states over several GPUs of this process (omplcu_nn_create_sharded):
+            every query is answered by all of them and merged by (distance, insertion order), so results are
+            those of the single-device structure.  Same timing rule as setDevice(). */
+        void setDevices(const std::vector<int> &devices)
+        {
+            devices_ = devices;
+            if (haveDesc_)
+                setSpace(b200::SpaceDescription(desc_));
         }
 
         bool reportsSortedResults() const override
@@ -167,7 +199,8 @@ namespace ompl
         {
             if (nn_ != nullptr)
                 b200::check(omplcu_nn_clear(nn_));
-            elems_.clear();
+            byId_.clear();
+            idOffset_ = kUnset;  // ids keep increasing across clear(): re-based at the next add
             idsOf_.clear();
         }
 
@@ -214,7 +247,7 @@ namespace ompl
                 return false;
             b200::check(rc);
             idsOf_.erase(best);
-            elems_.erase(id);
+            byId_[id - idOffset_] = _T();
             return true;
         }
 
@@ -234,7 +267,7 @@ namespace ompl
                     if (it->second > best->second)
                         best = it;
                 ids.push_back(best->second);
-                elems_.erase(best->second);
+                byId_[best->second - idOffset_] = _T();
                 idsOf_.erase(best);
             }
             std::size_t removed = 0;
@@ -284,7 +317,7 @@ namespace ompl
                 b200::check(omplcu_nn_list(nn_, ids.data(), n, &got));
             data.reserve(got);
             for (std::size_t i = 0; i < got; ++i)
-                data.push_back(elems_.at(ids[i]));
+                data.push_back(byId_[ids[i] - idOffset_]);
         }
 
         // ---- batch-submit entry points ----
@@ -313,7 +346,7 @@ namespace ompl
                 out[i].reserve(counts[i]);
                 for (std::uint32_t j = 0; j < counts[i]; ++j)
                 {
-                    out[i].push_back(elems_.at(ids[i * k + j]));
+                    out[i].push_back(byId_[ids[i * k + j] - idOffset_]);
                     if (dists != nullptr)
                         dists->push_back(d[i * k + j]);
                 }
@@ -341,7 +374,7 @@ namespace ompl
             {
                 out[i].reserve(offs[i + 1] - offs[i]);
                 for (std::uint64_t j = offs[i]; j < offs[i + 1]; ++j)
-                    out[i].push_back(elems_.at(ids[j]));
+                    out[i].push_back(byId_[ids[j] - idOffset_]);
             }
             omplcu_free(ids);
         }
@@ -359,9 +392,16 @@ namespace ompl
             if (!rowFun_)
                 throw Exception("NearestNeighborsCUDA: setRowFunction() was not called");
         }
+        // Ids are insertion sequence numbers, handed out consecutively by the device structure: the
+        // element of an id is a vector lookup (655 360 of them per headline batch), not a hash probe.
         void remember(std::uint64_t id, const _T &e)
         {
-            elems_.emplace(id, e);
+            if (idOffset_ == kUnset)
+                idOffset_ = id;
+            const std::uint64_t at = id - idOffset_;
+            if (byId_.size() <= at)
+                byId_.resize(at + 1);
+            byId_[at] = e;
             idsOf_.emplace(e, id);
         }
 
@@ -369,8 +409,15 @@ namespace ompl
         int device_{0};
         b200::SpaceHandle space_;
         omplcu_nn_t nn_{nullptr};
-        std::unordered_map<std::uint64_t, _T> elems_;       // id -> element
-        std::unordered_multimap<_T, std::uint64_t> idsOf_;  // element -> ids (for remove)
+        static constexpr std::uint64_t kUnset = ~std::uint64_t(0);
+        std::vector<int> devices_;                          // non-empty: sharded over these GPUs
+        b200::SpaceDescription desc_;
+        bool haveDesc_{false};
+        std::vector<_T> byId_;                              // id - idOffset_ -> element (_T() once removed)
+        std::uint64_t idOffset_{kUnset};
+        // element -> ids, for remove(); needs std::hash<_T> and operator== (pointers, integers such as
+        // PRM's Vertex, std::shared_ptr<...> as in BIT* all have them)
+        std::unordered_multimap<_T, std::uint64_t> idsOf_;
         mutable std::vector<double> row_;
     };
 }  // namespace ompl

@@ -21,6 +21,8 @@
 
 #include <atomic>
 #include <memory>
+#include <mutex>
+#include <typeinfo>
 #include <utility>
 #include <vector>
 
@@ -28,6 +30,11 @@
 #include "ompl/base/SpaceInformation.h"
 #include "ompl/base/StateSpace.h"
 #include "ompl/base/StateValidityChecker.h"
+#include "ompl/base/spaces/RealVectorStateSpace.h"
+#include "ompl/base/spaces/SE2StateSpace.h"
+#include "ompl/base/spaces/SE3StateSpace.h"
+#include "ompl/base/spaces/SO2StateSpace.h"
+#include "ompl/base/spaces/SO3StateSpace.h"
 #include "ompl_b200/NearestNeighborsCUDA.h"
 
 namespace ompl
@@ -36,10 +43,25 @@ namespace ompl
     {
         namespace detail
         {
+            // The device evaluates the STOCK distance / interpolate of these classes.  A subclass may
+            // override either (demos/KinematicChain.h:88-176 derives from RealVectorStateSpace and keeps
+            // its type id; DubinsStateSpace / ReedsSheppStateSpace derive from SE2StateSpace), so only the
+            // exact classes are accepted; everything else needs an explicit SpaceDescription.
+            template <typename Stock>
+            inline bool exactly(const base::StateSpace *s)
+            {
+                return typeid(*s) == typeid(Stock);
+            }
             inline void leaf(const base::StateSpace *s, double weight, SpaceDescription &d)
             {
                 const double lvs = s->getLongestValidSegmentLength();
                 const unsigned f = s->getValidSegmentCountFactor();
+                if (!(exactly<base::RealVectorStateSpace>(s) || exactly<base::SO2StateSpace>(s) ||
+                      exactly<base::SO3StateSpace>(s)))
+                    throw Exception("ompl::b200::describe: state space '" + s->getName() +
+                                    "' is not exactly RealVectorStateSpace, SO2StateSpace or SO3StateSpace; a subclass "
+                                    "may override distance() or interpolate(), which the device cannot know. Pass an "
+                                    "explicit SpaceDescription (e.g. SpaceDescription::kinematicChain) instead");
                 switch (s->getType())
                 {
                     case base::STATE_SPACE_REAL_VECTOR:
@@ -64,6 +86,13 @@ namespace ompl
             SpaceDescription d;
             if (space->isCompound())
             {
+                if (!(detail::exactly<base::CompoundStateSpace>(space.get()) ||
+                      detail::exactly<base::SE2StateSpace>(space.get()) ||
+                      detail::exactly<base::SE3StateSpace>(space.get())))
+                    throw Exception("ompl::b200::describe: compound state space '" + space->getName() +
+                                    "' is not exactly CompoundStateSpace, SE2StateSpace or SE3StateSpace (Dubins, "
+                                    "Reeds-Shepp and other subclasses override distance() / interpolate()); pass an "
+                                    "explicit SpaceDescription if the device metric really is the stock one");
                 // CompoundStateSpace::distance is the weighted SUM of component distances
                 // (StateSpace.cpp:1068-1076); nested compounds are not flattened because
                 // validSegmentCount takes the max per DIRECT component (:1085-1097).
@@ -102,6 +131,27 @@ namespace ompl
         {
             nn.setSpace(describe(space));
             nn.setRowFunction(rowsFrom<_T>(space, std::move(accessor)));
+        }
+
+        /** The same with a description supplied by the caller, for spaces describe() refuses: e.g.
+            bind(nn, chainSpace, accessor, SpaceDescription::kinematicChain(links, linkLength)). */
+        template <typename _T>
+        void bind(NearestNeighborsCUDA<_T> &nn, const base::StateSpacePtr &space,
+                  std::function<const base::State *(const _T &)> accessor, const SpaceDescription &description)
+        {
+            if (description.stride() != space->getDimension() && !space->isCompound())
+                throw Exception("ompl::b200::bind: the description's stride differs from the space's dimension");
+            nn.setSpace(description);
+            nn.setRowFunction(rowsFrom<_T>(space, std::move(accessor)));
+        }
+
+        /** KinematicChainSpace (demos/KinematicChain.h:88) described from the live space: links = dimension,
+            longest valid segment and count factor read from it after setup(). */
+        inline SpaceDescription describeKinematicChain(const base::StateSpacePtr &space, double linkLength)
+        {
+            return SpaceDescription::kinematicChain((int)space->getDimension(), linkLength,
+                                                    space->getLongestValidSegmentLength(),
+                                                    space->getValidSegmentCountFactor());
         }
 
         /** Owns an omplcu_checker_t. */
@@ -232,6 +282,21 @@ namespace ompl
               : MotionValidator(si), checker_(std::move(checker)), space_(b200::describe(si->getStateSpace()))
             {
             }
+            /** With an explicit description (spaces describe() refuses, e.g. the kinematic chain). */
+            BatchedDiscreteMotionValidator(const SpaceInformationPtr &si, b200::CheckerHandlePtr checker,
+                                           const b200::SpaceDescription &description)
+              : MotionValidator(si), checker_(std::move(checker)), space_(description)
+            {
+            }
+            /** One checker per GPU holding the same obstacle set: checkMotionBatch splits its segments over
+                them (omplcu_check_motions_multi). */
+            void setCheckers(std::vector<b200::CheckerHandlePtr> perDevice)
+            {
+                multi_ = std::move(perDevice);
+                multiRaw_.clear();
+                for (const auto &c : multi_)
+                    multiRaw_.push_back(c->get());
+            }
 
             bool checkMotion(const State *s1, const State *s2) const override
             {
@@ -271,8 +336,12 @@ namespace ompl
                 std::vector<double> a, b;
                 b200::gatherRows(si_->getStateSpace().get(), s1, n, stride, a);
                 b200::gatherRows(si_->getStateSpace().get(), s2, n, stride, b);
-                b200::check(
-                    omplcu_check_motions(checker_->get(), space_.get(), a.data(), b.data(), n, valid, lastT, nullptr));
+                if (multiRaw_.size() > 1)
+                    b200::check(omplcu_check_motions_multi(multiRaw_.data(), (int)multiRaw_.size(), space_.get(),
+                                                           a.data(), b.data(), n, valid, lastT, nullptr));
+                else
+                    b200::check(omplcu_check_motions(checker_->get(), space_.get(), a.data(), b.data(), n, valid,
+                                                     lastT, nullptr));
                 std::size_t nv = 0;
                 for (std::size_t i = 0; i < n; ++i)
                     nv += valid[i] != 0;
@@ -289,6 +358,8 @@ namespace ompl
                 (ok ? valid_ : invalid_) += (unsigned int)k;
             }
             b200::CheckerHandlePtr checker_;
+            std::vector<b200::CheckerHandlePtr> multi_;
+            std::vector<omplcu_checker_t> multiRaw_;
             b200::SpaceHandle space_;
             mutable std::mutex mu_;
         };

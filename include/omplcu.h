@@ -92,8 +92,26 @@ int omplcu_space_interpolate(omplcu_space_t sp, int device, const double *from, 
 int omplcu_space_segment_count(omplcu_space_t sp, int device, const double *a, const double *b, size_t n,
                                uint32_t *out);
 
+/* out[i] = StateSpace::satisfiesBounds(states[i]) (RealVectorStateSpace.cpp:200-208 with its +-DBL_EPSILON
+ * slack, SO2StateSpace.cpp:90-94, SO3StateSpace.cpp:213-216, compound: all components, StateSpace.cpp:1021-1028).
+ * low / high: `stride` doubles in state layout; entries of SO2 / SO3 components are ignored.  Valid-state
+ * samplers call it before isValid (base/samplers/src/UniformValidStateSampler.cpp:53). */
+int omplcu_space_satisfies_bounds(omplcu_space_t sp, int device, const double *low, const double *high,
+                                  const double *states, size_t n, uint8_t *out);
+/* StateSpace::getMaximumExtent (RealVectorStateSpace.cpp:167-176, SO2StateSpace.cpp:70-73, SO3StateSpace.cpp:166-169,
+ * StateSpace.cpp:996-1003); the longest valid segment of a space is this times the fraction (StateSpace.cpp:237-248). */
+int omplcu_space_maximum_extent(omplcu_space_t sp, const double *low, const double *high, double *extent);
+
 /* ---- nearest neighbours ---- */
 int omplcu_nn_create(omplcu_space_t sp, int device, omplcu_nn_t *out);
+/* The same structure with its states sharded over `ndev` GPUs of this process ("omplcu_nn_create(space,
+ * devices[], ndev, &h)"; 8(e)).  Every other omplcu_nn_* call works on the handle unchanged and returns exactly
+ * what a single-device handle holding all the states returns: states are split by insertion index (a bulk add
+ * into ndev contiguous blocks, a small add to the least-loaded shard), ids stay global insertion sequence
+ * numbers, every shard answers all queries on its own GPU, the per-shard (distance, id) lists are gathered on
+ * devices[0] over NVLink peer copies and merged there by (distance, id).  Device-pointer entry points take and
+ * return buffers on devices[0].  A device may be named more than once (several shards on one GPU). */
+int omplcu_nn_create_sharded(omplcu_space_t sp, const int *devices, int ndev, omplcu_nn_t *out);
 int omplcu_nn_destroy(omplcu_nn_t nn);
 /* ids handed out are id_base + insertion sequence (sharded roadmaps give each
  * rank a disjoint base).  Must be called while the structure is empty. */
@@ -163,6 +181,12 @@ int omplcu_check_states(omplcu_checker_t c, int stride, const double *states, si
  * success; last_state (n x stride, may be NULL) = lastValid.first on failure. */
 int omplcu_check_motions(omplcu_checker_t c, omplcu_space_t sp, const double *s1, const double *s2, size_t n,
                          uint8_t *valid, double *last_t, double *last_state);
+/* One batch split by index over `nchk` checkers, normally one per GPU holding the same obstacle set (SURVEY 8(e):
+ * validity shards by segment, no exchange).  Results are those of omplcu_check_states / omplcu_check_motions. */
+int omplcu_check_states_multi(const omplcu_checker_t *checkers, int nchk, int stride, const double *states, size_t n,
+                              uint8_t *valid);
+int omplcu_check_motions_multi(const omplcu_checker_t *checkers, int nchk, omplcu_space_t sp, const double *s1,
+                               const double *s2, size_t n, uint8_t *valid, double *last_t, double *last_state);
 int omplcu_check_states_device(omplcu_checker_t c, int stride, const double *d_states, size_t n, uint8_t *d_valid,
                                void *stream);
 int omplcu_check_motions_device(omplcu_checker_t c, omplcu_space_t sp, const double *d_s1, const double *d_s2,

@@ -45,7 +45,10 @@ SIGNATURES = {
     "omplcu_space_distance": [_vp, _i, _pd, _pd, _sz, _pd],
     "omplcu_space_interpolate": [_vp, _i, _pd, _pd, _pd, _sz, _pd],
     "omplcu_space_segment_count": [_vp, _i, _pd, _pd, _sz, _pd],
+    "omplcu_space_satisfies_bounds": [_vp, _i, _pd, _pd, _pd, _sz, _pd],
+    "omplcu_space_maximum_extent": [_vp, _pd, _pd, C.POINTER(C.c_double)],
     "omplcu_nn_create": [_vp, _i, C.POINTER(_vp)],
+    "omplcu_nn_create_sharded": [_vp, C.POINTER(C.c_int), _i, C.POINTER(_vp)],
     "omplcu_nn_destroy": [_vp],
     "omplcu_nn_set_id_base": [_vp, _u64],
     "omplcu_nn_add": [_vp, _pd, _sz, C.POINTER(_u64)],
@@ -71,6 +74,8 @@ SIGNATURES = {
     "omplcu_checker_get_stat": [_vp, C.c_char_p, C.POINTER(C.c_long)],
     "omplcu_check_states": [_vp, _i, _pd, _sz, _pd],
     "omplcu_check_motions": [_vp, _vp, _pd, _pd, _sz, _pd, _pd, _pd],
+    "omplcu_check_states_multi": [C.POINTER(_vp), _i, _i, _pd, _sz, _pd],
+    "omplcu_check_motions_multi": [C.POINTER(_vp), _i, _vp, _pd, _pd, _sz, _pd, _pd, _pd],
     "omplcu_check_states_device": [_vp, _i, _pd, _sz, _pd, _vp],
     "omplcu_check_motions_device": [_vp, _vp, _pd, _pd, _sz, _pd, _pd, _pd, _vp],
     "omplcu_check_motions_device_noalloc": [_vp, _vp, _pd, _pd, _sz, _pd, _pd, _pd, _vp],

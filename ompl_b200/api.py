@@ -246,15 +246,23 @@ class NearestNeighborsCUDA:
     Results are NearestNeighborsLinear's with ties broken by insertion order.
     """
 
-    def __init__(self, space, state_accessor=None, device=None):
+    def __init__(self, space, state_accessor=None, device=None, devices=None):
+        """`devices` (a list of GPU indices) shards the states over several GPUs of this process
+        (omplcu_nn_create_sharded); results are identical to the single-device structure."""
         self.space = space
         self.device = space.device if device is None else device
+        self.devices = None if devices is None else [int(d) for d in devices]
         self._accessor = state_accessor or (lambda e: e)
         self._dist_fun = None
         self._elem = {}  # id -> element
         self._ids_of = {}  # element key -> [ids] (insertion order)
         h = C.c_void_p()
-        check(lib().omplcu_nn_create(space.handle, self.device, C.byref(h)))
+        if self.devices is None:
+            check(lib().omplcu_nn_create(space.handle, self.device, C.byref(h)))
+        else:
+            arr = (C.c_int * len(self.devices))(*self.devices)
+            check(lib().omplcu_nn_create_sharded(space.handle, arr, len(self.devices), C.byref(h)))
+            self.device = self.devices[0]
         self._h = h
 
     def __del__(self):
@@ -365,6 +373,12 @@ class NearestNeighborsCUDA:
         got = C.c_size_t()
         check(lib().omplcu_nn_list(self._h, _ptr(out), n, C.byref(got)))
         return out[: got.value]
+
+    def get_row(self, i):
+        """Stored coordinates of the element with id `i` (omplcu_nn_get)."""
+        row = np.empty(self.space.stride, dtype=np.float64)
+        check(lib().omplcu_nn_get(self._h, int(i), _ptr(row)))
+        return row
 
     def list(self):
         return [self._elem.get(int(i), int(i)) for i in self.list_ids()]
@@ -523,9 +537,12 @@ class BatchedDiscreteMotionValidator:
     (base/MotionValidator.h:102-139): one count per segment, as
     DiscreteMotionValidator.cpp:139-142 does."""
 
-    def __init__(self, space, checker):
+    def __init__(self, space, checker, checkers=None):
+        """`checkers`: one checker per GPU with the same obstacle set; batches are then split by
+        segment over them (omplcu_check_motions_multi), results unchanged."""
         self.space = space
-        self.checker = checker
+        self.checker = checker if checker is not None else checkers[0]
+        self.checkers = list(checkers) if checkers else None
         self.valid_ = 0
         self.invalid_ = 0
 
@@ -550,8 +567,13 @@ class BatchedDiscreteMotionValidator:
         v = np.empty(n, dtype=np.uint8)
         t = np.empty(n, dtype=np.float64) if last_valid else None
         st = np.zeros_like(a) if (last_valid and last_state) else None
-        check(lib().omplcu_check_motions(self.checker.handle, self.space.handle, _ptr(a), _ptr(b), n, _ptr(v),
-                                         _ptr(t), _ptr(st)))
+        if self.checkers:
+            hs = (C.c_void_p * len(self.checkers))(*[c.handle.value for c in self.checkers])
+            check(lib().omplcu_check_motions_multi(hs, len(self.checkers), self.space.handle, _ptr(a), _ptr(b), n,
+                                                   _ptr(v), _ptr(t), _ptr(st)))
+        else:
+            check(lib().omplcu_check_motions(self.checker.handle, self.space.handle, _ptr(a), _ptr(b), n, _ptr(v),
+                                             _ptr(t), _ptr(st)))
         nv = int(v.sum())
         self.valid_ += nv
         self.invalid_ += n - nv

@@ -1,8 +1,10 @@
 // capi.cu -- extern "C" boundary of libomplcu.so (declared in include/omplcu.h).
 // No exception crosses the boundary: every entry point returns a status code and
 // stores the message in a thread-local string (omplcu_last_error).
+#include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 
 #include "nn.cuh"
 #include "validity.cuh"
@@ -19,7 +21,7 @@ struct omplcu_space_s
 };
 struct omplcu_nn_s
 {
-    NNIndex *impl;
+    NNApi *impl;
 };
 struct omplcu_checker_s
 {
@@ -62,6 +64,39 @@ namespace
         if (e != cudaSuccess)
             throw Error(OMPLCU_ERR_CUDA, std::string("no usable CUDA device: ") + cudaGetErrorString(e));
         REQUIRE(device >= 0 && device < n, "device index out of range");
+    }
+}  // namespace
+
+// A batch split by index over per-device checkers ("segments split evenly by index; the
+// obstacle set and space description are replicated"; no exchange).  One host thread per checker.
+namespace
+{
+    template <typename F>
+    void split_over(int nc, size_t n, F &&f)
+    {
+        std::vector<std::thread> th;
+        std::vector<std::exception_ptr> err(nc);
+        for (int i = 0; i < nc; ++i)
+        {
+            const size_t b0 = n * (size_t)i / nc, b1 = n * (size_t)(i + 1) / nc;
+            if (b1 == b0)
+                continue;
+            th.emplace_back([&, i, b0, b1] {
+                try
+                {
+                    f(i, b0, b1 - b0);
+                }
+                catch (...)
+                {
+                    err[i] = std::current_exception();
+                }
+            });
+        }
+        for (auto &t : th)
+            t.join();
+        for (auto &e : err)
+            if (e)
+                std::rethrow_exception(e);
     }
 }  // namespace
 
@@ -185,6 +220,55 @@ int omplcu_space_segment_count(omplcu_space_t sp, int device, const double *a, c
     });
 }
 
+int omplcu_space_satisfies_bounds(omplcu_space_t sp, int device, const double *low, const double *high,
+                                  const double *states, size_t n, uint8_t *out)
+{
+    return guarded([&] {
+        REQUIRE(sp, "space is NULL");
+        need_gpu(device);
+        space_satisfies_bounds_host(sp->desc, device, low, high, states, n, out);
+    });
+}
+
+// StateSpace::getMaximumExtent: RealVectorStateSpace.cpp:167-176 (also the chain space, which derives from
+// it), SO2StateSpace.cpp:70-73 (pi), SO3StateSpace.cpp:166-169 (pi / 2), CompoundStateSpace
+// (StateSpace.cpp:996-1003: sum of weight * extent over components with weight >= DBL_EPSILON).  One scalar
+// per space: host arithmetic, the same operations in the same order as the reference.
+int omplcu_space_maximum_extent(omplcu_space_t sp, const double *low, const double *high, double *extent)
+{
+    return guarded([&] {
+        REQUIRE(sp && extent, "omplcu_space_maximum_extent: NULL argument");
+        const SpaceDesc &d = sp->desc;
+        double tot = 0.0;
+        int off = 0;
+        for (int c = 0; c < d.ncomp; ++c)
+        {
+            const omplcu_component &k = d.comp[c];
+            double e = 0.0;
+            if (k.type == OMPLCU_RV || k.type == OMPLCU_CHAIN)
+            {
+                REQUIRE(low && high, "omplcu_space_maximum_extent: bounds are NULL");
+                for (int j = 0; j < k.dim; ++j)
+                {
+                    const double w = high[off + j] - low[off + j];
+                    e += w * w;
+                }
+                e = sqrt(e);
+            }
+            else if (k.type == OMPLCU_SO2)
+                e = 3.14159265358979323846;
+            else
+                e = .5 * 3.14159265358979323846;
+            if (!d.compound)
+                tot = e;
+            else if (k.weight >= 2.220446049250313e-16)
+                tot += k.weight * e;
+            off += k.dim;
+        }
+        *extent = tot;
+    });
+}
+
 /* ---- nearest neighbours ---- */
 int omplcu_nn_create(omplcu_space_t sp, int device, omplcu_nn_t *out)
 {
@@ -195,6 +279,27 @@ int omplcu_nn_create(omplcu_space_t sp, int device, omplcu_nn_t *out)
         try
         {
             h->impl = new NNIndex(sp->desc, device);
+        }
+        catch (...)
+        {
+            delete h;
+            throw;
+        }
+        *out = h;
+    });
+}
+
+int omplcu_nn_create_sharded(omplcu_space_t sp, const int *devices, int ndev, omplcu_nn_t *out)
+{
+    return guarded([&] {
+        REQUIRE(sp && out && devices, "omplcu_nn_create_sharded: NULL argument");
+        REQUIRE(ndev >= 1 && ndev <= 64, "omplcu_nn_create_sharded: 1..64 devices");
+        for (int i = 0; i < ndev; ++i)
+            need_gpu(devices[i]);
+        auto *h = new omplcu_nn_s;
+        try
+        {
+            h->impl = make_sharded_nn(sp->desc, devices, ndev);
         }
         catch (...)
         {
@@ -494,6 +599,37 @@ int omplcu_check_motions_device(omplcu_checker_t c, omplcu_space_t sp, const dou
     return guarded([&] {
         REQUIRE(c && sp, "checker or space is NULL");
         c->impl->check_motions_device(sp->desc, d_s1, d_s2, n, d_valid, d_last_t, d_last_state, (cudaStream_t)stream);
+    });
+}
+
+int omplcu_check_states_multi(const omplcu_checker_t *checkers, int nchk, int stride, const double *states, size_t n,
+                              uint8_t *valid)
+{
+    return guarded([&] {
+        REQUIRE(checkers && nchk >= 1, "omplcu_check_states_multi: no checkers");
+        for (int i = 0; i < nchk; ++i)
+            REQUIRE(checkers[i], "checker is NULL");
+        REQUIRE(n == 0 || (states && valid), "omplcu_check_states: NULL buffer");
+        split_over(nchk, n, [&](int i, size_t o, size_t cn) {
+            checkers[i]->impl->check_states_host(stride, states + o * (size_t)stride, cn, valid + o);
+        });
+    });
+}
+
+int omplcu_check_motions_multi(const omplcu_checker_t *checkers, int nchk, omplcu_space_t sp, const double *s1,
+                               const double *s2, size_t n, uint8_t *valid, double *last_t, double *last_state)
+{
+    return guarded([&] {
+        REQUIRE(checkers && nchk >= 1 && sp, "omplcu_check_motions_multi: no checkers or no space");
+        for (int i = 0; i < nchk; ++i)
+            REQUIRE(checkers[i], "checker is NULL");
+        REQUIRE(n == 0 || (s1 && s2 && valid), "omplcu_check_motions: NULL buffer");
+        const size_t st = (size_t)sp->desc.stride;
+        split_over(nchk, n, [&](int i, size_t o, size_t cn) {
+            checkers[i]->impl->check_motions_host(sp->desc, s1 + o * st, s2 + o * st, cn, valid + o,
+                                                  last_t ? last_t + o : nullptr,
+                                                  last_state ? last_state + o * st : nullptr);
+        });
     });
 }
 

@@ -110,6 +110,11 @@ namespace omplcu
         DevBuf() = default;
         DevBuf(const DevBuf &) = delete;
         DevBuf &operator=(const DevBuf &) = delete;
+        DevBuf(DevBuf &&o) noexcept : p(o.p), cap(o.cap)
+        {
+            o.p = nullptr;
+            o.cap = 0;
+        }
     };
 
     // ------------------------------------------------------------------

@@ -911,10 +911,15 @@ namespace omplcu
         }
     }
 
-    uint64_t NNIndex::add(const double *rows, size_t n)
+    uint64_t NNIndex::add_at(const double *rows, size_t n, uint64_t want_first)
     {
         std::lock_guard<std::mutex> lk(mu_);
         DeviceGuard g(device_);
+        if (want_first != OMPLCU_ID_NONE)
+        {
+            REQUIRE(want_first >= id_base_ + next_seq_, "omplcu_nn_add: ids must increase");
+            next_seq_ = want_first - id_base_;
+        }
         const uint64_t first_id = id_base_ + next_seq_;
         if (n == 0)
             return first_id;

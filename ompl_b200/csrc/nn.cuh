@@ -16,36 +16,72 @@ namespace omplcu
     // (datastructures/NearestNeighbors.h:46-115): coordinates only; the C++
     // adapter keeps id -> _T.  Slots are kept in insertion order, so slot order
     // == id order and "ties by insertion index" is "ties by slot".
-    class NNIndex
+    // What an omplcu_nn_t can do: one index on one GPU (NNIndex) or a roadmap sharded over several
+    // (ShardedNN, sharded.cu).
+    class NNApi
+    {
+    public:
+        virtual ~NNApi() = default;
+        virtual void set_id_base(uint64_t base) = 0;
+        virtual uint64_t add(const double *rows, size_t n) = 0;
+        virtual void remove(uint64_t id) = 0;
+        virtual size_t remove_batch(const uint64_t *ids, size_t n) = 0;
+        virtual void clear() = 0;
+        virtual size_t size() const = 0;
+        virtual size_t list(uint64_t *ids, size_t cap) const = 0;
+        virtual void get(uint64_t id, double *row) = 0;
+        virtual void knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                                cudaStream_t s) = 0;
+        virtual void knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists,
+                              uint32_t *counts) = 0;
+        virtual void radius_host(const double *q, size_t nq, const double *radii, uint64_t **ids, double **dists,
+                                 uint64_t *offsets) = 0;
+        virtual void set_option(const char *key, long v) = 0;
+        virtual long get_stat(const char *key) const = 0;
+    };
+
+    class NNIndex : public NNApi
     {
     public:
         NNIndex(const SpaceDesc &sp, int device);
-        ~NNIndex();
+        ~NNIndex() override;
 
-        void set_id_base(uint64_t base);
-        uint64_t add(const double *rows, size_t n);
-        void remove(uint64_t id);
-        size_t remove_batch(const uint64_t *ids, size_t n);
-        void clear();
-        size_t size() const
+        void set_id_base(uint64_t base) override;
+        uint64_t add(const double *rows, size_t n) override
+        {
+            return add_at(rows, n, OMPLCU_ID_NONE);
+        }
+        // first_id == OMPLCU_ID_NONE: the next sequence number; otherwise the ids of this batch are
+        // first_id .. first_id + n - 1, which must lie beyond every id handed out so far (a sharded
+        // roadmap gives each shard increasing blocks of the global insertion sequence)
+        uint64_t add_at(const double *rows, size_t n, uint64_t first_id);
+        void remove(uint64_t id) override;
+        size_t remove_batch(const uint64_t *ids, size_t n) override;
+        void clear() override;
+        size_t size() const override
         {
             return nlive_;
         }
-        size_t list(uint64_t *ids, size_t cap) const;
-        void get(uint64_t id, double *row);
+        size_t list(uint64_t *ids, size_t cap) const override;
+        void get(uint64_t id, double *row) override;
 
         // device pointers; synchronises the stream
-        void knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists, cudaStream_t s);
-        void knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts);
+        void knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                        cudaStream_t s) override;
+        void knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts) override;
         void radius_host(const double *q, size_t nq, const double *radii, uint64_t **ids, double **dists,
-                         uint64_t *offsets);
+                         uint64_t *offsets) override;
 
-        void set_option(const char *key, long v);
-        long get_stat(const char *key) const;
+        void set_option(const char *key, long v) override;
+        long get_stat(const char *key) const override;
 
         int device() const
         {
             return device_;
+        }
+        cudaStream_t stream() const
+        {
+            return stream_;
         }
         const SpaceDesc &space() const
         {
@@ -141,6 +177,9 @@ namespace omplcu
         long last_scan_ns_ = 0, scan_ns_total_ = 0, scan_count_ = 0;
         long last_fallbacks_ = 0, last_path_ = 0, launches_ = 0;
     };
+
+    // roadmap sharded over several GPUs of one process (sharded.cu)
+    NNApi *make_sharded_nn(const SpaceDesc &sp, const int *devices, int ndev);
 
     void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t part_stride,
                            size_t nq, size_t k,

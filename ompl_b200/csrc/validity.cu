@@ -1096,8 +1096,10 @@ namespace omplcu
         REQUIRE(states && valid, "omplcu_check_states: NULL buffer");
         REQUIRE(stride >= 1 && stride <= MAX_STRIDE, "state stride out of range (1..128)");
         DeviceGuard g(device_);
-        static std::mutex host_mu;
-        std::lock_guard<std::mutex> hl(host_mu);
+        // the staging buffers (st_a_, st_v_, ...) belong to this checker: ONE per-instance mutex for both
+        // host entry points, so isValid and checkMotion racing on one checker cannot overwrite or
+        // reallocate each other's staging, and checkers on other GPUs are not serialised
+        std::lock_guard<std::mutex> hl(host_mu_);
         st_a_.reserve(n * stride);
         st_v_.reserve(n);
         CUDA_CHECK(cudaMemcpyAsync(st_a_.p, states, n * stride * sizeof(double), cudaMemcpyHostToDevice, stream_));
@@ -1114,8 +1116,10 @@ namespace omplcu
         REQUIRE(s1 && s2 && valid, "omplcu_check_motions: NULL buffer");
         REQUIRE(!(last_state && !last_t), "omplcu_check_motions: last_state needs last_t");
         DeviceGuard g(device_);
-        static std::mutex host_mu;
-        std::lock_guard<std::mutex> hl(host_mu);
+        // the staging buffers (st_a_, st_v_, ...) belong to this checker: ONE per-instance mutex for both
+        // host entry points, so isValid and checkMotion racing on one checker cannot overwrite or
+        // reallocate each other's staging, and checkers on other GPUs are not serialised
+        std::lock_guard<std::mutex> hl(host_mu_);
         const size_t st = (size_t)sp.stride;
         st_a_.reserve(n * st);
         st_b_.reserve(n * st);
@@ -1225,6 +1229,71 @@ namespace omplcu
         space_interpolate_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, da.p, db.p, dt.p, n, dout.p);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaMemcpyAsync(out, dout.p, n * st * sizeof(double), cudaMemcpyDeviceToHost, ts.s));
+        CUDA_CHECK(cudaStreamSynchronize(ts.s));
+    }
+
+    namespace
+    {
+        // StateSpace::satisfiesBounds per component: RealVectorStateSpace.cpp:200-208 (+- DBL_EPSILON slack),
+        // SO2StateSpace.cpp:90-94 ([-pi, pi)), SO3StateSpace.cpp:177-181,213-216 (| |q| - 1 | < 1e-9, with
+        // the norm taken as exactly 1 when |q|^2 is within DBL_EPSILON of 1), CompoundStateSpace: all of them
+        // (StateSpace.cpp:1021-1028).  The kinematic chain space is a RealVectorStateSpace (demos/KinematicChain.h:88).
+        __global__ void satisfies_bounds_kernel(SpaceDesc sp, const double *states, size_t n, const double *low,
+                                                const double *high, uint8_t *out)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= n)
+                return;
+            const double *s = states + i * sp.stride;
+            const double eps = 2.220446049250313e-16;
+            bool ok = true;
+            int off = 0;
+            for (int c = 0; c < sp.ncomp; ++c)
+            {
+                const omplcu_component &k = sp.comp[c];
+                if (k.type == OMPLCU_RV || k.type == OMPLCU_CHAIN)
+                {
+                    for (int j = 0; j < k.dim; ++j)
+                        if (dsub(s[off + j], eps) > high[off + j] || dadd(s[off + j], eps) < low[off + j])
+                            ok = false;
+                }
+                else if (k.type == OMPLCU_SO2)
+                    ok = ok && (s[off] < kPi) && (s[off] >= -kPi);
+                else
+                {
+                    // quaternionNormSquared: x*x + y*y + z*z + w*w, left to right
+                    const double n2 = dadd(dadd(dadd(dmul(s[off], s[off]), dmul(s[off + 1], s[off + 1])),
+                                                dmul(s[off + 2], s[off + 2])),
+                                           dmul(s[off + 3], s[off + 3]));
+                    const double nrm = (fabs(dsub(n2, 1.0)) > eps) ? dsqrt(n2) : 1.0;
+                    ok = ok && (fabs(dsub(nrm, 1.0)) < 1e-9);
+                }
+                off += k.dim;
+            }
+            out[i] = ok ? 1 : 0;
+        }
+    }  // namespace
+
+    void space_satisfies_bounds_host(const SpaceDesc &sp, int device, const double *low, const double *high,
+                                     const double *states, size_t n, uint8_t *out)
+    {
+        if (n == 0)
+            return;
+        REQUIRE(states && out && low && high, "omplcu_space_satisfies_bounds: NULL buffer");
+        DeviceGuard g(device);
+        TmpStream ts;
+        DevBuf<double> ds, db;
+        DevBuf<uint8_t> dout;
+        const size_t st = (size_t)sp.stride;
+        ds.reserve(n * st);
+        db.reserve(2 * st);
+        dout.reserve(n);
+        CUDA_CHECK(cudaMemcpyAsync(ds.p, states, n * st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
+        CUDA_CHECK(cudaMemcpyAsync(db.p, low, st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
+        CUDA_CHECK(cudaMemcpyAsync(db.p + st, high, st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
+        satisfies_bounds_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, ds.p, n, db.p, db.p + st, dout.p);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemcpyAsync(out, dout.p, n, cudaMemcpyDeviceToHost, ts.s));
         CUDA_CHECK(cudaStreamSynchronize(ts.s));
     }
 

@@ -72,7 +72,7 @@ namespace omplcu
         int sms_ = 148;
         CheckerDesc desc_;
         cudaStream_t stream_ = nullptr, copy_stream_ = nullptr;
-        std::mutex mu_;
+        std::mutex mu_, host_mu_;  // device-side scratch / host-pointer staging (host_mu_ is taken first)
         DevBuf<double> params_;
         DevBuf<float4> filt_, narrow32_;
         DevBuf<uint32_t> cell_start_;
@@ -98,6 +98,8 @@ namespace omplcu
     void space_distance_host(const SpaceDesc &sp, int device, const double *a, const double *b, size_t n, double *out);
     void space_interpolate_host(const SpaceDesc &sp, int device, const double *a, const double *b, const double *t,
                                 size_t n, double *out);
+    void space_satisfies_bounds_host(const SpaceDesc &sp, int device, const double *low, const double *high,
+                                     const double *states, size_t n, uint8_t *out);
     void space_segment_count_host(const SpaceDesc &sp, int device, const double *a, const double *b, size_t n,
                                   uint32_t *out);
 }  // namespace omplcu

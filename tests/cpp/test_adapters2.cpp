@@ -1,0 +1,532 @@
+// test_adapters2.cpp -- second half of the C++ adapter tests (same build as test_adapters.cpp):
+//
+//   1. NearestNeighborsCUDA<_T> for the planners' real element types -- PRM's Vertex (unsigned long,
+//      geometric/planners/prm/PRM.h:125,130), FMT's Motion* (fmt/src/FMT.cpp:99), BIT*'s
+//      std::shared_ptr<Vertex> (informedtrees/bitstar/src/ImplicitGraph.cpp:112) -- against the
+//      reference's NearestNeighborsLinear over the same elements.
+//   2. describe() refuses subclasses that may override the metric (a KinematicChainSpace-like subclass of
+//      RealVectorStateSpace, demos/KinematicChain.h:88-176; a subclass of SE2StateSpace like Dubins); the
+//      explicit SpaceDescription::kinematicChain gives NearestNeighborsLinear's answers under the
+//      subclass's own distance(), and the chain motion validator agrees with DiscreteMotionValidator.
+//   3. setDevices(): a structure sharded over several GPUs (or several shards on one) == the plain one.
+//   4. getMotionStates / satisfiesBoundsBatch / getMaximumExtent against the reference's own
+//      StateSpace::interpolate / satisfiesBounds / getMaximumExtent.
+//   5. Thread safety: four host threads query one structure at once; two threads mix isValid and
+//      checkMotion on one checker (StateValidityChecker.h:87-89, MotionValidator.h:60-63).
+#include <atomic>
+#include <cmath>
+#include <cstdio>
+#include <memory>
+#include <random>
+#include <thread>
+
+#include "ompl/base/DiscreteMotionValidator.h"
+#include "ompl/base/spaces/RealVectorStateSpace.h"
+#include "ompl/base/spaces/SE2StateSpace.h"
+#include "ompl/base/spaces/SE3StateSpace.h"
+#include "ompl/datastructures/NearestNeighborsLinear.h"
+#include "ompl_b200/BatchPlanning.h"
+#include "ompl_b200/OmplBridge.h"
+
+namespace ob = ompl::base;
+
+static std::atomic<int> failures{0};
+#define CHECK(cond)                                                              \
+    do                                                                           \
+    {                                                                            \
+        if (!(cond))                                                             \
+        {                                                                        \
+            std::printf("FAIL %s:%d  %s\n", __FILE__, __LINE__, #cond);          \
+            ++failures;                                                          \
+        }                                                                        \
+    } while (0)
+
+static std::mt19937_64 gen(11);
+static double uni(double a, double b)
+{
+    return std::uniform_real_distribution<double>(a, b)(gen);
+}
+
+static std::shared_ptr<ob::RealVectorStateSpace> cube(unsigned d, double lo = 0, double hi = 1)
+{
+    auto rv = std::make_shared<ob::RealVectorStateSpace>(d);
+    ob::RealVectorBounds b(d);
+    b.setLow(lo);
+    b.setHigh(hi);
+    rv->setBounds(b);
+    rv->setup();
+    return rv;
+}
+
+static ob::State *randomRV(const ob::StateSpacePtr &sp, double lo, double hi)
+{
+    ob::State *s = sp->allocState();
+    for (unsigned i = 0; i < sp->getDimension(); ++i)
+        s->as<ob::RealVectorStateSpace::StateType>()->values[i] = uni(lo, hi);
+    return s;
+}
+
+// ---------------------------------------------------------------- 1. element types
+struct Motion  // fmt/FMT.h: Motion holds its state
+{
+    ob::State *state{nullptr};
+    ob::State *getState() const
+    {
+        return state;
+    }
+};
+struct BitVertex  // informedtrees/bitstar/Vertex.h: state() accessor
+{
+    ob::State *st{nullptr};
+    const ob::State *state() const
+    {
+        return st;
+    }
+};
+
+template <typename T, typename Make, typename StateOf>
+static void elementTypeTest(const char *name, Make make, StateOf stateOf)
+{
+    auto space = cube(5);
+    const unsigned n = 300, k = 7;
+    std::vector<ob::State *> states(n);
+    std::vector<T> elems;
+    for (unsigned i = 0; i < n; ++i)
+    {
+        states[i] = randomRV(space, 0, 1);
+        elems.push_back(make(i, states[i]));
+    }
+    auto dist = [&](const T &a, const T &b) { return space->distance(stateOf(a), stateOf(b)); };
+    ompl::NearestNeighborsLinear<T> lin;
+    lin.setDistanceFunction(dist);
+    ompl::NearestNeighborsCUDA<T> nn;  // default-constructible, as PRM.h:255-266 / BITstar.h:296-297 need
+    nn.setDistanceFunction(dist);
+    ompl::b200::bind<T>(nn, space, [&](const T &e) { return (const ob::State *)stateOf(e); });
+    lin.add(elems);
+    nn.add(std::vector<T>(elems.begin(), elems.begin() + 200));
+    for (unsigned i = 200; i < n; ++i)
+        nn.add(elems[i]);
+    CHECK(nn.size() == n);
+    std::vector<T> a, b;
+    nn.list(a);
+    lin.list(b);
+    CHECK(a == b);
+    for (unsigned i = 0; i < n; i += 3)
+    {
+        nn.nearestK(elems[i], k, a);
+        lin.nearestK(elems[i], k, b);
+        CHECK(a == b);
+        nn.nearestR(elems[i], 0.35, a);
+        lin.nearestR(elems[i], 0.35, b);
+        CHECK(a == b);
+        CHECK(nn.nearest(elems[i]) == elems[i]);
+    }
+    std::vector<std::vector<T>> batch;
+    nn.nearestKBatch(elems, k, batch);
+    for (unsigned i = 0; i < n; i += 5)
+    {
+        lin.nearestK(elems[i], k, b);
+        CHECK(batch[i] == b);
+    }
+    // remove (single and bulk), then re-add: ids keep increasing, the mapping must follow
+    for (unsigned i = 0; i < 100; ++i)
+    {
+        CHECK(nn.remove(elems[i]));
+        lin.remove(elems[i]);
+    }
+    CHECK(!nn.remove(elems[0]));
+    std::vector<T> bulk(elems.begin() + 100, elems.begin() + 150);
+    CHECK(nn.removeBatch(bulk) == 50);
+    for (auto &e : bulk)
+        lin.remove(e);
+    nn.add(elems[3]);
+    lin.add(elems[3]);
+    for (unsigned i = 150; i < n; i += 7)
+    {
+        nn.nearestK(elems[i], k, a);
+        lin.nearestK(elems[i], k, b);
+        CHECK(a == b);
+    }
+    nn.list(a);
+    lin.list(b);
+    CHECK(a == b);
+    nn.clear();
+    CHECK(nn.size() == 0);
+    nn.add(std::vector<T>(elems.begin(), elems.begin() + 20));  // ids continue after clear()
+    lin.clear();
+    lin.add(std::vector<T>(elems.begin(), elems.begin() + 20));
+    nn.nearestK(elems[5], 4, a);
+    lin.nearestK(elems[5], 4, b);
+    CHECK(a == b);
+    nn.clear();
+    elems.clear();
+    for (auto *s : states)
+        space->freeState(s);
+    std::printf("element type %s: done\n", name);
+}
+
+// ---------------------------------------------------------------- 2. subclasses that override the metric
+// The metric and interpolation of KinematicChainSpace (demos/KinematicChain.h:105-121,150-176), on a
+// RealVectorStateSpace subclass as there; getType() stays STATE_SPACE_REAL_VECTOR.
+class ChainSpace : public ob::RealVectorStateSpace
+{
+public:
+    ChainSpace(unsigned links, double linkLength) : ob::RealVectorStateSpace(links), linkLength_(linkLength)
+    {
+        ob::RealVectorBounds b(links);
+        b.setLow(-M_PI);
+        b.setHigh(M_PI);
+        setBounds(b);
+    }
+    double distance(const ob::State *s1, const ob::State *s2) const override
+    {
+        const auto *a = s1->as<StateType>(), *b = s2->as<StateType>();
+        double t1 = 0., t2 = 0., dx = 0., dy = 0., dist = 0.;
+        for (unsigned i = 0; i < dimension_; ++i)
+        {
+            t1 += a->values[i];
+            t2 += b->values[i];
+            dx += cos(t1) - cos(t2);
+            dy += sin(t1) - sin(t2);
+            dist += sqrt(dx * dx + dy * dy);
+        }
+        return dist * linkLength_;
+    }
+    void interpolate(const ob::State *from, const ob::State *to, const double t, ob::State *state) const override
+    {
+        const auto *f = from->as<StateType>(), *o = to->as<StateType>();
+        auto *s = state->as<StateType>();
+        for (unsigned i = 0; i < dimension_; ++i)
+        {
+            double diff = o->values[i] - f->values[i];
+            if (fabs(diff) <= M_PI)
+                s->values[i] = f->values[i] + diff * t;
+            else
+            {
+                diff = diff > 0.0 ? 2.0 * M_PI - diff : -2.0 * M_PI - diff;
+                s->values[i] = f->values[i] - diff * t;
+                if (s->values[i] > M_PI)
+                    s->values[i] -= 2.0 * M_PI;
+                else if (s->values[i] < -M_PI)
+                    s->values[i] += 2.0 * M_PI;
+            }
+        }
+    }
+    double linkLength_;
+};
+
+class DubinsLike : public ob::SE2StateSpace  // stands for DubinsStateSpace / ReedsSheppStateSpace
+{
+public:
+    double distance(const ob::State *, const ob::State *) const override
+    {
+        return 1.0;
+    }
+};
+
+class AlwaysValid : public ob::StateValidityChecker
+{
+public:
+    using ob::StateValidityChecker::StateValidityChecker;
+    bool isValid(const ob::State *) const override
+    {
+        return true;
+    }
+};
+
+template <typename F>
+static bool throwsOmpl(F &&f, const char *needle)
+{
+    try
+    {
+        f();
+    }
+    catch (const ompl::Exception &e)
+    {
+        return std::string(e.what()).find(needle) != std::string::npos;
+    }
+    return false;
+}
+
+static void subclassTest()
+{
+    const unsigned links = 10;
+    const double L = 1.0 / links;
+    auto chain = std::make_shared<ChainSpace>(links, L);
+    chain->setup();
+    ob::StateSpacePtr asBase = chain;
+    CHECK(chain->getType() == ob::STATE_SPACE_REAL_VECTOR);
+    CHECK(throwsOmpl([&] { ompl::b200::describe(asBase); }, "not exactly RealVectorStateSpace"));
+    ompl::NearestNeighborsCUDA<ob::State *> refused;
+    CHECK(throwsOmpl(
+        [&] { ompl::b200::bind<ob::State *>(refused, asBase, [](ob::State *const &s) { return (const ob::State *)s; }); },
+        "not exactly RealVectorStateSpace"));
+    ob::StateSpacePtr dub = std::make_shared<DubinsLike>();
+    {
+        ob::RealVectorBounds b(2);
+        b.setLow(0);
+        b.setHigh(1);
+        dub->as<ob::SE2StateSpace>()->setBounds(b);
+        dub->setup();
+    }
+    CHECK(throwsOmpl([&] { ompl::b200::describe(dub); }, "not exactly CompoundStateSpace"));
+    // stock spaces still pass
+    ompl::b200::describe(cube(3));
+    {
+        ob::StateSpacePtr se2 = std::make_shared<ob::SE2StateSpace>();
+        ob::RealVectorBounds b(2);
+        b.setLow(0);
+        b.setHigh(1);
+        se2->as<ob::SE2StateSpace>()->setBounds(b);
+        se2->setup();
+        CHECK(ompl::b200::describe(se2).components.size() == 2);
+    }
+
+    // explicit chain description: kNN under the subclass's own distance()
+    const unsigned n = 400, k = 8;
+    std::vector<ob::State *> states(n);
+    for (auto &s : states)
+        s = randomRV(asBase, -M_PI, M_PI);
+    auto dist = [&](ob::State *const &a, ob::State *const &b) { return asBase->distance(a, b); };
+    ompl::NearestNeighborsLinear<ob::State *> lin;
+    lin.setDistanceFunction(dist);
+    lin.add(states);
+    ompl::NearestNeighborsCUDA<ob::State *> nn;
+    ompl::b200::bind<ob::State *>(nn, asBase, [](ob::State *const &s) { return (const ob::State *)s; },
+                                  ompl::b200::describeKinematicChain(asBase, L));
+    nn.add(states);
+    std::vector<ob::State *> a, b;
+    for (unsigned i = 0; i < n; i += 2)
+    {
+        nn.nearestK(states[i], k, a);
+        lin.nearestK(states[i], k, b);
+        CHECK(a == b);
+        nn.nearestR(states[i], 0.8, a);
+        lin.nearestR(states[i], 0.8, b);
+        CHECK(a == b);
+    }
+    // chain motions: wrap-around interpolation + the chain metric's segment count vs DiscreteMotionValidator
+    auto siRef = std::make_shared<ob::SpaceInformation>(asBase);
+    siRef->setStateValidityChecker(std::make_shared<AlwaysValid>(siRef.get()));
+    ob::DiscreteMotionValidator ref(siRef.get());
+    auto si = std::make_shared<ob::SpaceInformation>(asBase);
+    auto handle = ompl::b200::CheckerHandle::allValid();
+    ob::BatchedDiscreteMotionValidator mv(si, handle, ompl::b200::describeKinematicChain(asBase, L));
+    std::vector<const ob::State *> s1(states.begin(), states.begin() + n / 2), s2(states.begin() + n / 2, states.end());
+    std::vector<std::uint8_t> ok(n / 2);
+    mv.checkMotionBatch(s1.data(), s2.data(), n / 2, ok.data(), nullptr);
+    for (unsigned i = 0; i < n / 2; ++i)
+        CHECK((ok[i] != 0) == ref.checkMotion(s1[i], s2[i]));
+    // the interpolated states themselves (getMotionStates) against the subclass's interpolate()
+    ompl::b200::SpaceHandle sh(ompl::b200::describeKinematicChain(asBase, L));
+    std::vector<ob::State *> path;
+    const unsigned got = ompl::b200::getMotionStates(si.get(), sh, states[0], states[1], path, 9, true, true);
+    CHECK(got == 11 && path.size() == 11);
+    ob::State *tmp = asBase->allocState();
+    for (unsigned j = 1; j < 10 && j < path.size(); ++j)
+    {
+        asBase->interpolate(states[0], states[1], (double)j / 10.0, tmp);
+        for (unsigned c = 0; c < links; ++c)
+            CHECK(tmp->as<ob::RealVectorStateSpace::StateType>()->values[c] ==
+                  path[j]->as<ob::RealVectorStateSpace::StateType>()->values[c]);
+    }
+    asBase->freeState(tmp);
+    for (auto *s : path)
+        asBase->freeState(s);
+    for (auto *s : states)
+        asBase->freeState(s);
+    std::printf("subclass / explicit description: done\n");
+}
+
+// ---------------------------------------------------------------- 3. setDevices
+static void shardedTest(int ndev)
+{
+    auto space = cube(7);
+    ob::StateSpacePtr sp = space;
+    const unsigned n = 6000, nq = 300, k = 10;
+    std::vector<ob::State *> states(n), queries(nq);
+    for (auto &s : states)
+        s = randomRV(sp, 0, 1);
+    for (auto &s : queries)
+        s = randomRV(sp, 0, 1);
+    for (unsigned i = 0; i < 50; ++i)  // exact duplicates: ties must resolve by insertion order across shards
+        sp->copyState(states[n - 1 - i], states[i]);
+    auto acc = [](ob::State *const &s) { return (const ob::State *)s; };
+    ompl::NearestNeighborsCUDA<ob::State *> one, many;
+    ompl::b200::bind<ob::State *>(one, sp, acc);
+    std::vector<int> devs;
+    for (int i = 0; i < 3; ++i)
+        devs.push_back(i % ndev);
+    many.setDevices(devs);  // before the space is known: applied by bind -> setSpace
+    ompl::b200::bind<ob::State *>(many, sp, acc);
+    long shards = 0;
+    CHECK(omplcu_nn_get_stat(many.handle(), "shards", &shards) == OMPLCU_OK && shards == 3);
+    one.add(states);
+    many.add(std::vector<ob::State *>(states.begin(), states.begin() + 5000));
+    for (unsigned i = 5000; i < n; ++i)
+        many.add(states[i]);
+    CHECK(many.size() == n);
+    std::vector<std::vector<ob::State *>> a, b;
+    std::vector<double> da, db;
+    one.nearestKBatch(queries, k, a, &da);
+    many.nearestKBatch(queries, k, b, &db);
+    CHECK(a == b && da == db);
+    one.nearestKBatch(std::vector<ob::State *>(states.begin(), states.begin() + 60), k, a, &da);
+    many.nearestKBatch(std::vector<ob::State *>(states.begin(), states.begin() + 60), k, b, &db);
+    CHECK(a == b && da == db);
+    std::vector<ob::State *> ra, rb;
+    for (unsigned i = 0; i < 40; ++i)
+    {
+        one.nearestR(queries[i], 0.45, ra);
+        many.nearestR(queries[i], 0.45, rb);
+        CHECK(ra == rb && !ra.empty());
+    }
+    for (unsigned i = 0; i < 1000; i += 2)
+    {
+        CHECK(one.remove(states[i]));
+        CHECK(many.remove(states[i]));
+    }
+    one.nearestKBatch(queries, k, a);
+    many.nearestKBatch(queries, k, b);
+    CHECK(a == b);
+    one.list(ra);
+    many.list(rb);
+    CHECK(ra == rb);
+    for (auto *s : states)
+        sp->freeState(s);
+    for (auto *s : queries)
+        sp->freeState(s);
+    std::printf("sharded structure (3 shards over %d device(s)): done\n", ndev);
+}
+
+// ---------------------------------------------------------------- 4. motion states, bounds, extent
+static void spaceHelpersTest()
+{
+    auto se3 = std::make_shared<ob::SE3StateSpace>();
+    ob::RealVectorBounds b(3);
+    b.setLow(-1);
+    b.setHigh(2);
+    se3->setBounds(b);
+    se3->setup();
+    ob::StateSpacePtr sp = se3;
+    auto si = std::make_shared<ob::SpaceInformation>(sp);
+    ompl::b200::SpaceHandle sh(ompl::b200::describe(sp));
+    auto rnd = [&](double lo, double hi) {
+        ob::State *s = sp->allocState();
+        double q[4], nrm = 0;
+        for (double &v : q)
+        {
+            v = std::normal_distribution<double>()(gen);
+            nrm += v * v;
+        }
+        nrm = std::sqrt(nrm);
+        sp->copyFromReals(s, {uni(lo, hi), uni(lo, hi), uni(lo, hi), q[0] / nrm, q[1] / nrm, q[2] / nrm, q[3] / nrm});
+        return s;
+    };
+    ob::State *s1 = rnd(-1, 2), *s2 = rnd(-1, 2), *tmp = sp->allocState();
+    std::vector<double> r1, r2;
+    for (unsigned count : {0u, 1u, 5u, 33u})
+        for (bool endpoints : {false, true})
+        {
+            std::vector<ob::State *> got;
+            const unsigned added = ompl::b200::getMotionStates(si.get(), sh, s1, s2, got, count, endpoints, true);
+            const unsigned want = count + (endpoints ? 2 : 0);  // SpaceInformation.cpp:201-272
+            CHECK(added == want && got.size() == want);
+            const unsigned seg = count + 1;
+            for (unsigned j = 0; j < got.size(); ++j)
+            {
+                const unsigned idx = endpoints ? j : j + 1;  // position 0..seg along the motion
+                if (idx == 0)
+                    sp->copyState(tmp, s1);
+                else if (idx == seg)
+                    sp->copyState(tmp, s2);
+                else
+                    sp->interpolate(s1, s2, (double)idx / (double)seg, tmp);
+                sp->copyToReals(r1, tmp);
+                sp->copyToReals(r2, got[j]);
+                for (unsigned c = 0; c < r1.size(); ++c)
+                    CHECK(r1[c] == r2[c] || std::fabs(r1[c] - r2[c]) < 4e-15);  // slerp: sin/acos last bits
+            }
+            for (auto *s : got)
+                sp->freeState(s);
+        }
+    // alloc == false: never more than the caller's vector holds
+    {
+        std::vector<ob::State *> mine(4);
+        for (auto &s : mine)
+            s = sp->allocState();
+        CHECK(ompl::b200::getMotionStates(si.get(), sh, s1, s2, mine, 9, true, false) == 4);
+        sp->copyToReals(r1, mine[0]);
+        sp->copyToReals(r2, s1);
+        CHECK(r1 == r2);
+        for (auto *s : mine)
+            sp->freeState(s);
+    }
+    // bounds: states straddling every face by 0, +-DBL_EPSILON / 2, +-3 DBL_EPSILON; broken quaternions
+    const double eps = std::numeric_limits<double>::epsilon();
+    std::vector<ob::State *> probe;
+    for (double off : {0.0, eps * 0.5, -eps * 0.5, eps, -eps, 3 * eps, -3 * eps, 1e-3, -1e-3})
+        for (int face = 0; face < 2; ++face)
+            for (int ax = 0; ax < 3; ++ax)
+            {
+                ob::State *s = rnd(0, 1);
+                std::vector<double> r;
+                sp->copyToReals(r, s);
+                r[ax] = (face ? 2.0 : -1.0) + off * (face ? 2.0 : 1.0);
+                sp->copyFromReals(s, r);
+                probe.push_back(s);
+            }
+    for (double scale : {1.0 + 1e-10, 1.0 - 1e-10, 1.0 + 1e-8, 1.0 - 1e-8, 1.0 + 1e-16, 0.0, 2.0})
+    {
+        ob::State *s = rnd(0, 1);
+        std::vector<double> r;
+        sp->copyToReals(r, s);
+        for (int c = 3; c < 7; ++c)
+            r[c] *= scale;
+        sp->copyFromReals(s, r);
+        probe.push_back(s);
+    }
+    std::vector<double> low = {-1, -1, -1, 0, 0, 0, 0}, high = {2, 2, 2, 0, 0, 0, 0};
+    std::vector<std::uint8_t> in(probe.size());
+    std::vector<const ob::State *> cprobe(probe.begin(), probe.end());
+    ompl::b200::satisfiesBoundsBatch(sp.get(), sh, low, high, cprobe.data(), cprobe.size(), in.data());
+    unsigned inside = 0;
+    for (std::size_t i = 0; i < probe.size(); ++i)
+    {
+        CHECK((in[i] != 0) == sp->satisfiesBounds(probe[i]));
+        inside += in[i];
+    }
+    CHECK(inside > 0 && inside < probe.size());
+    CHECK(ompl::b200::getMaximumExtent(sh, low, high) == sp->getMaximumExtent());
+    {
+        auto rv = cube(7, -0.3, 1.9);
+        ompl::b200::SpaceHandle h(ompl::b200::describe(rv));
+        CHECK(ompl::b200::getMaximumExtent(h, std::vector<double>(7, -0.3), std::vector<double>(7, 1.9)) ==
+              rv->getMaximumExtent());
+        auto so2 = std::make_shared<ob::SO2StateSpace>();
+        so2->setup();
+        ompl::b200::SpaceHandle h2(ompl::b200::describe(so2));
+        CHECK(ompl::b200::getMaximumExtent(h2, {0.0}, {0.0}) == so2->getMaximumExtent());
+        std::vector<double> vals = {-M_PI, M_PI, -M_PI - 1e-15, M_PI - 1e-15, 0.0, 4.0};
+        std::vector<ob::State *> ss;
+        for (double v : vals)
+        {
+            ss.push_back(so2->allocState());
+            ss.back()->as<ob::SO2StateSpace::StateType>()->value = v;
+        }
+        std::vector<const ob::State *> css(ss.begin(), ss.end());
+        std::vector<std::uint8_t> ok(ss.size());
+        ompl::b200::satisfiesBoundsBatch(so2.get(), h2, {0.0}, {0.0}, css.data(), css.size(), ok.data());
+        for (std::size_t i = 0; i < ss.size(); ++i)
+        {
+            CHECK((ok[i] != 0) == so2->satisfiesBounds(ss[i]));
+            so2->freeState(ss[i]);
+        }
+    }
+    for (auto *s : probe)
+        sp->freeState(s);
+    sp->freeState(s1);
+    sp->freeState(s2);
+    sp->freeState(tmp);
+    std::printf("getMotionStates / satisfiesBounds / getMaximumExtent: done\n");
+}
