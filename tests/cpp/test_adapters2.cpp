@@ -530,3 +530,162 @@ static void spaceHelpersTest()
     sp->freeState(tmp);
     std::printf("getMotionStates / satisfiesBounds / getMaximumExtent: done\n");
 }
+
+// ---------------------------------------------------------------- 5. thread safety
+static void threadTest()
+{
+    auto space = cube(7);
+    ob::StateSpacePtr sp = space;
+    const unsigned n = 20000, nq = 64, k = 10, nthreads = 4;
+    std::vector<ob::State *> states(n);
+    for (auto &s : states)
+        s = randomRV(sp, 0, 1);
+    auto dist = [&](ob::State *const &a, ob::State *const &b) { return sp->distance(a, b); };
+    ompl::NearestNeighborsLinear<ob::State *> lin;
+    lin.setDistanceFunction(dist);
+    lin.add(states);
+    ompl::NearestNeighborsCUDA<ob::State *> nn;
+    ompl::b200::bind<ob::State *>(nn, sp, [](ob::State *const &s) { return (const ob::State *)s; });
+    nn.add(states);
+    // GNAT is what OMPL hands multithreaded planners because const queries run concurrently
+    // (tools/config/SelfConfig.h:112-113): the same must hold here.
+    std::vector<std::thread> th;
+    for (unsigned t = 0; t < nthreads; ++t)
+        th.emplace_back([&, t] {
+            std::vector<ob::State *> a, b;
+            for (unsigned i = t; i < nq * nthreads; i += nthreads)
+            {
+                nn.nearestK(states[i], k, a);
+                lin.nearestK(states[i], k, b);
+                CHECK(a == b);
+                if (i % 8 == 0)
+                {
+                    nn.nearestR(states[i], 0.3, a);
+                    lin.nearestR(states[i], 0.3, b);
+                    CHECK(a == b);
+                }
+                if (i % 16 == 1)
+                {
+                    std::vector<std::vector<ob::State *>> out;
+                    nn.nearestKBatch(std::vector<ob::State *>(states.begin() + i, states.begin() + i + 300), k, out);
+                    lin.nearestK(states[i + 7], k, b);
+                    CHECK(out[7] == b);
+                }
+            }
+        });
+    for (auto &t : th)
+        t.join();
+    for (auto *s : states)
+        sp->freeState(s);
+
+    // one checker, two threads: isValid batches against checkMotion batches (both use the checker's staging)
+    auto se2 = std::make_shared<ob::SE2StateSpace>();
+    ob::RealVectorBounds b(2);
+    b.setLow(0);
+    b.setHigh(1);
+    se2->setBounds(b);
+    se2->setup();
+    ob::StateSpacePtr sp2 = se2;
+    std::vector<double> circ = {0.5, 0.5, 0.2, 0.2, 0.8, 0.1, 0.8, 0.2, 0.15};
+    auto valid = [&](double x, double y) {
+        for (std::size_t i = 0; i < circ.size(); i += 3)
+        {
+            const double dx = circ[i] - x, dy = circ[i + 1] - y;
+            if (dx * dx + dy * dy < circ[i + 2] * circ[i + 2])
+                return false;
+        }
+        return true;
+    };
+    auto si = std::make_shared<ob::SpaceInformation>(sp2);
+    auto handle = ompl::b200::CheckerHandle::circles2D(circ);
+    auto svc = std::make_shared<ob::BatchedStateValidityChecker>(si, handle);
+    si->setStateValidityChecker(svc);
+    ob::BatchedDiscreteMotionValidator mv(si, handle);
+    const unsigned m = 3000;
+    std::vector<ob::State *> pa(m), pb(m);
+    for (unsigned i = 0; i < m; ++i)
+    {
+        pa[i] = sp2->allocState();
+        pb[i] = sp2->allocState();
+        sp2->copyFromReals(pa[i], {uni(0, 1), uni(0, 1), uni(-3, 3)});
+        sp2->copyFromReals(pb[i], {uni(0, 1), uni(0, 1), uni(-3, 3)});
+    }
+    std::vector<const ob::State *> ca(pa.begin(), pa.end()), cb(pb.begin(), pb.end());
+    std::vector<std::uint8_t> mref(m);
+    mv.checkMotionBatch(ca.data(), cb.data(), m, mref.data(), nullptr);
+    std::thread t1([&] {
+        for (int rep = 0; rep < 20; ++rep)
+        {
+            std::vector<std::uint8_t> ok(m);
+            svc->isValidBatch(ca.data(), m - rep * 50, ok.data());  // varying sizes: staging is re-reserved
+            for (unsigned i = 0; i < m - rep * 50; ++i)
+            {
+                const auto *s = pa[i]->as<ob::SE2StateSpace::StateType>();
+                CHECK((ok[i] != 0) == valid(s->getX(), s->getY()));
+            }
+        }
+    });
+    std::thread t2([&] {
+        for (int rep = 0; rep < 20; ++rep)
+        {
+            std::vector<std::uint8_t> ok(m);
+            mv.checkMotionBatch(ca.data(), cb.data(), m - rep * 30, ok.data(), nullptr);
+            for (unsigned i = 0; i < m - rep * 30; ++i)
+                CHECK(ok[i] == mref[i]);
+        }
+    });
+    t1.join();
+    t2.join();
+    for (unsigned i = 0; i < m; ++i)
+    {
+        sp2->freeState(pa[i]);
+        sp2->freeState(pb[i]);
+    }
+    std::printf("concurrent queries / mixed isValid + checkMotion: done\n");
+}
+
+// PRM keeps the state of a Vertex in a property map (prm/PRM.h:125-130, stateProperty_[v]); a table here
+static std::vector<ob::State *> g_vertexState;
+
+int main()
+{
+    int ndev = 0;
+    if (omplcu_device_count(&ndev) != OMPLCU_OK || ndev == 0)
+    {
+        std::printf("no CUDA device: %s\n", omplcu_last_error());
+        return 2;
+    }
+    g_vertexState.assign(400, nullptr);
+    elementTypeTest<unsigned long>(
+        "unsigned long (PRM Vertex)",
+        [](unsigned i, ob::State *s) {
+            g_vertexState[i] = s;
+            return (unsigned long)i;
+        },
+        [](const unsigned long &v) -> ob::State * { return g_vertexState[v]; });
+    {
+        std::vector<std::unique_ptr<Motion>> own;
+        elementTypeTest<Motion *>(
+            "Motion* (FMT)",
+            [&](unsigned, ob::State *s) {
+                own.emplace_back(new Motion);
+                own.back()->state = s;
+                return own.back().get();
+            },
+            [](Motion *const &m) -> ob::State * { return m->getState(); });
+    }
+    elementTypeTest<std::shared_ptr<BitVertex>>(
+        "std::shared_ptr<Vertex> (BIT*)",
+        [](unsigned, ob::State *s) {
+            auto v = std::make_shared<BitVertex>();
+            v->st = s;
+            return v;
+        },
+        [](const std::shared_ptr<BitVertex> &v) -> ob::State * { return v->st; });
+    subclassTest();
+    shardedTest(ndev);
+    spaceHelpersTest();
+    threadTest();
+    std::printf(failures ? "FAILED (%d)\n" : "all adapter tests (part 2) passed\n", failures.load());
+    return failures ? 1 : 0;
+}
