@@ -44,8 +44,33 @@ N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
 N_SEGMENTS = 1_000_000
 MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
-TC_TRAFFIC = 356.8e6  # dram__bytes_read.sum + dram__bytes_write.sum per launch, profiles/r1_scan_tc_d7_ncu_summary.csv
+TC_CAPTURE = "r1_scan_tc_d7_ncu_summary.csv"    # ncu --set full of the tensor-core scan (roofline.traffic is read from it)
+FP32_CAPTURE = "r1_scan_v3_ncu_summary.csv"     # ... of the FP32-pipe scan
+MOTION_CAPTURE = "r1_motion_v5_ncu_summary.csv"  # ... of motion_group_kernel
 UNIT = "queries/s"
+
+
+def bench_config():
+    """The workload, with the SAME keys in both arms (the driver compares the two dicts)."""
+    return {"workload": "synthetic batched kNN: RealVectorStateSpace(7), "
+                        f"{N_STATES // 1_000_000}M states, 64K queries, k=10",
+            "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM}
+
+
+def ncu_traffic(summary_csv):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch, read from a committed ncu summary under
+    profiles/ (scripts/ncu_summary.py format); None if the file or the metrics are absent."""
+    unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+    tot, seen = 0.0, 0
+    try:
+        for ln in open(os.path.join(ROOT, "profiles", summary_csv)):
+            f = [x.strip().strip('"') for x in ln.split(",")]
+            if len(f) >= 3 and f[0] in ("dram__bytes_read.sum", "dram__bytes_write.sum") and f[1] in unit:
+                tot += float(f[2]) * unit[f[1]]
+                seen += 1
+    except (OSError, ValueError):
+        return None
+    return tot if seen == 2 else None
 
 
 def make_inputs(n_states=None, n_queries=N_QUERIES):
@@ -176,9 +201,8 @@ def run_reference_arm(args):
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps,
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), 1M states, 64K queries, k=10",
-                   "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
-                   "queries_per_step": per_step},
+        "config": bench_config(),
+        "queries_per_step": per_step,
         "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
                          "build_s": build_s},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -214,23 +238,12 @@ def run_gpu_arm(args):
         raise SystemExit("bench.py: no CUDA device (there is no CPU fallback; use --impl reference for the CPU arm)")
     torch.cuda.set_device(local)
     dist = None
+    nccl = None  # process group of the device-timed legs (created after the one-process e2e leg, see below)
     if world > 1:
         import torch.distributed as dist
 
-        # NCCL prints its version banner on stdout when the first communicator comes up; stdout is
-        # reserved for the one JSON line, so park it on stderr until the communicator exists
-        sys.stdout.flush()
-        saved_stdout = os.dup(1)
-        os.dup2(2, 1)
-        try:
-            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-            warm = torch.zeros(1, device=torch.device("cuda", local))
-            dist.all_reduce(warm)
-            torch.cuda.synchronize()
-        finally:
-            sys.stdout.flush()
-            os.dup2(saved_stdout, 1)
-            os.close(saved_stdout)
+        # default group: gloo (host-side barriers and the rendezvous); the NCCL group comes later
+        dist.init_process_group("gloo")
     dev = torch.device("cuda", local)
     L = lib()
 
@@ -246,6 +259,35 @@ def run_gpu_arm(args):
     assert N_QUERIES % R_QB == 0
     NQB = N_QUERIES // R_QB           # queries answered by this rank
     qlo = sh_r * NQB
+    e2e_note = "omplcu_nn_knn on one handle: host buffers in, host buffers out"
+    e2e_wall_ms, motion_e2e, e2e_ids = None, None, None
+    if world > 1:
+        # End to end at N GPUs = what ONE caller process gets from a roadmap sharded over the N GPUs:
+        # omplcu_nn_create_sharded(devices[0..N-1]) and the same host-pointer call.  Rank 0 drives all GPUs (the
+        # library has one host thread per shard) while the other ranks wait at a host-side barrier.  This leg
+        # runs BEFORE the NCCL communicator exists: with torch's NCCL peer mappings in place, rank 0's own
+        # contexts on the other GPUs made cudaMalloc fail with "resource already mapped".
+        dist.barrier()
+        if rank == 0:
+            e2e_wall_ms, motion_e2e, e2e_ids = sharded_e2e(args, torch, world, pts, qs, not args.no_motion)
+        dist.barrier()
+        e2e_note = (f"omplcu_nn_create_sharded over {world} GPUs in ONE process (rank 0), omplcu_nn_knn with host "
+                    "buffers: one H2D, NVLink peer copies to the shards, per-shard scan, peer gather, device merge, "
+                    "one D2H; results identical to the device-timed leg")
+        # NCCL prints its version banner on stdout when the first communicator comes up; stdout is
+        # reserved for the one JSON line, so park it on stderr until the communicator exists
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            nccl = dist.new_group(backend="nccl", device_id=torch.device("cuda", local))
+            warm = torch.zeros(1, device=torch.device("cuda", local))
+            dist.all_reduce(warm, group=nccl)
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     sp = ob.RealVectorStateSpace(DIM, device=local)
     nn = ob.NearestNeighborsCUDA(sp)
     nn.set_id_base(lo)
@@ -281,7 +323,7 @@ def run_gpu_arm(args):
     def step_device():
         check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), NQB, K, d_ids.data_ptr(), d_d.data_ptr(), sptr))
         if world > 1:
-            packed.all_gather()
+            packed.all_gather(group=nccl)
             merge_blocks()
 
     h_ids = np.empty((NQB, K), dtype=np.uint64)
@@ -297,18 +339,10 @@ def run_gpu_arm(args):
         # host buffers in, host buffers out: the reference-facing call
         check(L.omplcu_nn_knn(nn.handle, qs.ctypes.data, NQB, K, h_ids.ctypes.data, h_d.ctypes.data,
                               h_cnt.ctypes.data))
-        if world > 1:
-            # sharded roadmap: merge needs the other shards' lists; exchange on the device
-            d_ids.copy_(torch.from_numpy(h_ids.view(np.int64)), non_blocking=True)
-            d_d.copy_(torch.from_numpy(h_d), non_blocking=True)
-            packed.all_gather()
-            merge_blocks()
-            h_all_ids.view(np.int64)[:] = m_ids.cpu().numpy()
-            h_all_d[:] = m_d.cpu().numpy()
 
     def barrier():
         if world > 1:
-            dist.barrier()
+            dist.barrier(group=nccl)
         torch.cuda.synchronize()
 
     def timed(step, steps, warmup, sampler=None):
@@ -336,7 +370,7 @@ def run_gpu_arm(args):
         ms = max(dev_ms, 0.0)
         t = torch.tensor([ms, wall * 1e3], dtype=torch.float64, device=dev)
         if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=nccl)
         return float(t[0]), float(t[1]), clocks
 
     l0 = nn.stat("launches")
@@ -348,11 +382,11 @@ def run_gpu_arm(args):
     scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
     fallbacks = nn.stat("last_fallbacks")
     used_tc = nn.stat("last_tc") == 1
-    _, e2e_wall_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
-
-    # sanity: device-resident and host-pointer results agree (same code path underneath)
     res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
-    assert (res_ids == h_all_ids).all(), "device and host entry points disagree"
+    if world == 1:
+        _, e2e_wall_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
+        # sanity: device-resident and host-pointer results agree (same code path underneath)
+        assert (res_ids == h_all_ids).all(), "device and host entry points disagree"
 
     # the same step on the FP32-pipe scan kernel (the round-1 default), for the second roofline
     fp32_leg = None
@@ -363,7 +397,12 @@ def run_gpu_arm(args):
         fp32_leg = (f_ms / max(args.steps // 2, 2), nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1))
         nn.set_option("tc_scan", -1)
 
-    motion = None if args.no_motion else motion_block(args, torch, dist, dev, local, rank, world, timed)
+    motion = None if args.no_motion else motion_block(args, torch, dist, nccl, dev, local, rank, world, timed)
+
+    if world > 1 and rank == 0:
+        assert (e2e_ids == res_ids).all(), "sharded handle (one process) and the torchrun ranks disagree"
+        if motion is not None and motion_e2e is not None:
+            motion["e2e"] = motion_e2e
 
     if rank == 0:
         t_step = dev_ms / args.steps
@@ -393,7 +432,8 @@ def run_gpu_arm(args):
                 "unit": "TFLOP/s", "frac": a / fp32_peak if fp32_peak else None,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
                 # (profiles/r1_scan_v3_ncu_summary.csv); algorithmic: 32 MB filter copy + 1.8 MB queries + lists
-                "traffic": 34.9e6 if world == 1 else None, "traffic_unit": "bytes/launch",
+                "traffic": ncu_traffic(FP32_CAPTURE) if world == 1 else None,
+                "traffic_unit": f"bytes/launch (profiles/{FP32_CAPTURE})",
                 "peak_source": fp32_src, "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * DIM,
                 "frac_executed": exe / (kernel_ns * 1e-9) / 1e12 / fp32_peak if fp32_peak else None,
                 "kernel_ms": kernel_ns * 1e-6, "kernel_share_of_step": kernel_ns * 1e-6 / step_ms,
@@ -412,7 +452,8 @@ def run_gpu_arm(args):
                 "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of one launch, ncu --set full
                 # (profiles/r1_scan_tc_ncu_summary.csv); algorithmic: 64 MB operand image + queries + lists
-                "traffic": TC_TRAFFIC if world == 1 else None, "traffic_unit": "bytes/launch",
+                "traffic": ncu_traffic(TC_CAPTURE) if world == 1 else None,
+                "traffic_unit": f"bytes/launch (profiles/{TC_CAPTURE})",
                 "peak_source": "MEASURED_PEAKS.json bf16_tflops (dense BF16 cuBLAS, burst: the kernel is timed alone)"
                 if "bf16_tflops" in peaks else "fallback 2250 TFLOP/s (B200_PROFILING.md): MEASURED_PEAKS.json absent",
                 "flops_per_pair_algorithmic": 3 * DIM, "flops_per_pair_executed": 2 * kpad,
@@ -438,16 +479,14 @@ def run_gpu_arm(args):
             "vs_baseline": None,
             "dtype": "bf16x2 split filter on tensor cores (f32 accumulate) + f64 exact re-rank" if used_tc
             else "f32 filter + f64 exact re-rank", "data": "synthetic",
-            "config": {"workload": "synthetic batched kNN: RealVectorStateSpace(7), "
-                                   f"{N_STATES // 1_000_000}M states, 64K queries, k=10",
-                       "n_states": N_STATES, "n_queries": N_QUERIES, "k": K, "dim": DIM,
-                       "sharding": f"{S_SH} state shard(s) by insertion index x {R_QB} query block(s) over {world} ranks; "
-                                   "one NCCL all-gather of the packed (distance, id) lists + merge by (distance, id)"
-                       if world > 1 else "single GPU",
-                       "l2": "flushed between timed iterations (256 MB write)"},
+            "config": bench_config(),
+            "sharding": f"{S_SH} state shard(s) by insertion index x {R_QB} query block(s) over {world} ranks; "
+                        "one NCCL all-gather of the packed (distance, id) lists + merge by (distance, id)"
+            if world > 1 else "single GPU",
+            "l2": "flushed between timed iterations (256 MB write)",
             "clocks": clocks,
-            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes) * world,
-                    "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes) * world},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(qs_all.nbytes),
+                    "d2h_bytes_per_step": int(N_QUERIES * K * 16), "path": e2e_note},
             "gpu_launches": int(launches_timed),
             "roofline": roofline,
             "exact_fallback_queries": int(fallbacks),
@@ -469,10 +508,82 @@ def run_gpu_arm(args):
         dist.destroy_process_group()
 
 
+def sharded_e2e(args, torch, world, pts, qs_all, with_motion):
+    """Rank 0 only.  kNN (and motion checks) end to end through the multi-GPU entry points of the library
+    with pinned host buffers; wall clock around the synchronous calls, L2 of every GPU flushed between
+    timed iterations.  Returns (kNN ms over args.steps, motion e2e dict or None, the neighbour ids)."""
+    import ompl_b200 as ob
+    from ompl_b200 import workloads
+    from ompl_b200._lib import check, lib
+
+    L = lib()
+    devs = list(range(world))
+
+    def pin(a):
+        rc = torch.cuda.cudart().cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+        assert int(rc) == 0, f"cudaHostRegister failed: {rc}"
+
+    def flush_all():
+        for d in devs:
+            check(L.omplcu_device_flush_l2(d))
+
+    def wall(step, steps, warmup):
+        for _ in range(warmup):
+            flush_all()
+            step()
+        t = 0.0
+        for _ in range(steps):
+            flush_all()
+            t0 = time.perf_counter()
+            step()
+            t += time.perf_counter() - t0
+        return t * 1e3
+
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(DIM, device=0), devices=devs)
+    nn.add_rows(pts)
+    q = qs_all.copy()  # fresh buffers: parts of the originals are already registered by the per-rank legs
+    h_ids = np.empty((N_QUERIES, K), dtype=np.uint64)
+    h_d = np.empty((N_QUERIES, K), dtype=np.float64)
+    h_cnt = np.empty(N_QUERIES, dtype=np.uint32)
+    for a in (q, h_ids, h_d):
+        pin(a)
+
+    def step():
+        check(L.omplcu_nn_knn(nn.handle, q.ctypes.data, N_QUERIES, K, h_ids.ctypes.data, h_d.ctypes.data,
+                              h_cnt.ctypes.data))
+
+    ms = wall(step, args.steps, max(args.warmup, 2))
+    del nn
+    motion_e2e = None
+    if with_motion:
+        s1, s2 = workloads.m3_segments(N_SEGMENTS)
+        sph, box = workloads.se3_obstacles()
+        robot = workloads.se3_robot()
+        sp = ob.SE3StateSpace(-1.0, 1.0, device=0)
+        chks = [ob.SE3ObstacleValidityChecker(robot, sph, box, device=d) for d in devs]
+        hs = (C.c_void_p * world)(*[c.handle.value for c in chks])
+        a, b = s1.copy(), s2.copy()
+        hv = np.empty(N_SEGMENTS, dtype=np.uint8)
+        ht = np.empty(N_SEGMENTS, dtype=np.float64)
+        for arr in (a, b, hv, ht):
+            pin(arr)
+
+        def mstep():
+            check(L.omplcu_check_motions_multi(hs, world, sp.handle, a.ctypes.data, b.ctypes.data, N_SEGMENTS,
+                                               hv.ctypes.data, ht.ctypes.data, None))
+
+        mms = wall(mstep, args.steps, max(args.warmup, 2))
+        motion_e2e = {"value": N_SEGMENTS / (mms / args.steps * 1e-3), "unit": "segments/s",
+                      "h2d_bytes_per_step": int(a.nbytes + b.nbytes), "d2h_bytes_per_step": int(hv.nbytes + ht.nbytes),
+                      "path": f"omplcu_check_motions_multi over {world} per-GPU checkers in one process (rank 0), "
+                              "segments split by index, host buffers", "valid_segments": int(hv.sum())}
+    return ms, motion_e2e, h_ids
+
+
 # ---------------------------------------------------------------------------
 # second half of BASELINE.json's metric: motion checks/sec (SURVEY.md 8d, workload M3)
 # ---------------------------------------------------------------------------
-def motion_block(args, torch, dist, dev, local, rank, world, timed):
+def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
     """1M SE3 segments against 500 spheres + 500 boxes at resolution 0.01, split by
     segment over the ranks (no collective on the data path).  Returns the "motion"
     object of the JSON line (rank 0) or None."""
@@ -511,12 +622,17 @@ def motion_block(args, torch, dist, dev, local, rank, world, timed):
     l0 = chk.stat("launches")
     dev_ms, _, _ = timed(step_device, args.steps, args.warmup)
     launches = (chk.stat("launches") - l0) * args.steps // (args.steps + args.warmup)
-    _, e2e_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
-    assert (dv.cpu().numpy() == hv).all() and (dt.cpu().numpy() == ht).all(), "device and host entry points disagree"
+    e2e_ms = float("nan")
+    if world == 1:
+        _, e2e_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
+        assert (dv.cpu().numpy() == hv).all() and (dt.cpu().numpy() == ht).all(), "device and host entry points disagree"
+    else:
+        hv[:] = dv.cpu().numpy()  # e2e at N > 1 is measured by rank 0 through omplcu_check_motions_multi
+        ht[:] = dt.cpu().numpy()
     tot = torch.tensor([chk.stat("last_states"), chk.stat("last_states_evaluated"), int(hv.sum())],
                        dtype=torch.float64, device=dev)
     if world > 1:
-        dist.all_reduce(tot)
+        dist.all_reduce(tot, group=nccl)
     if rank != 0:
         return None
     states, evaluated, nvalid = (int(x) for x in tot.tolist())
@@ -546,8 +662,8 @@ def motion_block(args, torch, dist, dev, local, rank, world, timed):
         "gpu_launches": int(launches),
         "roofline": {
             "bound": "hbm", "kernel": "motion_group_kernel<SE3,8,32>", "peak": hbm_peak, "unit": "GB/s",
-            "achieved": gbs, "frac": gbs / hbm_peak, "traffic": 127.5e6 if world == 1 else None,
-            "traffic_unit": "bytes/launch (ncu, profiles/r1_motion_v2_ncu_summary.csv)",
+            "achieved": gbs, "frac": gbs / hbm_peak, "traffic": ncu_traffic(MOTION_CAPTURE) if world == 1 else None,
+            "traffic_unit": f"bytes/launch (ncu, profiles/{MOTION_CAPTURE})",
             "brute_force_equivalent_tflops": alg / (t_step * 1e-3) / 1e12,
             "note": "per rank. Inputs are read once (ncu: 116 MB in, 11 MB out per 1M segments), so HBM is the only "
                     "hardware roof the algorithmic figure can be put against, and the kernel is nowhere near it: "

@@ -73,6 +73,8 @@ const char *omplcu_last_error(void);
 int omplcu_version(void);
 int omplcu_device_count(int *count);
 void omplcu_free(void *p);
+/* Benchmark hygiene (no reference counterpart): evict the L2 of `device` by writing a library-owned 256 MB buffer. */
+int omplcu_device_flush_l2(int device);
 /* FP32 FMA pipe peak of `device` in TFLOP/s (FMA = 2 flop), measured with a
  * register-only micro-benchmark: scalar FFMA and packed FFMA2.  This is the
  * roofline denominator for the FP32-bound kNN scan. */

@@ -79,6 +79,7 @@ SIGNATURES = {
     "omplcu_check_states_device": [_vp, _i, _pd, _sz, _pd, _vp],
     "omplcu_check_motions_device": [_vp, _vp, _pd, _pd, _sz, _pd, _pd, _pd, _vp],
     "omplcu_check_motions_device_noalloc": [_vp, _vp, _pd, _pd, _sz, _pd, _pd, _pd, _vp],
+    "omplcu_device_flush_l2": [_i],
     "omplcu_measure_fp32_peak": [_i, C.POINTER(C.c_double), C.POINTER(C.c_double)],
 }
 

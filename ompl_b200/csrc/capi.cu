@@ -131,6 +131,28 @@ void omplcu_free(void *p)
     free(p);
 }
 
+// Benchmark hygiene: evict `device`'s L2 by writing a library-owned 256 MB buffer (> 126 MB L2) and waiting
+// for it.  Lets one process flush the L2 of every GPU a sharded handle uses without creating framework
+// contexts on them.
+int omplcu_device_flush_l2(int device)
+{
+    return guarded([&] {
+        need_gpu(device);
+        REQUIRE(device < 64, "device index out of range");
+        static std::mutex mu;
+        static void *buf[64] = {};
+        const size_t bytes = (size_t)256 << 20;
+        DeviceGuard g(device);
+        {
+            std::lock_guard<std::mutex> lk(mu);
+            if (!buf[device])
+                CUDA_CHECK(cudaMalloc(&buf[device], bytes));
+        }
+        CUDA_CHECK(cudaMemsetAsync(buf[device], 1, bytes, 0));
+        CUDA_CHECK(cudaStreamSynchronize(0));
+    });
+}
+
 int omplcu_measure_fp32_peak(int device, double *tflops_ffma, double *tflops_ffma2)
 {
     return guarded([&] {
