@@ -519,9 +519,12 @@ def sharded_e2e(args, torch, world, pts, qs_all, with_motion):
     L = lib()
     devs = list(range(world))
 
+    pinned = []
+
     def pin(a):
         rc = torch.cuda.cudart().cudaHostRegister(a.ctypes.data, a.nbytes, 0)
         assert int(rc) == 0, f"cudaHostRegister failed: {rc}"
+        pinned.append(a)
 
     def flush_all():
         for d in devs:
@@ -577,6 +580,11 @@ def sharded_e2e(args, torch, world, pts, qs_all, with_motion):
                       "h2d_bytes_per_step": int(a.nbytes + b.nbytes), "d2h_bytes_per_step": int(hv.nbytes + ht.nbytes),
                       "path": f"omplcu_check_motions_multi over {world} per-GPU checkers in one process (rank 0), "
                               "segments split by index, host buffers", "valid_segments": int(hv.sum())}
+    # the arrays die with this frame: unregister them, or a later allocation that reuses their pages fails
+    # to register ("part or all of the requested memory range is already mapped")
+    h_ids = h_ids.copy()
+    for a in pinned:
+        torch.cuda.cudart().cudaHostUnregister(a.ctypes.data)
     return ms, motion_e2e, h_ids
 
 
