@@ -3,7 +3,8 @@
 each timed through the host-pointer API (what a caller sees) with a parity sample against the oracle.
 bench.py carries the headline (M1 at 1M states, M3); this script produces the table in DESIGN.md 9.
 
-    python scripts/bench_workloads.py [m1 m1ties m2 m4] > profiles/r1_workloads.jsonl
+    python scripts/bench_workloads.py [m1 m1ties m2 m4] [--log=profiles/r2_workloads.log] > profiles/r2_workloads.jsonl
+(--log: the same lines as a tools::Benchmark log for the reference's scripts/ompl_benchmark_statistics.py)
 """
 import json
 import os
@@ -33,8 +34,39 @@ def timed(fn, reps=3):
     return best, out
 
 
+RECORDS = []
+
+
 def emit(**kw):
+    RECORDS.append(kw)
     print(json.dumps(kw), flush=True)
+
+
+def write_benchmark_log(path):
+    """The emitted lines as a tools::Benchmark log (one "planner" per workload line, one run each), which the
+    reference's scripts/ompl_benchmark_statistics.py turns into its sqlite database."""
+    from ompl_b200 import benchmark_log as bl
+
+    log = bl.BenchmarkLog("ompl_b200_workloads", run_count=1)
+    log.setup_info = "SURVEY 8(d) workloads M1-M4 through the host-pointer API of libomplcu.so\n"
+    log.cpu_info = f"{CORES} host threads\n"
+    for i, r in enumerate(RECORDS):
+        name = "_".join(str(r.get(k)) for k in ("workload", "n_states", "k", "dim", "links") if r.get(k) is not None)
+        pl = log.add_planner(f"NearestNeighborsCUDA_{name}_{i}", {"nearest_neighbors STRING": "NearestNeighborsCUDA"})
+        run = {}
+        for k, v in r.items():
+            if isinstance(v, bool):
+                run[f"{k.replace('_', ' ')} BOOLEAN"] = "1" if v else "0"
+            elif isinstance(v, int):
+                run[f"{k.replace('_', ' ')} INTEGER"] = str(v)
+            elif isinstance(v, float):
+                run[f"{k.replace('_', ' ')} REAL"] = repr(v)
+        if "ms" in r:
+            run["time REAL"] = repr(r["ms"] * 1e-3)
+            log.total_duration += r["ms"] * 1e-3
+        pl.runs.append(run)
+    with open(path, "w") as f:
+        log.save(f)
 
 
 def m1(n_list=(1_000_000, 4_000_000, 16_000_000), nq=65536, k=10, d=7):
@@ -152,6 +184,9 @@ def m4(n=100_000):
 
 
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["m1", "m1ties", "m2", "m4"]
+    which = [a for a in sys.argv[1:] if not a.startswith("--log=")] or ["m1", "m1ties", "m2", "m4"]
     for w in which:
         {"m1": m1, "m1ties": m1ties, "m2": m2, "m4": m4}[w]()
+    for a in sys.argv[1:]:
+        if a.startswith("--log="):
+            write_benchmark_log(a[len("--log="):])

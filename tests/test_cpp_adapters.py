@@ -51,9 +51,10 @@ def test_cpp_adapters_against_reference_classes(gpu):
 
 @pytest.mark.gpu
 def test_cpp_adapters_element_types_subclasses_sharding_threads(gpu):
-    out = _run(BIN2, "all adapter tests (part 2) passed")
+    out = _run(BIN2, "all adapter tests (part 2) passed",
+               os.path.join(ROOT, "tests", "golden", "benchmark_log_sample.log"))
     for part in ("unsigned long (PRM Vertex)", "Motion* (FMT)", "std::shared_ptr<Vertex> (BIT*)",
-                 "subclass / explicit description", "sharded structure", "getMotionStates", "concurrent queries"):
+                 "subclass / explicit description", "sharded structure", "getMotionStates", "concurrent queries", "default structure selector"):
         assert part in out, part
 
 
