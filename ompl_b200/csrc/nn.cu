@@ -851,13 +851,59 @@ namespace omplcu
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
         if (const char *e = getenv("OMPLCU_THR_SCAN"))
             thr_mode_ = atoi(e);  // default for the "thr_scan" option
-        counters_.reserve(4);
-        CUDA_CHECK(cudaEventCreate(&ev0_));
-        CUDA_CHECK(cudaEventCreate(&ev1_));
-        CUDA_CHECK(cudaEventCreate(&ev2_));
-        CUDA_CHECK(cudaEventCreate(&ev3_));
-        kept_.reserve(1);
         CUDA_CHECK(cudaStreamSynchronize(stream_));
+    }
+
+    // ---- per-query contexts ----
+    NNIndex::Lease::Lease(NNIndex &i) : ix(i), c(nullptr)
+    {
+        {
+            std::lock_guard<std::mutex> lk(ix.pool_mu_);
+            if (!ix.free_.empty())
+            {
+                c = ix.free_.back();
+                ix.free_.pop_back();
+                return;
+            }
+        }
+        // all contexts are busy (or this is the first query): a new one.  The caller holds a DeviceGuard.
+        std::unique_ptr<QCtx> n(new QCtx);
+        CUDA_CHECK(cudaStreamCreateWithFlags(&n->stream, cudaStreamNonBlocking));
+        CUDA_CHECK(cudaEventCreate(&n->ev0_));
+        CUDA_CHECK(cudaEventCreate(&n->ev1_));
+        CUDA_CHECK(cudaEventCreate(&n->ev2_));
+        CUDA_CHECK(cudaEventCreate(&n->ev3_));
+        n->counters_.reserve(4);
+        n->kept_.reserve(1);
+        c = n.get();
+        std::lock_guard<std::mutex> lk(ix.pool_mu_);
+        ix.pool_.push_back(std::move(n));
+    }
+
+    NNIndex::Lease::~Lease()
+    {
+        std::lock_guard<std::mutex> lk(ix.pool_mu_);
+        ix.free_.push_back(c);
+    }
+
+    void NNIndex::publish(const QCtx &c)
+    {
+        std::lock_guard<std::mutex> lk(stat_mu_);
+        last_collect_redo_ = c.last_collect_redo_;
+        last_tc_ = c.last_tc_;
+        last_thr_ = c.last_thr_;
+        last_kept_ = c.last_kept_;
+        last_rank_ = c.last_rank_;
+        last_sample_ns_ = c.last_sample_ns_;
+        last_main_ns_ = c.last_main_ns_;
+        last_scan_ns_ = c.last_scan_ns_;
+        last_fallbacks_ = c.last_fallbacks_;
+        last_path_ = c.last_path_;
+        if (profile_ && c.last_path_ == 1)
+        {
+            scan_ns_total_ += c.last_scan_ns_;
+            scan_count_++;
+        }
     }
 
     NNIndex::~NNIndex()
@@ -868,19 +914,22 @@ namespace omplcu
             cudaStreamSynchronize(stream_);
             cudaStreamDestroy(stream_);
         }
-        if (ev0_)
-            cudaEventDestroy(ev0_);
-        if (ev1_)
-            cudaEventDestroy(ev1_);
-        if (ev2_)
-            cudaEventDestroy(ev2_);
-        if (ev3_)
-            cudaEventDestroy(ev3_);
+        for (auto &c : pool_)
+        {
+            if (c->stream)
+            {
+                cudaStreamSynchronize(c->stream);
+                cudaStreamDestroy(c->stream);
+            }
+            for (cudaEvent_t e : {c->ev0_, c->ev1_, c->ev2_, c->ev3_})
+                if (e)
+                    cudaEventDestroy(e);
+        }
     }
 
     void NNIndex::set_id_base(uint64_t base)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         REQUIRE(nslots_ == 0, "omplcu_nn_set_id_base: structure is not empty");
         id_base_ = base;
     }
@@ -913,7 +962,7 @@ namespace omplcu
 
     uint64_t NNIndex::add_at(const double *rows, size_t n, uint64_t want_first)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
         if (want_first != OMPLCU_ID_NONE)
         {
@@ -971,7 +1020,7 @@ namespace omplcu
 
     void NNIndex::remove(uint64_t id)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
         auto it = std::lower_bound(h_ids_.begin(), h_ids_.end(), id);
         if (it == h_ids_.end() || *it != id || !h_alive_[it - h_ids_.begin()])
@@ -992,7 +1041,7 @@ namespace omplcu
     // Bulk removal: one kernel marks every slot, one synchronisation.  Absent ids are skipped.
     size_t NNIndex::remove_batch(const uint64_t *ids, size_t n)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
         std::vector<uint32_t> slots;
         slots.reserve(n);
@@ -1086,7 +1135,7 @@ namespace omplcu
 
     void NNIndex::clear()
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
         if (fast_space_ && nslots_)
         {
@@ -1106,7 +1155,7 @@ namespace omplcu
 
     size_t NNIndex::list(uint64_t *ids, size_t cap) const
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::shared_lock<std::shared_mutex> lk(rw_);
         size_t c = 0;
         for (size_t s = 0; s < nslots_; ++s)
             if (h_alive_[s])
@@ -1120,7 +1169,7 @@ namespace omplcu
 
     void NNIndex::get(uint64_t id, double *row)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::shared_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
         auto it = std::lower_bound(h_ids_.begin(), h_ids_.end(), id);
         if (it == h_ids_.end() || *it != id || !h_alive_[it - h_ids_.begin()])
@@ -1133,7 +1182,7 @@ namespace omplcu
 
     void NNIndex::set_option(const char *key, long v)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::unique_lock<std::shared_mutex> lk(rw_);
         if (!strcmp(key, "force_exact"))
             force_exact_ = v != 0;
         else if (!strcmp(key, "sample_thresholds"))
@@ -1164,6 +1213,7 @@ namespace omplcu
         {
             // time the scan kernel with CUDA events on the launching stream
             profile_ = v != 0;
+            std::lock_guard<std::mutex> sl(stat_mu_);
             scan_ns_total_ = 0;
             scan_count_ = 0;
         }
@@ -1173,7 +1223,7 @@ namespace omplcu
 
     long NNIndex::get_stat(const char *key) const
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::lock_guard<std::mutex> lk(stat_mu_);
         if (!strcmp(key, "last_fallbacks"))
             return last_fallbacks_;
         if (!strcmp(key, "last_path"))
@@ -1223,6 +1273,8 @@ namespace omplcu
         {
             const size_t smem = scan_smem_bytes(D, RQ, L);
             static bool configured[64] = {};  // per device
+            static std::mutex configured_mu;
+            std::lock_guard<std::mutex> cl(configured_mu);
             int dev = 0;
             cudaGetDevice(&dev);
             if (!configured[dev & 63])
@@ -1350,7 +1402,7 @@ namespace omplcu
     }  // namespace
 
     // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
-    void NNIndex::knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+    void NNIndex::knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
                            double *d_dists, cudaStream_t s)
     {
         const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
@@ -1372,11 +1424,11 @@ namespace omplcu
         }
         const bool tc_auto = nq >= TC_MIN_BATCH;  // measured faster than the FP32 scans at every batched size
         const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
-        last_tc_ = tc ? 1 : 0;
-        last_thr_ = 0;
+        c.last_tc_ = tc ? 1 : 0;
+        c.last_thr_ = 0;
         if (tc && (thr_mode_ == 1 || (thr_mode_ < 0 && nslots_ >= THR_MIN_SLOTS)) && nslots_ >= 4096)
         {
-            knn_fast_thr(d_q, nq, kk, kstride, d_ids, d_dists, s);
+            knn_fast_thr(c, d_q, nq, kk, kstride, d_ids, d_dists, s);
             return;
         }
         const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));
@@ -1413,25 +1465,25 @@ namespace omplcu
         if ((size_t)smax * L > 512)
             throw Error(OMPLCU_ERR_INTERNAL, "scan: too many segments per query tile");
 
-        qp_.reserve((size_t)D_ * qpad);
-        qaux_.reserve(2 * (size_t)qpad);
-        cand_vals_.reserve((size_t)smax * qpad);
-        cand_ids_.reserve((size_t)smax * L * qpad);
-        ovf_list_.reserve(nq);
+        c.qp_.reserve((size_t)D_ * qpad);
+        c.qaux_.reserve(2 * (size_t)qpad);
+        c.cand_vals_.reserve((size_t)smax * qpad);
+        c.cand_ids_.reserve((size_t)smax * L * qpad);
+        c.ovf_list_.reserve(nq);
 
-        CUDA_CHECK(cudaMemsetAsync(cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
-        CUDA_CHECK(cudaMemsetAsync(cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
-        CUDA_CHECK(cudaMemsetAsync(counters_.p, 0, sizeof(unsigned), s));
-        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, qp_.p, qaux_.p, qpad);
+        CUDA_CHECK(cudaMemsetAsync(c.cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
+        CUDA_CHECK(cudaMemsetAsync(c.counters_.p, 0, sizeof(unsigned), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
         launches_++;
 
         ScanParams P;
         P.filt = filt_.p;
-        P.qp = qp_.p;
+        P.qp = c.qp_.p;
         P.qpad = qpad;
         P.init_thr = nullptr;
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev0_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev0_, s));
         // Starting bounds (knn_scan.cuh): a strided sample of the points gives every query a
         // value T with at least L sample points below it; the full pass starts its lists at T
         // and skips most of the early insertions.  Self-verifying: the re-rank's band check
@@ -1440,38 +1492,44 @@ namespace omplcu
         if (sample_thr_ && !hd && !tc && nslots_ >= 16 * (size_t)nsample && L <= 64)
         {
             const int rw = rowf_ / 4;
-            sample_thr_buf_.reserve(qpad + (size_t)nsample * rowf_);
-            float4 *rows = reinterpret_cast<float4 *>(sample_thr_buf_.p + qpad);  // qpad is a multiple of 256
+            c.sample_thr_buf_.reserve(qpad + (size_t)nsample * rowf_);
+            float4 *rows = reinterpret_cast<float4 *>(c.sample_thr_buf_.p + qpad);  // qpad is a multiple of 256
             const uint32_t step = (uint32_t)(nslots_ / nsample);
             sample_gather_kernel<<<nblk((size_t)nsample * rw, 256), 256, 0, s>>>(
                 reinterpret_cast<const float4 *>(filt_.p), rw, step, nsample, rows);
-            launch_thr_sample(D_, rows, nsample, qp_.p, qpad, (uint32_t)L, sample_thr_buf_.p, s);
+            launch_thr_sample(D_, rows, nsample, c.qp_.p, qpad, (uint32_t)L, c.sample_thr_buf_.p, s);
             CUDA_CHECK(cudaGetLastError());
             launches_ += 2;
-            P.init_thr = sample_thr_buf_.p;
+            P.init_thr = c.sample_thr_buf_.p;
         }
-        P.cand_thr = cand_vals_.p;
-        P.cand_ids = cand_ids_.p;
+        P.cand_thr = c.cand_vals_.p;
+        P.cand_ids = c.cand_ids_.p;
         P.units = U;
         P.total_units = TU;
         P.smax = smax;
         if (tc)
         {
-            if (tc_version_ != mut_version_)
             {
-                tc_pimg_.reserve((size_t)U * tc_sh.nkc * tc_sh.chunk_elems());
-                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
-                tc_version_ = mut_version_;
-                launches_++;
+                // shared operand image: rebuilt by the first query after a mutation, finished before any
+                // other query (on another stream) may read it
+                std::lock_guard<std::mutex> pl(prep_mu_);
+                if (tc_version_ != mut_version_)
+                {
+                    tc_pimg_.reserve((size_t)U * tc_sh.nkc * tc_sh.chunk_elems());
+                    tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+                    CUDA_CHECK(cudaStreamSynchronize(s));
+                    tc_version_ = mut_version_;
+                    launches_++;
+                }
             }
-            tc_qimg_.reserve((size_t)(qpad / TC_QT) * tc_sh.nkc * tc_sh.chunk_elems());
-            tc_build_query_image(qp_.p, qpad, D_, tc_qimg_.p, s);
+            c.tc_qimg_.reserve((size_t)(qpad / TC_QT) * tc_sh.nkc * tc_sh.chunk_elems());
+            tc_build_query_image(c.qp_.p, qpad, D_, c.tc_qimg_.p, s);
             launches_++;
             TcScanParams T{};
             T.pimg = tc_pimg_.p;
-            T.qimg = tc_qimg_.p;
-            T.cand_thr = cand_vals_.p;
-            T.cand_ids = cand_ids_.p;
+            T.qimg = c.tc_qimg_.p;
+            T.cand_thr = c.cand_vals_.p;
+            T.cand_ids = c.cand_ids_.p;
             T.units = U;
             T.total_units = TU;
             T.qpad = qpad;
@@ -1489,29 +1547,27 @@ namespace omplcu
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev1_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev1_, s));
 
-        knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(cand_vals_.p, cand_ids_.p, smax, (uint32_t)L, qpad,
-                                                          pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
+        knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad,
+                                                          pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p, nq,
                                                           (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists,
-                                                          ovf_list_.p, counters_.p,
+                                                          c.ovf_list_.p, c.counters_.p,
                                                           tc ? tc_err_units(D_) : (double)(D_ + 3));
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         unsigned novf = 0;
-        CUDA_CHECK(cudaMemcpyAsync(&novf, counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(&novf, c.counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        last_fallbacks_ = novf;
+        c.last_fallbacks_ = novf;
         if (profile_)
         {
             float ms = 0.f;
-            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev1_));
-            last_scan_ns_ = (long)(ms * 1e6);
-            scan_ns_total_ += last_scan_ns_;
-            scan_count_++;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev0_, c.ev1_));
+            c.last_scan_ns_ = (long)(ms * 1e6);
         }
         if (novf)
-            knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
+            knn_exact(c, d_q, c.ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }
 
     namespace
@@ -1549,7 +1605,7 @@ namespace omplcu
     //      against tau; unprovable queries (row overflow, fewer than k kept, band) go to the exact path
     // Nothing here converges, so the cost per (query, segment) is the appends, not a list warm-up:
     // the time is linear in the points a rank owns, which is what makes a sharded roadmap scale.
-    void NNIndex::knn_fast_thr(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+    void NNIndex::knn_fast_thr(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
                                double *d_dists, cudaStream_t s)
     {
         TcShape sh = tc_shape(D_);
@@ -1600,54 +1656,62 @@ namespace omplcu
         constexpr int MAXC = 1024;
         uint32_t cap = (uint32_t)(mean + 6.0 * sd) + 64;
         cap = std::min<uint32_t>(MAXC, ((cap + 31) / 32) * 32);
-        last_rank_ = r;
+        c.last_rank_ = r;
 
-        qp_.reserve((size_t)D_ * qpad);
-        qaux_.reserve(2 * (size_t)qpad);
-        cand_vals_.reserve((size_t)smax_s * qpad);
-        cand_ids_.reserve((size_t)smax_s * Ls * qpad);
-        list_vals_.reserve((size_t)smax_s * Ls * qpad);
-        tau_.reserve(qpad);
-        app_cnt_.reserve((size_t)smax * qpad);
-        app_ids_.reserve((size_t)smax * qpad * cap);
-        ovf_list_.reserve(nq);
-        CUDA_CHECK(cudaMemsetAsync(list_vals_.p, 0x7F, (size_t)smax_s * Ls * qpad * sizeof(float), s));  // "empty"
-        CUDA_CHECK(cudaMemsetAsync(app_cnt_.p, 0, (size_t)smax * qpad * sizeof(uint32_t), s));
-        CUDA_CHECK(cudaMemsetAsync(counters_.p, 0, sizeof(unsigned), s));
-        CUDA_CHECK(cudaMemsetAsync(kept_.p, 0, sizeof(unsigned long long), s));
-        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, qp_.p, qaux_.p, qpad);
+        c.qp_.reserve((size_t)D_ * qpad);
+        c.qaux_.reserve(2 * (size_t)qpad);
+        c.cand_vals_.reserve((size_t)smax_s * qpad);
+        c.cand_ids_.reserve((size_t)smax_s * Ls * qpad);
+        c.list_vals_.reserve((size_t)smax_s * Ls * qpad);
+        c.tau_.reserve(qpad);
+        c.app_cnt_.reserve((size_t)smax * qpad);
+        c.app_ids_.reserve((size_t)smax * qpad * cap);
+        c.ovf_list_.reserve(nq);
+        CUDA_CHECK(cudaMemsetAsync(c.list_vals_.p, 0x7F, (size_t)smax_s * Ls * qpad * sizeof(float), s));  // "empty"
+        CUDA_CHECK(cudaMemsetAsync(c.app_cnt_.p, 0, (size_t)smax * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(c.counters_.p, 0, sizeof(unsigned), s));
+        CUDA_CHECK(cudaMemsetAsync(c.kept_.p, 0, sizeof(unsigned long long), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
         launches_++;
-        if (tc_version_ != mut_version_)
         {
-            tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
-            tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+            std::lock_guard<std::mutex> pl(prep_mu_);  // shared images, see knn_fast
+            bool built = false;
+            if (tc_version_ != mut_version_)
+            {
+                tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
+                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+                built = true;
+                launches_++;
+            }
+            if (tc_sversion_ != mut_version_ || tc_sstep_ != step)
+            {
+                tc_simg_.reserve((size_t)Us * sh.nkc * sh.chunk_elems());
+                tc_build_sample_image(filt_.p, rowf_, D_, nslots_, step, (size_t)Us, tc_simg_.p, s);
+                built = true;
+                launches_++;
+            }
+            if (built)
+                CUDA_CHECK(cudaStreamSynchronize(s));
             tc_version_ = mut_version_;
-            launches_++;
-        }
-        if (tc_sversion_ != mut_version_ || tc_sstep_ != step)
-        {
-            tc_simg_.reserve((size_t)Us * sh.nkc * sh.chunk_elems());
-            tc_build_sample_image(filt_.p, rowf_, D_, nslots_, step, (size_t)Us, tc_simg_.p, s);
             tc_sversion_ = mut_version_;
             tc_sstep_ = step;
-            launches_++;
         }
-        tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
-        tc_build_query_image(qp_.p, qpad, D_, tc_qimg_.p, s);
+        c.tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
+        tc_build_query_image(c.qp_.p, qpad, D_, c.tc_qimg_.p, s);
         launches_++;
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev0_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev0_, s));
         TcScanParams T{};
-        T.qimg = tc_qimg_.p;
+        T.qimg = c.tc_qimg_.p;
         T.qpad = qpad;
         T.sh = sh;
         T.diag = tc_variant_;
         T.dbg = nullptr;
         // 1. sample lists
         T.pimg = tc_simg_.p;
-        T.cand_thr = cand_vals_.p;
-        T.cand_ids = cand_ids_.p;
-        T.list_vals = list_vals_.p;
+        T.cand_thr = c.cand_vals_.p;
+        T.cand_ids = c.cand_ids_.p;
+        T.list_vals = c.list_vals_.p;
         T.units = Us;
         T.total_units = TUs;
         T.smax = smax_s;
@@ -1658,17 +1722,17 @@ namespace omplcu
         T.sh = sh;
         // 2. bounds
         if ((size_t)smax_s * Ls > 64)
-            tau_select_kernel<32><<<nblk((size_t)qpad * 32, 128), 128, 0, s>>>(list_vals_.p, smax_s * Ls, qpad, r, tau_.p);
+            tau_select_kernel<32><<<nblk((size_t)qpad * 32, 128), 128, 0, s>>>(c.list_vals_.p, smax_s * Ls, qpad, r, c.tau_.p);
         else
-            tau_select_kernel<1><<<nblk(qpad, 128), 128, 0, s>>>(list_vals_.p, smax_s * Ls, qpad, r, tau_.p);
+            tau_select_kernel<1><<<nblk(qpad, 128), 128, 0, s>>>(c.list_vals_.p, smax_s * Ls, qpad, r, c.tau_.p);
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev2_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev2_, s));
         // 3. threshold scan
         T.pimg = tc_pimg_.p;
         T.list_vals = nullptr;
-        T.tau = tau_.p;
-        T.app_ids = app_ids_.p;
-        T.app_cnt = app_cnt_.p;
+        T.tau = c.tau_.p;
+        T.app_ids = c.app_ids_.p;
+        T.app_cnt = c.app_cnt_.p;
         T.cap = cap;
         T.units = U;
         T.total_units = TU;
@@ -1680,7 +1744,7 @@ namespace omplcu
         launches_ += 3;
         CUDA_CHECK(cudaGetLastError());
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev1_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev1_, s));
         // 4. exact epilogue
         const size_t rr_smem = (size_t)48 * MAXC + 4096;
         static std::once_flag rr_once[64];
@@ -1689,35 +1753,33 @@ namespace omplcu
                                             (int)rr_smem));
         });
         knn_rerank_thr_kernel<MAXC><<<nblk(nq, 4), 128, rr_smem, s>>>(
-            app_ids_.p, app_cnt_.p, smax, cap, qpad, tau_.p, pts64_.p, ids_.p, D_, d_q, qaux_.p, pmax2_.p, nq,
-            (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, ovf_list_.p, counters_.p, tc_err_units(D_),
-            profile_ ? kept_.p : nullptr);
+            c.app_ids_.p, c.app_cnt_.p, smax, cap, qpad, c.tau_.p, pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p, nq,
+            (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, tc_err_units(D_),
+            profile_ ? c.kept_.p : nullptr);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         if (profile_)
-            CUDA_CHECK(cudaEventRecord(ev3_, s));
+            CUDA_CHECK(cudaEventRecord(c.ev3_, s));
         unsigned novf = 0;
-        CUDA_CHECK(cudaMemcpyAsync(&novf, counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(&novf, c.counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        last_fallbacks_ = novf;
-        last_thr_ = 1;
+        c.last_fallbacks_ = novf;
+        c.last_thr_ = 1;
         if (profile_)
         {
             float ms = 0.f;
-            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev1_));
-            last_scan_ns_ = (long)(ms * 1e6);
-            scan_ns_total_ += last_scan_ns_;
-            scan_count_++;
-            CUDA_CHECK(cudaEventElapsedTime(&ms, ev0_, ev2_));
-            last_sample_ns_ = (long)(ms * 1e6);
-            CUDA_CHECK(cudaEventElapsedTime(&ms, ev2_, ev1_));
-            last_main_ns_ = (long)(ms * 1e6);
+            CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev0_, c.ev1_));
+            c.last_scan_ns_ = (long)(ms * 1e6);
+            CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev0_, c.ev2_));
+            c.last_sample_ns_ = (long)(ms * 1e6);
+            CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev2_, c.ev1_));
+            c.last_main_ns_ = (long)(ms * 1e6);
             unsigned long long kept = 0;
-            CUDA_CHECK(cudaMemcpy(&kept, kept_.p, sizeof(kept), cudaMemcpyDeviceToHost));
-            last_kept_ = (long)kept;
+            CUDA_CHECK(cudaMemcpy(&kept, c.kept_.p, sizeof(kept), cudaMemcpyDeviceToHost));
+            c.last_kept_ = (long)kept;
         }
         if (novf)
-            knn_exact(d_q, ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
+            knn_exact(c, d_q, c.ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }
 
     // Large index (>= 32K slots), any k and any metric (FMT*'s k ~ 2100 of 100K; SE3 / chain kNN): sorting
@@ -1728,28 +1790,32 @@ namespace omplcu
     // or more than `cap` slots goes to the full sort.  Returns false if the sample cannot help.
     // Chain metric only: bring the per-slot trig table up to date and tabulate the queries.
     // Returns true if the exact-path kernels should use the tables.
-    bool NNIndex::prepare_chain_tables(const double *d_q, size_t nq, cudaStream_t s)
+    bool NNIndex::prepare_chain_tables(QCtx &c, const double *d_q, size_t nq, cudaStream_t s)
     {
         if (sp_.compound || sp_.ncomp != 1 || sp_.comp[0].type != OMPLCU_CHAIN)
             return false;
         const int d = sp_.comp[0].dim;
-        trig_.reserve(std::max<size_t>(nslots_, 1) * 2 * d, true, s);
-        if (trig_rows_ < nslots_)
         {
-            chain_trig_kernel<<<nblk(nslots_ - trig_rows_, 128), 128, 0, s>>>(pts64_.p + trig_rows_ * d,
-                                                                               nslots_ - trig_rows_, d,
-                                                                               trig_.p + trig_rows_ * 2 * d);
-            trig_rows_ = nslots_;
-            launches_++;
+            std::lock_guard<std::mutex> pl(prep_mu_);  // the per-slot table is shared between concurrent queries
+            trig_.reserve(std::max<size_t>(nslots_, 1) * 2 * d, true, s);
+            if (trig_rows_ < nslots_)
+            {
+                chain_trig_kernel<<<nblk(nslots_ - trig_rows_, 128), 128, 0, s>>>(pts64_.p + trig_rows_ * d,
+                                                                                   nslots_ - trig_rows_, d,
+                                                                                   trig_.p + trig_rows_ * 2 * d);
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                trig_rows_ = nslots_;
+                launches_++;
+            }
         }
-        qtrig_.reserve(std::max<size_t>(nq, 1) * 2 * d);
-        chain_trig_kernel<<<nblk(nq, 128), 128, 0, s>>>(d_q, nq, d, qtrig_.p);
+        c.qtrig_.reserve(std::max<size_t>(nq, 1) * 2 * d);
+        chain_trig_kernel<<<nblk(nq, 128), 128, 0, s>>>(d_q, nq, d, c.qtrig_.p);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         return true;
     }
 
-    bool NNIndex::knn_exact_collect(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+    bool NNIndex::knn_exact_collect(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                                     uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         const uint32_t m = 1024;
@@ -1765,118 +1831,118 @@ namespace omplcu
             return false;
         const size_t budget = (size_t)1 << 26;
         const size_t nb_max = std::max<size_t>(1, std::min(nsel, budget / cap));
-        ex_keys_.reserve(nb_max * cap);
-        ex_keys2_.reserve(nb_max * cap);
-        ex_vals_.reserve(nb_max * cap);
-        ex_vals2_.reserve(nb_max * cap);
-        ex_offs_.reserve(2 * nb_max + 2);
-        col_sd_.reserve(nb_max * m);
-        col_bound_.reserve(nb_max);
-        col_cnt_.reserve(nb_max);
-        col_redo_.reserve(nsel);
-        CUDA_CHECK(cudaMemsetAsync(counters_.p + 1, 0, sizeof(unsigned), s));
-        const bool tables = prepare_chain_tables(d_q, exact_nq_, s);
-        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
-        int *beg = ex_offs_.p, *end = ex_offs_.p + nb_max + 1;
+        c.ex_keys_.reserve(nb_max * cap);
+        c.ex_keys2_.reserve(nb_max * cap);
+        c.ex_vals_.reserve(nb_max * cap);
+        c.ex_vals2_.reserve(nb_max * cap);
+        c.ex_offs_.reserve(2 * nb_max + 2);
+        c.col_sd_.reserve(nb_max * m);
+        c.col_bound_.reserve(nb_max);
+        c.col_cnt_.reserve(nb_max);
+        c.col_redo_.reserve(nsel);
+        CUDA_CHECK(cudaMemsetAsync(c.counters_.p + 1, 0, sizeof(unsigned), s));
+        const bool tables = prepare_chain_tables(c, d_q, c.exact_nq_, s);
+        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
+        int *beg = c.ex_offs_.p, *end = c.ex_offs_.p + nb_max + 1;
         for (size_t b0 = 0; b0 < nsel; b0 += nb_max)
         {
             const size_t nb = std::min(nb_max, nsel - b0);
             const size_t items = nb * cap;
             REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
-            CUDA_CHECK(cudaMemsetAsync(col_cnt_.p, 0, nb * sizeof(uint32_t), s));
-            sample_dist_kernel<<<nblk(nb * m, 256), 256, 0, s>>>(pm, alive_.p, step, m, d_sel, b0, nb, col_sd_.p);
-            rank_select_kernel<<<nblk(nb, 4), 128, 0, s>>>(col_sd_.p, m, nb, R, col_bound_.p);
-            collect_kernel<<<nblk(nb * nslots_, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, col_bound_.p,
-                                                                   cap, ex_keys_.p, ex_vals_.p, col_cnt_.p);
-            collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(col_cnt_.p, cap, nb, beg, end);
+            CUDA_CHECK(cudaMemsetAsync(c.col_cnt_.p, 0, nb * sizeof(uint32_t), s));
+            sample_dist_kernel<<<nblk(nb * m, 256), 256, 0, s>>>(pm, alive_.p, step, m, d_sel, b0, nb, c.col_sd_.p);
+            rank_select_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.col_sd_.p, m, nb, R, c.col_bound_.p);
+            collect_kernel<<<nblk(nb * nslots_, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, c.col_bound_.p,
+                                                                   cap, c.ex_keys_.p, c.ex_vals_.p, c.col_cnt_.p);
+            collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(c.col_cnt_.p, cap, nb, beg, end);
             CUDA_CHECK(cudaGetLastError());
             size_t tmp = 0, tmp2 = 0;
             // pass 1: by slot (payload: distance); pass 2: stable by distance (payload: slot)
-            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_vals_.p, ex_vals2_.p, ex_keys_.p,
-                                                                ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
-            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, ex_keys2_.p, ex_keys_.p, ex_vals2_.p,
-                                                                ex_vals_.p, (int)items, (int)nb, beg, end, 0, 64, s));
-            cub_tmp_.reserve(std::max(tmp, tmp2));
-            tmp = tmp2 = cub_tmp_.cap;
-            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_vals_.p, ex_vals2_.p, ex_keys_.p,
-                                                                ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
-            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp2, ex_keys2_.p, ex_keys_.p,
-                                                                ex_vals2_.p, ex_vals_.p, (int)items, (int)nb, beg, end,
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, c.ex_vals_.p, c.ex_vals2_.p, c.ex_keys_.p,
+                                                                c.ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, c.ex_keys2_.p, c.ex_keys_.p, c.ex_vals2_.p,
+                                                                c.ex_vals_.p, (int)items, (int)nb, beg, end, 0, 64, s));
+            c.cub_tmp_.reserve(std::max(tmp, tmp2));
+            tmp = tmp2 = c.cub_tmp_.cap;
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp, c.ex_vals_.p, c.ex_vals2_.p, c.ex_keys_.p,
+                                                                c.ex_keys2_.p, (int)items, (int)nb, beg, end, 0, 32, s));
+            CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp2, c.ex_keys2_.p, c.ex_keys_.p,
+                                                                c.ex_vals2_.p, c.ex_vals_.p, (int)items, (int)nb, beg, end,
                                                                 0, 64, s));
-            collect_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(ex_keys_.p, ex_vals_.p, col_cnt_.p, cap, ids_.p,
+            collect_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(c.ex_keys_.p, c.ex_vals_.p, c.col_cnt_.p, cap, ids_.p,
                                                                    d_sel, b0, nb, (uint32_t)kk, (uint32_t)kstride,
-                                                                   d_ids, d_dists, col_redo_.p, counters_.p + 1);
+                                                                   d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1);
             CUDA_CHECK(cudaGetLastError());
             launches_ += 16;
         }
         unsigned nredo = 0;
-        CUDA_CHECK(cudaMemcpyAsync(&nredo, counters_.p + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaMemcpyAsync(&nredo, c.counters_.p + 1, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        last_collect_redo_ = nredo;
+        c.last_collect_redo_ = nredo;
         if (nredo)
-            knn_exact_sort(d_q, col_redo_.p, nredo, kk, kstride, d_ids, d_dists, s);
+            knn_exact_sort(c, d_q, c.col_redo_.p, nredo, kk, kstride, d_ids, d_dists, s);
         return true;
     }
 
-    void NNIndex::knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+    void NNIndex::knn_exact(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                             uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         if (nsel == 0 || nslots_ == 0)
             return;
-        if (knn_exact_collect(d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s))
+        if (knn_exact_collect(c, d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s))
             return;
-        knn_exact_sort(d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s);
+        knn_exact_sort(c, d_q, d_sel, nsel, kk, kstride, d_ids, d_dists, s);
     }
 
-    void NNIndex::knn_exact_sort(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+    void NNIndex::knn_exact_sort(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                                  uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         if (nsel == 0 || nslots_ == 0)
             return;
         REQUIRE(nslots_ < ((size_t)1 << 31), "exact path: too many slots");
         size_t nb_max = std::max<size_t>(1, std::min(nsel, EXACT_PAIR_BUDGET / nslots_));
-        ex_keys_.reserve(nb_max * nslots_);
-        ex_keys2_.reserve(nb_max * nslots_);
-        ex_vals_.reserve(nb_max * nslots_);
-        ex_vals2_.reserve(nb_max * nslots_);
-        ex_offs_.reserve(nb_max + 1);
+        c.ex_keys_.reserve(nb_max * nslots_);
+        c.ex_keys2_.reserve(nb_max * nslots_);
+        c.ex_vals_.reserve(nb_max * nslots_);
+        c.ex_vals2_.reserve(nb_max * nslots_);
+        c.ex_offs_.reserve(nb_max + 1);
         std::vector<int> offs(nb_max + 1);
         for (size_t b = 0; b <= nb_max; ++b)
             offs[b] = (int)(b * nslots_);
-        CUDA_CHECK(cudaMemcpyAsync(ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+        CUDA_CHECK(cudaMemcpyAsync(c.ex_offs_.p, offs.data(), (nb_max + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
-        const bool tables = prepare_chain_tables(d_q, exact_nq_, s);
-        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
+        const bool tables = prepare_chain_tables(c, d_q, c.exact_nq_, s);
+        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
         for (size_t b0 = 0; b0 < nsel; b0 += nb_max)
         {
             const size_t nb = std::min(nb_max, nsel - b0);
             const size_t items = nb * nslots_;
             REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
-            dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, ex_keys_.p,
-                                                              ex_vals_.p);
+            dist_rows_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, c.ex_keys_.p,
+                                                              c.ex_vals_.p);
             launches_++;
             CUDA_CHECK(cudaGetLastError());
             size_t tmp = 0;
             if (nb == 1)
             {
-                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
-                                                           ex_vals2_.p, (int)items, 0, 64, s));
-                cub_tmp_.reserve(tmp);
-                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
-                                                           ex_vals2_.p, (int)items, 0, 64, s));
+                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, c.ex_keys_.p, c.ex_keys2_.p, c.ex_vals_.p,
+                                                           c.ex_vals2_.p, (int)items, 0, 64, s));
+                c.cub_tmp_.reserve(tmp);
+                CUDA_CHECK(cub::DeviceRadixSort::SortPairs(c.cub_tmp_.p, tmp, c.ex_keys_.p, c.ex_keys2_.p, c.ex_vals_.p,
+                                                           c.ex_vals2_.p, (int)items, 0, 64, s));
             }
             else
             {
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_keys_.p, ex_keys2_.p, ex_vals_.p,
-                                                                    ex_vals2_.p, (int)items, (int)nb, ex_offs_.p,
-                                                                    ex_offs_.p + 1, 0, 64, s));
-                cub_tmp_.reserve(tmp);
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_keys_.p, ex_keys2_.p,
-                                                                    ex_vals_.p, ex_vals2_.p, (int)items, (int)nb,
-                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, c.ex_keys_.p, c.ex_keys2_.p, c.ex_vals_.p,
+                                                                    c.ex_vals2_.p, (int)items, (int)nb, c.ex_offs_.p,
+                                                                    c.ex_offs_.p + 1, 0, 64, s));
+                c.cub_tmp_.reserve(tmp);
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp, c.ex_keys_.p, c.ex_keys2_.p,
+                                                                    c.ex_vals_.p, c.ex_vals2_.p, (int)items, (int)nb,
+                                                                    c.ex_offs_.p, c.ex_offs_.p + 1, 0, 64, s));
             }
             launches_ += 8;
-            exact_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(ex_keys2_.p, ex_vals2_.p, nslots_, ids_.p, d_sel, b0,
+            exact_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(c.ex_keys2_.p, c.ex_vals2_.p, nslots_, ids_.p, d_sel, b0,
                                                                  nb, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists);
             launches_++;
             CUDA_CHECK(cudaGetLastError());
@@ -1887,26 +1953,36 @@ namespace omplcu
     void NNIndex::knn_device(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
                              cudaStream_t s)
     {
-        std::lock_guard<std::mutex> lk(mu_);
+        std::shared_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
+        Lease L(*this);
+        knn_locked(*L.c, d_q, nq, k, d_ids, d_dists, s);
+        publish(*L.c);
+    }
+
+    // rw_ is held (shared) by the caller; `c` is the caller's leased context
+    void NNIndex::knn_locked(QCtx &c, const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                             cudaStream_t s)
+    {
         if (nq == 0 || k == 0)
             return;
         REQUIRE(d_q && d_ids, "omplcu_nn_knn: NULL buffer");
         REQUIRE(k < ((size_t)1 << 31), "omplcu_nn_knn: k too large");
         const size_t kk = std::min(k, nlive_);
-        last_fallbacks_ = 0;
-        exact_nq_ = nq;
+        c.last_fallbacks_ = 0;
+        c.last_path_ = 0;
+        c.exact_nq_ = nq;
         if (kk > 0)
         {
             if (fast_eligible(kk))
             {
-                last_path_ = 1;
-                knn_fast(d_q, nq, kk, k, d_ids, d_dists, s);
+                c.last_path_ = 1;
+                knn_fast(c, d_q, nq, kk, k, d_ids, d_dists, s);
             }
             else
             {
-                last_path_ = 2;
-                knn_exact(d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
+                c.last_path_ = 2;
+                knn_exact(c, d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
             }
         }
         if (kk < k)
@@ -1918,6 +1994,9 @@ namespace omplcu
         CUDA_CHECK(cudaStreamSynchronize(s));
     }
 
+    // Host pointers in, host pointers out.  One shared lock spans staging, query and copy-out, so the
+    // count reported (min(k, size)) is the one the query used; staging lives in the leased context, so
+    // host threads do not serialise on it.
     void NNIndex::knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts)
     {
         if (nq == 0)
@@ -1926,26 +2005,25 @@ namespace omplcu
         const size_t st = (size_t)sp_.stride;
         size_t kk;
         {
+            std::shared_lock<std::shared_mutex> lk(rw_);
             DeviceGuard g(device_);
-            // staging buffers are per-handle: serialise host-pointer calls
-            std::lock_guard<std::mutex> hl(host_mu_);
-            {
-                std::lock_guard<std::mutex> lk(mu_);
-                q_stage_.reserve(nq * st);
-                out_i_.reserve(nq * std::max<size_t>(k, 1));
-                out_d_.reserve(nq * std::max<size_t>(k, 1));
-                kk = std::min(k, nlive_);
-            }
-            CUDA_CHECK(cudaMemcpyAsync(q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, stream_));
+            Lease L(*this);
+            QCtx &c = *L.c;
+            c.q_stage_.reserve(nq * st);
+            c.out_i_.reserve(nq * std::max<size_t>(k, 1));
+            c.out_d_.reserve(nq * std::max<size_t>(k, 1));
+            kk = std::min(k, nlive_);
+            CUDA_CHECK(cudaMemcpyAsync(c.q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, c.stream));
             if (k > 0)
             {
-                knn_device(q_stage_.p, nq, k, out_i_.p, out_d_.p, stream_);
-                CUDA_CHECK(cudaMemcpyAsync(ids, out_i_.p, nq * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream_));
+                knn_locked(c, c.q_stage_.p, nq, k, c.out_i_.p, c.out_d_.p, c.stream);
+                CUDA_CHECK(cudaMemcpyAsync(ids, c.out_i_.p, nq * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
                 if (dists)
                     CUDA_CHECK(
-                        cudaMemcpyAsync(dists, out_d_.p, nq * k * sizeof(double), cudaMemcpyDeviceToHost, stream_));
+                        cudaMemcpyAsync(dists, c.out_d_.p, nq * k * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
             }
-            CUDA_CHECK(cudaStreamSynchronize(stream_));
+            CUDA_CHECK(cudaStreamSynchronize(c.stream));
+            publish(c);
         }
         if (counts)
             for (size_t i = 0; i < nq; ++i)
@@ -1967,35 +2045,37 @@ namespace omplcu
         if (nq == 0)
             return;
         REQUIRE(q && radii, "omplcu_nn_radius: NULL buffer");
-        std::lock_guard<std::mutex> lk(mu_);
+        std::shared_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
-        cudaStream_t s = stream_;
+        Lease L(*this);
+        QCtx &c = *L.c;
+        cudaStream_t s = c.stream;
         const size_t st = (size_t)sp_.stride;
-        size_t total = 0;  // neighbours found so far (all batches), kept on the device in rad_ids_/rad_d_
+        size_t total = 0;  // neighbours found so far (all batches), kept on the device in c.rad_ids_/c.rad_d_
         if (nslots_ > 0 && nlive_ > 0)
         {
             REQUIRE(nslots_ < ((size_t)1 << 31), "radius: too many slots");
-            q_stage_.reserve(nq * st);
-            rad_r_.reserve(nq);
-            CUDA_CHECK(cudaMemcpyAsync(q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, s));
-            CUDA_CHECK(cudaMemcpyAsync(rad_r_.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
+            c.q_stage_.reserve(nq * st);
+            c.rad_r_.reserve(nq);
+            CUDA_CHECK(cudaMemcpyAsync(c.q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, s));
+            CUDA_CHECK(cudaMemcpyAsync(c.rad_r_.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
             const size_t nb_max = std::max<size_t>(1, std::min(nq, RADIUS_PAIR_BUDGET / nslots_));
-            ex_keys_.reserve(nb_max * nslots_);
-            col_cnt_.reserve(2 * nb_max);
-            rad_off_.reserve(nb_max);
-            ex_offs_.reserve(nb_max + 1);
+            c.ex_keys_.reserve(nb_max * nslots_);
+            c.col_cnt_.reserve(2 * nb_max);
+            c.rad_off_.reserve(nb_max);
+            c.ex_offs_.reserve(nb_max + 1);
             std::vector<uint32_t> cnt(nb_max);
             std::vector<unsigned long long> boff(nb_max);
             std::vector<int> seg(nb_max + 1);
-            const bool tables = prepare_chain_tables(q_stage_.p, nq, s);
-            const PairMetric pm{sp_, pts64_.p, q_stage_.p, tables ? trig_.p : nullptr, tables ? qtrig_.p : nullptr};
+            const bool tables = prepare_chain_tables(c, c.q_stage_.p, nq, s);
+            const PairMetric pm{sp_, pts64_.p, c.q_stage_.p, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
             for (size_t b0 = 0; b0 < nq; b0 += nb_max)
             {
                 const size_t nb = std::min(nb_max, nq - b0);
                 const size_t items = nb * nslots_;
-                uint32_t *d_cnt = col_cnt_.p, *d_fill = col_cnt_.p + nb_max;
-                CUDA_CHECK(cudaMemsetAsync(col_cnt_.p, 0, 2 * nb_max * sizeof(uint32_t), s));
-                radius_dist_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, b0, nb, rad_r_.p, ex_keys_.p,
+                uint32_t *d_cnt = c.col_cnt_.p, *d_fill = c.col_cnt_.p + nb_max;
+                CUDA_CHECK(cudaMemsetAsync(c.col_cnt_.p, 0, 2 * nb_max * sizeof(uint32_t), s));
+                radius_dist_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, b0, nb, c.rad_r_.p, c.ex_keys_.p,
                                                                     d_cnt);
                 launches_++;
                 CUDA_CHECK(cudaGetLastError());
@@ -2013,35 +2093,35 @@ namespace omplcu
                 if (tot == 0)
                     continue;
                 REQUIRE(tot < ((unsigned long long)1 << 31), "radius: too many neighbours in one batch");
-                ex_keys2_.reserve(tot);
-                ex_keys3_.reserve(tot);
-                ex_vals_.reserve(tot);
-                ex_vals2_.reserve(tot);
-                rad_ids_.reserve(total + tot, true, s);
-                rad_d_.reserve(total + tot, true, s);
-                CUDA_CHECK(cudaMemcpyAsync(rad_off_.p, boff.data(), nb * sizeof(unsigned long long),
+                c.ex_keys2_.reserve(tot);
+                c.ex_keys3_.reserve(tot);
+                c.ex_vals_.reserve(tot);
+                c.ex_vals2_.reserve(tot);
+                c.rad_ids_.reserve(total + tot, true, s);
+                c.rad_d_.reserve(total + tot, true, s);
+                CUDA_CHECK(cudaMemcpyAsync(c.rad_off_.p, boff.data(), nb * sizeof(unsigned long long),
                                            cudaMemcpyHostToDevice, s));
-                CUDA_CHECK(cudaMemcpyAsync(ex_offs_.p, seg.data(), (nb + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
-                radius_compact_kernel<<<nblk(items, 256), 256, 0, s>>>(ex_keys_.p, nslots_, b0, nb, rad_r_.p, rad_off_.p,
-                                                                       d_fill, ex_keys2_.p, ex_vals_.p);
+                CUDA_CHECK(cudaMemcpyAsync(c.ex_offs_.p, seg.data(), (nb + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+                radius_compact_kernel<<<nblk(items, 256), 256, 0, s>>>(c.ex_keys_.p, nslots_, b0, nb, c.rad_r_.p, c.rad_off_.p,
+                                                                       d_fill, c.ex_keys2_.p, c.ex_vals_.p);
                 // by slot (payload distance), then stably by distance (payload slot)
                 size_t tmp = 0, tmp2 = 0;
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, ex_vals_.p, ex_vals2_.p, ex_keys2_.p,
-                                                                    ex_keys3_.p, (int)tot, (int)nb, ex_offs_.p,
-                                                                    ex_offs_.p + 1, 0, 32, s));
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, ex_keys3_.p, ex_keys2_.p,
-                                                                    ex_vals2_.p, ex_vals_.p, (int)tot, (int)nb,
-                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
-                cub_tmp_.reserve(std::max(tmp, tmp2));
-                tmp = tmp2 = cub_tmp_.cap;
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp, ex_vals_.p, ex_vals2_.p,
-                                                                    ex_keys2_.p, ex_keys3_.p, (int)tot, (int)nb,
-                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 32, s));
-                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(cub_tmp_.p, tmp2, ex_keys3_.p, ex_keys2_.p,
-                                                                    ex_vals2_.p, ex_vals_.p, (int)tot, (int)nb,
-                                                                    ex_offs_.p, ex_offs_.p + 1, 0, 64, s));
-                radius_emit_kernel<<<nblk(tot, 256), 256, 0, s>>>(ex_keys2_.p, ex_vals_.p, ids_.p, tot,
-                                                                  rad_ids_.p + total, rad_d_.p + total);
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp, c.ex_vals_.p, c.ex_vals2_.p, c.ex_keys2_.p,
+                                                                    c.ex_keys3_.p, (int)tot, (int)nb, c.ex_offs_.p,
+                                                                    c.ex_offs_.p + 1, 0, 32, s));
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, c.ex_keys3_.p, c.ex_keys2_.p,
+                                                                    c.ex_vals2_.p, c.ex_vals_.p, (int)tot, (int)nb,
+                                                                    c.ex_offs_.p, c.ex_offs_.p + 1, 0, 64, s));
+                c.cub_tmp_.reserve(std::max(tmp, tmp2));
+                tmp = tmp2 = c.cub_tmp_.cap;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp, c.ex_vals_.p, c.ex_vals2_.p,
+                                                                    c.ex_keys2_.p, c.ex_keys3_.p, (int)tot, (int)nb,
+                                                                    c.ex_offs_.p, c.ex_offs_.p + 1, 0, 32, s));
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp2, c.ex_keys3_.p, c.ex_keys2_.p,
+                                                                    c.ex_vals2_.p, c.ex_vals_.p, (int)tot, (int)nb,
+                                                                    c.ex_offs_.p, c.ex_offs_.p + 1, 0, 64, s));
+                radius_emit_kernel<<<nblk(tot, 256), 256, 0, s>>>(c.ex_keys2_.p, c.ex_vals_.p, ids_.p, tot,
+                                                                  c.rad_ids_.p + total, c.rad_d_.p + total);
                 launches_ += 18;
                 CUDA_CHECK(cudaGetLastError());
                 total += tot;
@@ -2059,9 +2139,9 @@ namespace omplcu
         }
         if (total)
         {
-            CUDA_CHECK(cudaMemcpyAsync(*ids, rad_ids_.p, total * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(*ids, c.rad_ids_.p, total * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
             if (dists)
-                CUDA_CHECK(cudaMemcpyAsync(*dists, rad_d_.p, total * sizeof(double), cudaMemcpyDeviceToHost, s));
+                CUDA_CHECK(cudaMemcpyAsync(*dists, c.rad_d_.p, total * sizeof(double), cudaMemcpyDeviceToHost, s));
         }
         CUDA_CHECK(cudaStreamSynchronize(s));
     }

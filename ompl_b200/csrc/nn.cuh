@@ -1,6 +1,9 @@
 // nn.cuh -- device-resident nearest-neighbour index (host-side class).
 #pragma once
+#include <atomic>
+#include <memory>
 #include <mutex>
+#include <shared_mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -89,27 +92,36 @@ namespace omplcu
         }
 
     private:
+        struct QCtx;
         void reserve_slots(size_t n);
         void compact();
         bool fast_eligible(size_t kk) const;
-        void knn_fast(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
+        void knn_locked(QCtx &c, const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                        cudaStream_t s);
+        void knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                       cudaStream_t s);
         // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
-        void knn_fast_thr(const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
+        void knn_fast_thr(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                           cudaStream_t s);
         // exact sort path over the selected queries (d_sel == nullptr: all nq)
-        bool prepare_chain_tables(const double *d_q, size_t nq, cudaStream_t s);
-        bool knn_exact_collect(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+        bool prepare_chain_tables(QCtx &c, const double *d_q, size_t nq, cudaStream_t s);
+        bool knn_exact_collect(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                                uint64_t *d_ids, double *d_dists, cudaStream_t s);
-        void knn_exact_sort(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+        void knn_exact_sort(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                             uint64_t *d_ids, double *d_dists, cudaStream_t s);
-        void knn_exact(const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
+        void knn_exact(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                        uint64_t *d_ids, double *d_dists, cudaStream_t s);
 
         int device_;
         SpaceDesc sp_;
-        cudaStream_t stream_ = nullptr;
-        mutable std::mutex mu_, host_mu_;
+        cudaStream_t stream_ = nullptr;  // mutations (add / remove / compact / clear)
+        // Concurrency (SURVEY 8(b) "Threading"; GNAT is what OMPL hands multithreaded planners because const
+        // queries run concurrently, tools/config/SelfConfig.h:112-113): queries hold rw_ shared and run on
+        // their own leased context (stream + scratch), mutations hold it exclusively.  prep_mu_ guards the
+        // operand images that queries rebuild lazily after a mutation; stat_mu_ the published statistics.
+        mutable std::shared_mutex rw_;
+        std::mutex prep_mu_;
+        mutable std::mutex stat_mu_, pool_mu_;
 
         size_t nslots_ = 0, nlive_ = 0;
         uint64_t id_base_ = 0, next_seq_ = 0;
@@ -120,7 +132,7 @@ namespace omplcu
         DevBuf<uint64_t> ids_;
         DevBuf<uint8_t> alive_;
 
-        // FP32 filter copy (plain RealVector spaces with dim <= 16)
+        // FP32 filter copy (plain RealVector spaces with dim <= 128)
         bool fast_space_ = false;
         int D_ = 0, rowf_ = 0;
         size_t filt_rows_ = 0;  // rows initialised (multiple of SCAN_PT)
@@ -129,53 +141,71 @@ namespace omplcu
         DevBuf<unsigned> pmax2_;  // bits of max fl32(|pt|^2)
         bool have_center_ = false;
 
-        // query scratch
-        DevBuf<double> q_stage_, out_d_;
-        DevBuf<uint64_t> out_i_;
-        DevBuf<float> qp_, cand_vals_, sample_thr_buf_;
-        DevBuf<double> qaux_;
-        DevBuf<uint32_t> cand_ids_, ovf_list_;
-        DevBuf<unsigned> counters_;
-        DevBuf<double> ex_keys_, ex_keys2_;
-        DevBuf<uint32_t> ex_vals_, ex_vals2_;
-        DevBuf<int> ex_offs_;
-        DevBuf<double> col_sd_, col_bound_, trig_, qtrig_, rad_r_, rad_d_, ex_keys3_;
-        DevBuf<uint64_t> rad_ids_;
-        DevBuf<unsigned long long> rad_off_;
-        size_t trig_rows_ = 0, exact_nq_ = 0;
-        DevBuf<uint32_t> col_cnt_, col_redo_;
-        bool collect_ = true;
-        long last_collect_redo_ = 0;
-        DevBuf<unsigned char> cub_tmp_;
+        // shared, rebuilt lazily by the first query after a mutation (under prep_mu_, then synchronised):
+        // BF16 split-operand images of the filter copy (knn_scan_tc.cuh), the strided sample image of the
+        // threshold path, the chain metric's per-slot trig table
+        DevBuf<uint16_t> tc_pimg_, tc_simg_;
+        unsigned long mut_version_ = 1, tc_version_ = 0, tc_sversion_ = 0;
+        size_t tc_sstep_ = 0;
+        DevBuf<double> trig_;
+        size_t trig_rows_ = 0;
 
-        // tensor-core scan (knn_scan_tc.cuh): BF16 split-operand images of the filter copy, rebuilt
-        // lazily when the point set changed since the last tensor-core query
-        DevBuf<uint16_t> tc_pimg_, tc_qimg_;
-        unsigned long mut_version_ = 1, tc_version_ = 0;
-        int tc_mode_ = -1;        // -1 auto (d >= 64 and >= 1024 queries), 0 off, 1 whenever eligible
+        // Everything one query in flight needs: a stream, its scratch, its statistics.
+        struct QCtx
+        {
+            cudaStream_t stream = nullptr;
+            cudaEvent_t ev0_ = nullptr, ev1_ = nullptr, ev2_ = nullptr, ev3_ = nullptr;
+            DevBuf<double> q_stage_, out_d_;
+            DevBuf<uint64_t> out_i_;
+            DevBuf<float> qp_, cand_vals_, sample_thr_buf_;
+            DevBuf<double> qaux_;
+            DevBuf<uint32_t> cand_ids_, ovf_list_;
+            DevBuf<unsigned> counters_;
+            DevBuf<double> ex_keys_, ex_keys2_;
+            DevBuf<uint32_t> ex_vals_, ex_vals2_;
+            DevBuf<int> ex_offs_;
+            DevBuf<double> col_sd_, col_bound_, qtrig_, rad_r_, rad_d_, ex_keys3_;
+            DevBuf<uint64_t> rad_ids_;
+            DevBuf<unsigned long long> rad_off_;
+            size_t exact_nq_ = 0;
+            DevBuf<uint32_t> col_cnt_, col_redo_;
+            DevBuf<unsigned char> cub_tmp_;
+            DevBuf<uint16_t> tc_qimg_;
+            DevBuf<float> tau_, list_vals_;
+            DevBuf<uint32_t> app_ids_, app_cnt_;
+            DevBuf<unsigned long long> kept_;
+            long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
+            long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
+        };
+        // leases a context for the duration of a query (creates one if all are busy)
+        struct Lease
+        {
+            NNIndex &ix;
+            QCtx *c;
+            explicit Lease(NNIndex &i);
+            ~Lease();
+        };
+        std::vector<std::unique_ptr<QCtx>> pool_;
+        std::vector<QCtx *> free_;
+        void publish(const QCtx &c);  // copy the query's statistics to the handle (last_* stats)
+
+        // options
+        bool collect_ = true;
+        int tc_mode_ = -1;        // -1 auto, 0 off, 1 whenever eligible
         int tc_na_ = 0;
         int tc_variant_ = 0;      // image layout / descriptor variants (diagnostics)
         float *tc_dbg_ = nullptr; // device buffer for raw scan values (diagnostics), caller-owned
-        long last_tc_ = 0;
-        // threshold path (knn_fast_thr): sample image, bounds, append rows
-        DevBuf<uint16_t> tc_simg_;
-        unsigned long tc_sversion_ = 0;
-        size_t tc_sstep_ = 0;
-        DevBuf<float> tau_, list_vals_;
-        DevBuf<uint32_t> app_ids_, app_cnt_;
-        DevBuf<unsigned long long> kept_;
         int thr_mode_ = 0;        // -1 auto (index of >= 32768 slots), 0 never, 1 whenever the tensor-core scan runs
         int thr_step_ = 16;       // sample stride
-        long last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
-        cudaEvent_t ev2_ = nullptr, ev3_ = nullptr;
-        long last_sample_ns_ = 0, last_main_ns_ = 0;
-
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
         bool force_exact_ = false, profile_ = false;
-        cudaEvent_t ev0_ = nullptr, ev1_ = nullptr;
-        long last_scan_ns_ = 0, scan_ns_total_ = 0, scan_count_ = 0;
-        long last_fallbacks_ = 0, last_path_ = 0, launches_ = 0;
+
+        // published statistics (stat_mu_)
+        long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
+        long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
+        long scan_ns_total_ = 0, scan_count_ = 0;
+        std::atomic<long> launches_{0};
     };
 
     // roadmap sharded over several GPUs of one process (sharded.cu)
