@@ -439,6 +439,98 @@ namespace omplcu
             }
         }
 
+        // ---- filter in front of the exact large-k / radius paths ----
+        // tau[q] = an upper bound on the scan value of ANY point within distance bound[q] of query q (the band
+        // formula of knn_rerank_kernel with Dk = bound), rounded up, one ulp added: the threshold scan keeps
+        // every slot with s < tau, hence every point within the bound.  Padded queries keep nothing.
+        __global__ void scan_bound_kernel(const double *bound, size_t nq, uint32_t qpad, const double *qaux,
+                                          const unsigned *pmax2_bits, int D, double err_units, float *tau)
+        {
+            const size_t qi = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (qi >= qpad)
+                return;
+            if (qi >= nq)
+            {
+                tau[qi] = -3.0e38f;
+                return;
+            }
+            const double u = 5.9604644775390625e-08;  // 2^-24
+            const double dk = bound[qi];
+            const double qn = qaux[2 * qi], qnorm = qaux[2 * qi + 1];
+            const double pmax2 = (double)__uint_as_float(*pmax2_bits) * (1.0 + 2.0 * u);
+            const double pmax = sqrt(pmax2) * (1.0 + 1e-9);
+            const double delta = (double)(D + 4) * 1.1102230246251565e-16;
+            const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
+            const double A = dk * (1.0 + delta) + rho + 1e-150;
+            const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+            const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
+            float t = 3.0e38f;  // no usable bound (NaN, infinite radius, overflow): keep everything
+            if (tau64 == tau64 && tau64 < 1e37 && dk >= 0.0)
+            {
+                t = __double2float_ru(tau64);
+                t = __uint_as_float(t >= 0.f ? __float_as_uint(t) + 1u : (__float_as_uint(t) == 0x80000000u ? 1u : __float_as_uint(t) - 1u));
+            }
+            tau[qi] = t;
+        }
+
+        // One warp per query: the slots the threshold scan kept (rows in segment order, each in scan order,
+        // i.e. increasing slot) get their exact distance; those within bound[b] are written to the query's
+        // segment [b * cap2, ...) IN SLOT ORDER (ballot compaction), so one stable sort by distance finishes
+        // the (distance, slot) order.  A row that overflowed, or more than cap2 survivors, marks the query
+        // (cnt = cap2 + 1): the caller redoes it exactly.
+        __global__ void __launch_bounds__(128) kept_collect_kernel(const uint32_t *app_ids, const uint32_t *app_cnt,
+                                                                   uint32_t smax, uint32_t cap, uint32_t qpad,
+                                                                   const double *pts, const uint8_t *alive, int D,
+                                                                   const double *q, const double *bound, size_t nb,
+                                                                   uint32_t cap2, double *keys, uint32_t *vals,
+                                                                   uint32_t *cnt)
+        {
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const double *qrow = q + b * D;
+            const double bd = bound[b];
+            uint32_t n = 0;
+            bool over = false;
+            for (uint32_t s = 0; s < smax && !over; ++s)
+            {
+                const uint32_t c = app_cnt[(size_t)s * qpad + b];
+                if (c > cap)
+                {
+                    over = true;
+                    break;
+                }
+                const uint32_t *row = app_ids + ((size_t)s * qpad + b) * cap;
+                for (uint32_t i0 = 0; i0 < c; i0 += 32)
+                {
+                    const uint32_t i = i0 + lane;
+                    bool keep = false;
+                    uint32_t slot = 0;
+                    double d = 0.0;
+                    if (i < c)
+                    {
+                        slot = row[i];
+                        if (alive[slot])
+                        {
+                            d = rv_distance(pts + (size_t)slot * D, qrow, D);
+                            keep = d <= bd;
+                        }
+                    }
+                    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                    const uint32_t pos = n + __popc(bal & ((1u << lane) - 1u));
+                    if (keep && pos < cap2)
+                    {
+                        keys[b * cap2 + pos] = d;
+                        vals[b * cap2 + pos] = slot;
+                    }
+                    n += __popc(bal);
+                }
+            }
+            if (lane == 0)
+                cnt[b] = (over || n > cap2) ? cap2 + 1u : n;
+        }
+
         // compact copy of every step-th filter row (the sample thr_sample_kernel reads)
         __global__ void sample_gather_kernel(const float4 *filt, int rw, uint32_t step, uint32_t nsample, float4 *out)
         {
@@ -890,6 +982,7 @@ namespace omplcu
     {
         std::lock_guard<std::mutex> lk(stat_mu_);
         last_collect_redo_ = c.last_collect_redo_;
+        last_filter_ = c.last_filter_;
         last_tc_ = c.last_tc_;
         last_thr_ = c.last_thr_;
         last_kept_ = c.last_kept_;
@@ -1234,6 +1327,8 @@ namespace omplcu
             return launches_;
         if (!strcmp(key, "last_thr"))
             return last_thr_;
+        if (!strcmp(key, "last_filter"))
+            return last_filter_;
         if (!strcmp(key, "last_kept"))
             return last_kept_;
         if (!strcmp(key, "last_rank"))
@@ -1782,6 +1877,79 @@ namespace omplcu
             knn_exact(c, d_q, c.ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }
 
+    bool NNIndex::filter_usable() const
+    {
+        return fast_space_ && !force_exact_ && D_ <= TC_MAX_DIM && tc_mode_ != 0 && nslots_ >= 4096 &&
+               tc_thr_pick_stages(tc_shape(D_)) > 0;
+    }
+
+    // See nn.cuh.  Returns smax (rows per query); *qpad_out = the row pitch of app_cnt_ / app_ids_.
+    uint32_t NNIndex::filter_scan(QCtx &c, const double *d_q, size_t nq, const double *d_bound, uint32_t cap,
+                                  uint32_t *qpad_out, cudaStream_t s)
+    {
+        TcShape sh = tc_shape(D_);
+        if (tc_na_ > 0 && tc_na_ < sh.na)
+            sh.na = tc_na_;
+        const int stages = tc_thr_pick_stages(sh);
+        REQUIRE(stages > 0, "filter scan: shape does not fit shared memory");
+        const size_t QT = (size_t)TC_QT * sh.na;
+        const size_t qtiles = (nq + QT - 1) / QT;
+        const uint32_t qpad = (uint32_t)(qtiles * QT);
+        const unsigned long long U = (nslots_ + TC_PT - 1) / TC_PT, TU = qtiles * U;
+        const unsigned long long G = std::max<unsigned long long>(1, std::min<unsigned long long>(sm_count_, TU));
+        uint32_t smax = 1;
+        for (size_t t = 0; t < qtiles; ++t)
+        {
+            const unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
+            const unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
+            const unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
+            smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
+        }
+        c.qp_.reserve((size_t)D_ * qpad);
+        c.qaux_.reserve(2 * (size_t)qpad);
+        c.tau_.reserve(qpad);
+        c.app_cnt_.reserve((size_t)smax * qpad);
+        c.app_ids_.reserve((size_t)smax * qpad * cap);
+        CUDA_CHECK(cudaMemsetAsync(c.app_cnt_.p, 0, (size_t)smax * qpad * sizeof(uint32_t), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
+        scan_bound_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_bound, nq, qpad, c.qaux_.p, pmax2_.p, D_,
+                                                          tc_err_units(D_), c.tau_.p);
+        launches_ += 2;
+        {
+            std::lock_guard<std::mutex> pl(prep_mu_);  // shared operand image, see knn_fast
+            if (tc_version_ != mut_version_)
+            {
+                tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
+                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                tc_version_ = mut_version_;
+                launches_++;
+            }
+        }
+        c.tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
+        tc_build_query_image(c.qp_.p, qpad, D_, c.tc_qimg_.p, s);
+        TcScanParams T{};
+        T.pimg = tc_pimg_.p;
+        T.qimg = c.tc_qimg_.p;
+        T.qpad = qpad;
+        T.sh = sh;
+        T.tau = c.tau_.p;
+        T.app_ids = c.app_ids_.p;
+        T.app_cnt = c.app_cnt_.p;
+        T.cap = cap;
+        T.units = U;
+        T.total_units = TU;
+        T.smax = smax;
+        T.nstages = stages;
+        T.diag = 0;
+        T.dbg = nullptr;
+        tc_launch_thr_scan(T, (unsigned)G, s);
+        launches_ += 2;
+        CUDA_CHECK(cudaGetLastError());
+        *qpad_out = qpad;
+        return smax;
+    }
+
     // Large index (>= 32K slots), any k and any metric (FMT*'s k ~ 2100 of 100K; SE3 / chain kNN): sorting
     // every slot per query is the cost of the full path.  Here an exact distance bound per query comes from a strided sample (the R-th
     // smallest of m sample distances, R chosen 4 sigma above k*m/n), only slots within the bound are
@@ -1841,6 +2009,11 @@ namespace omplcu
         c.col_cnt_.reserve(nb_max);
         c.col_redo_.reserve(nsel);
         CUDA_CHECK(cudaMemsetAsync(c.counters_.p + 1, 0, sizeof(unsigned), s));
+        // filter rows: room for every survivor of a query in each of its rows (a query's neighbours are spread
+        // over the point ranges of its segments in no particular way)
+        const bool filt = d_sel == nullptr && filter_usable();
+        const uint32_t fcap = ((cap + 64 + 31) / 32) * 32;
+        c.last_filter_ = filt ? 1 : 0;
         const bool tables = prepare_chain_tables(c, d_q, c.exact_nq_, s);
         const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
         int *beg = c.ex_offs_.p, *end = c.ex_offs_.p + nb_max + 1;
@@ -1852,6 +2025,32 @@ namespace omplcu
             CUDA_CHECK(cudaMemsetAsync(c.col_cnt_.p, 0, nb * sizeof(uint32_t), s));
             sample_dist_kernel<<<nblk(nb * m, 256), 256, 0, s>>>(pm, alive_.p, step, m, d_sel, b0, nb, c.col_sd_.p);
             rank_select_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.col_sd_.p, m, nb, R, c.col_bound_.p);
+            if (filt)
+            {
+                // Plain RealVector space: the tensor-core threshold scan keeps every slot whose scan value is
+                // below the scan-value image of the query's exact distance bound (a superset of the slots within
+                // the bound); only those get an FP64 distance.  Everything downstream is unchanged: the same
+                // exact distances, the same bound, the same redo rule.  The survivors arrive in slot order, so
+                // one stable sort by distance gives the (distance, slot) order.
+                uint32_t fq = 0;
+                const uint32_t rows = filter_scan(c, d_q + b0 * sp_.stride, nb, c.col_bound_.p, fcap, &fq, s);
+                kept_collect_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pts64_.p,
+                                                                alive_.p, D_, d_q + b0 * sp_.stride, c.col_bound_.p,
+                                                                nb, cap, c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p);
+                collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(c.col_cnt_.p, cap, nb, beg, end);
+                CUDA_CHECK(cudaGetLastError());
+                size_t tmp2 = 0;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, c.ex_keys2_.p, c.ex_keys_.p,
+                                                                    c.ex_vals2_.p, c.ex_vals_.p, (int)items, (int)nb,
+                                                                    beg, end, 0, 64, s));
+                c.cub_tmp_.reserve(tmp2);
+                tmp2 = c.cub_tmp_.cap;
+                CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp2, c.ex_keys2_.p, c.ex_keys_.p,
+                                                                    c.ex_vals2_.p, c.ex_vals_.p, (int)items, (int)nb,
+                                                                    beg, end, 0, 64, s));
+            }
+            else
+            {
             collect_kernel<<<nblk(nb * nslots_, 256), 256, 0, s>>>(pm, alive_.p, nslots_, d_sel, b0, nb, c.col_bound_.p,
                                                                    cap, c.ex_keys_.p, c.ex_vals_.p, c.col_cnt_.p);
             collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(c.col_cnt_.p, cap, nb, beg, end);
@@ -1869,6 +2068,7 @@ namespace omplcu
             CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp2, c.ex_keys2_.p, c.ex_keys_.p,
                                                                 c.ex_vals2_.p, c.ex_vals_.p, (int)items, (int)nb, beg, end,
                                                                 0, 64, s));
+            }
             collect_emit_kernel<<<nblk(nb * kk, 256), 256, 0, s>>>(c.ex_keys_.p, c.ex_vals_.p, c.col_cnt_.p, cap, ids_.p,
                                                                    d_sel, b0, nb, (uint32_t)kk, (uint32_t)kstride,
                                                                    d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1);

@@ -101,6 +101,12 @@ namespace omplcu
         void knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                       cudaStream_t s);
         // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
+        // Tensor-core filter in front of an exact path that has a per-query exact distance bound (the sample
+        // bound of the large-k path, the radius of nearestR): every slot within d_bound[q] of query q ends up
+        // in the query's rows of c.app_ids_ / c.app_cnt_ (smax rows of `cap` slots, in slot order).
+        bool filter_usable() const;
+        uint32_t filter_scan(QCtx &c, const double *d_q, size_t nq, const double *d_bound, uint32_t cap,
+                             uint32_t *qpad_out, cudaStream_t s);
         void knn_fast_thr(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                           cudaStream_t s);
         // exact sort path over the selected queries (d_sel == nullptr: all nq)
@@ -174,6 +180,7 @@ namespace omplcu
             DevBuf<float> tau_, list_vals_;
             DevBuf<uint32_t> app_ids_, app_cnt_;
             DevBuf<unsigned long long> kept_;
+            long last_filter_ = 0;
             long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
             long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
         };
@@ -202,6 +209,7 @@ namespace omplcu
         bool force_exact_ = false, profile_ = false;
 
         // published statistics (stat_mu_)
+        long last_filter_ = 0;
         long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
         long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
         long scan_ns_total_ = 0, scan_count_ = 0;
