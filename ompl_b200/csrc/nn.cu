@@ -531,6 +531,64 @@ namespace omplcu
                 cnt[b] = (over || n > cap2) ? cap2 + 1u : n;
         }
 
+        // fixed-capacity per-query segments [b * cap2, b * cap2 + cnt[b]) -> contiguous at offs[b], order kept
+        __global__ void __launch_bounds__(128) segment_pack_kernel(const double *keys, const uint32_t *vals,
+                                                                   const uint32_t *cnt, uint32_t cap2,
+                                                                   const unsigned long long *offs, size_t nb,
+                                                                   double *out_keys, uint32_t *out_vals)
+        {
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const uint32_t n = cnt[b];
+            const unsigned long long o = offs[b];
+            for (uint32_t i = lane; i < n; i += 32)
+            {
+                out_keys[o + i] = keys[b * cap2 + i];
+                out_vals[o + i] = vals[b * cap2 + i];
+            }
+        }
+
+        // Small result lists (every query of the batch has at most MAXN survivors): pack, order by
+        // (distance, slot) and emit in one kernel, one warp per query -- no segmented radix sort over
+        // tens of thousands of tiny segments.
+        template <int MAXN>
+        __global__ void __launch_bounds__(128) radius_sort_emit_kernel(const double *keys, const uint32_t *vals,
+                                                                       const uint32_t *cnt, uint32_t cap2,
+                                                                       const unsigned long long *offs, size_t nb,
+                                                                       const uint64_t *slot_ids, uint64_t *out_ids,
+                                                                       double *out_dists)
+        {
+            __shared__ double s_key[4][MAXN];
+            __shared__ uint32_t s_slot[4][MAXN];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const uint32_t n = cnt[b];
+            const unsigned long long o = offs[b];
+            for (uint32_t i = lane; i < n; i += 32)
+            {
+                s_key[w][i] = keys[b * cap2 + i];
+                s_slot[w][i] = vals[b * cap2 + i];
+            }
+            __syncwarp();
+            for (uint32_t i = lane; i < n; i += 32)
+            {
+                const double key = s_key[w][i];
+                const uint32_t slot = s_slot[w][i];
+                uint32_t rank = 0;
+                for (uint32_t j = 0; j < n; ++j)
+                {
+                    const double kj = s_key[w][j];
+                    rank += (kj < key || (kj == key && s_slot[w][j] < slot)) ? 1u : 0u;
+                }
+                out_ids[o + rank] = slot_ids[slot];
+                out_dists[o + rank] = key;
+            }
+        }
+
         // compact copy of every step-th filter row (the sample thr_sample_kernel reads)
         __global__ void sample_gather_kernel(const float4 *filt, int rw, uint32_t step, uint32_t nsample, float4 *out)
         {
@@ -2259,8 +2317,18 @@ namespace omplcu
             c.rad_r_.reserve(nq);
             CUDA_CHECK(cudaMemcpyAsync(c.q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, s));
             CUDA_CHECK(cudaMemcpyAsync(c.rad_r_.p, radii, nq * sizeof(double), cudaMemcpyHostToDevice, s));
-            const size_t nb_max = std::max<size_t>(1, std::min(nq, RADIUS_PAIR_BUDGET / nslots_));
-            c.ex_keys_.reserve(nb_max * nslots_);
+            // Plain RealVector spaces: the tensor-core threshold scan keeps, per query, every slot whose scan
+            // value is below the scan-value image of the radius (a superset of the slots within it); only those get
+            // an FP64 distance and the inclusive test d <= r of NearestNeighborsLinear.h:139.  A batch in which
+            // some query has more than RCAP neighbours (or an unbounded radius) takes the all-pairs path below.
+            const bool filt = filter_usable();
+            constexpr uint32_t RCAP = 2048;
+            c.last_filter_ = 0;
+            const size_t nb_max = filt ? std::min<size_t>(nq, 8192)
+                                       : std::max<size_t>(1, std::min(nq, RADIUS_PAIR_BUDGET / nslots_));
+            const size_t nb_pairs = std::max<size_t>(1, std::min(nb_max, RADIUS_PAIR_BUDGET / nslots_));  // all-pairs sub-batch
+            if (!filt)
+                c.ex_keys_.reserve(nb_max * nslots_);
             c.col_cnt_.reserve(2 * nb_max);
             c.rad_off_.reserve(nb_max);
             c.ex_offs_.reserve(nb_max + 1);
@@ -2269,11 +2337,90 @@ namespace omplcu
             std::vector<int> seg(nb_max + 1);
             const bool tables = prepare_chain_tables(c, c.q_stage_.p, nq, s);
             const PairMetric pm{sp_, pts64_.p, c.q_stage_.p, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
-            for (size_t b0 = 0; b0 < nq; b0 += nb_max)
+            size_t nb_done = 0;
+            for (size_t b0 = 0; b0 < nq; b0 += nb_done)
             {
-                const size_t nb = std::min(nb_max, nq - b0);
-                const size_t items = nb * nslots_;
+                size_t nb = std::min(nb_max, nq - b0);
+                nb_done = nb;
                 uint32_t *d_cnt = c.col_cnt_.p, *d_fill = c.col_cnt_.p + nb_max;
+                if (filt)
+                {
+                    uint32_t fq = 0;
+                    const uint32_t rows = filter_scan(c, c.q_stage_.p + b0 * st, nb, c.rad_r_.p + b0, RCAP, &fq, s);
+                    c.col_sd_.reserve(nb_max * RCAP);
+                    c.col_redo_.reserve(nb_max * RCAP);
+                    kept_collect_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, RCAP, fq, pts64_.p,
+                                                                    alive_.p, D_, c.q_stage_.p + b0 * st,
+                                                                    c.rad_r_.p + b0, nb, RCAP, c.col_sd_.p,
+                                                                    c.col_redo_.p, d_cnt);
+                    launches_++;
+                    CUDA_CHECK(cudaGetLastError());
+                    CUDA_CHECK(cudaMemcpyAsync(cnt.data(), d_cnt, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+                    CUDA_CHECK(cudaStreamSynchronize(s));
+                    bool fits = true;
+                    for (size_t b = 0; b < nb; ++b)
+                        fits = fits && cnt[b] <= RCAP;
+                    if (fits)
+                    {
+                        unsigned long long tot = 0;
+                        for (size_t b = 0; b < nb; ++b)
+                        {
+                            boff[b] = tot;
+                            seg[b] = (int)tot;
+                            tot += cnt[b];
+                            offsets[b0 + b + 1] = offsets[b0 + b] + cnt[b];
+                        }
+                        seg[nb] = (int)tot;
+                        c.last_filter_ = 1;
+                        if (tot == 0)
+                            continue;
+                        c.ex_keys2_.reserve(tot);
+                        c.ex_keys3_.reserve(tot);
+                        c.ex_vals_.reserve(tot);
+                        c.ex_vals2_.reserve(tot);
+                        c.rad_ids_.reserve(total + tot, true, s);
+                        c.rad_d_.reserve(total + tot, true, s);
+                        CUDA_CHECK(cudaMemcpyAsync(c.rad_off_.p, boff.data(), nb * sizeof(unsigned long long),
+                                                   cudaMemcpyHostToDevice, s));
+                        CUDA_CHECK(cudaMemcpyAsync(c.ex_offs_.p, seg.data(), (nb + 1) * sizeof(int), cudaMemcpyHostToDevice, s));
+                        uint32_t cmax = 0;
+                        for (size_t b = 0; b < nb; ++b)
+                            cmax = std::max(cmax, cnt[b]);
+                        if (cmax <= 256)
+                        {
+                            radius_sort_emit_kernel<256><<<nblk(nb, 4), 128, 0, s>>>(
+                                c.col_sd_.p, c.col_redo_.p, d_cnt, RCAP, c.rad_off_.p, nb, ids_.p, c.rad_ids_.p + total,
+                                c.rad_d_.p + total);
+                            launches_++;
+                            CUDA_CHECK(cudaGetLastError());
+                            total += tot;
+                            continue;
+                        }
+                        // survivors are in slot order already: one stable sort by distance
+                        segment_pack_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.col_sd_.p, c.col_redo_.p, d_cnt, RCAP, c.rad_off_.p,
+                                                                        nb, c.ex_keys3_.p, c.ex_vals2_.p);
+                        size_t tmp2 = 0;
+                        CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(nullptr, tmp2, c.ex_keys3_.p, c.ex_keys2_.p,
+                                                                            c.ex_vals2_.p, c.ex_vals_.p, (int)tot, (int)nb,
+                                                                            c.ex_offs_.p, c.ex_offs_.p + 1, 0, 64, s));
+                        c.cub_tmp_.reserve(tmp2);
+                        tmp2 = c.cub_tmp_.cap;
+                        CUDA_CHECK(cub::DeviceSegmentedRadixSort::SortPairs(c.cub_tmp_.p, tmp2, c.ex_keys3_.p, c.ex_keys2_.p,
+                                                                            c.ex_vals2_.p, c.ex_vals_.p, (int)tot, (int)nb,
+                                                                            c.ex_offs_.p, c.ex_offs_.p + 1, 0, 64, s));
+                        radius_emit_kernel<<<nblk(tot, 256), 256, 0, s>>>(c.ex_keys2_.p, c.ex_vals_.p, ids_.p, tot,
+                                                                          c.rad_ids_.p + total, c.rad_d_.p + total);
+                        launches_ += 10;
+                        CUDA_CHECK(cudaGetLastError());
+                        total += tot;
+                        continue;
+                    }
+                    // too many neighbours for the filtered path: all pairs, in sub-batches the distance matrix allows
+                    nb = std::min(nb, nb_pairs);
+                    nb_done = nb;
+                    c.ex_keys_.reserve(nb_pairs * nslots_);
+                }
+                const size_t items = nb * nslots_;
                 CUDA_CHECK(cudaMemsetAsync(c.col_cnt_.p, 0, 2 * nb_max * sizeof(uint32_t), s));
                 radius_dist_kernel<<<nblk(items, 256), 256, 0, s>>>(pm, alive_.p, nslots_, b0, nb, c.rad_r_.p, c.ex_keys_.p,
                                                                     d_cnt);
@@ -2344,6 +2491,8 @@ namespace omplcu
                 CUDA_CHECK(cudaMemcpyAsync(*dists, c.rad_d_.p, total * sizeof(double), cudaMemcpyDeviceToHost, s));
         }
         CUDA_CHECK(cudaStreamSynchronize(s));
+        c.last_path_ = 2;
+        publish(c);
     }
 
     void merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t part_stride,
