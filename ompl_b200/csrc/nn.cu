@@ -589,6 +589,158 @@ namespace omplcu
             }
         }
 
+        // Re-rank for small batches whose scan was cut into many segments (up to one per SM, so that a lone
+        // query streams the point image on all of them): one warp per query, up to a few thousand candidates in
+        // dynamic shared memory.  Same exact distances, same (distance, slot) order and the same band check as
+        // knn_rerank_kernel; the kk best are extracted one by one (every lane caches the best of its own
+        // candidates, a shuffle tree picks the winner, only the winning lane rescans) instead of ranking all pairs.
+        constexpr int SEL_THREADS = 1024;
+
+        // RealVectorStateSpace::distance with the loads of eight coordinates issued before their (sequential)
+        // accumulation: the same operations in the same order as rv_distance, hence the same bits, but the
+        // memory latency of a scattered row is paid once per eight coordinates instead of once per coordinate.
+        __device__ __forceinline__ double rv_distance_mlp(const double *a, const double *b, int d)
+        {
+            double dist = 0.0;
+            int i = 0;
+            for (; i + 8 <= d; i += 8)
+            {
+                double v[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    v[j] = a[i + j];
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                {
+                    const double diff = dsub(v[j], b[i + j]);
+                    dist = dadd(dist, dmul(diff, diff));
+                }
+            }
+            double v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                v[j] = (i + j < d) ? a[i + j] : 0.0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                if (i + j < d)
+                {
+                    const double diff = dsub(v[j], b[i + j]);
+                    dist = dadd(dist, dmul(diff, diff));
+                }
+            return dsqrt(dist);
+        }
+
+        __global__ void __launch_bounds__(SEL_THREADS) knn_rerank_select_kernel(
+            const float *cand_thr, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
+            const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
+            const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
+            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units)
+        {
+            extern __shared__ __align__(16) unsigned char sel_smem[];
+            const int lane = threadIdx.x & 31;
+            const size_t qi = blockIdx.x;
+            if (qi >= nq)
+                return;
+            const uint32_t n = smax * L;
+            double *s_key = reinterpret_cast<double *>(sel_smem);
+            double *s_q = s_key + n;
+            uint32_t *s_slot = reinterpret_cast<uint32_t *>(s_q + D);
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            for (int i = threadIdx.x; i < D; i += SEL_THREADS)
+                s_q[i] = q[qi * D + i];
+            __syncthreads();
+            // exact distances: the whole block (the candidates' rows are scattered loads); the selection below
+            // is one warp's work
+            for (uint32_t c = threadIdx.x; c < n; c += SEL_THREADS)
+            {
+                const uint32_t slot = cand_ids[(size_t)c * qpad + qi];
+                s_key[c] = slot != SLOT_NONE ? rv_distance_mlp(pts + (size_t)slot * D, s_q, D) : inf;
+                s_slot[c] = slot;
+            }
+            __syncthreads();
+            if (threadIdx.x >= 32)
+                return;
+            double bk = inf;
+            uint32_t bs = SLOT_NONE, bi = 0;
+            auto rescan = [&]() {
+                bk = inf;
+                bs = SLOT_NONE;
+                bi = 0;
+                for (uint32_t c = lane; c < n; c += 32)
+                {
+                    const uint32_t sl = s_slot[c];
+                    if (sl == SLOT_NONE)
+                        continue;
+                    const double k = s_key[c];
+                    // a NaN distance never wins a comparison: it stays behind and the band check below fails on it
+                    if (bs == SLOT_NONE || k < bk || (k == bk && sl < bs))
+                    {
+                        bk = k;
+                        bs = sl;
+                        bi = c;
+                    }
+                }
+            };
+            rescan();
+            double dk = -1.0;
+            for (uint32_t r = 0; r < kk; ++r)
+            {
+                double wk = bk;
+                uint32_t ws = bs, wi = bi;
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    const double ok = __shfl_xor_sync(0xffffffffu, wk, o);
+                    const uint32_t os = __shfl_xor_sync(0xffffffffu, ws, o);
+                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, wi, o);
+                    if (os != SLOT_NONE && (ws == SLOT_NONE || ok < wk || (ok == wk && os < ws)))
+                    {
+                        wk = ok;
+                        ws = os;
+                        wi = oi;
+                    }
+                }
+                if (ws == SLOT_NONE)
+                    break;  // fewer than kk candidates: dk stays negative, the query is redone exactly
+                if (lane == 0)
+                {
+                    out_ids[qi * kstride + r] = slot_ids[ws];
+                    if (out_dists)
+                        out_dists[qi * kstride + r] = wk;
+                }
+                if (r == kk - 1)
+                    dk = wk;
+                if ((wi & 31u) == (uint32_t)lane)
+                {
+                    s_slot[wi] = SLOT_NONE;
+                    rescan();
+                }
+                __syncwarp();
+            }
+            // ---- band check (knn_rerank_kernel) ----
+            const double u = 5.9604644775390625e-08;  // 2^-24
+            const double qn = qaux[2 * qi], qnorm = qaux[2 * qi + 1];
+            const double pmax2 = (double)__uint_as_float(*pmax2_bits) * (1.0 + 2.0 * u);
+            const double pmax = sqrt(pmax2) * (1.0 + 1e-9);
+            const double delta = (double)(D + 4) * 1.1102230246251565e-16;
+            const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
+            const double A = dk * (1.0 + delta) + rho + 1e-150;
+            const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+            const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
+            bool bad = !(tau64 == tau64) || !(tau64 < 1e37) || dk < 0.0 || !(dk == dk);
+            for (uint32_t s = lane; s < smax; s += 32)
+            {
+                const double vmax = (double)cand_thr[(size_t)s * qpad + qi];
+                if (vmax < 1e38 && !(vmax - fabs(vmax) * 1.52587890625e-05 - 1e-37 > tau64))
+                    bad = true;
+            }
+            bad = __any_sync(0xffffffffu, bad);
+            if (bad && lane == 0)
+            {
+                const unsigned pos = atomicAdd(ovf_count, 1u);
+                ovf_list[pos] = (uint32_t)qi;
+            }
+        }
+
         // compact copy of every step-th filter row (the sample thr_sample_kernel reads)
         __global__ void sample_gather_kernel(const float4 *filt, int rw, uint32_t step, uint32_t nsample, float4 *out)
         {
@@ -1575,6 +1727,13 @@ namespace omplcu
             tc_sh.na /= 2;  // long lists: fewer resident query tiles
             tc_stages = tc_pick_stages(tc_sh, tc_L);
         }
+        // a small batch needs no more resident query tiles than it fills: a lone query runs 1 MMA chain per point
+        // tile instead of 4
+        while (tc_sh.na > 1 && nq <= (size_t)TC_QT * (tc_sh.na / 2))
+        {
+            tc_sh.na /= 2;
+            tc_stages = tc_pick_stages(tc_sh, tc_L);
+        }
         const bool tc_auto = nq >= TC_MIN_BATCH;  // measured faster than the FP32 scans at every batched size
         const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
         c.last_tc_ = tc ? 1 : 0;
@@ -1601,7 +1760,13 @@ namespace omplcu
         resident = std::max(resident, 1);
         if (scan_ctas_per_sm_ > 0)
             resident = std::min(resident, scan_ctas_per_sm_);
-        const unsigned max_seg = 512 / L;  // candidate slots per query <= 512
+        // candidate slots per query: 512 for the all-pairs ranking of knn_rerank_kernel; a batch of one query
+        // tile may be cut into up to one segment per SM (2560 slots, knn_rerank_select_kernel), so that a
+        // single query -- the literal nearestK of PRM::addMilestone, prm/src/PRM.cpp:575 -- streams the image
+        // on every SM instead of 31
+        constexpr unsigned FEW_SLOTS = 2560;
+        const bool few = tc && qtiles == 1;
+        const unsigned max_seg = (few ? FEW_SLOTS : 512u) / L;
         unsigned long long G = (unsigned long long)sm_count_ * resident;
         G = std::min<unsigned long long>(G, TU);
         G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
@@ -1615,7 +1780,7 @@ namespace omplcu
             unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
             smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
         }
-        if ((size_t)smax * L > 512)
+        if ((size_t)smax * L > (few ? FEW_SLOTS : 512u))
             throw Error(OMPLCU_ERR_INTERNAL, "scan: too many segments per query tile");
 
         c.qp_.reserve((size_t)D_ * qpad);
@@ -1702,6 +1867,11 @@ namespace omplcu
         if (profile_)
             CUDA_CHECK(cudaEventRecord(c.ev1_, s));
 
+        if ((size_t)smax * L > 512)
+            knn_rerank_select_kernel<<<(unsigned)nq, SEL_THREADS, (size_t)smax * L * 12 + (size_t)D_ * 8, s>>>(
+                c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad, pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p,
+                nq, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, tc_err_units(D_));
+        else
         knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad,
                                                           pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p, nq,
                                                           (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists,
