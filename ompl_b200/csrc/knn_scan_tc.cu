@@ -197,6 +197,42 @@ namespace omplcu
                          "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
                          : "memory");
         }
+        // The same with the A operand read from tensor memory (lane = row, every 32-bit column holds two
+        // consecutive K elements, low half first): D[tmem] (+)= A[tmem] * B[smem]^T
+        __device__ __forceinline__ void umma_bf16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                                     uint32_t accumulate)
+        {
+            asm volatile("{\n"
+                         ".reg .pred p;\n"
+                         "setp.ne.b32 p, %4, 0;\n"
+                         "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n"
+                         "}\n" ::"r"(tmem_d),
+                         "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+                         : "memory");
+        }
+        // four consecutive columns of this thread's TMEM lane <- four registers
+        __device__ __forceinline__ void tmem_st4(uint32_t taddr, uint32_t a, uint32_t b, uint32_t c, uint32_t d)
+        {
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x4.b32 [%0], {%1, %2, %3, %4};" ::"r"(taddr), "r"(a), "r"(b),
+                         "r"(c), "r"(d)
+                         : "memory");
+        }
+        __device__ __forceinline__ void tmem_st_wait()
+        {
+            asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+        }
+        // one lane of a converged warp
+        __device__ __forceinline__ bool elect_one()
+        {
+            uint32_t pred;
+            asm volatile("{\n"
+                         ".reg .pred p;\n"
+                         "elect.sync _|p, 0xffffffff;\n"
+                         "selp.u32 %0, 1, 0, p;\n"
+                         "}\n"
+                         : "=r"(pred));
+            return pred != 0;
+        }
         // shared-memory matrix descriptor, K-major, no swizzle (cute::UMMA::SmemDescriptor):
         //   [0,14) start >> 4, [16,30) leading byte offset >> 4, [32,46) stride byte offset >> 4,
         //   [46,48) version = 1 on sm_100, [61,64) layout type = 0 (no swizzle)
@@ -345,9 +381,18 @@ namespace omplcu
         // Work: the (query super-tile x point tile) rectangle, linearised (super-tile major) and cut
         // into gridDim.x equal pieces as in knn_scan.cuh.  A super-tile is NA query tiles of 128; per
         // point tile the CTA runs NA "jobs" (one accumulator each, job j -> TMEM buffer j % 4).
-        template <int L, int NA, bool DBG>
+        // TS (NA == 1 only, the d >= 53 shapes): the query tile is the TMEM-resident A operand.  An SS-mode
+        // tcgen05.mma of M 128 x N 128 x K 16 reads 4 KB of A and 4 KB of B from shared memory in its 64 clk,
+        // the SM's whole shared-memory bandwidth, and at K = 320 that is what bounds the kernel (ncu round 1:
+        // tensor pipe 39 %, tc_wavefronts_mem_shared 38 %).  With A in tensor memory (kpad / 2 columns, written by
+        // the selection warps with tcgen05.st at the start of a query super-tile: thread = lane = query) an MMA
+        // reads only B.  Columns [0, 256): A; [256, 512): two 128-column accumulators (job j -> buffer j % 2).
+        template <int L, int NA, bool DBG, bool TS = false>
         __global__ void __launch_bounds__(tc_threads(NA), 1) knn_scan_tc_kernel(const TcScanParams P)
         {
+            static_assert(!TS || NA == 1, "the TMEM-resident query tile is built for one resident tile");
+            constexpr uint32_t NBUF = TS ? 2u : (uint32_t)TC_ACC;      // accumulator buffers of the general path
+            constexpr uint32_t ACC0 = TS ? 256u : 0u;                  // first accumulator column
             extern __shared__ __align__(1024) uint8_t tc_smem[];
             constexpr int LS = L + 4;
             const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw;
@@ -361,7 +406,9 @@ namespace omplcu
             constexpr int W = 32;  // columns per selection step
             TcSmem *S = reinterpret_cast<TcSmem *>(scr + 4 * NA * W * 32);
 
-            const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+            // the warp index through a shuffle: the compiler then knows that it is warp-uniform and keeps the
+            // issuer's descriptors and loop counters in uniform registers
+            const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
             const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
             const unsigned long long u0 = TU * g / G, u1 = TU * (g + 1) / G;
 
@@ -372,7 +419,7 @@ namespace omplcu
                     mbar_init(&S->full[i], 1);
                     mbar_init(&S->empty[i], NA);
                 }
-                mbar_init(&S->a_full, 1);
+                mbar_init(&S->a_full, TS ? TC_QT : 1);
                 mbar_init(&S->a_empty, NA);
                 for (int i = 0; i < 2 * TC_ACC; ++i)
                 {
@@ -402,7 +449,7 @@ namespace omplcu
                             t = u / U;
                             pt = u % U;
                         }
-                        if (t != cur)
+                        if (!TS && t != cur)
                         {
                             mbar_wait(&S->a_empty, aph ^ 1);  // the MMAs of the previous super-tile are done with sA
                             mbar_expect_tx(&S->a_full, NA * a_tile_bytes);
@@ -430,9 +477,13 @@ namespace omplcu
             else if (warp <= NA)
             {
                 // one issuer per resident tile: the four accumulator chains (MMA -> selection -> MMA) advance
-                // independently instead of queueing behind one thread's barrier waits
-                if (lane == 0)
+                // independently instead of queueing behind one thread's barrier waits.  The WHOLE warp runs the
+                // loop (uniform control flow, uniform operands); one elected lane issues the tcgen05 instructions.
+                // With the loop under `if (lane == 0)` every MMA cost ~16 instructions of register -> uniform
+                // register broadcasts and the issuer, not the tensor pipe, paced the d >= 53 shapes (ncu round 2:
+                // 110 instructions per 4-MMA chunk, 166 clk per MMA against 64 clk of tensor time).
                 {
+                    const bool leader = elect_one();
                     const int a = warp - 1;
                     constexpr uint32_t idesc = umma_idesc_bf16(TC_QT, TC_PT);
                     const uint32_t dl = (P.diag & 1) ? TC_SBO : TC_LBO, ds = (P.diag & 1) ? TC_LBO : TC_SBO;
@@ -451,7 +502,8 @@ namespace omplcu
                         if (t != cur)
                         {
                             if (cur != ~0ull)
-                                umma_commit(&S->a_empty);
+                                if (leader)
+                                    umma_commit(&S->a_empty);
                             mbar_wait(&S->a_full, aph);
                             aph ^= 1;
                             cur = t;
@@ -472,7 +524,7 @@ namespace omplcu
                                 mbar_wait(&S->t_empty[b], ((jt >> 1) & 1) ^ 1);
                                 tc_fence_after();
                                 const uint64_t bh = bd + h * ((TC_PT / 2 / 8) * TC_SBO >> 4);  // rows 64 h .. 64 h + 63
-                                if (!(P.diag & 8))
+                                if (leader && !(P.diag & 8))
                                 {
                                     umma_bf16(tmem + b * (TC_PT / 2), ad, bh, idesc64, 0u);
                                     umma_bf16(tmem + b * (TC_PT / 2), ad + (2 * TC_LBO >> 4), bh + (2 * TC_LBO >> 4), idesc64, 1u);
@@ -482,9 +534,13 @@ namespace omplcu
                                         umma_bf16(tmem + b * (TC_PT / 2), ad + 3 * (2 * TC_LBO >> 4), bh + 3 * (2 * TC_LBO >> 4), idesc64, 1u);
                                     }
                                 }
-                                umma_commit(&S->t_full[b]);
+                                if (leader)
+                                    umma_commit(&S->t_full[b]);
+                                __syncwarp();
                             }
-                            umma_commit(&S->empty[st]);
+                            if (leader)
+                                umma_commit(&S->empty[st]);
+                            __syncwarp();
                             if (++st == nst)
                             {
                                 st = 0;
@@ -492,18 +548,33 @@ namespace omplcu
                             }
                             continue;
                         }
-                        const uint32_t buf = job & (TC_ACC - 1);
-                        const uint32_t dcol = tmem + buf * TC_PT;
+                        const uint32_t buf = job & (NBUF - 1);
+                        const uint32_t dcol = tmem + ACC0 + buf * TC_PT;
                         for (int kc = 0; kc < nkc; ++kc)
                         {
                             mbar_wait(&S->full[st], ph);
                             if (kc == 0)
-                                mbar_wait(&S->t_empty[buf], ((job / TC_ACC) & 1) ^ 1);
+                                mbar_wait(&S->t_empty[buf], ((job / NBUF) & 1) ^ 1);
                             tc_fence_after();
                             // descriptors differ in the start address only (low word, units of 16 bytes)
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
-                            if (!(P.diag & 8))  // diagnostics: barriers and commits only
+                            if (TS)
+                            {
+                                // A: 8 columns per K = 16 step, chunk kc starts at column kc * kw * 4
+                                const uint32_t ac = tmem + (uint32_t)kc * (uint32_t)kw * 4u;
+                                if (leader && !(P.diag & 8))
+                                {
+                                    umma_bf16_ts(dcol, ac, bd, idesc, kc ? 1u : 0u);
+                                    umma_bf16_ts(dcol, ac + 8, bd + (2 * TC_LBO >> 4), idesc, 1u);
+                                    if (kw == 8)
+                                    {
+                                        umma_bf16_ts(dcol, ac + 16, bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
+                                        umma_bf16_ts(dcol, ac + 24, bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
+                                    }
+                                }
+                            }
+                            else if (leader && !(P.diag & 8))  // diagnostics: barriers and commits only
                             {
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
                                 umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
@@ -513,9 +584,13 @@ namespace omplcu
                                     umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
                                 }
                             }
-                            umma_commit(&S->empty[st]);  // the stage is free once all NA issuers' MMAs have read it
-                            if (kc == nkc - 1)
-                                umma_commit(&S->t_full[buf]);
+                            if (leader)
+                            {
+                                umma_commit(&S->empty[st]);  // the stage is free once all NA issuers' MMAs have read it
+                                if (kc == nkc - 1)
+                                    umma_commit(&S->t_full[buf]);
+                            }
+                            __syncwarp();
                             if (++st == nst)
                             {
                                 st = 0;
@@ -535,6 +610,10 @@ namespace omplcu
                 // and the next victim.  The hot loop is two copies of the W-column step (the two register
                 // buffers of the TMEM load pipeline) and stays resident in the instruction cache.
                 const int a = (warp - 1 - NA) >> 2, wq = warp & 3, qrow = wq * 32 + lane;
+                const int qrow_idx = qrow;
+                uint32_t aph_sel = 0;
+                (void)qrow_idx;
+                (void)aph_sel;
                 float *lvq = lv + (a * TC_QT + qrow) * LS;
                 uint32_t *liq = li + a * L * TC_QT + qrow;
                 float *scr_q = scr + (warp - 1 - NA) * W * 32 + lane;
@@ -616,6 +695,27 @@ namespace omplcu
                             flush(cur);
                         reset();
                         cur = t;
+                        if constexpr (TS)
+                        {
+                            // this thread's query row of the operand image -> its TMEM lane, columns [0, kpad / 2)
+                            mbar_wait(&S->a_empty, aph_sel ^ 1);  // the MMAs of the previous super-tile have read A
+                            aph_sel ^= 1;
+                            tc_fence_after();
+                            const uint16_t *qrow = P.qimg + (size_t)t * (a_tile_bytes / 2) +
+                                                   (size_t)(qrow_idx >> 3) * (TC_SBO / 2) + (size_t)(qrow_idx & 7) * 8;
+                            const uint32_t ta = tmem + ((uint32_t)(wq * 32) << 16);
+                            for (int kc = 0; kc < nkc; ++kc)
+                                for (int j = 0; j < kw; ++j)
+                                {
+                                    const uint4 v = *reinterpret_cast<const uint4 *>(
+                                        qrow + (size_t)kc * (chunk_bytes / 2) + (size_t)j * (TC_LBO / 2));
+                                    __syncwarp();
+                                    tmem_st4(ta + (uint32_t)(kc * kw + j) * 4u, v.x, v.y, v.z, v.w);
+                                }
+                            tmem_st_wait();
+                            tc_fence_before();
+                            mbar_arrive(&S->a_full);
+                        }
                     }
                     const uint32_t slot0 = (uint32_t)(pt * TC_PT);
                     if constexpr (NA == 4)
@@ -648,10 +748,10 @@ namespace omplcu
                         }
                         continue;
                     }
-                    const int buf = (int)(job & (TC_ACC - 1));
-                    mbar_wait(&S->t_full[buf], (uint32_t)((job / TC_ACC) & 1));
+                    const int buf = (int)(job & (NBUF - 1));
+                    mbar_wait(&S->t_full[buf], (uint32_t)((job / NBUF) & 1));
                     tc_fence_after();
-                    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
+                    const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + ACC0 + (uint32_t)buf * TC_PT;
                     if (!(P.diag & 2))
                     {
                         {
@@ -1026,9 +1126,19 @@ namespace omplcu
             knn_scan_tc_kernel<L, NA, false><<<grid, tc_threads(NA), smem, s>>>(P);
         }
         template <int L>
+        void tc_launch_ts(const TcScanParams &P, unsigned grid, cudaStream_t s)
+        {
+            const size_t smem = tc_smem_bytes(P.sh, P.nstages, L);
+            CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, 1, false, true>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            knn_scan_tc_kernel<L, 1, false, true><<<grid, tc_threads(1), smem, s>>>(P);
+        }
+        template <int L>
         void tc_launch_na(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
-            if (P.sh.na == 4)
+            if (P.sh.na == 1 && P.ts && !P.dbg && P.sh.kpad() <= 512)
+                tc_launch_ts<L>(P, grid, s);
+            else if (P.sh.na == 4)
                 tc_launch<L, 4>(P, grid, s);
             else if (P.sh.na == 2)
                 tc_launch<L, 2>(P, grid, s);

@@ -76,6 +76,7 @@ namespace omplcu
         int nstages;
         int diag;               // diagnostics: 1 swap descriptor fields, 2 no selection, 4 no insertion
         float *dbg;             // [qpad][units*TC_PT] raw scan values, or nullptr
+        int ts;                 // list kernel, one resident tile: query tile as the TMEM-resident A operand
         // list kernel only: the list values themselves, [smax*L][qpad] (tagged, i.e. rounded up by < 128 ulp;
         // EMPTY markers > 1e38 where the list did not fill), or nullptr.  Read by the threshold selection.
         float *list_vals;

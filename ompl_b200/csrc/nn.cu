@@ -1151,6 +1151,8 @@ namespace omplcu
         }
         if (const char *e = getenv("OMPLCU_TC_SCAN"))
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
+        if (const char *e = getenv("OMPLCU_TC_TS"))
+            tc_ts_ = atoi(e);
         if (const char *e = getenv("OMPLCU_THR_SCAN"))
             thr_mode_ = atoi(e);  // default for the "thr_scan" option
         CUDA_CHECK(cudaStreamSynchronize(stream_));
@@ -1498,6 +1500,10 @@ namespace omplcu
             tc_mode_ = (int)v;  // -1 auto, 0 never, 1 whenever the space is eligible
         else if (!strcmp(key, "tc_tiles"))
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
+        else if (!strcmp(key, "tc_ts"))
+            tc_ts_ = (int)v;  // one resident tile (d >= 53, or small batches): query tile in tensor memory
+        else if (!strcmp(key, "l2_window"))
+            l2_window_ = v != 0;  // persisting L2 window over the operand image during the tensor-core scan
         else if (!strcmp(key, "thr_scan"))
             thr_mode_ = (int)v;  // -1 auto, 0 never (list scan), 1 whenever the tensor-core scan runs
         else if (!strcmp(key, "thr_sample_step"))
@@ -1856,7 +1862,45 @@ namespace omplcu
             T.nstages = tc_stages;
             T.diag = tc_variant_;
             T.dbg = tc_dbg_;
+            T.ts = tc_ts_;
+            // The operand image is re-read once per query super-tile by CTAs that drift apart: ask L2 to keep it
+            // (persisting access-policy window on this stream) so the re-reads do not go back to DRAM.
+            bool window = false;
+            if (l2_window_ && qtiles > 1)
+            {
+                static std::once_flag lim[64];
+                std::call_once(lim[device_ & 63], [] {
+                    int dev = 0, maxp = 0;
+                    cudaGetDevice(&dev);
+                    cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, dev);
+                    if (maxp > 0)
+                        cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, (size_t)maxp);
+                    cudaGetLastError();
+                });
+                int maxw = 0, maxp = 0;
+                cudaDeviceGetAttribute(&maxw, cudaDevAttrMaxAccessPolicyWindowSize, device_);
+                cudaDeviceGetAttribute(&maxp, cudaDevAttrMaxPersistingL2CacheSize, device_);
+                const size_t bytes = (size_t)U * tc_sh.nkc * tc_sh.chunk_elems() * sizeof(uint16_t);
+                if (maxw > 0 && maxp > 0)
+                {
+                    cudaStreamAttrValue av{};
+                    av.accessPolicyWindow.base_ptr = tc_pimg_.p;
+                    av.accessPolicyWindow.num_bytes = std::min(bytes, (size_t)maxw);
+                    av.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)maxp / (double)std::max<size_t>(bytes, 1));
+                    av.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+                    av.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+                    window = cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &av) == cudaSuccess;
+                    cudaGetLastError();
+                }
+            }
             tc_launch_scan(L, T, (unsigned)G, s);
+            if (window)
+            {
+                cudaStreamAttrValue av{};
+                av.accessPolicyWindow.num_bytes = 0;
+                cudaStreamSetAttribute(s, cudaStreamAttributeAccessPolicyWindow, &av);
+                cudaGetLastError();
+            }
         }
         else if (hd)
             hd_any(cfg, 1, D_, rowf_, &P, (unsigned)G, s, nullptr);

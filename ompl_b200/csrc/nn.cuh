@@ -206,6 +206,8 @@ namespace omplcu
         int thr_step_ = 16;       // sample stride
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
+        bool l2_window_ = false;
+        int tc_ts_ = 0;
         bool force_exact_ = false, profile_ = false;
 
         // published statistics (stat_mu_)
