@@ -832,7 +832,7 @@ namespace omplcu
             uint8_t *sB = sA + (size_t)NA * a_tile_bytes;  // [nst][chunk]
             TcThrSmem *S = reinterpret_cast<TcThrSmem *>(sB + (size_t)nst * chunk_bytes);
 
-            const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+            const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
             const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
             const unsigned long long u0 = TU * g / G, u1 = TU * (g + 1) / G;
 
@@ -900,8 +900,9 @@ namespace omplcu
             }
             else if (warp <= NA)
             {
-                if (lane == 0)
+                // whole warp, one elected lane issues (see knn_scan_tc_kernel)
                 {
+                    const bool leader = elect_one();
                     const int a = warp - 1;
                     constexpr uint32_t idesc = umma_idesc_bf16(TC_QT, TC_PT);
                     const uint32_t a0 = (smem_u32(sA) & 0x3FFFFu) + (uint32_t)a * a_tile_bytes, b0 = smem_u32(sB) & 0x3FFFFu;
@@ -919,7 +920,7 @@ namespace omplcu
                         }
                         if (t != cur)
                         {
-                            if (cur != ~0ull)
+                            if (cur != ~0ull && leader)
                                 umma_commit(&S->a_empty);
                             mbar_wait(&S->a_full, aph);
                             aph ^= 1;
@@ -935,7 +936,7 @@ namespace omplcu
                             tc_fence_after();
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
-                            if (!no_mma)
+                            if (leader && !no_mma)
                             {
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
                                 umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
@@ -945,9 +946,13 @@ namespace omplcu
                                     umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
                                 }
                             }
-                            umma_commit(&S->empty[st]);
-                            if (kc == nkc - 1)
-                                umma_commit(&S->t_full[buf]);
+                            if (leader)
+                            {
+                                umma_commit(&S->empty[st]);
+                                if (kc == nkc - 1)
+                                    umma_commit(&S->t_full[buf]);
+                            }
+                            __syncwarp();
                             if (++st == nst)
                             {
                                 st = 0;

@@ -207,7 +207,7 @@ namespace omplcu
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
         bool l2_window_ = false;
-        int tc_ts_ = 0;
+        int tc_ts_ = 1;           // one resident tile: query tile in tensor memory (0: shared memory)
         bool force_exact_ = false, profile_ = false;
 
         // published statistics (stat_mu_)
