@@ -44,9 +44,9 @@ N_STATES, N_QUERIES, K, DIM = 1_000_000, 65536, 10, 7
 N_SEGMENTS = 1_000_000
 MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 0.01)"
 METRIC = "kNN queries/sec (k=10, 1M states)"
-TC_CAPTURE = "r1_scan_tc_d7_ncu_summary.csv"    # ncu --set full of the tensor-core scan (roofline.traffic is read from it)
+TC_CAPTURE = "r2_scan_tc_d7_ncu_summary.csv"    # ncu --set full of the tensor-core scan (roofline.traffic is read from it)
 FP32_CAPTURE = "r1_scan_v3_ncu_summary.csv"     # ... of the FP32-pipe scan
-MOTION_CAPTURE = "r1_motion_v5_ncu_summary.csv"  # ... of motion_group_kernel
+MOTION_CAPTURE = "r2_motion_v5_ncu_summary.csv"  # ... of motion_group_kernel
 UNIT = "queries/s"
 
 
@@ -460,12 +460,14 @@ def run_gpu_arm(args):
                 "frac_executed": exe / (scan_ns * 1e-9) / 1e12 / tpeak,
                 "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                 "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
-                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu: 21 % busy) and neither is HBM: "
-                        "the kernel is bound by the MMA -> TMEM -> selection hand-over and the selection itself (ncu: issue "
-                        "slots 65 % busy: 31 % min-trees over the accumulators, 27 % list insertions while the per-query "
-                        "thresholds converge, 25 % mbarrier polls, 18 % bookkeeping; profiles/r1_scan_tc_d7_instruction_mix.txt) "
-                        "and by shared-memory operand reads; achieved exceeds the FP32 "
-                        "FMA peak (vs_fp32_pipe_peak > 1), which bounded the round-1 FP32 scan (roofline_fp32_scan)",
+                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu round 2: 25 % busy) and neither is HBM: "
+                        "the kernel is bound by instruction issue in the selection warps (issue slots 64 % busy; of the executed "
+                        "instructions 19 % are the FMNMX3 min-trees over the accumulators, 28 % branch / sync / nop overhead of the "
+                        "per-step TMEM load handshake, 29 % integer bookkeeping and list insertions, 6 % mbarrier polls; "
+                        "profiles/r2_scan_tc_d7_instruction_mix.txt). Every FP32 accumulator value costs at least 1 issue clock per SM "
+                        "sub-partition whatever instruction looks at it (scripts/ubench_reduce.cu), i.e. 1.76 ms for this "
+                        "launch; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which bounded the FP32 scan "
+                        "(roofline_fp32_scan)",
             }
             if fp32_leg:
                 roofline_fp32 = fp32_roofline(fp32_leg[1], fp32_leg[0])
@@ -692,6 +694,114 @@ def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
     return out
 
 
+def run_m4(args):
+    """Second driver-visible line: kNN on RealVectorStateSpace(100), 100K states, 65536 queries, k = 10 (SURVEY 8(d),
+    M4 'plain L2 at d = 100'): the shape north_star reserves for tensor cores.  One GPU; same timing rules."""
+    import torch
+
+    import ompl_b200 as ob
+    from ompl_b200._lib import check, lib
+
+    n, nq, k, d = 100_000, 65536, 10, 100
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device")
+    dev = torch.device("cuda", 0)
+    L = lib()
+    pts, qs = np.random.default_rng(4).random((n, d)), np.random.default_rng(5).random((nq, d))
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    nn.set_option("profile", 1)
+    d_q = torch.from_numpy(qs).to(dev)
+    d_ids = torch.empty((nq, k), dtype=torch.int64, device=dev)
+    d_d = torch.empty((nq, k), dtype=torch.float64, device=dev)
+    h_ids, h_d, h_cnt = np.empty((nq, k), np.uint64), np.empty((nq, k)), np.empty(nq, np.uint32)
+    for a in (qs, h_ids, h_d):
+        torch.cuda.cudart().cudaHostRegister(a.ctypes.data, a.nbytes, 0)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    stream = torch.cuda.current_stream()
+    sptr = C.c_void_p(stream.cuda_stream)
+
+    def step_device():
+        check(L.omplcu_nn_knn_device(nn.handle, d_q.data_ptr(), nq, k, d_ids.data_ptr(), d_d.data_ptr(), sptr))
+
+    def step_e2e():
+        check(L.omplcu_nn_knn(nn.handle, qs.ctypes.data, nq, k, h_ids.ctypes.data, h_d.ctypes.data, h_cnt.ctypes.data))
+
+    def timed(step, steps, warmup):
+        for _ in range(warmup):
+            flush.fill_(1)
+            step()
+        torch.cuda.synchronize()
+        ms = 0.0
+        for _ in range(steps):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(stream)
+            step()
+            b.record(stream)
+            b.synchronize()
+            ms += a.elapsed_time(b)
+        return ms
+
+    l0 = nn.stat("launches")
+    sampler = ClockSampler(0)
+    for _ in range(args.warmup):
+        step_device()
+    sampler.start()
+    dev_ms = timed(step_device, args.steps, 0)
+    clocks = sampler.stop()
+    launches = (nn.stat("launches") - l0) * args.steps // (args.steps + args.warmup)
+    scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
+    e2e_ms = timed(step_e2e, args.steps, max(args.warmup, 1))
+    assert (d_ids.cpu().numpy().astype(np.uint64) == h_ids).all()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except OSError:
+        pass
+    tpeak = peaks.get("bf16_tflops", 2250.0)
+    kpad = (3 * d + 3 + 31) // 32 * 32
+    pairs = float(nq) * n
+    t_step = dev_ms / args.steps
+    ach = 3.0 * d * pairs / (scan_ns * 1e-9) / 1e12
+    out = {
+        "metric": "kNN queries/sec (k=10, 100K states, d=100)", "value": nq / (t_step * 1e-3), "unit": UNIT, "n_gpus": 1,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_step, "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16x2 split filter on tensor cores (f32 accumulate) + f64 exact re-rank", "data": "synthetic",
+        "config": {"workload": "M4 plain L2: RealVectorStateSpace(100), 100K states, 64K queries, k=10",
+                   "n_states": n, "n_queries": nq, "k": k, "dim": d},
+        "l2": "flushed between timed iterations (256 MB write)", "clocks": clocks,
+        "e2e": {"value": nq / (e2e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes),
+                "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes)},
+        "gpu_launches": int(launches),
+        "roofline": {"bound": "tensor", "kernel": "knn_scan_tc_kernel<16,1,TS> (query tile in TMEM)", "achieved": ach,
+                     "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
+                     "traffic": ncu_traffic("r2_scan_tc_d100_ncu_summary.csv"),
+                     "traffic_unit": "bytes/launch (profiles/r2_scan_tc_d100_ncu_summary.csv)",
+                     "flops_per_pair_algorithmic": 3 * d, "flops_per_pair_executed": 2 * kpad,
+                     "frac_executed": 2.0 * kpad * pairs / (scan_ns * 1e-9) / 1e12 / tpeak,
+                     "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
+                     "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks
+                     else "fallback 2250 TFLOP/s"},
+        "exact_fallback_queries": int(nn.stat("last_fallbacks")),
+    }
+    if not args.no_cpu:
+        from oracle import oracle_py as orc
+
+        cores = host_threads()
+        m = 64 * cores
+        t0 = time.perf_counter()
+        oi, od = orc.knn(orc.space_rv(d), pts, qs[:m], k, nthreads=cores)
+        secs = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": m / secs, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"first {m} of the 65536 queries, {cores} threads, NearestNeighborsLinear "
+                                         "restatement (oracle port)",
+                               "matches_gpu": bool((h_ids[:m] == oi).all() and (h_d[:m] == od).all())}
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -706,11 +816,16 @@ def main():
     ap.add_argument("--fp32-scan", action="store_true", help="use the FP32-pipe scan kernel instead of the tensor-core scan")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline legs (profiling runs)")
     ap.add_argument("--no-motion", action="store_true", help="skip the motion-validity block (profiling runs)")
+    ap.add_argument("--workload", default="m1", choices=["m1", "m4"],
+                    help="m1: the metric's workload (default). m4: SURVEY 8(d) 'plain L2 at d = 100' (100K states, 65536 "
+                         "queries, k = 10), the dense-contraction shape of the tensor-core path; same JSON contract, N = 1")
     args = ap.parse_args()
     if args.states:
         global N_STATES
         N_STATES = args.states  # scaling studies on larger roadmaps; the default run is BASELINE's 1M states
-    if args.impl == "reference":
+    if args.workload == "m4":
+        run_m4(args)
+    elif args.impl == "reference":
         run_reference_arm(args)
     else:
         run_gpu_arm(args)
