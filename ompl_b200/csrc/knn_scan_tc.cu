@@ -524,7 +524,7 @@ namespace omplcu
                                 mbar_wait(&S->t_empty[b], ((jt >> 1) & 1) ^ 1);
                                 tc_fence_after();
                                 const uint64_t bh = bd + h * ((TC_PT / 2 / 8) * TC_SBO >> 4);  // rows 64 h .. 64 h + 63
-                                if (leader && !(P.diag & 8))
+                                if (leader && !(DBG && (P.diag & 8)))
                                 {
                                     umma_bf16(tmem + b * (TC_PT / 2), ad, bh, idesc64, 0u);
                                     umma_bf16(tmem + b * (TC_PT / 2), ad + (2 * TC_LBO >> 4), bh + (2 * TC_LBO >> 4), idesc64, 1u);
@@ -563,7 +563,7 @@ namespace omplcu
                             {
                                 // A: 8 columns per K = 16 step, chunk kc starts at column kc * kw * 4
                                 const uint32_t ac = tmem + (uint32_t)kc * (uint32_t)kw * 4u;
-                                if (leader && !(P.diag & 8))
+                                if (leader && !(DBG && (P.diag & 8)))
                                 {
                                     umma_bf16_ts(dcol, ac, bd, idesc, kc ? 1u : 0u);
                                     umma_bf16_ts(dcol, ac + 8, bd + (2 * TC_LBO >> 4), idesc, 1u);
@@ -574,7 +574,7 @@ namespace omplcu
                                     }
                                 }
                             }
-                            else if (leader && !(P.diag & 8))  // diagnostics: barriers and commits only
+                            else if (leader && !(DBG && (P.diag & 8)))  // diagnostics: barriers and commits only
                             {
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
                                 umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
@@ -650,7 +650,7 @@ namespace omplcu
                         m1 = fminf(m1, fminf(__uint_as_float(v[i + 2]), __uint_as_float(v[i + 3])));
                     }
                     const float mn = fminf(m0, m1);
-                    if (mn < thr && !(P.diag & 4))
+                    if (mn < thr && !(DBG && (P.diag & 4)))
                     {
                         // the columns that beat the threshold at entry; m0 covers columns 0,1 mod 4, m1 columns 2,3
                         // mod 4, so usually only one of the two halves has to be looked at
@@ -729,16 +729,15 @@ namespace omplcu
                             mbar_wait(&S->t_full[b], (jt >> 1) & 1);
                             tc_fence_after();
                             const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + b * (TC_PT / 2);
-                            if (!(P.diag & 2))
+                            if (!(DBG && (P.diag & 2)))
                             {
                                 uint32_t ra[W];
 #pragma unroll 1
                                 for (int c = 0; c < TC_PT / 2 / W; ++c)
                                 {
-                                    __syncwarp();
                                     tmem_ld_issue(taddr + c * W, ra);
                                     tmem_ld_wait(ra);
-                                    if (DBG)
+                                    if (DBG && P.dbg)
                                         tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + h * (TC_PT / 2) + c * W);
                                     step(ra, slot0 + h * (TC_PT / 2) + c * W);
                                 }
@@ -752,26 +751,23 @@ namespace omplcu
                     mbar_wait(&S->t_full[buf], (uint32_t)((job / NBUF) & 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + ACC0 + (uint32_t)buf * TC_PT;
-                    if (!(P.diag & 2))
+                    if (!(DBG && (P.diag & 2)))
                     {
                         {
                             uint32_t ra[W], rb[W];
-                            __syncwarp();
                             tmem_ld_issue(taddr, ra);
 #pragma unroll 1
                             for (int c = 0; c < TC_PT / W; c += 2)
                             {
-                                __syncwarp();
                                 tmem_ld_wait(ra);
                                 tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
-                                if (DBG)
+                                if (DBG && P.dbg)
                                     tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
                                 step(ra, slot0 + c * W);
-                                __syncwarp();
                                 tmem_ld_wait(rb);
                                 if (c + 2 < TC_PT / W)
                                     tmem_ld_issue(taddr + (c + 2) * W, ra);
-                                if (DBG)
+                                if (DBG && P.dbg)
                                     tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
                                 step(rb, slot0 + (c + 1) * W);
                             }
@@ -1119,7 +1115,7 @@ namespace omplcu
         void tc_launch(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
             const size_t smem = tc_smem_bytes(P.sh, P.nstages, L);
-            if (P.dbg)
+            if (P.dbg || (P.diag & ~1))  // raw-value dump or a diagnostic variant: the instrumented instantiation
             {
                 CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, NA, true>,
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -1141,7 +1137,7 @@ namespace omplcu
         template <int L>
         void tc_launch_na(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
-            if (P.sh.na == 1 && P.ts && !P.dbg && P.sh.kpad() <= 512)
+            if (P.sh.na == 1 && P.ts && !P.dbg && !(P.diag & ~1) && P.sh.kpad() <= 512)
                 tc_launch_ts<L>(P, grid, s);
             else if (P.sh.na == 4)
                 tc_launch<L, 4>(P, grid, s);
