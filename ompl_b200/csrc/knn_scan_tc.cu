@@ -221,6 +221,26 @@ namespace omplcu
         {
             asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
         }
+        // mbarrier wait / arrive on a precomputed shared-memory address.  The wait carries a suspend-time hint:
+        // the thread sleeps in hardware until the phase completes (or the hint expires) instead of re-issuing
+        // try_wait -- in round 1 a quarter of the kernel's executed instructions were polls.
+        __device__ __forceinline__ void mbar_wait_addr(uint32_t bar, uint32_t parity)
+        {
+            asm volatile("{\n"
+                         ".reg .pred p;\n"
+                         "WAITA_LOOP:\n"
+                         "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1, %2;\n"
+                         "@p bra WAITA_DONE;\n"
+                         "bra WAITA_LOOP;\n"
+                         "WAITA_DONE:\n"
+                         "}\n" ::"r"(bar),
+                         "r"(parity), "r"(1000000u)
+                         : "memory");
+        }
+        __device__ __forceinline__ void mbar_arrive_addr(uint32_t bar)
+        {
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+        }
         // one lane of a converged warp
         __device__ __forceinline__ bool elect_one()
         {
@@ -451,7 +471,7 @@ namespace omplcu
                         }
                         if (!TS && t != cur)
                         {
-                            mbar_wait(&S->a_empty, aph ^ 1);  // the MMAs of the previous super-tile are done with sA
+                            mbar_wait_addr(smem_u32(&S->a_empty), aph ^ 1);  // the MMAs of the previous super-tile are done with sA
                             mbar_expect_tx(&S->a_full, NA * a_tile_bytes);
                             tma_bulk_g2s(sA, P.qimg + (size_t)t * NA * (a_tile_bytes / 2), NA * a_tile_bytes,
                                          &S->a_full);
@@ -461,7 +481,7 @@ namespace omplcu
                         const uint16_t *src = P.pimg + (size_t)pt * (a_tile_bytes / 2);
                         for (int kc = 0; kc < nkc; ++kc)
                         {
-                            mbar_wait(&S->empty[st], ph ^ 1);
+                            mbar_wait_addr(smem_u32(&S->empty[st]), ph ^ 1);
                             mbar_expect_tx(&S->full[st], chunk_bytes);
                             tma_bulk_g2s(sB + (size_t)st * chunk_bytes, src + (size_t)kc * (chunk_bytes / 2),
                                          chunk_bytes, &S->full[st]);
@@ -504,7 +524,7 @@ namespace omplcu
                             if (cur != ~0ull)
                                 if (leader)
                                     umma_commit(&S->a_empty);
-                            mbar_wait(&S->a_full, aph);
+                            mbar_wait_addr(smem_u32(&S->a_full), aph);
                             aph ^= 1;
                             cur = t;
                         }
@@ -514,14 +534,14 @@ namespace omplcu
                             // alternately with the two halves of the point tile, so that the selection of one half
                             // overlaps the MMAs and the hand-over of the other.
                             constexpr uint32_t idesc64 = umma_idesc_bf16(TC_QT, TC_PT / 2);
-                            mbar_wait(&S->full[st], ph);
+                            mbar_wait_addr(smem_u32(&S->full[st]), ph);
                             const uint64_t ad = desc0 + (a0 >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
 #pragma unroll
                             for (uint32_t h = 0; h < 2; ++h)
                             {
                                 const uint32_t jt = 2 * (job >> 2) + h, b = 2 * (uint32_t)a + (jt & 1);
-                                mbar_wait(&S->t_empty[b], ((jt >> 1) & 1) ^ 1);
+                                mbar_wait_addr(smem_u32(&S->t_empty[b]), ((jt >> 1) & 1) ^ 1);
                                 tc_fence_after();
                                 const uint64_t bh = bd + h * ((TC_PT / 2 / 8) * TC_SBO >> 4);  // rows 64 h .. 64 h + 63
                                 if (leader && !(DBG && (P.diag & 8)))
@@ -552,9 +572,9 @@ namespace omplcu
                         const uint32_t dcol = tmem + ACC0 + buf * TC_PT;
                         for (int kc = 0; kc < nkc; ++kc)
                         {
-                            mbar_wait(&S->full[st], ph);
+                            mbar_wait_addr(smem_u32(&S->full[st]), ph);
                             if (kc == 0)
-                                mbar_wait(&S->t_empty[buf], ((job / NBUF) & 1) ^ 1);
+                                mbar_wait_addr(smem_u32(&S->t_empty[buf]), ((job / NBUF) & 1) ^ 1);
                             tc_fence_after();
                             // descriptors differ in the start address only (low word, units of 16 bytes)
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
@@ -684,6 +704,12 @@ namespace omplcu
                         }
                     }
                 };
+                // loop invariants the compiler does not hoist by itself (they hang off run-time shapes): the
+                // shared addresses of this tile's two accumulator barriers and the TMEM address of its lane quadrant
+                const uint32_t tfull0 = smem_u32(&S->t_full[2 * a]), tempty0 = smem_u32(&S->t_empty[2 * a]);
+                const uint32_t tq = tmem + ((uint32_t)(wq * 32) << 16);
+                (void)tfull0;
+                (void)tempty0;
                 unsigned long long cur = ~0ull, job = a, t = 0, pt = 0;
                 for (unsigned long long u = u0; u < u1; ++u, job += NA, ++pt)
                 {
@@ -698,7 +724,7 @@ namespace omplcu
                         if constexpr (TS)
                         {
                             // this thread's query row of the operand image -> its TMEM lane, columns [0, kpad / 2)
-                            mbar_wait(&S->a_empty, aph_sel ^ 1);  // the MMAs of the previous super-tile have read A
+                            mbar_wait_addr(smem_u32(&S->a_empty), aph_sel ^ 1);  // the MMAs of the previous super-tile have read A
                             aph_sel ^= 1;
                             tc_fence_after();
                             const uint16_t *qrow = P.qimg + (size_t)t * (a_tile_bytes / 2) +
@@ -725,10 +751,10 @@ namespace omplcu
 #pragma unroll 1
                         for (uint32_t h = 0; h < 2; ++h)
                         {
-                            const uint32_t jt = 2 * (uint32_t)(job >> 2) + h, b = 2 * (uint32_t)a + (jt & 1);
-                            mbar_wait(&S->t_full[b], (jt >> 1) & 1);
+                            const uint32_t jt = 2 * (uint32_t)(job >> 2) + h, bb = jt & 1, b = 2 * (uint32_t)a + bb;
+                            mbar_wait_addr(tfull0 + 8 * bb, (jt >> 1) & 1);
                             tc_fence_after();
-                            const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + b * (TC_PT / 2);
+                            const uint32_t taddr = tq + b * (TC_PT / 2);
                             if (!(DBG && (P.diag & 2)))
                             {
                                 uint32_t ra[W];
@@ -743,12 +769,12 @@ namespace omplcu
                                 }
                             }
                             tc_fence_before();
-                            mbar_arrive(&S->t_empty[b]);
+                            mbar_arrive_addr(tempty0 + 8 * bb);
                         }
                         continue;
                     }
                     const int buf = (int)(job & (NBUF - 1));
-                    mbar_wait(&S->t_full[buf], (uint32_t)((job / NBUF) & 1));
+                    mbar_wait_addr(smem_u32(&S->t_full[buf]), (uint32_t)((job / NBUF) & 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + ACC0 + (uint32_t)buf * TC_PT;
                     if (!(DBG && (P.diag & 2)))
@@ -871,7 +897,7 @@ namespace omplcu
                         }
                         if (t != cur)
                         {
-                            mbar_wait(&S->a_empty, aph ^ 1);
+                            mbar_wait_addr(smem_u32(&S->a_empty), aph ^ 1);
                             mbar_expect_tx(&S->a_full, NA * a_tile_bytes);
                             tma_bulk_g2s(sA, P.qimg + (size_t)t * NA * (a_tile_bytes / 2), NA * a_tile_bytes,
                                          &S->a_full);
@@ -881,7 +907,7 @@ namespace omplcu
                         const uint16_t *src = P.pimg + (size_t)pt * (a_tile_bytes / 2);
                         for (int kc = 0; kc < nkc; ++kc)
                         {
-                            mbar_wait(&S->empty[st], ph ^ 1);
+                            mbar_wait_addr(smem_u32(&S->empty[st]), ph ^ 1);
                             mbar_expect_tx(&S->full[st], chunk_bytes);
                             tma_bulk_g2s(sB + (size_t)st * chunk_bytes, src + (size_t)kc * (chunk_bytes / 2),
                                          chunk_bytes, &S->full[st]);
@@ -918,7 +944,7 @@ namespace omplcu
                         {
                             if (cur != ~0ull && leader)
                                 umma_commit(&S->a_empty);
-                            mbar_wait(&S->a_full, aph);
+                            mbar_wait_addr(smem_u32(&S->a_full), aph);
                             aph ^= 1;
                             cur = t;
                         }
@@ -926,9 +952,9 @@ namespace omplcu
                         const uint32_t dcol = tmem + buf * TC_PT;
                         for (int kc = 0; kc < nkc; ++kc)
                         {
-                            mbar_wait(&S->full[st], ph);
+                            mbar_wait_addr(smem_u32(&S->full[st]), ph);
                             if (kc == 0)
-                                mbar_wait(&S->t_empty[buf], ((job / TC_ACC) & 1) ^ 1);
+                                mbar_wait_addr(smem_u32(&S->t_empty[buf]), ((job / TC_ACC) & 1) ^ 1);
                             tc_fence_after();
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
@@ -1025,7 +1051,7 @@ namespace omplcu
                     }
                     const uint32_t slot0 = (uint32_t)(pt * TC_PT);
                     const int buf = (int)(job & (TC_ACC - 1));
-                    mbar_wait(&S->t_full[buf], (uint32_t)((job / TC_ACC) & 1));
+                    mbar_wait_addr(smem_u32(&S->t_full[buf]), (uint32_t)((job / TC_ACC) & 1));
                     tc_fence_after();
                     const uint32_t taddr = tmem + ((uint32_t)(wq * 32) << 16) + (uint32_t)buf * TC_PT;
                     if (!no_sel)
