@@ -32,7 +32,7 @@ namespace omplcu
             return 32 * (1 + NA + 4 * NA);
         }
         constexpr int TC_ACC = 4;  // accumulator buffers (4 x 128 = all 512 TMEM columns)
-        constexpr int TC_MAX_STAGES = 8;
+        constexpr int TC_MAX_STAGES = 12;
 
         // ---------------- operand images ----------------
         // Within a 128-row block the image is [chunk][column group j][row group g][row r][8 BF16]:
@@ -183,6 +183,41 @@ namespace omplcu
         {
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                              smem_u32(bar))
+                         : "memory");
+        }
+        // ---- CTA pairs (cluster of 2): both CTAs scan the same point tiles for two different query tiles; each
+        // fetches half of every chunk and the copy is multicast into both CTAs' rings, so the L2 serves every
+        // chunk once per pair
+        __device__ __forceinline__ uint32_t cluster_ctarank()
+        {
+            uint32_t r;
+            asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+            return r;
+        }
+        __device__ __forceinline__ void cluster_sync_all()
+        {
+            asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        }
+        __device__ __forceinline__ void mbar_fence_init_cluster()
+        {
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        }
+        // the bytes land at the same offset of every CTA in `mask`, and complete_tx is signalled on the barrier at
+        // the same offset of each of them
+        __device__ __forceinline__ void tma_bulk_g2s_mc(void *dst, const void *src, uint32_t bytes, uint64_t *bar,
+                                                        uint16_t mask)
+        {
+            asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1], "
+                         "%2, [%3], %4;" ::"r"(smem_u32(dst)),
+                         "l"(src), "r"(bytes), "r"(smem_u32(bar)), "h"(mask)
+                         : "memory");
+        }
+        // umma_commit arriving on the barrier at this offset in every CTA of `mask`
+        __device__ __forceinline__ void umma_commit_mc(uint64_t *bar, uint16_t mask)
+        {
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                             smem_u32(bar)),
+                         "h"(mask)
                          : "memory");
         }
         // D[tmem] (+)= A[smem] * B[smem]^T, BF16 x BF16 -> FP32, issued by one thread
@@ -407,19 +442,27 @@ namespace omplcu
         // tensor pipe 39 %, tc_wavefronts_mem_shared 38 %).  With A in tensor memory (kpad / 2 columns, written by
         // the selection warps with tcgen05.st at the start of a query super-tile: thread = lane = query) an MMA
         // reads only B.  Columns [0, 256): A; [256, 512): two 128-column accumulators (job j -> buffer j % 2).
-        template <int L, int NA, bool DBG, bool TS = false>
+        // PAIR (TS only): CTAs 2c and 2c + 1 are a cluster and together own the work piece of "CTA" c of a grid
+        // half the size, on super-tiles of TWO query tiles: rank r takes tile 2 t + r.  Both walk the same point
+        // tiles in step; rank r fetches half r of every chunk and multicasts it into both rings, a stage is free
+        // once both CTAs' MMAs have read it (multicast commit, empty barriers count 2).  The L2 -> SM feed is what
+        // bounds the d >= 53 shapes (feed alone 2.75 of 3.3 ms at d = 100, at the chip's L2 output rate).
+        template <int L, int NA, bool DBG, bool TS = false, bool PAIR = false>
         __global__ void __launch_bounds__(tc_threads(NA), 1) knn_scan_tc_kernel(const TcScanParams P)
         {
             static_assert(!TS || NA == 1, "the TMEM-resident query tile is built for one resident tile");
+            static_assert(!PAIR || TS, "CTA pairs are built on the TMEM-resident query tile");
+            constexpr int TPS = PAIR ? 2 : NA;  // query tiles per super-tile
+            const uint32_t crank = PAIR ? cluster_ctarank() : 0u;
             constexpr uint32_t NBUF = TS ? 2u : (uint32_t)TC_ACC;      // accumulator buffers of the general path
             constexpr uint32_t ACC0 = TS ? 256u : 0u;                  // first accumulator column
             extern __shared__ __align__(1024) uint8_t tc_smem[];
             constexpr int LS = L + 4;
-            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw;
+            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw, k16 = P.sh.k16;
             const uint32_t chunk_bytes = (uint32_t)kw * 2048u;
             const uint32_t a_tile_bytes = (uint32_t)nkc * chunk_bytes;
-            uint8_t *sA = tc_smem;                                    // [NA][nkc][chunk]
-            uint8_t *sB = sA + (size_t)NA * a_tile_bytes;             // [nst][chunk]
+            uint8_t *sA = tc_smem;                                    // [NA][nkc][chunk] (TS: not there, the tile lives in TMEM)
+            uint8_t *sB = sA + (TS ? 0 : (size_t)NA * a_tile_bytes);  // [nst][chunk]
             float *lv = reinterpret_cast<float *>(sB + (size_t)nst * chunk_bytes);  // [NA][128][LS]
             uint32_t *li = reinterpret_cast<uint32_t *>(lv + NA * TC_QT * LS);      // [NA][L][128]
             float *scr = reinterpret_cast<float *>(li + NA * L * TC_QT);            // [4 NA warps][W][32] slow-path staging
@@ -429,7 +472,8 @@ namespace omplcu
             // the warp index through a shuffle: the compiler then knows that it is warp-uniform and keeps the
             // issuer's descriptors and loop counters in uniform registers
             const int tid = threadIdx.x, warp = __shfl_sync(0xffffffffu, tid >> 5, 0), lane = tid & 31;
-            const unsigned long long TU = P.total_units, U = P.units, G = gridDim.x, g = blockIdx.x;
+            const unsigned long long TU = P.total_units, U = P.units, G = PAIR ? gridDim.x / 2 : gridDim.x,
+                                     g = PAIR ? blockIdx.x / 2 : blockIdx.x;
             const unsigned long long u0 = TU * g / G, u1 = TU * (g + 1) / G;
 
             if (tid == 0)
@@ -437,7 +481,7 @@ namespace omplcu
                 for (int i = 0; i < TC_MAX_STAGES; ++i)
                 {
                     mbar_init(&S->full[i], 1);
-                    mbar_init(&S->empty[i], NA);
+                    mbar_init(&S->empty[i], TPS);
                 }
                 mbar_init(&S->a_full, TS ? TC_QT : 1);
                 mbar_init(&S->a_empty, NA);
@@ -447,11 +491,15 @@ namespace omplcu
                     mbar_init(&S->t_empty[i], TC_QT);
                 }
                 mbar_fence_init();
+                if (PAIR)
+                    mbar_fence_init_cluster();
             }
             if (warp == 1)
                 tmem_alloc(&S->tmem_base, 512);
             tc_fence_before();
             __syncthreads();
+            if (PAIR)
+                cluster_sync_all();  // the peer's barriers exist before anything is multicast at them
             tc_fence_after();
             const uint32_t tmem = S->tmem_base;
 
@@ -462,6 +510,8 @@ namespace omplcu
                     int st = 0;
                     uint32_t ph = 0, aph = 0;
                     unsigned long long cur = ~0ull, t = 0, pt = 0;
+                    (void)aph;
+                    (void)cur;
                     for (unsigned long long u = u0; u < u1; ++u, ++pt)
                     {
                         if (u == u0 || pt == U)
@@ -483,6 +533,11 @@ namespace omplcu
                         {
                             mbar_wait_addr(smem_u32(&S->empty[st]), ph ^ 1);
                             mbar_expect_tx(&S->full[st], chunk_bytes);
+                            if (PAIR)  // my half, into both rings; the peer sends the other half
+                                tma_bulk_g2s_mc(sB + (size_t)st * chunk_bytes + crank * (chunk_bytes / 2),
+                                                src + (size_t)kc * (chunk_bytes / 2) + crank * (chunk_bytes / 4),
+                                                chunk_bytes / 2, &S->full[st], (uint16_t)3);
+                            else
                             tma_bulk_g2s(sB + (size_t)st * chunk_bytes, src + (size_t)kc * (chunk_bytes / 2),
                                          chunk_bytes, &S->full[st]);
                             if (++st == nst)
@@ -546,12 +601,15 @@ namespace omplcu
                                 const uint64_t bh = bd + h * ((TC_PT / 2 / 8) * TC_SBO >> 4);  // rows 64 h .. 64 h + 63
                                 if (leader && !(DBG && (P.diag & 8)))
                                 {
+                                    // k16 <= 4 here; spelled out: a counted loop costs the issuer ~2 % of the kernel
                                     umma_bf16(tmem + b * (TC_PT / 2), ad, bh, idesc64, 0u);
-                                    umma_bf16(tmem + b * (TC_PT / 2), ad + (2 * TC_LBO >> 4), bh + (2 * TC_LBO >> 4), idesc64, 1u);
-                                    if (kw == 8)
+                                    if (k16 > 1)
+                                        umma_bf16(tmem + b * (TC_PT / 2), ad + (2 * TC_LBO >> 4), bh + (2 * TC_LBO >> 4), idesc64, 1u);
+                                    if (k16 > 2)
                                     {
                                         umma_bf16(tmem + b * (TC_PT / 2), ad + 2 * (2 * TC_LBO >> 4), bh + 2 * (2 * TC_LBO >> 4), idesc64, 1u);
-                                        umma_bf16(tmem + b * (TC_PT / 2), ad + 3 * (2 * TC_LBO >> 4), bh + 3 * (2 * TC_LBO >> 4), idesc64, 1u);
+                                        if (k16 > 3)
+                                            umma_bf16(tmem + b * (TC_PT / 2), ad + 3 * (2 * TC_LBO >> 4), bh + 3 * (2 * TC_LBO >> 4), idesc64, 1u);
                                     }
                                 }
                                 if (leader)
@@ -576,6 +634,8 @@ namespace omplcu
                             if (kc == 0)
                                 mbar_wait_addr(smem_u32(&S->t_empty[buf]), ((job / NBUF) & 1) ^ 1);
                             tc_fence_after();
+                            // MMAs of this chunk: the last chunk stops where K ends (the rest is zero padding)
+                            const uint32_t nm = (uint32_t)min(kw / 2, k16 - kc * (kw / 2));
                             // descriptors differ in the start address only (low word, units of 16 bytes)
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
@@ -586,27 +646,23 @@ namespace omplcu
                                 if (leader && !(DBG && (P.diag & 8)))
                                 {
                                     umma_bf16_ts(dcol, ac, bd, idesc, kc ? 1u : 0u);
-                                    umma_bf16_ts(dcol, ac + 8, bd + (2 * TC_LBO >> 4), idesc, 1u);
-                                    if (kw == 8)
-                                    {
-                                        umma_bf16_ts(dcol, ac + 16, bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
-                                        umma_bf16_ts(dcol, ac + 24, bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
-                                    }
+                                    for (uint32_t i = 1; i < nm; ++i)
+                                        umma_bf16_ts(dcol, ac + 8 * i, bd + i * (2 * TC_LBO >> 4), idesc, 1u);
                                 }
                             }
                             else if (leader && !(DBG && (P.diag & 8)))  // diagnostics: barriers and commits only
                             {
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
-                                umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
-                                if (kw == 8)
-                                {
-                                    umma_bf16(dcol, ad + 2 * (2 * TC_LBO >> 4), bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
-                                    umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
-                                }
+                                for (uint32_t i = 1; i < nm; ++i)
+                                    umma_bf16(dcol, ad + i * (2 * TC_LBO >> 4), bd + i * (2 * TC_LBO >> 4), idesc, 1u);
                             }
                             if (leader)
                             {
-                                umma_commit(&S->empty[st]);  // the stage is free once all NA issuers' MMAs have read it
+                                // the stage is free once all NA issuers' (PAIR: both CTAs') MMAs have read it
+                                if (PAIR)
+                                    umma_commit_mc(&S->empty[st], (uint16_t)3);
+                                else
+                                    umma_commit(&S->empty[st]);
                                 if (kc == nkc - 1)
                                     umma_commit(&S->t_full[buf]);
                             }
@@ -650,7 +706,7 @@ namespace omplcu
                     const unsigned long long x = t * U;
                     const unsigned long long gfirst = ((x + 1) * G + TU - 1) / TU - 1;
                     const unsigned seg = (unsigned)(g - gfirst);
-                    const size_t q = ((size_t)t * NA + a) * TC_QT + qrow;
+                    const size_t q = ((size_t)t * TPS + (PAIR ? (int)crank : a)) * TC_QT + qrow;
                     P.cand_thr[(size_t)seg * P.qpad + q] = thr;
                     for (int i = 0; i < L; ++i)
                         P.cand_ids[((size_t)seg * L + i) * P.qpad + q] = liq[i * TC_QT];
@@ -727,7 +783,7 @@ namespace omplcu
                             mbar_wait_addr(smem_u32(&S->a_empty), aph_sel ^ 1);  // the MMAs of the previous super-tile have read A
                             aph_sel ^= 1;
                             tc_fence_after();
-                            const uint16_t *qrow = P.qimg + (size_t)t * (a_tile_bytes / 2) +
+                            const uint16_t *qrow = P.qimg + (size_t)(t * TPS + crank) * (a_tile_bytes / 2) +
                                                    (size_t)(qrow_idx >> 3) * (TC_SBO / 2) + (size_t)(qrow_idx & 7) * 8;
                             const uint32_t ta = tmem + ((uint32_t)(wq * 32) << 16);
                             for (int kc = 0; kc < nkc; ++kc)
@@ -764,7 +820,7 @@ namespace omplcu
                                     tmem_ld_issue(taddr + c * W, ra);
                                     tmem_ld_wait(ra);
                                     if (DBG && P.dbg)
-                                        tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + h * (TC_PT / 2) + c * W);
+                                        tc_dump<W>(P, ra, ((size_t)t * TPS + (PAIR ? (int)crank : a)) * TC_QT + qrow, slot0 + h * (TC_PT / 2) + c * W);
                                     step(ra, slot0 + h * (TC_PT / 2) + c * W);
                                 }
                             }
@@ -788,13 +844,13 @@ namespace omplcu
                                 tmem_ld_wait(ra);
                                 tmem_ld_issue(taddr + (c + 1) * W, rb);  // in flight during the tree below
                                 if (DBG && P.dbg)
-                                    tc_dump<W>(P, ra, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + c * W);
+                                    tc_dump<W>(P, ra, ((size_t)t * TPS + (PAIR ? (int)crank : a)) * TC_QT + qrow, slot0 + c * W);
                                 step(ra, slot0 + c * W);
                                 tmem_ld_wait(rb);
                                 if (c + 2 < TC_PT / W)
                                     tmem_ld_issue(taddr + (c + 2) * W, ra);
                                 if (DBG && P.dbg)
-                                    tc_dump<W>(P, rb, ((size_t)t * NA + a) * TC_QT + qrow, slot0 + (c + 1) * W);
+                                    tc_dump<W>(P, rb, ((size_t)t * TPS + (PAIR ? (int)crank : a)) * TC_QT + qrow, slot0 + (c + 1) * W);
                                 step(rb, slot0 + (c + 1) * W);
                             }
                         }
@@ -807,6 +863,8 @@ namespace omplcu
             }
             tc_fence_before();
             __syncthreads();
+            if (PAIR)
+                cluster_sync_all();  // no CTA leaves while the peer may still multicast into it
             if (warp == 1)
             {
                 __syncwarp();
@@ -847,7 +905,7 @@ namespace omplcu
         {
             extern __shared__ __align__(1024) uint8_t tc_smem[];
             static_assert(W == 16 || W == 32, "columns per selection step");
-            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw;
+            const int nkc = P.sh.nkc, nst = P.nstages, kw = P.sh.kw, k16 = P.sh.k16;
             const uint32_t chunk_bytes = (uint32_t)kw * 2048u;
             const uint32_t a_tile_bytes = (uint32_t)nkc * chunk_bytes;
             uint8_t *sA = tc_smem;                         // [NA][nkc][chunk]
@@ -956,17 +1014,14 @@ namespace omplcu
                             if (kc == 0)
                                 mbar_wait_addr(smem_u32(&S->t_empty[buf]), ((job / TC_ACC) & 1) ^ 1);
                             tc_fence_after();
+                            const uint32_t nm = (uint32_t)min(kw / 2, k16 - kc * (kw / 2));
                             const uint64_t ad = desc0 + ((a0 + (uint32_t)kc * chunk_bytes) >> 4);
                             const uint64_t bd = desc0 + ((b0 + (uint32_t)st * chunk_bytes) >> 4);
                             if (leader && !no_mma)
                             {
                                 umma_bf16(dcol, ad, bd, idesc, kc ? 1u : 0u);
-                                umma_bf16(dcol, ad + (2 * TC_LBO >> 4), bd + (2 * TC_LBO >> 4), idesc, 1u);
-                                if (kw == 8)
-                                {
-                                    umma_bf16(dcol, ad + 2 * (2 * TC_LBO >> 4), bd + 2 * (2 * TC_LBO >> 4), idesc, 1u);
-                                    umma_bf16(dcol, ad + 3 * (2 * TC_LBO >> 4), bd + 3 * (2 * TC_LBO >> 4), idesc, 1u);
-                                }
+                                for (uint32_t i = 1; i < nm; ++i)
+                                    umma_bf16(dcol, ad + i * (2 * TC_LBO >> 4), bd + i * (2 * TC_LBO >> 4), idesc, 1u);
                             }
                             if (leader)
                             {
@@ -1094,19 +1149,61 @@ namespace omplcu
         }
     }  // namespace
 
-    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L)
+    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L, bool ts)
     {
         const size_t chunk = (size_t)sh.kw * 2048;
-        return (size_t)sh.na * sh.nkc * chunk + (size_t)nstages * chunk + (size_t)sh.na * TC_QT * (2 * L + 4) * 4 +
-               (size_t)4 * sh.na * 32 * 32 * 4 + sizeof(TcSmem) + 64;
+        return (ts ? 0 : (size_t)sh.na * sh.nkc * chunk) + (size_t)nstages * chunk +
+               (size_t)sh.na * TC_QT * (2 * L + 4) * 4 + (size_t)4 * sh.na * 32 * 32 * 4 + sizeof(TcSmem) + 64;
     }
 
-    int tc_pick_stages(const TcShape &sh, int L)
+    int tc_pick_stages(const TcShape &sh, int L, bool ts)
     {
-        for (int st = TC_MAX_STAGES; st >= 3; --st)
-            if (tc_smem_bytes(sh, st, L) <= 227 * 1024)
+        for (int st = TC_MAX_STAGES; st >= 2; --st)
+            if (tc_smem_bytes(sh, st, L, ts) <= 227 * 1024)
                 return st;
         return 0;
+    }
+
+    TcShape tc_shape(int D)
+    {
+        static const int mc = [] {
+            const char *e = std::getenv("OMPLCU_TC_CHUNK_MMAS");
+            const int x = e ? std::atoi(e) : 0;
+            return x > 0 && x <= 32 ? x : 10;
+        }();
+        TcShape s;
+        s.k16 = (3 * D + 3 + 15) / 16;
+        s.na = s.k16 <= 4 ? 4 : (s.k16 <= 10 ? 2 : 1);  // d <= 20: 4 tiles (<= 32 KB of query operand), d <= 52: 2, else 1
+        s.nkc = 1;
+        s.kw = 2 * s.k16;
+        if (s.na == 4)
+            return s;  // the 4-tile kernel wants K in one chunk (<= 16 KB)
+        // measured at d = 100 / 64 / 32 (profiles/r2_experiments.md): a padded column group costs its bytes, one more
+        // chunk about as much as 0.6 MMA slots
+        long best = -1;
+        for (int nkc = (s.k16 + mc - 1) / mc; nkc <= s.k16; ++nkc)
+        {
+            TcShape c = s;
+            c.nkc = nkc;
+            c.kw = 2 * ((s.k16 + nkc - 1) / nkc);
+            // a k <= 10 query must get 3 stages and 48 KB in flight (query tile in tensor memory where the shape
+            // allows it), and 2 stages with the tile in shared memory (option tc_ts = 0, diagnostics)
+            const int st = tc_pick_stages(c, 16, tc_ts_usable(c));
+            if (st < 3 || (size_t)st * c.kw * 2048 < 48 * 1024 || tc_pick_stages(c, 16, false) < 2)
+                continue;
+            const long cost = 10L * c.nkc * (c.kw / 2) + 6L * c.nkc;
+            if (best < 0 || cost < best)
+            {
+                best = cost;
+                s = c;
+            }
+        }
+        return s;
+    }
+
+    bool tc_ts_usable(const TcShape &sh)
+    {
+        return sh.na == 1 && sh.kpad() <= 512;  // the tile takes kpad / 2 of the 256 TMEM columns below the accumulators
     }
 
     void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint16_t *out, cudaStream_t s)
@@ -1155,15 +1252,44 @@ namespace omplcu
         template <int L>
         void tc_launch_ts(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
-            const size_t smem = tc_smem_bytes(P.sh, P.nstages, L);
+            const size_t smem = tc_smem_bytes(P.sh, P.nstages, L, true);
             CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, 1, false, true>,
                                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (P.diag & ~1)  // diagnostic switches live in the instrumented instantiation
+            {
+                CUDA_CHECK(cudaFuncSetAttribute(knn_scan_tc_kernel<L, 1, true, true>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+                knn_scan_tc_kernel<L, 1, true, true><<<grid, tc_threads(1), smem, s>>>(P);
+                return;
+            }
             knn_scan_tc_kernel<L, 1, false, true><<<grid, tc_threads(1), smem, s>>>(P);
+        }
+        template <int L>
+        void tc_launch_pair(const TcScanParams &P, unsigned grid, cudaStream_t s)  // grid: CTAs, even
+        {
+            const size_t smem = tc_smem_bytes(P.sh, P.nstages, L, true);
+            auto kern = (P.diag & ~1) ? knn_scan_tc_kernel<L, 1, true, true, true> : knn_scan_tc_kernel<L, 1, false, true, true>;
+            CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            cudaLaunchConfig_t cfg{};
+            cfg.gridDim = dim3(grid);
+            cfg.blockDim = dim3(tc_threads(1));
+            cfg.dynamicSmemBytes = smem;
+            cfg.stream = s;
+            cudaLaunchAttribute at[1];
+            at[0].id = cudaLaunchAttributeClusterDimension;
+            at[0].val.clusterDim.x = 2;
+            at[0].val.clusterDim.y = 1;
+            at[0].val.clusterDim.z = 1;
+            cfg.attrs = at;
+            cfg.numAttrs = 1;
+            CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, P));
         }
         template <int L>
         void tc_launch_na(const TcScanParams &P, unsigned grid, cudaStream_t s)
         {
-            if (P.sh.na == 1 && P.ts && !P.dbg && !(P.diag & ~1) && P.sh.kpad() <= 512)
+            if (P.ts && P.pair)
+                tc_launch_pair<L>(P, grid, s);
+            else if (P.ts)  // decided by the caller (tc_ts_usable, no diagnostics): the ring depth was sized for it
                 tc_launch_ts<L>(P, grid, s);
             else if (P.sh.na == 4)
                 tc_launch<L, 4>(P, grid, s);

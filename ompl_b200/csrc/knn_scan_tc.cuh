@@ -17,6 +17,7 @@
 
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <cstdlib>
 
 namespace omplcu
 {
@@ -25,11 +26,15 @@ namespace omplcu
     constexpr int TC_MAX_DIM = 128;
     constexpr int TC_MIN_BATCH = 1;     // "auto": measured faster than the FP32 scans down to a single query (0.51 vs 0.97 ms at 1M x 7-D)
 
-    // K = 3 d + 3, padded to a whole number of chunks.  A chunk is kw 16-byte column groups
-    // (kw = 4: 32 BF16, 8 KB per 128 rows; kw = 8: 64 BF16, 16 KB), whichever pads less.
+    // K = 3 d + 3 is covered by k16 = ceil(K / 16) tcgen05.mma instructions (K = 16 each).  The operand images are
+    // cut into nkc chunks of kw 16-byte column groups (kw even: two groups per MMA; 2 KB per group and 128 rows), a
+    // chunk being the unit of the TMA ring.  Every chunk costs a ring hand-shake and a tcgen05.commit on top of its
+    // MMAs (measured ~200 clk, profiles/r2_experiments.md), so chunks hold up to tc_chunk_mmas() MMAs; columns
+    // beyond 16 k16 are zero padding that is copied but never multiplied.
     struct TcShape
     {
         int kw, nkc, na;  // column groups per chunk, chunks, resident query tiles
+        int k16;          // MMAs per (query tile, point tile) pair
         __host__ __device__ int kpad() const
         {
             return nkc * kw * 8;
@@ -39,16 +44,10 @@ namespace omplcu
             return (size_t)kw * 8 * TC_PT;
         }
     };
-    inline TcShape tc_shape(int D)
-    {
-        const int k32 = (3 * D + 3 + 31) / 32;
-        TcShape s;
-        s.kw = (k32 % 2 == 0) ? 8 : 4;
-        s.nkc = (k32 % 2 == 0) ? k32 / 2 : k32;
-        const size_t a_bytes = (size_t)k32 * 32 * TC_QT * 2;
-        s.na = a_bytes <= 16384 ? 4 : (a_bytes <= 40960 ? 2 : 1);  // d <= 20: 4 tiles, d <= 52: 2, else 1
-        return s;
-    }
+    // The shape is a function of the dimension alone (the point image is built once and shared by all queries): fewest
+    // padded bytes plus a per-chunk charge, under "4 ring stages fit beside a k <= 10 query's lists" (knn_scan_tc.cu).
+    // OMPLCU_TC_CHUNK_MMAS caps the MMAs per chunk (tuning; default 10).
+    TcShape tc_shape(int D);
 
     // Scan-value error bound in units of u = 2^-24 times (pmax2 + 2 |qt| pmax), see DESIGN.md 3.5:
     //   3      pn as stored (rounding of the FP32 norm, as in the FP32 kernels)
@@ -61,7 +60,7 @@ namespace omplcu
     //   x 1.02 second-order terms of the above
     inline double tc_err_units(int D)
     {
-        return 1.02 * (3.0 + 768.0 + 32.0 * (tc_shape(D).kpad() / 16));
+        return 1.02 * (3.0 + 768.0 + 32.0 * ((3 * D + 3 + 15) / 16));
     }
 
     struct TcScanParams
@@ -77,6 +76,7 @@ namespace omplcu
         int diag;               // diagnostics: 1 swap descriptor fields, 2 no selection, 4 no insertion
         float *dbg;             // [qpad][units*TC_PT] raw scan values, or nullptr
         int ts;                 // list kernel, one resident tile: query tile as the TMEM-resident A operand
+        int pair;               // ts only: CTA pairs share every point chunk (grid = 2 x work pieces, super-tiles of 2 query tiles)
         // list kernel only: the list values themselves, [smax*L][qpad] (tagged, i.e. rounded up by < 128 ulp;
         // EMPTY markers > 1e38 where the list did not fill), or nullptr.  Read by the threshold selection.
         float *list_vals;
@@ -87,8 +87,9 @@ namespace omplcu
         uint32_t cap;           // multiple of 32, >= 64
     };
 
-    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L);
-    int tc_pick_stages(const TcShape &sh, int L);  // 0: does not fit
+    size_t tc_smem_bytes(const TcShape &sh, int nstages, int L, bool ts = false);
+    int tc_pick_stages(const TcShape &sh, int L, bool ts = false);  // 0: does not fit
+    bool tc_ts_usable(const TcShape &sh);  // query tile as TMEM-resident A operand possible for this shape
 
     // images
     void tc_build_point_image(const float *filt, int rowf, int D, size_t units, uint16_t *out, cudaStream_t s);

@@ -28,6 +28,7 @@ namespace omplcu
         constexpr int KNN_MAX_FAST_DIM = 128;  // 1..16: knn_scan.cuh, 17..128: knn_scan_hd.cuh
         constexpr int KNN_MAX_REG_DIM = 16;
         constexpr size_t EXACT_PAIR_BUDGET = (size_t)1 << 25;
+        constexpr unsigned RESCAN_MIN = 64;  // unproven queries of a tensor-core pass worth a batched FP32-pipe pass
         constexpr size_t RADIUS_PAIR_BUDGET = (size_t)1 << 27;  // 8 B per pair: 1 GB of distances per batch
         constexpr size_t THR_MIN_SLOTS = 32768;  // below: the list scan (its warm-up is cheaper than a sample pass)
 
@@ -116,6 +117,24 @@ namespace omplcu
             dst[i] = src[(size_t)live_slots[r] * stride + c];
             if (c == 0)
                 dst_ids[r] = src_ids[live_slots[r]];
+        }
+
+        // ---- second pass over the queries the tensor-core filter could not prove (knn_fast) ----
+        __global__ void gather_rows_kernel(const double *q, const uint32_t *sel, size_t nsel, int D, double *out)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i < nsel * (size_t)D)
+                out[i] = q[(size_t)sel[i / D] * D + i % D];
+        }
+        __global__ void scatter_results_kernel(const uint64_t *ids, const double *dists, const uint32_t *sel, size_t nsel,
+                                               uint32_t kk, uint32_t kstride, uint64_t *out_ids, double *out_dists)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nsel * (size_t)kk)
+                return;
+            const size_t o = (size_t)sel[i / kk] * kstride + i % kk;
+            out_ids[o] = ids[i];
+            out_dists[o] = dists[i];
         }
 
         // ---- query preparation for the scan ----
@@ -1153,6 +1172,8 @@ namespace omplcu
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
         if (const char *e = getenv("OMPLCU_TC_TS"))
             tc_ts_ = atoi(e);
+        if (const char *e = getenv("OMPLCU_TC_PAIR"))
+            tc_pair_ = atoi(e);
         if (const char *e = getenv("OMPLCU_THR_SCAN"))
             thr_mode_ = atoi(e);  // default for the "thr_scan" option
         CUDA_CHECK(cudaStreamSynchronize(stream_));
@@ -1203,6 +1224,7 @@ namespace omplcu
         last_main_ns_ = c.last_main_ns_;
         last_scan_ns_ = c.last_scan_ns_;
         last_fallbacks_ = c.last_fallbacks_;
+        last_rescans_ = c.last_rescans_;
         last_path_ = c.last_path_;
         if (profile_ && c.last_path_ == 1)
         {
@@ -1502,6 +1524,8 @@ namespace omplcu
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
         else if (!strcmp(key, "tc_ts"))
             tc_ts_ = (int)v;  // one resident tile (d >= 53, or small batches): query tile in tensor memory
+        else if (!strcmp(key, "tc_pair"))
+            tc_pair_ = (int)v;  // with tc_ts: CTA pairs (clusters of 2) share every point chunk by TMA multicast
         else if (!strcmp(key, "l2_window"))
             l2_window_ = v != 0;  // persisting L2 window over the operand image during the tensor-core scan
         else if (!strcmp(key, "thr_scan"))
@@ -1535,6 +1559,10 @@ namespace omplcu
         std::lock_guard<std::mutex> lk(stat_mu_);
         if (!strcmp(key, "last_fallbacks"))
             return last_fallbacks_;
+        if (!strcmp(key, "tc_demoted"))
+            return tc_demoted_.load() ? 1 : 0;  // "auto" gave up on the tensor-core filter for this set (too dense)
+        if (!strcmp(key, "last_rescans"))
+            return last_rescans_;  // queries the tensor-core filter passed on to the FP32-pipe scan
         if (!strcmp(key, "last_path"))
             return last_path_;
         if (!strcmp(key, "last_tc"))
@@ -1714,7 +1742,7 @@ namespace omplcu
 
     // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
     void NNIndex::knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
-                           double *d_dists, cudaStream_t s)
+                           double *d_dists, cudaStream_t s, bool no_tc)
     {
         const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
         const int RQ = cfg == 2 ? 2 : 4;
@@ -1728,7 +1756,7 @@ namespace omplcu
             tc_sh.na = tc_na_;
         const int tc_L = cfg == 0 ? 16 : (cfg == 1 ? 24 : 48);
         int tc_stages = tc_pick_stages(tc_sh, tc_L);
-        while (tc_stages == 0 && tc_sh.na > 1)
+        while (tc_stages < 3 && tc_sh.na > 1)
         {
             tc_sh.na /= 2;  // long lists: fewer resident query tiles
             tc_stages = tc_pick_stages(tc_sh, tc_L);
@@ -1740,8 +1768,18 @@ namespace omplcu
             tc_sh.na /= 2;
             tc_stages = tc_pick_stages(tc_sh, tc_L);
         }
+        // one resident tile: the query tile goes into tensor memory and its shared-memory copy makes room for a
+        // deeper TMA ring (these shapes are bound by the L2 -> SM feed)
+        const bool use_ts = tc_ts_ && tc_ts_usable(tc_sh) && !tc_dbg_;
+        if (use_ts)
+            tc_stages = tc_pick_stages(tc_sh, tc_L, true);
+        // ... and CTA pairs share every point chunk (knn_scan_tc.cu, PAIR): super-tiles of two query tiles
+        const bool pair = use_ts && tc_pair_ && nq > (size_t)TC_QT && sm_count_ >= 2;
         const bool tc_auto = nq >= TC_MIN_BATCH;  // measured faster than the FP32 scans at every batched size
-        const bool tc = D_ <= TC_MAX_DIM && tc_stages > 0 && (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto));
+        if (tc_demoted_.load(std::memory_order_relaxed) && nslots_ < tc_demote_slots_.load(std::memory_order_relaxed) / 2)
+            tc_demoted_.store(false, std::memory_order_relaxed);  // the set thinned out: give the tensor cores another go
+        const bool tc = !no_tc && D_ <= TC_MAX_DIM && tc_stages > 0 &&
+                        (tc_mode_ == 1 || (tc_mode_ < 0 && tc_auto && !tc_demoted_.load(std::memory_order_relaxed)));
         c.last_tc_ = tc ? 1 : 0;
         c.last_thr_ = 0;
         if (tc && (thr_mode_ == 1 || (thr_mode_ < 0 && nslots_ >= THR_MIN_SLOTS)) && nslots_ >= 4096)
@@ -1750,7 +1788,7 @@ namespace omplcu
             return;
         }
         const int L = tc ? tc_L : (cfg == 0 ? 12 : (cfg == 1 ? 16 : 42));
-        const size_t QT = tc ? (size_t)TC_QT * tc_sh.na : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
+        const size_t QT = tc ? (size_t)TC_QT * (pair ? 2 : tc_sh.na) : hd ? (size_t)HD_QT : (size_t)SCAN_THREADS * RQ;
         const size_t PT = tc ? (size_t)TC_PT : hd ? (size_t)HD_PT : (size_t)SCAN_PT;
         const size_t qtiles = (nq + QT - 1) / QT;
         const uint32_t qpad = (uint32_t)(qtiles * QT);
@@ -1773,7 +1811,9 @@ namespace omplcu
         constexpr unsigned FEW_SLOTS = 2560;
         const bool few = tc && qtiles == 1;
         const unsigned max_seg = (few ? FEW_SLOTS : 512u) / L;
-        unsigned long long G = (unsigned long long)sm_count_ * resident;
+        unsigned long long G = (unsigned long long)sm_count_ * resident;  // work pieces
+        if (tc && pair)
+            G = (unsigned long long)sm_count_ / 2;  // one per CTA pair
         G = std::min<unsigned long long>(G, TU);
         G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
         G = std::max<unsigned long long>(G, 1);
@@ -1862,7 +1902,8 @@ namespace omplcu
             T.nstages = tc_stages;
             T.diag = tc_variant_;
             T.dbg = tc_dbg_;
-            T.ts = tc_ts_;
+            T.ts = use_ts ? 1 : 0;
+            T.pair = pair ? 1 : 0;
             // The operand image is re-read once per query super-tile by CTAs that drift apart: ask L2 to keep it
             // (persisting access-policy window on this stream) so the re-reads do not go back to DRAM.
             bool window = false;
@@ -1893,7 +1934,7 @@ namespace omplcu
                     cudaGetLastError();
                 }
             }
-            tc_launch_scan(L, T, (unsigned)G, s);
+            tc_launch_scan(L, T, (unsigned)(pair ? 2 * G : G), s);
             if (window)
             {
                 cudaStreamAttrValue av{};
@@ -1933,7 +1974,47 @@ namespace omplcu
             CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev0_, c.ev1_));
             c.last_scan_ns_ = (long)(ms * 1e6);
         }
-        if (novf)
+        if (!no_tc)
+            c.last_rescans_ = 0;
+        if (tc && tc_mode_ < 0)
+        {
+            // "auto" keeps score: once a quarter of the recent queries came back unproven the set is too dense for the
+            // BF16 split's band (2-D / 3-D roadmaps at 1M states) and the FP32-pipe scan becomes the first filter
+            const long seen = tc_seen_.fetch_add((long)nq) + (long)nq, unp = tc_unproven_.fetch_add((long)novf) + (long)novf;
+            if (seen >= 64)
+            {
+                if (unp * 4 > seen)
+                {
+                    tc_demote_slots_.store(nslots_, std::memory_order_relaxed);
+                    tc_demoted_.store(true, std::memory_order_relaxed);
+                }
+                tc_seen_.store(0);
+                tc_unproven_.store(0);
+            }
+        }
+        if (novf >= RESCAN_MIN && tc && tc_mode_ < 0)
+        {
+            // Many unproven queries: a dense low-dimensional set, where the k-th distance is inside the BF16 split's
+            // error band (800 u against the FP32 scan's (d + 3) u; 17 % of the queries at 1M x 3-D).  Give them to
+            // the FP32-pipe scan as one batch; only what that cannot prove either goes to the exact path.
+            c.re_sel_.reserve(novf);
+            c.re_q_.reserve((size_t)novf * D_);
+            c.re_ids_.reserve((size_t)novf * kk);
+            c.re_d_.reserve((size_t)novf * kk);
+            CUDA_CHECK(cudaMemcpyAsync(c.re_sel_.p, c.ovf_list_.p, novf * sizeof(uint32_t), cudaMemcpyDeviceToDevice, s));
+            gather_rows_kernel<<<nblk((size_t)novf * D_, 256), 256, 0, s>>>(d_q, c.re_sel_.p, novf, D_, c.re_q_.p);
+            launches_++;
+            const long scan_ns = c.last_scan_ns_;
+            knn_fast(c, c.re_q_.p, novf, kk, kk, c.re_ids_.p, c.re_d_.p, s, true);
+            scatter_results_kernel<<<nblk((size_t)novf * kk, 256), 256, 0, s>>>(c.re_ids_.p, c.re_d_.p, c.re_sel_.p, novf,
+                                                                                 (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists);
+            launches_++;
+            CUDA_CHECK(cudaGetLastError());
+            c.last_tc_ = 1;
+            c.last_rescans_ = novf;          // c.last_fallbacks_: what the second pass sent to the exact path
+            c.last_scan_ns_ += scan_ns;
+        }
+        else if (novf)
             knn_exact(c, d_q, c.ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
     }
 
@@ -2004,7 +2085,7 @@ namespace omplcu
         const int Ls = r <= 8 ? 8 : (r <= 16 ? 16 : (r <= 24 ? 24 : 48));
         TcShape shs = sh;
         int stages_s = tc_pick_stages(shs, Ls);
-        while (stages_s == 0 && shs.na > 1)
+        while (stages_s < 3 && shs.na > 1)
         {
             shs.na /= 2;
             stages_s = tc_pick_stages(shs, Ls);

@@ -99,7 +99,7 @@ namespace omplcu
         void knn_locked(QCtx &c, const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
                         cudaStream_t s);
         void knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
-                      cudaStream_t s);
+                      cudaStream_t s, bool no_tc = false);
         // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
         // Tensor-core filter in front of an exact path that has a per-query exact distance bound (the sample
         // bound of the large-k path, the radius of nearestR): every slot within d_bound[q] of query q ends up
@@ -180,6 +180,10 @@ namespace omplcu
             DevBuf<float> tau_, list_vals_;
             DevBuf<uint32_t> app_ids_, app_cnt_;
             DevBuf<unsigned long long> kept_;
+            DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered
+            DevBuf<double> re_q_, re_d_;
+            DevBuf<uint64_t> re_ids_;
+            long last_rescans_ = 0;
             long last_filter_ = 0;
             long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
             long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
@@ -207,6 +211,10 @@ namespace omplcu
         int sm_count_ = 148, scan_ctas_per_sm_ = 0;
         bool sample_thr_ = true;
         bool l2_window_ = false;
+        std::atomic<long> tc_seen_{0}, tc_unproven_{0};  // auto mode: recent queries / unproven by the tensor-core filter
+        std::atomic<bool> tc_demoted_{false};
+        std::atomic<size_t> tc_demote_slots_{0};
+        int tc_pair_ = 1;         // with tc_ts_: clusters of 2 CTAs share the point chunks (TMA multicast)
         int tc_ts_ = 1;           // one resident tile: query tile in tensor memory (0: shared memory)
         bool force_exact_ = false, profile_ = false;
 
@@ -214,6 +222,7 @@ namespace omplcu
         long last_filter_ = 0;
         long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
         long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
+        long last_rescans_ = 0;
         long scan_ns_total_ = 0, scan_count_ = 0;
         std::atomic<long> launches_{0};
     };

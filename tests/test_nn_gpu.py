@@ -442,8 +442,8 @@ def test_merge_topk_equals_single_index(gpu):
 
 # ---------------------------------------------------------------- tensor-core scan (knn_scan_tc.cu)
 def _tc_err_units(d):
-    k32 = (3 * d + 3 + 31) // 32
-    return 1.02 * (3.0 + 768.0 + 32.0 * (k32 * 32 // 16))
+    k16 = (3 * d + 3 + 15) // 16  # tcgen05.mma instructions (K = 16) per pair of tiles
+    return 1.02 * (3.0 + 768.0 + 32.0 * k16)
 
 
 @pytest.mark.parametrize("d", [1, 7, 9, 10, 20, 21, 33, 52, 53, 64, 100, 128])
@@ -452,7 +452,7 @@ def test_tensor_core_scan_values_within_the_stated_error_bound(gpu, scan_kernel,
     s = |pt|^2 - 2 qt.pt on the FP32-rounded operands: the band check of the re-rank assumes
     |s_tc - s| <= tc_err_units(d) * 2^-24 * (pmax2 + 2 |qt| pmax) (knn_scan_tc.cuh).  The measured
     error must stay below half of that bound; every operand-image shape is covered
-    (chunks of 32 / 64 columns, 1 / 2 / 4 resident query tiles)."""
+    (one or several chunks, odd and even MMA counts, 1 / 2 / 4 resident query tiles)."""
     if scan_kernel != "tensor-core-scan":
         pytest.skip("tensor-core scan only")
     import torch

@@ -110,3 +110,30 @@ def test_chain_metric_near_ties_keep_a_valid_order(gpu):
                 assert close(de, np.full(len(extra), od[q, -1])).all()
     assert swaps > 0, "the data was built to contain ties below the tolerance"
     print(f"chain near-ties: {swaps} of {len(qs)} queries differ from the glibc order, all inside the tolerance")
+
+
+def test_dense_low_dimensional_set_second_pass_on_the_fp32_scan(gpu, monkeypatch):
+    """A dense 2-D roadmap (PRM on R^2 at 1M milestones): the k-th neighbour distance is inside the error band of the
+    BF16 split, so the tensor-core filter cannot prove the queries.  In its default ("auto") mode the structure hands
+    them to the FP32-pipe scan as ONE batch (band ~100x narrower) instead of redoing each exactly, and after a call
+    like that makes the FP32-pipe scan the first filter for this set.  Answers stay bit-identical to the oracle and
+    to the FP32-only structure throughout."""
+    monkeypatch.delenv("OMPLCU_TC_SCAN", raising=False)
+    n, nq, k, d = 1_000_000, 4096, 10, 2
+    pts, qs = helpers.uniform_points(11, n, d), helpers.uniform_points(12, nq, d)
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    ids, dist = nn.nearestKBatch(qs, k)
+    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1
+    assert nn.stat("last_rescans") >= nq // 4, "expected unproven queries at this density"
+    assert nn.stat("last_fallbacks") <= nn.stat("last_rescans") // 10
+    assert nn.stat("tc_demoted") == 1
+    ids1, dist1 = nn.nearestKBatch(qs, k)  # now straight to the FP32-pipe scan
+    assert nn.stat("last_tc") == 0 and nn.stat("last_rescans") == 0
+    assert (ids == ids1).all() and (dist == dist1).all()
+    nn.set_option("tc_scan", 0)
+    ids0, dist0 = nn.nearestKBatch(qs, k)
+    assert (ids == ids0).all() and (dist == dist0).all()
+    sub = helpers.rng(6).choice(nq, 256, replace=False)
+    oi, od = orc.knn(orc.space_rv(d), pts, qs[sub], k, nthreads=16)
+    assert (ids[sub] == oi).all() and (dist[sub] == od).all()
