@@ -1172,6 +1172,10 @@ namespace omplcu
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
         if (const char *e = getenv("OMPLCU_TC_TS"))
             tc_ts_ = atoi(e);
+        if (const char *e = getenv("OMPLCU_TC_ALIGN"))
+            tc_align_ = atoi(e) != 0;
+        if (const char *e = getenv("OMPLCU_TC_GRID"))
+            tc_grid_ = atoi(e);
         if (const char *e = getenv("OMPLCU_TC_PAIR"))
             tc_pair_ = atoi(e);
         if (const char *e = getenv("OMPLCU_THR_SCAN"))
@@ -1524,6 +1528,8 @@ namespace omplcu
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
         else if (!strcmp(key, "tc_ts"))
             tc_ts_ = (int)v;  // one resident tile (d >= 53, or small batches): query tile in tensor memory
+        else if (!strcmp(key, "tc_align"))
+            tc_align_ = v != 0;  // work pieces of the tensor-core scan end on query-tile boundaries when that costs < 15 % of the SMs
         else if (!strcmp(key, "tc_pair"))
             tc_pair_ = (int)v;  // with tc_ts: CTA pairs (clusters of 2) share every point chunk by TMA multicast
         else if (!strcmp(key, "l2_window"))
@@ -1814,9 +1820,31 @@ namespace omplcu
         unsigned long long G = (unsigned long long)sm_count_ * resident;  // work pieces
         if (tc && pair)
             G = (unsigned long long)sm_count_ / 2;  // one per CTA pair
+        if (tc && tc_grid_ > 0)
+            G = std::min<unsigned long long>(G, (unsigned long long)tc_grid_);
         G = std::min<unsigned long long>(G, TU);
         G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
         G = std::max<unsigned long long>(G, 1);
+        if (tc && tc_align_ && tc_sh.na >= 2 && !pair)
+        {
+            // Pieces that end on query-tile boundaries: every (query, piece) pair pays a list warm-up of about
+            // L (1 + ln(points / L)) insertions and adds L candidates to the re-rank, so 128 super-tiles on 128 CTAs
+            // (one segment per query) beat the same work cut into 148 equal pieces (2.15 segments per query) at
+            // every size measured but the largest, where it is a tie (profiles/r2_experiments.md).  Not for the
+            // tensor-bound shapes (one resident tile), which want every SM.
+            unsigned long long Ga = 0;
+            if (qtiles <= G)
+                Ga = qtiles * (G / qtiles);
+            else
+                for (unsigned long long x = G; x >= 1; --x)
+                    if (qtiles % x == 0)
+                    {
+                        Ga = x;
+                        break;
+                    }
+            if (Ga * 100 >= G * 85)
+                G = Ga;
+        }
         // pieces overlapping one query tile (same formulas as the kernel)
         uint32_t smax = 1;
         for (size_t t = 0; t < qtiles; ++t)

@@ -214,6 +214,8 @@ namespace omplcu
         std::atomic<long> tc_seen_{0}, tc_unproven_{0};  // auto mode: recent queries / unproven by the tensor-core filter
         std::atomic<bool> tc_demoted_{false};
         std::atomic<size_t> tc_demote_slots_{0};
+        bool tc_align_ = true;    // tensor-core scan: work pieces end on query-tile boundaries where that is nearly free
+        int tc_grid_ = 0;         // experiments: upper limit on the tensor-core scan's work pieces (0: one per SM)
         int tc_pair_ = 1;         // with tc_ts_: clusters of 2 CTAs share the point chunks (TMA multicast)
         int tc_ts_ = 1;           // one resident tile: query tile in tensor memory (0: shared memory)
         bool force_exact_ = false, profile_ = false;

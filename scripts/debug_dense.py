@@ -6,8 +6,9 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import ompl_b200 as ob
 n, nq, k, d = (int(a) for a in (sys.argv[1:5] if len(sys.argv) > 4 else "1000000 8192 10 3".split()))
 r = np.random.default_rng(1)
-pts, qs = r.uniform(0, 1, (n, d)), r.uniform(0, 1, (nq, d))
-for mode in (-1, 1, 0):
+lo, hi = (float(a) for a in os.environ.get("RANGE", "0 1").split())
+pts, qs = r.uniform(lo, hi, (n, d)), r.uniform(lo, hi, (nq, d))
+for mode in [int(a) for a in os.environ.get("MODES", "-1 1 0").split()]:
     nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
     nn.set_option("tc_scan", mode)
     nn.add_rows(pts)
