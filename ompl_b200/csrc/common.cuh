@@ -117,6 +117,36 @@ namespace omplcu
         }
     };
 
+    // Page-locked host staging that only grows (small host-pointer calls: one asynchronous copy each way
+    // instead of the driver's synchronous pageable path).
+    struct PinBuf
+    {
+        unsigned char *p = nullptr;
+        size_t cap = 0;
+        void reserve(size_t n)
+        {
+            if (n <= cap)
+                return;
+            size_t ncap = cap ? cap : 4096;
+            while (ncap < n)
+                ncap *= 2;
+            if (p)
+                cudaFreeHost(p);
+            p = nullptr;
+            cap = 0;
+            CUDA_CHECK(cudaMallocHost(reinterpret_cast<void **>(&p), ncap));
+            cap = ncap;
+        }
+        ~PinBuf()
+        {
+            if (p)
+                cudaFreeHost(p);
+        }
+        PinBuf() = default;
+        PinBuf(const PinBuf &) = delete;
+        PinBuf &operator=(const PinBuf &) = delete;
+    };
+
     // ------------------------------------------------------------------
     // exact FP64 device math
     // ------------------------------------------------------------------

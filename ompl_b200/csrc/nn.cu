@@ -119,6 +119,125 @@ namespace omplcu
                 dst_ids[r] = src_ids[live_slots[r]];
         }
 
+        // ---- filter scan for a handful of queries (the literal nearestK of PRM::addMilestone, prm/src/PRM.cpp:575) ----
+        // A tensor-core tile has 128 query rows; with 1 - 8 queries nearly all of them are padding and the call is
+        // bound by the MMA -> selection hand-over per point tile (66 us at 1M states).  Here a lane owns a point: the
+        // warp reads 32 consecutive rows of the FP32 filter copy (coalesced), every lane evaluates the scan value of
+        // its point against each query exactly as knn_scan_kernel does (s = pn, then one FMA per coordinate in
+        // order: same value, same (d + 3) u error bound), and the warp keeps, per query, the FEW_L smallest values
+        // of the rows it has seen: list entry i lives in lane i's registers, the minimum over the batch and the
+        // list maximum come from redux.sync on an order-preserving integer image of the floats.  Every warp is one
+        // segment of the candidate arrays (cand_thr = its list maximum once full), which knn_rerank_select_kernel
+        // re-ranks exactly and proves like any other scan's.  HBM/L2-bound: one pass over 4 (d + 1) bytes per point.
+        constexpr int FEW_MAXQ = 8, FEW_L = 4, FEW_WARPS = 4, FEW_UB = 4;
+        __device__ __forceinline__ uint32_t few_key(float v)
+        {
+            // monotone float -> unsigned; +inf (dead rows), NaN and the padding sort last and are never kept
+            const uint32_t b = __float_as_uint(v);
+            return v < 3.0e38f ? ((b & 0x80000000u) ? ~b : (b | 0x80000000u)) : 0xFFFFFFFFu;
+        }
+        __device__ __forceinline__ float few_unkey(uint32_t k)
+        {
+            return __uint_as_float((k & 0x80000000u) ? (k & 0x7FFFFFFFu) : ~k);
+        }
+        template <int NQ>
+        __global__ void __launch_bounds__(FEW_WARPS * 32) knn_few_kernel(const float *filt, int rowf, int D, size_t nslots,
+                                                                        const float *qp, uint32_t qpad, float *cand_thr,
+                                                                        uint32_t *cand_ids)
+        {
+            extern __shared__ float few_q[];  // [D][NQ]
+            for (int i = threadIdx.x; i < D * NQ; i += blockDim.x)
+                few_q[i] = qp[(size_t)(i / NQ) * qpad + (i % NQ)];
+            __syncthreads();
+            const unsigned full = 0xffffffffu;
+            const int lane = threadIdx.x & 31;
+            const size_t gw = blockIdx.x * (size_t)FEW_WARPS + (threadIdx.x >> 5), GW = gridDim.x * (size_t)FEW_WARPS;
+            const size_t nbatch = (nslots + 31) / 32;
+            uint32_t lk[NQ], lid[NQ], thr[NQ];  // list entry `lane` (lanes < FEW_L) and the list maximum, per query
+#pragma unroll
+            for (int j = 0; j < NQ; ++j)
+            {
+                lk[j] = lane < FEW_L ? 0xFFFFFFFFu : 0u;
+                lid[j] = SLOT_NONE;
+                thr[j] = 0xFFFFFFFFu;
+            }
+            const int nc4 = (D + 3) / 4;
+            for (size_t b0 = gw; b0 < nbatch; b0 += GW * FEW_UB)
+            {
+                float acc[FEW_UB][NQ];
+                uint32_t row[FEW_UB];
+#pragma unroll
+                for (int u = 0; u < FEW_UB; ++u)
+                {
+                    const size_t b = b0 + (size_t)u * GW, r = b * 32 + lane;
+                    const bool live = b < nbatch && r < nslots;
+                    row[u] = live ? (uint32_t)r : SLOT_NONE;
+                    const float pn = live ? filt[r * rowf + D] : __uint_as_float(0x7f800000u);
+#pragma unroll
+                    for (int j = 0; j < NQ; ++j)
+                        acc[u][j] = pn;
+                }
+                for (int c4 = 0; c4 < nc4; ++c4)
+                {
+                    float4 x[FEW_UB];
+#pragma unroll
+                    for (int u = 0; u < FEW_UB; ++u)
+                        x[u] = row[u] != SLOT_NONE
+                                   ? *reinterpret_cast<const float4 *>(filt + (size_t)row[u] * rowf + 4 * c4)
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);
+                    const int c = 4 * c4;
+#pragma unroll
+                    for (int e = 0; e < 4; ++e)
+                        if (c + e < D)
+                        {
+#pragma unroll
+                            for (int j = 0; j < NQ; ++j)
+                            {
+                                const float qv = few_q[(c + e) * NQ + j];
+#pragma unroll
+                                for (int u = 0; u < FEW_UB; ++u)
+                                    acc[u][j] = fmaf(qv, e == 0 ? x[u].x : e == 1 ? x[u].y : e == 2 ? x[u].z : x[u].w, acc[u][j]);
+                            }
+                        }
+                }
+#pragma unroll
+                for (int u = 0; u < FEW_UB; ++u)
+#pragma unroll
+                    for (int j = 0; j < NQ; ++j)
+                    {
+                        uint32_t key = few_key(acc[u][j]);
+                        uint32_t m = __reduce_min_sync(full, key);
+                        while (m < thr[j])
+                        {
+                            const int src = __ffs(__ballot_sync(full, key == m)) - 1;   // lowest row first
+                            const uint32_t id = __shfl_sync(full, row[u], src);
+                            const int dst = __ffs(__ballot_sync(full, lane < FEW_L && lk[j] == thr[j])) - 1;
+                            if (lane == dst)
+                            {
+                                lk[j] = m;
+                                lid[j] = id;
+                            }
+                            if (lane == src)
+                                key = 0xFFFFFFFFu;
+                            thr[j] = __reduce_max_sync(full, lk[j]);
+                            m = __reduce_min_sync(full, key);
+                        }
+                    }
+            }
+            if (lane < FEW_L)
+            {
+#pragma unroll
+                for (int j = 0; j < NQ; ++j)
+                    cand_ids[(gw * FEW_L + lane) * qpad + j] = lid[j];
+            }
+            if (lane == 0)
+            {
+#pragma unroll
+                for (int j = 0; j < NQ; ++j)
+                    cand_thr[gw * qpad + j] = thr[j] != 0xFFFFFFFFu ? few_unkey(thr[j]) : __uint_as_float(0x7F7F7F7Fu);
+            }
+        }
+
         // ---- second pass over the queries the tensor-core filter could not prove (knn_fast) ----
         __global__ void gather_rows_kernel(const double *q, const uint32_t *sel, size_t nsel, int D, double *out)
         {
@@ -140,9 +259,11 @@ namespace omplcu
         // ---- query preparation for the scan ----
         // qp[c][q] = -2 * fl32(q_c - center_c); qaux[q] = (|qt|^2, |qt|) in FP64
         __global__ void query_prep_kernel(const double *q, size_t nq, const double *center, int D, float *qp,
-                                          double *qaux, uint32_t qpad)
+                                          double *qaux, uint32_t qpad, unsigned *zero = nullptr)
         {
             size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i == 0 && zero)
+                *zero = 0;  // the re-rank's fallback counter (saves a memset launch per call)
             if (i >= qpad)
                 return;
             double qn = 0.0;
@@ -677,20 +798,26 @@ namespace omplcu
                 s_slot[c] = slot;
             }
             __syncthreads();
-            if (threadIdx.x >= 32)
-                return;
+            // Selection in two levels: every warp extracts the kk best of its own 1/32 of the candidates (2 - 3 per
+            // lane), then warp 0 extracts the kk best of those 32 kk survivors.  The kk best overall are among the
+            // survivors, and both levels order by (distance, slot), so the result is the one-level result; a round
+            // costs a lane-local scan of a few entries and a shuffle tree instead of a scan of n / 32 entries.
+            double *s_key2 = reinterpret_cast<double *>(s_slot + n + (n & 1u));
+            uint32_t *s_slot2 = reinterpret_cast<uint32_t *>(s_key2 + (size_t)(SEL_THREADS / 32) * kk);
+            const uint32_t warp = threadIdx.x >> 5;
             double bk = inf;
             uint32_t bs = SLOT_NONE, bi = 0;
-            auto rescan = [&]() {
+            // best live entry among this lane's share of [lo, hi) of (key, slot)
+            auto rescan = [&](const double *key, const uint32_t *slot, uint32_t lo, uint32_t hi) {
                 bk = inf;
                 bs = SLOT_NONE;
                 bi = 0;
-                for (uint32_t c = lane; c < n; c += 32)
+                for (uint32_t c = lo + lane; c < hi; c += 32)
                 {
-                    const uint32_t sl = s_slot[c];
+                    const uint32_t sl = slot[c];
                     if (sl == SLOT_NONE)
                         continue;
-                    const double k = s_key[c];
+                    const double k = key[c];
                     // a NaN distance never wins a comparison: it stays behind and the band check below fails on it
                     if (bs == SLOT_NONE || k < bk || (k == bk && sl < bs))
                     {
@@ -700,12 +827,11 @@ namespace omplcu
                     }
                 }
             };
-            rescan();
-            double dk = -1.0;
-            for (uint32_t r = 0; r < kk; ++r)
-            {
-                double wk = bk;
-                uint32_t ws = bs, wi = bi;
+            // one extraction round over the lanes' cached bests; returns false when nothing is left
+            auto pick = [&](double &wk, uint32_t &ws, uint32_t &wi) {
+                wk = bk;
+                ws = bs;
+                wi = bi;
                 for (int o = 16; o > 0; o >>= 1)
                 {
                     const double ok = __shfl_xor_sync(0xffffffffu, wk, o);
@@ -718,7 +844,41 @@ namespace omplcu
                         wi = oi;
                     }
                 }
-                if (ws == SLOT_NONE)
+                return ws != SLOT_NONE;
+            };
+            {
+                const uint32_t per = (n + SEL_THREADS / 32 - 1) / (SEL_THREADS / 32);
+                const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
+                rescan(s_key, s_slot, lo, hi);
+                for (uint32_t r = 0; r < kk; ++r)
+                {
+                    double wk;
+                    uint32_t ws, wi;
+                    const bool any = pick(wk, ws, wi);
+                    if (lane == 0)
+                    {
+                        s_key2[warp * kk + r] = any ? wk : inf;
+                        s_slot2[warp * kk + r] = any ? ws : SLOT_NONE;
+                    }
+                    if (any && ((wi - lo) & 31u) == (uint32_t)lane)
+                    {
+                        s_slot[wi] = SLOT_NONE;
+                        rescan(s_key, s_slot, lo, hi);
+                    }
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x >= 32)
+                return;
+            const uint32_t n2 = (SEL_THREADS / 32) * kk;
+            rescan(s_key2, s_slot2, 0, n2);
+            double dk = -1.0;
+            for (uint32_t r = 0; r < kk; ++r)
+            {
+                double wk;
+                uint32_t ws, wi;
+                if (!pick(wk, ws, wi))
                     break;  // fewer than kk candidates: dk stays negative, the query is redone exactly
                 if (lane == 0)
                 {
@@ -730,8 +890,8 @@ namespace omplcu
                     dk = wk;
                 if ((wi & 31u) == (uint32_t)lane)
                 {
-                    s_slot[wi] = SLOT_NONE;
-                    rescan();
+                    s_slot2[wi] = SLOT_NONE;
+                    rescan(s_key2, s_slot2, 0, n2);
                 }
                 __syncwarp();
             }
@@ -1229,6 +1389,7 @@ namespace omplcu
         last_scan_ns_ = c.last_scan_ns_;
         last_fallbacks_ = c.last_fallbacks_;
         last_rescans_ = c.last_rescans_;
+        last_few_ = c.last_few_;
         last_path_ = c.last_path_;
         if (profile_ && c.last_path_ == 1)
         {
@@ -1528,6 +1689,8 @@ namespace omplcu
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
         else if (!strcmp(key, "tc_ts"))
             tc_ts_ = (int)v;  // one resident tile (d >= 53, or small batches): query tile in tensor memory
+        else if (!strcmp(key, "few_scan"))
+            few_mode_ = v != 0;  // up to 8 queries: lane-per-point FP32 scan instead of a mostly empty tensor-core tile
         else if (!strcmp(key, "tc_align"))
             tc_align_ = v != 0;  // work pieces of the tensor-core scan end on query-tile boundaries when that costs < 15 % of the SMs
         else if (!strcmp(key, "tc_pair"))
@@ -1567,6 +1730,8 @@ namespace omplcu
             return last_fallbacks_;
         if (!strcmp(key, "tc_demoted"))
             return tc_demoted_.load() ? 1 : 0;  // "auto" gave up on the tensor-core filter for this set (too dense)
+        if (!strcmp(key, "last_few"))
+            return last_few_;  // the last query ran the few-query scan (knn_few_kernel)
         if (!strcmp(key, "last_rescans"))
             return last_rescans_;  // queries the tensor-core filter passed on to the FP32-pipe scan
         if (!strcmp(key, "last_path"))
@@ -1747,9 +1912,74 @@ namespace omplcu
     }  // namespace
 
     // scan configuration: (RQ, L) = (4, 16) for k <= 12, (2, 48) for k <= 40
+    // nq <= FEW_MAXQ queries: knn_few_kernel (one warp = one segment of FEW_L candidates), then the same exact
+    // re-rank, band check and fallback as every other filter.
+    void NNIndex::knn_few(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+                          double *d_dists, cudaStream_t s)
+    {
+        const uint32_t qpad = 32;
+        const unsigned grid = (unsigned)std::max<size_t>(1, std::min<size_t>((size_t)sm_count_, (nslots_ + 127) / 128));
+        const uint32_t smax = grid * FEW_WARPS;
+        c.qp_.reserve((size_t)D_ * qpad);
+        c.qaux_.reserve(2 * (size_t)qpad);
+        c.cand_vals_.reserve((size_t)smax * qpad);
+        c.cand_ids_.reserve((size_t)smax * FEW_L * qpad);
+        c.ovf_list_.reserve(nq);
+        query_prep_kernel<<<1, 32, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad, c.counters_.p);
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(c.ev0_, s));
+        const size_t qsm = (size_t)D_ * FEW_MAXQ * sizeof(float);
+        if (nq == 1)
+            knn_few_kernel<1><<<grid, FEW_WARPS * 32, qsm, s>>>(filt_.p, rowf_, D_, nslots_, c.qp_.p, qpad, c.cand_vals_.p,
+                                                                c.cand_ids_.p);
+        else if (nq <= 4)
+            knn_few_kernel<4><<<grid, FEW_WARPS * 32, qsm, s>>>(filt_.p, rowf_, D_, nslots_, c.qp_.p, qpad, c.cand_vals_.p,
+                                                                c.cand_ids_.p);
+        else
+            knn_few_kernel<FEW_MAXQ><<<grid, FEW_WARPS * 32, qsm, s>>>(filt_.p, rowf_, D_, nslots_, c.qp_.p, qpad,
+                                                                       c.cand_vals_.p, c.cand_ids_.p);
+        if (profile_)
+            CUDA_CHECK(cudaEventRecord(c.ev1_, s));
+        knn_rerank_select_kernel<<<(unsigned)nq, SEL_THREADS,
+                                   (size_t)smax * FEW_L * 12 + (size_t)D_ * 8 + 8 + (size_t)(SEL_THREADS / 32) * kk * 12, s>>>(
+            c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)FEW_L, qpad, pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p, nq,
+            (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, (double)(D_ + 3));
+        launches_ += 3;
+        CUDA_CHECK(cudaGetLastError());
+        const bool ho = c.ho_ids_ && c.ho_entries_ == nq * kstride && kk == kstride;
+        if (ho)
+        {
+            CUDA_CHECK(cudaMemcpyAsync(c.ho_ids_, d_ids, c.ho_entries_ * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(c.ho_dists_, d_dists, c.ho_entries_ * sizeof(double), cudaMemcpyDeviceToHost, s));
+        }
+        unsigned novf = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&novf, c.counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        c.ho_done_ = ho && novf == 0;
+        c.last_fallbacks_ = novf;
+        c.last_tc_ = 0;
+        c.last_thr_ = 0;
+        c.last_rescans_ = 0;
+        c.last_few_ = 1;
+        if (profile_)
+        {
+            float ms = 0.f;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, c.ev0_, c.ev1_));
+            c.last_scan_ns_ = (long)(ms * 1e6);
+        }
+        if (novf)
+            knn_exact(c, d_q, c.ovf_list_.p, novf, kk, kstride, d_ids, d_dists, s);
+    }
+
     void NNIndex::knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
                            double *d_dists, cudaStream_t s, bool no_tc)
     {
+        c.last_few_ = 0;
+        if (!no_tc && few_mode_ && nq <= (size_t)FEW_MAXQ && tc_mode_ < 0 && thr_mode_ <= 0 && nslots_ < ((size_t)1 << 32) - 64)
+        {
+            knn_few(c, d_q, nq, kk, kstride, d_ids, d_dists, s);
+            return;
+        }
         const int cfg = kk <= 10 ? 0 : (kk <= 14 ? 1 : 2);
         const int RQ = cfg == 2 ? 2 : 4;
         const bool hd = D_ > KNN_MAX_REG_DIM;  // register-tiled kernel of knn_scan_hd.cuh
@@ -1862,13 +2092,15 @@ namespace omplcu
         c.cand_vals_.reserve((size_t)smax * qpad);
         c.cand_ids_.reserve((size_t)smax * L * qpad);
         c.ovf_list_.reserve(nq);
-
-        CUDA_CHECK(cudaMemsetAsync(c.cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
-        CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
-        CUDA_CHECK(cudaMemsetAsync(c.counters_.p, 0, sizeof(unsigned), s));
-        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
+        // Rows of segments that no piece writes must read "no candidate, not full".  When every query tile is cut
+        // into exactly smax pieces (aligned pieces, or one tile) the tensor-core scan writes every row itself.
+        if (!(tc && G % qtiles == 0 && G / qtiles == smax))
+        {
+            CUDA_CHECK(cudaMemsetAsync(c.cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
+            CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
+        }
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad, c.counters_.p);
         launches_++;
-
         ScanParams P;
         P.filt = filt_.p;
         P.qp = c.qp_.p;
@@ -1981,7 +2213,8 @@ namespace omplcu
             CUDA_CHECK(cudaEventRecord(c.ev1_, s));
 
         if ((size_t)smax * L > 512)
-            knn_rerank_select_kernel<<<(unsigned)nq, SEL_THREADS, (size_t)smax * L * 12 + (size_t)D_ * 8, s>>>(
+            knn_rerank_select_kernel<<<(unsigned)nq, SEL_THREADS,
+                                       (size_t)smax * L * 12 + (size_t)D_ * 8 + 8 + (size_t)(SEL_THREADS / 32) * kk * 12, s>>>(
                 c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad, pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p,
                 nq, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, tc_err_units(D_));
         else
@@ -1993,8 +2226,16 @@ namespace omplcu
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         unsigned novf = 0;
+        const bool ho = c.ho_ids_ && !no_tc && c.ho_entries_ == nq * kstride && kk == kstride;
+        if (ho)
+        {
+            // small host-pointer call: the results travel with the fallback counter (pinned memory)
+            CUDA_CHECK(cudaMemcpyAsync(c.ho_ids_, d_ids, c.ho_entries_ * sizeof(uint64_t), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaMemcpyAsync(c.ho_dists_, d_dists, c.ho_entries_ * sizeof(double), cudaMemcpyDeviceToHost, s));
+        }
         CUDA_CHECK(cudaMemcpyAsync(&novf, c.counters_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
+        c.ho_done_ = ho && novf == 0;
         c.last_fallbacks_ = novf;
         if (profile_)
         {
@@ -2543,7 +2784,7 @@ namespace omplcu
 
     // rw_ is held (shared) by the caller; `c` is the caller's leased context
     void NNIndex::knn_locked(QCtx &c, const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
-                             cudaStream_t s)
+                             cudaStream_t s, bool sync)
     {
         if (nq == 0 || k == 0)
             return;
@@ -2572,7 +2813,8 @@ namespace omplcu
             launches_++;
             CUDA_CHECK(cudaGetLastError());
         }
-        CUDA_CHECK(cudaStreamSynchronize(s));
+        if (sync)
+            CUDA_CHECK(cudaStreamSynchronize(s));
     }
 
     // Host pointers in, host pointers out.  One shared lock spans staging, query and copy-out, so the
@@ -2594,14 +2836,54 @@ namespace omplcu
             c.out_i_.reserve(nq * std::max<size_t>(k, 1));
             c.out_d_.reserve(nq * std::max<size_t>(k, 1));
             kk = std::min(k, nlive_);
-            CUDA_CHECK(cudaMemcpyAsync(c.q_stage_.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, c.stream));
+            // Small calls (the literal nearestK of PRM::addMilestone, prm/src/PRM.cpp:575) go through pinned staging:
+            // pageable copies are synchronous round trips of 10 - 15 us each, more than the scan of a 100K roadmap.
+            const size_t qbytes = nq * st * sizeof(double), entries = nq * k;
+            const bool small = k > 0 && qbytes + entries * 16 <= ((size_t)1 << 20);
+            if (small)
+            {
+                c.pin_.reserve(qbytes + entries * 16 + 16);
+                memcpy(c.pin_.p, q, qbytes);
+                const size_t off = (qbytes + 15) & ~(size_t)15;
+                c.ho_ids_ = reinterpret_cast<uint64_t *>(c.pin_.p + off);
+                c.ho_dists_ = reinterpret_cast<double *>(c.pin_.p + off + entries * 8);
+                c.ho_entries_ = entries;
+                c.ho_done_ = false;
+            }
+            CUDA_CHECK(cudaMemcpyAsync(c.q_stage_.p, small ? (const void *)c.pin_.p : (const void *)q, qbytes,
+                                       cudaMemcpyHostToDevice, c.stream));
             if (k > 0)
             {
-                knn_locked(c, c.q_stage_.p, nq, k, c.out_i_.p, c.out_d_.p, c.stream);
-                CUDA_CHECK(cudaMemcpyAsync(ids, c.out_i_.p, nq * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
-                if (dists)
-                    CUDA_CHECK(
-                        cudaMemcpyAsync(dists, c.out_d_.p, nq * k * sizeof(double), cudaMemcpyDeviceToHost, c.stream));
+                struct Clear
+                {
+                    QCtx &c;
+                    ~Clear()
+                    {
+                        c.ho_ids_ = nullptr;
+                        c.ho_dists_ = nullptr;
+                        c.ho_entries_ = 0;
+                    }
+                } clear{c};
+                knn_locked(c, c.q_stage_.p, nq, k, c.out_i_.p, c.out_d_.p, c.stream, !small);
+                if (small)
+                {
+                    if (!c.ho_done_)  // another path than the fast one, or some queries were redone exactly
+                    {
+                        CUDA_CHECK(cudaMemcpyAsync(c.ho_ids_, c.out_i_.p, entries * 8, cudaMemcpyDeviceToHost, c.stream));
+                        CUDA_CHECK(cudaMemcpyAsync(c.ho_dists_, c.out_d_.p, entries * 8, cudaMemcpyDeviceToHost, c.stream));
+                        CUDA_CHECK(cudaStreamSynchronize(c.stream));
+                    }
+                    memcpy(ids, c.ho_ids_, entries * 8);
+                    if (dists)
+                        memcpy(dists, c.ho_dists_, entries * 8);
+                }
+                else
+                {
+                    CUDA_CHECK(cudaMemcpyAsync(ids, c.out_i_.p, nq * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, c.stream));
+                    if (dists)
+                        CUDA_CHECK(cudaMemcpyAsync(dists, c.out_d_.p, nq * k * sizeof(double), cudaMemcpyDeviceToHost,
+                                                   c.stream));
+                }
             }
             CUDA_CHECK(cudaStreamSynchronize(c.stream));
             publish(c);

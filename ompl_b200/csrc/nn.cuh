@@ -97,9 +97,11 @@ namespace omplcu
         void compact();
         bool fast_eligible(size_t kk) const;
         void knn_locked(QCtx &c, const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
-                        cudaStream_t s);
+                        cudaStream_t s, bool sync = true);
         void knn_fast(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                       cudaStream_t s, bool no_tc = false);
+        void knn_few(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
+                     cudaStream_t s);
         // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
         // Tensor-core filter in front of an exact path that has a per-query exact distance bound (the sample
         // bound of the large-k path, the radius of nearestR): every slot within d_bound[q] of query q ends up
@@ -180,10 +182,17 @@ namespace omplcu
             DevBuf<float> tau_, list_vals_;
             DevBuf<uint32_t> app_ids_, app_cnt_;
             DevBuf<unsigned long long> kept_;
+            // small host-pointer calls (knn_host): pinned staging, and the place knn_fast copies the results to
+            // together with its fallback counter, so that the common call synchronises once
+            PinBuf pin_;
+            uint64_t *ho_ids_ = nullptr;
+            double *ho_dists_ = nullptr;
+            size_t ho_entries_ = 0;
+            bool ho_done_ = false;
             DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered
             DevBuf<double> re_q_, re_d_;
             DevBuf<uint64_t> re_ids_;
-            long last_rescans_ = 0;
+            long last_rescans_ = 0, last_few_ = 0;
             long last_filter_ = 0;
             long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
             long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
@@ -214,6 +223,8 @@ namespace omplcu
         std::atomic<long> tc_seen_{0}, tc_unproven_{0};  // auto mode: recent queries / unproven by the tensor-core filter
         std::atomic<bool> tc_demoted_{false};
         std::atomic<size_t> tc_demote_slots_{0};
+        bool few_mode_ = true;    // auto mode, up to 8 queries: knn_few_kernel
+        long last_few_ = 0;
         bool tc_align_ = true;    // tensor-core scan: work pieces end on query-tile boundaries where that is nearly free
         int tc_grid_ = 0;         // experiments: upper limit on the tensor-core scan's work pieces (0: one per SM)
         int tc_pair_ = 1;         // with tc_ts_: clusters of 2 CTAs share the point chunks (TMA multicast)

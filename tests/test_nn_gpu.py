@@ -493,7 +493,10 @@ def test_tensor_core_scan_is_the_default(gpu, monkeypatch):
     _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
     assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1
     _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(3, 1, d), 10)
-    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1  # single queries too (measured faster)
+    assert nn.stat("last_path") == 1 and nn.stat("last_few") == 1  # up to 8 queries: the few-query scan (tests/test_nn_few_gpu.py)
+    nn.set_option("few_scan", 0)
+    _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(3, 1, d), 10)
+    assert nn.stat("last_path") == 1 and nn.stat("last_tc") == 1  # without it: the tensor-core scan, even for one query
     nn.set_option("tc_scan", 0)
     _check_knn(nn, orc.space_rv(d), pts, np.arange(n), helpers.uniform_points(2, 200, d), 10)
     assert nn.stat("last_tc") == 0
