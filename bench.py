@@ -345,11 +345,15 @@ def run_gpu_arm(args):
             dist.barrier(group=nccl)
         torch.cuda.synchronize()
 
+    scan_mark = [0, 0]
+
     def timed(step, steps, warmup, sampler=None):
         for _ in range(warmup):
             flush.fill_(1)
             step()
         barrier()
+        # the kernel time reported with the roofline is the mean over the TIMED steps only
+        scan_mark[0], scan_mark[1] = nn.stat("scan_ns_total"), nn.stat("scan_count")
         if sampler:
             sampler.start()
         ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
@@ -379,7 +383,7 @@ def run_gpu_arm(args):
     dev_ms, _, clocks = timed(step_device, args.steps, args.warmup, sampler)
     launches = nn.stat("launches") - l0 + (args.steps + args.warmup) * (R_QB if world > 1 else 0)
     launches_timed = launches * args.steps // (args.steps + args.warmup)
-    scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
+    scan_ns = (nn.stat("scan_ns_total") - scan_mark[0]) / max(nn.stat("scan_count") - scan_mark[1], 1)
     fallbacks = nn.stat("last_fallbacks")
     used_tc = nn.stat("last_tc") == 1
     res_ids = (m_ids if world > 1 else d_ids).cpu().numpy().astype(np.uint64)
@@ -394,7 +398,8 @@ def run_gpu_arm(args):
         nn.set_option("tc_scan", 0)
         nn.set_option("profile", 1)
         f_ms, _, _ = timed(step_device, max(args.steps // 2, 2), 3)
-        fp32_leg = (f_ms / max(args.steps // 2, 2), nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1))
+        fp32_leg = (f_ms / max(args.steps // 2, 2),
+                    (nn.stat("scan_ns_total") - scan_mark[0]) / max(nn.stat("scan_count") - scan_mark[1], 1))
         nn.set_option("tc_scan", -1)
 
     motion = None if args.no_motion else motion_block(args, torch, dist, nccl, dev, local, rank, world, timed)
@@ -443,10 +448,10 @@ def run_gpu_arm(args):
 
         roofline_fp32 = None
         if used_tc:
-            kpad = (3 * DIM + 3 + 31) // 32 * 32
+            kpad = (3 * DIM + 3 + 15) // 16 * 16  # K issued: ceil((3 d + 3) / 16) tcgen05.mma of K = 16
             tpeak = peaks.get("bf16_tflops", 2250.0)
             ach = alg_flops / (scan_ns * 1e-9) / 1e12
-            exe = 2.0 * kpad * pairs            # MMA flops issued: K = 3d + 3 padded to 32
+            exe = 2.0 * kpad * pairs            # MMA flops issued: K = 3d + 3 padded to 16
             roofline = {
                 "bound": "tensor", "kernel": "knn_scan_tc_kernel<16,4> (+ query image kernel)", "achieved": ach,
                 "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
@@ -460,13 +465,13 @@ def run_gpu_arm(args):
                 "frac_executed": exe / (scan_ns * 1e-9) / 1e12 / tpeak,
                 "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                 "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
-                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu round 2: 25 % busy) and neither is HBM: "
-                        "the kernel is bound by instruction issue in the selection warps (issue slots 64 % busy; of the executed "
-                        "instructions 19 % are the FMNMX3 min-trees over the accumulators, 28 % branch / sync / nop overhead of the "
-                        "per-step TMEM load handshake, 29 % integer bookkeeping and list insertions, 6 % mbarrier polls; "
-                        "profiles/r2_scan_tc_d7_instruction_mix.txt). Every FP32 accumulator value costs at least 1 issue clock per SM "
-                        "sub-partition whatever instruction looks at it (scripts/ubench_reduce.cu), i.e. 1.76 ms for this "
-                        "launch; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which bounded the FP32 scan "
+                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu round 2: 30 % busy) and neither is HBM: "
+                        "the kernel is bound by instruction issue and latency in the selection warps (issue slots 63 % busy; of the "
+                        "executed instructions 23 % are the FMNMX3 min-trees over the accumulators, 23 % branch / sync / nop overhead "
+                        "of the per-half-tile TMEM hand-over, 25 % integer bookkeeping and list insertions, 13 % compares, 12 % "
+                        "mbarrier polls; profiles/r2_scan_tc_d7_instruction_mix.txt). Every FP32 accumulator value costs at least 1 "
+                        "issue clock per SM sub-partition whatever instruction looks at it (scripts/ubench_reduce.cu), i.e. 1.76 ms "
+                        "for this launch; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which bounded the FP32 scan "
                         "(roofline_fp32_scan)",
             }
             if fp32_leg:
@@ -749,10 +754,11 @@ def run_m4(args):
     for _ in range(args.warmup):
         step_device()
     sampler.start()
+    mark = (nn.stat("scan_ns_total"), nn.stat("scan_count"))  # kernel time: mean over the timed steps only
     dev_ms = timed(step_device, args.steps, 0)
     clocks = sampler.stop()
     launches = (nn.stat("launches") - l0) * args.steps // (args.steps + args.warmup)
-    scan_ns = nn.stat("scan_ns_total") / max(nn.stat("scan_count"), 1)
+    scan_ns = (nn.stat("scan_ns_total") - mark[0]) / max(nn.stat("scan_count") - mark[1], 1)
     e2e_ms = timed(step_e2e, args.steps, max(args.warmup, 1))
     assert (d_ids.cpu().numpy().astype(np.uint64) == h_ids).all()
     peaks = {}
@@ -761,7 +767,7 @@ def run_m4(args):
     except OSError:
         pass
     tpeak = peaks.get("bf16_tflops", 2250.0)
-    kpad = (3 * d + 3 + 31) // 32 * 32
+    kpad = (3 * d + 3 + 15) // 16 * 16  # K issued: ceil((3 d + 3) / 16) tcgen05.mma of K = 16
     pairs = float(nq) * n
     t_step = dev_ms / args.steps
     ach = 3.0 * d * pairs / (scan_ns * 1e-9) / 1e12
@@ -776,7 +782,8 @@ def run_m4(args):
         "e2e": {"value": nq / (e2e_ms / args.steps * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(qs.nbytes),
                 "d2h_bytes_per_step": int(h_ids.nbytes + h_d.nbytes)},
         "gpu_launches": int(launches),
-        "roofline": {"bound": "tensor", "kernel": "knn_scan_tc_kernel<16,1,TS> (query tile in TMEM)", "achieved": ach,
+        "roofline": {"bound": "tensor", "kernel": "knn_scan_tc_kernel<16,1,TS,PAIR> (query tile in TMEM, CTA pairs share "
+                                                  "the point chunks by TMA multicast)", "achieved": ach,
                      "peak": tpeak, "unit": "TFLOP/s", "frac": ach / tpeak,
                      "traffic": ncu_traffic("r2_scan_tc_d100_ncu_summary.csv"),
                      "traffic_unit": "bytes/launch (profiles/r2_scan_tc_d100_ncu_summary.csv)",
@@ -784,7 +791,14 @@ def run_m4(args):
                      "frac_executed": 2.0 * kpad * pairs / (scan_ns * 1e-9) / 1e12 / tpeak,
                      "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                      "peak_source": "MEASURED_PEAKS.json bf16_tflops (burst)" if "bf16_tflops" in peaks
-                     else "fallback 2250 TFLOP/s"},
+                     else "fallback 2250 TFLOP/s",
+                     "frac_executed_of_sustained_peak": (2.0 * kpad * pairs / (scan_ns * 1e-9) / 1e12 /
+                                                         peaks["bf16_tflops_sustained"])
+                     if "bf16_tflops_sustained" in peaks else None,
+                     "note": "tensor-bound: without the selection the same MMAs take 2.6 of the 3.1 ms (profiles/"
+                             "r2_experiments.md), the rate of the sustained cuBLAS figure of MEASURED_PEAKS.json (the chip "
+                             "runs at its power cap under dense BF16 MMA); ncu: tensor pipe 63 % of cycles at the capture's "
+                             "clocks, DRAM 0.3 GB per launch"},
         "exact_fallback_queries": int(nn.stat("last_fallbacks")),
     }
     if not args.no_cpu:
