@@ -155,10 +155,15 @@ int omplcu_merge_topk_strided_device(int device, const double *d_dists, const ui
 /* Tuning / introspection.  Options: "force_exact" (0/1); "tc_scan" (-1 auto and 1: tensor-core filter scan
  * whenever the space is eligible (plain RealVector, d <= 128, k <= 40), 0 never: FP32-pipe scans; the environment
  * variable OMPLCU_TC_SCAN sets the default for new handles); "sample_thresholds", "collect",
- * "scan_ctas_per_sm", "tc_tiles", "profile" (tuning); "tc_scan_values_out" (diagnostics: device pointer that
- * receives the raw scan values).  Stats: "last_fallbacks", "last_path" (1 filter scan + exact re-rank,
- * 2 exact sort), "last_tc" (1 if the last scan ran on the tensor cores), "launches" (kernels launched by
- * this handle so far), "last_scan_ns", "slots". */
+ * "scan_ctas_per_sm", "tc_tiles", "profile" (tuning); "few_scan" (1: calls of up to 8 queries in auto mode run the
+ * lane-per-point scan, default), "tc_ts" (query tile in tensor memory), "tc_pair" (CTA pairs share the point chunks),
+ * "tc_align" (work pieces end on query-tile boundaries), "thr_scan", "l2_window" (tuning);
+ * "tc_scan_values_out" (diagnostics: device pointer that receives the raw scan values).  Stats: "last_fallbacks"
+ * (queries redone by the exact path), "last_rescans" (queries the tensor-core filter passed on to the FP32-pipe scan),
+ * "tc_demoted" (auto mode made the FP32-pipe scan the first filter: the set is too dense for the BF16 band),
+ * "last_path" (1 filter scan + exact re-rank, 2 exact sort), "last_tc" (1 if the last scan ran on the tensor cores),
+ * "last_few" (1 if it was the few-query scan), "launches" (kernels launched by this handle so far), "last_scan_ns",
+ * "slots". */
 int omplcu_nn_set_option(omplcu_nn_t nn, const char *key, long value);
 int omplcu_nn_get_stat(omplcu_nn_t nn, const char *key, long *value);
 
