@@ -238,6 +238,48 @@ namespace omplcu
             }
         }
 
+        // ---- Morton order for large query batches (knn_fast) ----
+        // The selection's slow path runs whenever ANY of a warp's 32 queries sees a value below its threshold.  When
+        // the lanes hold nearby queries the same points are near all of them and the hits coincide: 5 % off the scan
+        // at 1M states, 16 % at 125K (profiles/r2_experiments.md).  Two bits per dimension (the first 16 dimensions)
+        // are all that helps; the sort is stable, so the order within a cell is the caller's.
+        constexpr int QSORT_DIMS = 16;
+        __global__ void qsort_bbox_kernel(const double *q, size_t nq, int D, int nd, uint32_t *bbox)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            for (int c = 0; c < nd; ++c)
+            {
+                const uint32_t key = i < nq ? few_key((float)q[i * D + c]) : 0xFFFFFFFFu;
+                const uint32_t lo = __reduce_min_sync(0xffffffffu, key);
+                const uint32_t hi = __reduce_max_sync(0xffffffffu, key == 0xFFFFFFFFu ? 0u : key);
+                if ((threadIdx.x & 31) == 0)
+                {
+                    atomicMin(&bbox[c], lo);
+                    atomicMax(&bbox[QSORT_DIMS + c], hi);
+                }
+            }
+        }
+        __global__ void qsort_key_kernel(const double *q, size_t nq, int D, int nd, const uint32_t *bbox, uint32_t *keys,
+                                         uint32_t *idx)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nq)
+                return;
+            uint32_t cell[QSORT_DIMS];
+            for (int c = 0; c < nd; ++c)
+            {
+                const float lo = few_unkey(bbox[c]), hi = few_unkey(bbox[QSORT_DIMS + c]);
+                const float t = ((float)q[i * D + c] - lo) / fmaxf(hi - lo, 1e-30f) * 4.0f;
+                cell[c] = t >= 0.f ? min((uint32_t)t, 3u) : 0u;  // NaN -> 0
+            }
+            uint32_t key = 0;
+            for (int b = 1; b >= 0; --b)
+                for (int c = 0; c < nd; ++c)
+                    key = (key << 1) | ((cell[c] >> b) & 1u);
+            keys[i] = key;
+            idx[i] = (uint32_t)i;
+        }
+
         // ---- second pass over the queries the tensor-core filter could not prove (knn_fast) ----
         __global__ void gather_rows_kernel(const double *q, const uint32_t *sel, size_t nsel, int D, double *out)
         {
@@ -258,20 +300,24 @@ namespace omplcu
 
         // ---- query preparation for the scan ----
         // qp[c][q] = -2 * fl32(q_c - center_c); qaux[q] = (|qt|^2, |qt|) in FP64
+        // perm (optional): position i of the scan holds query perm[i] (knn_fast sorts large batches along a Morton
+        // curve so that the lanes of a selection warp hold nearby queries)
         __global__ void query_prep_kernel(const double *q, size_t nq, const double *center, int D, float *qp,
-                                          double *qaux, uint32_t qpad, unsigned *zero = nullptr)
+                                          double *qaux, uint32_t qpad, unsigned *zero = nullptr,
+                                          const uint32_t *perm = nullptr)
         {
             size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
             if (i == 0 && zero)
                 *zero = 0;  // the re-rank's fallback counter (saves a memset launch per call)
             if (i >= qpad)
                 return;
+            const size_t src = (perm && i < nq) ? perm[i] : i;
             double qn = 0.0;
             for (int c = 0; c < D; ++c)
             {
                 float v = 0.f;
                 if (i < nq)
-                    v = __double2float_rn(q[i * D + c] - center[c]);
+                    v = __double2float_rn(q[src * D + c] - center[c]);
                 qp[(size_t)c * qpad + i] = -2.f * v;
                 qn += (double)v * (double)v;
             }
@@ -294,17 +340,19 @@ namespace omplcu
             const float *cand_thr, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
             const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
             const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
-            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units)
+            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units,
+            const uint32_t *perm = nullptr)
         {
             __shared__ double s_key[4][MAXC];
             __shared__ uint32_t s_slot[4][MAXC];
             __shared__ double s_dk[4];
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-            const size_t qi = blockIdx.x * 4ull + w;
+            const size_t qi = blockIdx.x * 4ull + w;  // position in the scan's order
             if (qi >= nq)
                 return;
+            const size_t qo = perm ? perm[qi] : qi;   // the caller's query index
             const uint32_t n = smax * L;
-            const double *qrow = q + qi * D;
+            const double *qrow = q + qo * D;
             for (uint32_t c = lane; c < n; c += 32)
             {
                 const uint32_t slot = cand_ids[(size_t)c * qpad + qi];
@@ -332,9 +380,9 @@ namespace omplcu
                 }
                 if (rank < kk)
                 {
-                    out_ids[qi * kstride + rank] = slot_ids[slot];
+                    out_ids[qo * kstride + rank] = slot_ids[slot];
                     if (out_dists)
-                        out_dists[qi * kstride + rank] = key;
+                        out_dists[qo * kstride + rank] = key;
                     if (rank == kk - 1)
                         s_dk[w] = key;
                 }
@@ -365,7 +413,7 @@ namespace omplcu
             if (bad && lane == 0)
             {
                 unsigned pos = atomicAdd(ovf_count, 1u);
-                ovf_list[pos] = (uint32_t)qi;
+                ovf_list[pos] = (uint32_t)qo;
             }
         }
 
@@ -774,20 +822,22 @@ namespace omplcu
             const float *cand_thr, const uint32_t *cand_ids, uint32_t smax, uint32_t L, uint32_t qpad,
             const double *pts, const uint64_t *slot_ids, int D, const double *q, const double *qaux,
             const unsigned *pmax2_bits, size_t nq, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
-            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units)
+            double *out_dists, uint32_t *ovf_list, unsigned *ovf_count, double err_units,
+            const uint32_t *perm = nullptr)
         {
             extern __shared__ __align__(16) unsigned char sel_smem[];
             const int lane = threadIdx.x & 31;
-            const size_t qi = blockIdx.x;
+            const size_t qi = blockIdx.x;  // position in the scan's order
             if (qi >= nq)
                 return;
+            const size_t qo = perm ? perm[qi] : qi;  // the caller's query index
             const uint32_t n = smax * L;
             double *s_key = reinterpret_cast<double *>(sel_smem);
             double *s_q = s_key + n;
             uint32_t *s_slot = reinterpret_cast<uint32_t *>(s_q + D);
             const double inf = __longlong_as_double(0x7ff0000000000000ll);
             for (int i = threadIdx.x; i < D; i += SEL_THREADS)
-                s_q[i] = q[qi * D + i];
+                s_q[i] = q[qo * D + i];
             __syncthreads();
             // exact distances: the whole block (the candidates' rows are scattered loads); the selection below
             // is one warp's work
@@ -882,9 +932,9 @@ namespace omplcu
                     break;  // fewer than kk candidates: dk stays negative, the query is redone exactly
                 if (lane == 0)
                 {
-                    out_ids[qi * kstride + r] = slot_ids[ws];
+                    out_ids[qo * kstride + r] = slot_ids[ws];
                     if (out_dists)
-                        out_dists[qi * kstride + r] = wk;
+                        out_dists[qo * kstride + r] = wk;
                 }
                 if (r == kk - 1)
                     dk = wk;
@@ -916,7 +966,7 @@ namespace omplcu
             if (bad && lane == 0)
             {
                 const unsigned pos = atomicAdd(ovf_count, 1u);
-                ovf_list[pos] = (uint32_t)qi;
+                ovf_list[pos] = (uint32_t)qo;
             }
         }
 
@@ -1689,6 +1739,8 @@ namespace omplcu
             tc_na_ = (int)v;  // upper limit on resident query tiles per CTA (1, 2, 4); 0 = by shape
         else if (!strcmp(key, "tc_ts"))
             tc_ts_ = (int)v;  // one resident tile (d >= 53, or small batches): query tile in tensor memory
+        else if (!strcmp(key, "sort_queries"))
+            sort_queries_ = v != 0;  // batches of >= 4096 queries are scanned in Morton order (results in the caller's order)
         else if (!strcmp(key, "few_scan"))
             few_mode_ = v != 0;  // up to 8 queries: lane-per-point FP32 scan instead of a mostly empty tensor-core tile
         else if (!strcmp(key, "tc_align"))
@@ -2099,7 +2151,29 @@ namespace omplcu
             CUDA_CHECK(cudaMemsetAsync(c.cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
             CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));  // 3.4e38: "not full"
         }
-        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad, c.counters_.p);
+        // large batches: scan order = Morton order of the queries (qsort_*_kernel above); results go back to the
+        // caller's rows through `perm`
+        const uint32_t *perm = nullptr;
+        if (tc && sort_queries_ && nq >= 4096 && !tc_dbg_ && tc_sh.na >= 2)  // the one-tile shapes are tensor-bound: no gain
+        {
+            const int nd = std::min(D_, QSORT_DIMS);
+            c.qs_keys_.reserve(2 * nq);
+            c.qs_idx_.reserve(2 * nq);
+            c.qs_bbox_.reserve(2 * QSORT_DIMS);
+            CUDA_CHECK(cudaMemsetAsync(c.qs_bbox_.p, 0xFF, QSORT_DIMS * sizeof(uint32_t), s));
+            CUDA_CHECK(cudaMemsetAsync(c.qs_bbox_.p + QSORT_DIMS, 0, QSORT_DIMS * sizeof(uint32_t), s));
+            qsort_bbox_kernel<<<nblk(nq, 256), 256, 0, s>>>(d_q, nq, D_, nd, c.qs_bbox_.p);
+            qsort_key_kernel<<<nblk(nq, 256), 256, 0, s>>>(d_q, nq, D_, nd, c.qs_bbox_.p, c.qs_keys_.p, c.qs_idx_.p);
+            cub::DoubleBuffer<uint32_t> dk(c.qs_keys_.p, c.qs_keys_.p + nq), dv(c.qs_idx_.p, c.qs_idx_.p + nq);
+            size_t tmp = 0;
+            CUDA_CHECK(cub::DeviceRadixSort::SortPairs(nullptr, tmp, dk, dv, (int)nq, 0, 2 * nd, s));
+            c.cub_tmp_.reserve(tmp);
+            CUDA_CHECK(cub::DeviceRadixSort::SortPairs(c.cub_tmp_.p, tmp, dk, dv, (int)nq, 0, 2 * nd, s));
+            perm = dv.Current();
+            launches_ += 4;
+        }
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_q, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad, c.counters_.p,
+                                                          perm);
         launches_++;
         ScanParams P;
         P.filt = filt_.p;
@@ -2216,13 +2290,13 @@ namespace omplcu
             knn_rerank_select_kernel<<<(unsigned)nq, SEL_THREADS,
                                        (size_t)smax * L * 12 + (size_t)D_ * 8 + 8 + (size_t)(SEL_THREADS / 32) * kk * 12, s>>>(
                 c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad, pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p,
-                nq, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, tc_err_units(D_));
+                nq, (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists, c.ovf_list_.p, c.counters_.p, tc_err_units(D_), perm);
         else
         knn_rerank_kernel<512><<<nblk(nq, 4), 128, 0, s>>>(c.cand_vals_.p, c.cand_ids_.p, smax, (uint32_t)L, qpad,
                                                           pts64_.p, ids_.p, D_, d_q, c.qaux_.p, pmax2_.p, nq,
                                                           (uint32_t)kk, (uint32_t)kstride, d_ids, d_dists,
                                                           c.ovf_list_.p, c.counters_.p,
-                                                          tc ? tc_err_units(D_) : (double)(D_ + 3));
+                                                          tc ? tc_err_units(D_) : (double)(D_ + 3), perm);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         unsigned novf = 0;

@@ -189,6 +189,7 @@ namespace omplcu
             double *ho_dists_ = nullptr;
             size_t ho_entries_ = 0;
             bool ho_done_ = false;
+            DevBuf<uint32_t> qs_keys_, qs_idx_, qs_bbox_;  // Morton order of a large query batch (knn_fast)
             DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered
             DevBuf<double> re_q_, re_d_;
             DevBuf<uint64_t> re_ids_;
@@ -223,6 +224,7 @@ namespace omplcu
         std::atomic<long> tc_seen_{0}, tc_unproven_{0};  // auto mode: recent queries / unproven by the tensor-core filter
         std::atomic<bool> tc_demoted_{false};
         std::atomic<size_t> tc_demote_slots_{0};
+        bool sort_queries_ = true;  // large batches: scan the queries in Morton order
         bool few_mode_ = true;    // auto mode, up to 8 queries: knn_few_kernel
         long last_few_ = 0;
         bool tc_align_ = true;    // tensor-core scan: work pieces end on query-tile boundaries where that is nearly free
