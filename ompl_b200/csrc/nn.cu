@@ -37,6 +37,122 @@ namespace omplcu
             return __int_as_float(0x7f800000);
         }
 
+        // ---- Euclidean lower-bound embedding of SO(2) / SO(3) / compound spaces ----
+        // The tensor-core filter works on squared Euclidean distances.  For a space whose components are
+        // RealVector, SO(2) and SO(3) (SE(2), SE(3), any weighted compound of them) there is a map E into R^D with
+        //        || E(x) - E(y) ||  <=  distance(x, y) + slack            for all states x, y,
+        // so "every slot within B of the query" (what the exact paths need, B being their exact distance bound) is a
+        // subset of "every slot whose embedded point is within B + slack of the embedded query", which is what
+        // filter_scan returns; the exact distance of the kept slots then decides as before.  Per component, with
+        // weight w (CompoundStateSpace::distance is the weighted SUM, StateSpace.cpp:1068-1076, and
+        // a + b >= sqrt(a^2 + b^2) for non-negative terms):
+        //   RealVector   w x                                   the distance itself
+        //   SO(2)        w (cos a, sin a)                      chord 2 sin(t/2) <= t = SO2StateSpace::distance
+        //                                                      (angles in [-pi, pi], SO2StateSpace.cpp:108-115)
+        //   SO(3)        w (q_i^2 / sqrt 2, q_i q_j (i < j))   = vec(q q^T) / sqrt 2: ||.||^2 = 1 - <q1,q2>^2 = sin^2 t
+        //                                                      <= t^2, t = acos|<q1,q2>| (SO3StateSpace.cpp:254-262)
+        // SO(3) slack: the reference returns 0 once |<q1,q2>| > 1 - 1e-9, where sin t is still up to 4.5e-5, and
+        // quaternions whose squared norm is off by eta add 2 eta under the root: 7e-5 per unit of weight covers
+        // eta <= 1e-9.  A state outside these assumptions (|angle| > pi, | |q|^2 - 1 | > 1e-9) raises a flag:
+        // a point switches the filter off for the structure, a query is sent to the unfiltered path.
+        __host__ __device__ inline int embed_dim(const omplcu_component &c)
+        {
+            return c.type == OMPLCU_RV ? c.dim : c.type == OMPLCU_SO2 ? 2 : c.type == OMPLCU_SO3 ? 10 : -1;
+        }
+        constexpr double EMBED_SO3_SLACK = 7e-5;
+        template <typename PS>
+        __host__ __device__ inline bool embed_state(const SpaceDesc &sp, PS st, double *out)
+        {
+            bool ok = true;
+            int off = 0, o = 0;
+            for (int i = 0; i < sp.ncomp; ++i)
+            {
+                const omplcu_component &c = sp.comp[i];
+                const double w = sp.compound ? c.weight : 1.0;
+                if (c.type == OMPLCU_RV)
+                {
+                    for (int k = 0; k < c.dim; ++k)
+                        out[o++] = w * st[off + k];
+                }
+                else if (c.type == OMPLCU_SO2)
+                {
+                    const double a = st[off];
+                    ok = ok && fabs(a) <= 3.14159265358979323846 * (1.0 + 1e-15);
+                    out[o++] = w * cos(a);
+                    out[o++] = w * sin(a);
+                }
+                else
+                {
+                    const double q0 = st[off], q1 = st[off + 1], q2 = st[off + 2], q3 = st[off + 3];
+                    const double n2 = q0 * q0 + q1 * q1 + q2 * q2 + q3 * q3;
+                    ok = ok && fabs(n2 - 1.0) <= 1e-9;
+                    const double h = w * 0.70710678118654752440;
+                    out[o++] = h * q0 * q0;
+                    out[o++] = h * q1 * q1;
+                    out[o++] = h * q2 * q2;
+                    out[o++] = h * q3 * q3;
+                    out[o++] = w * q0 * q1;
+                    out[o++] = w * q0 * q2;
+                    out[o++] = w * q0 * q3;
+                    out[o++] = w * q1 * q2;
+                    out[o++] = w * q1 * q3;
+                    out[o++] = w * q2 * q3;
+                }
+                off += c.dim;
+            }
+            return ok;
+        }
+
+        // filt_append_kernel for an embedded space: row = fl32(E(state) - c), norm as there
+        __global__ void filt_append_embed_kernel(SpaceDesc sp, const double *pts, const double *center, float *filt,
+                                                 unsigned *pmax2, int D, int rowf, size_t first, size_t n, unsigned *bad)
+        {
+            size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            float pn = 0.f;
+            if (i < n)
+            {
+                double e[KNN_MAX_FAST_DIM];
+                if (!embed_state(sp, pts + (first + i) * sp.stride, e))
+                    atomicOr(bad, 1u);
+                float *f = filt + (first + i) * rowf;
+                double acc = 0.0;
+                for (int c = 0; c < D; ++c)
+                {
+                    float v = __double2float_rn(e[c] - center[c]);
+                    f[c] = v;
+                    acc += (double)v * (double)v;
+                }
+                pn = __double2float_rn(acc);
+                if (!(pn < 3.0e38f))
+                    atomicOr(bad, 1u);  // non-finite coordinates: let the exact path deal with them
+                f[D] = pn;
+                for (int c = D + 1; c < rowf; ++c)
+                    f[c] = 0.f;
+            }
+            unsigned b = __float_as_uint(pn < 3.0e38f ? pn : 0.f);
+            for (int o = 16; o > 0; o >>= 1)
+                b = max(b, __shfl_xor_sync(0xffffffffu, b, o));
+            if ((threadIdx.x & 31) == 0 && b)
+                atomicMax(pmax2, b);
+        }
+
+        // queries of an exact path -> embedded queries and the bound the filter has to honour
+        // (bound_in: exact distance bound per query, or per-query radius)
+        __global__ void embed_queries_kernel(SpaceDesc sp, const double *q, size_t nq, int D, double slack,
+                                             const double *bound_in, double *out, double *bound_out)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= nq)
+                return;
+            double e[KNN_MAX_FAST_DIM];
+            const bool ok = embed_state(sp, q + i * sp.stride, e);
+            for (int c = 0; c < D; ++c)
+                out[i * D + c] = e[c];
+            const double b = bound_in[i];
+            // not ok / NaN / negative: an infinite bound keeps every slot, the row overflows, the query is redone unfiltered
+            bound_out[i] = (ok && b >= 0.0) ? b * (1.0 + 1e-9) + slack + 1e-12 : __longlong_as_double(0x7ff0000000000000ll);
+        }
+
         // ---- filter-copy maintenance ----
         // rows [first, first+n): coords 0, norm +inf  ("dead": never passes the filter)
         __global__ void filt_fill_dead_kernel(float *filt, int rowf, int D, size_t first, size_t n)
@@ -1099,6 +1215,107 @@ namespace omplcu
             }
         };
 
+        // kept_collect_kernel for any metric: exact distance of the slots the (embedded) filter kept, survivors within
+        // the query's exact bound written in slot order.  Query b of this batch is query q0 + b of pm.
+        __global__ void __launch_bounds__(128) kept_collect_metric_kernel(const uint32_t *app_ids, const uint32_t *app_cnt,
+                                                                          uint32_t smax, uint32_t cap, uint32_t qpad,
+                                                                          PairMetric pm, size_t q0, const uint8_t *alive,
+                                                                          const double *bound, size_t nb, uint32_t cap2,
+                                                                          double *keys, uint32_t *vals, uint32_t *cnt)
+        {
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const double bd = bound[b];
+            uint32_t n = 0;
+            bool over = false;
+            for (uint32_t s = 0; s < smax && !over; ++s)
+            {
+                const uint32_t c = app_cnt[(size_t)s * qpad + b];
+                if (c > cap)
+                {
+                    over = true;
+                    break;
+                }
+                const uint32_t *row = app_ids + ((size_t)s * qpad + b) * cap;
+                for (uint32_t i0 = 0; i0 < c; i0 += 32)
+                {
+                    const uint32_t i = i0 + lane;
+                    bool keep = false;
+                    uint32_t slot = 0;
+                    double d = 0.0;
+                    if (i < c)
+                    {
+                        slot = row[i];
+                        if (alive[slot])
+                        {
+                            d = pm(slot, q0 + b);
+                            keep = d <= bd;
+                        }
+                    }
+                    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                    const uint32_t pos = n + __popc(bal & ((1u << lane) - 1u));
+                    if (keep && pos < cap2)
+                    {
+                        keys[b * cap2 + pos] = d;
+                        vals[b * cap2 + pos] = slot;
+                    }
+                    n += __popc(bal);
+                }
+            }
+            if (lane == 0)
+                cnt[b] = (over || n > cap2) ? cap2 + 1u : n;
+        }
+
+        // Embedded spaces, bound for the filter: the kk-th smallest EXACT distance among the (<= 512) slots a list scan
+        // on the embedding found for the query.  Any kk real points bound the kk-th nearest distance from above, and
+        // the embedding's nearest are nearly the metric's nearest, so the bound is tight (a few times kk slots lie
+        // within it, against thousands for a bound from a 1024-point sample).  Fewer than kk candidates: +inf.
+        __global__ void __launch_bounds__(128) cand_bound_kernel(const uint32_t *cand_ids, uint32_t n, uint32_t qpad,
+                                                                 PairMetric pm, size_t q0, const uint8_t *alive, size_t nb,
+                                                                 uint32_t kk, double *bound)
+        {
+            __shared__ double s_key[4][512];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const uint32_t slot = cand_ids[(size_t)c * qpad + b];
+                double d = inf;
+                if (slot != SLOT_NONE && alive[slot])
+                {
+                    d = pm(slot, q0 + b);
+                    if (!(d == d))
+                        d = inf;
+                }
+                s_key[w][c] = d;
+            }
+            __syncwarp();
+            double out = inf;
+            for (uint32_t c = lane; c < n; c += 32)
+            {
+                const double key = s_key[w][c];
+                if (!(key < inf))
+                    continue;
+                uint32_t rank = 0;
+                for (uint32_t o = 0; o < n; ++o)
+                {
+                    const double ko = s_key[w][o];
+                    rank += (ko < key || (ko == key && o < c)) ? 1u : 0u;
+                }
+                if (rank == kk - 1)
+                    out = key;
+            }
+            for (int o = 16; o > 0; o >>= 1)
+                out = fmin(out, __shfl_xor_sync(0xffffffffu, out, o));
+            if (lane == 0)
+                bound[b] = out;
+        }
+
         // out[row][2i] = cos(theta_i), out[row][2i+1] = sin(theta_i), theta_i = s_0 + ... + s_i
         __global__ void chain_trig_kernel(const double *rows, size_t n, int d, double *out)
         {
@@ -1370,13 +1587,34 @@ namespace omplcu
         sm_count_ = prop.multiProcessorCount;
         fast_space_ = (!sp_.compound && sp_.ncomp == 1 && sp_.comp[0].type == OMPLCU_RV &&
                        sp_.comp[0].dim >= 1 && sp_.comp[0].dim <= KNN_MAX_FAST_DIM);
-        if (fast_space_)
+        if (!fast_space_)
         {
+            // SO(2) / SO(3) / compound spaces of them: Euclidean lower-bound embedding in front of the exact paths
+            int ed = 0;
+            bool ok = sp_.ncomp >= 1, rot = false;
+            for (int i = 0; i < sp_.ncomp && ok; ++i)
+            {
+                const int e = embed_dim(sp_.comp[i]);
+                ok = e > 0 && (!sp_.compound || (sp_.comp[i].weight >= 0.0 && std::isfinite(sp_.comp[i].weight)));
+                ed += e;
+                rot = rot || sp_.comp[i].type != OMPLCU_RV;
+                if (sp_.comp[i].type == OMPLCU_SO3)
+                    embed_slack_ += (sp_.compound ? sp_.comp[i].weight : 1.0) * EMBED_SO3_SLACK;
+            }
+            embed_ = ok && ed >= 1 && ed <= KNN_MAX_FAST_DIM && (rot || sp_.compound);
+            if (embed_)
+                D_ = ed;
+        }
+        if (fast_space_)
             D_ = sp_.comp[0].dim;
+        if (fast_space_ || embed_)
+        {
             rowf_ = scan_rowf(D_);
             center_.reserve(D_);
             pmax2_.reserve(1);
+            embed_bad_.reserve(1);
             CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
+            CUDA_CHECK(cudaMemsetAsync(embed_bad_.p, 0, sizeof(unsigned), stream_));
         }
         if (const char *e = getenv("OMPLCU_TC_SCAN"))
             tc_mode_ = atoi(e);  // default for the "tc_scan" option: -1 auto, 0 never, 1 whenever eligible
@@ -1482,7 +1720,7 @@ namespace omplcu
         pts64_.reserve(n * st, true, stream_);
         ids_.reserve(n, true, stream_);
         alive_.reserve(n, true, stream_);
-        if (fast_space_)
+        if (fast_space_ || embed_)
         {
             size_t rows = ((n + SCAN_PT - 1) / SCAN_PT) * SCAN_PT;
             if (rows > filt_rows_)
@@ -1522,19 +1760,25 @@ namespace omplcu
                                    stream_));
         fill_ids_kernel<<<nblk(n, 256), 256, 0, stream_>>>(ids_.p, alive_.p, nslots_, n, first_id);
         launches_++;
-        if (fast_space_)
+        if (fast_space_ || embed_)
         {
             if (!have_center_)
             {
                 // centre = mean of the first batch (any fixed vector is valid; a
                 // central one keeps the FP32 error bound tight)
                 std::vector<double> c(D_, 0.0);
-                for (size_t i = 0; i < n; ++i)
+                const size_t nmean = embed_ ? std::min<size_t>(n, 4096) : n;
+                std::vector<double> e(embed_ ? D_ : 0);
+                for (size_t i = 0; i < nmean; ++i)
+                {
+                    if (embed_)
+                        embed_state(sp_, rows + i * st, e.data());
                     for (int d = 0; d < D_; ++d)
-                        c[d] += rows[i * st + d];
+                        c[d] += embed_ ? e[d] : rows[i * st + d];
+                }
                 for (int d = 0; d < D_; ++d)
                 {
-                    c[d] /= (double)n;
+                    c[d] /= (double)nmean;
                     if (!std::isfinite(c[d]))
                         c[d] = 0.0;
                 }
@@ -1543,6 +1787,10 @@ namespace omplcu
                 CUDA_CHECK(cudaStreamSynchronize(stream_));  // c is a stack-scoped vector
                 have_center_ = true;
             }
+            if (embed_)
+                filt_append_embed_kernel<<<nblk(n, 128), 128, 0, stream_>>>(sp_, pts64_.p, center_.p, filt_.p, pmax2_.p, D_,
+                                                                            rowf_, nslots_, n, embed_bad_.p);
+            else
             filt_append_kernel<<<nblk(n, 256), 256, 0, stream_>>>(pts64_.p, center_.p, filt_.p, pmax2_.p, D_, rowf_,
                                                                   nslots_, n);
             launches_++;
@@ -1571,7 +1819,7 @@ namespace omplcu
         h_alive_[slot] = 0;
         nlive_--;
         mut_version_++;
-        mark_dead_kernel<<<1, 1, 0, stream_>>>(alive_.p, fast_space_ ? filt_.p : nullptr, rowf_, D_, slot);
+        mark_dead_kernel<<<1, 1, 0, stream_>>>(alive_.p, (fast_space_ || embed_) ? filt_.p : nullptr, rowf_, D_, slot);
         launches_++;
         CUDA_CHECK(cudaGetLastError());
         const size_t dead = nslots_ - nlive_;
@@ -1603,7 +1851,7 @@ namespace omplcu
         d_slots.reserve(slots.size());
         CUDA_CHECK(cudaMemcpyAsync(d_slots.p, slots.data(), slots.size() * sizeof(uint32_t), cudaMemcpyHostToDevice,
                                    stream_));
-        mark_dead_batch_kernel<<<nblk(slots.size(), 256), 256, 0, stream_>>>(alive_.p, fast_space_ ? filt_.p : nullptr,
+        mark_dead_batch_kernel<<<nblk(slots.size(), 256), 256, 0, stream_>>>(alive_.p, (fast_space_ || embed_) ? filt_.p : nullptr,
                                                                              rowf_, D_, d_slots.p, slots.size());
         launches_++;
         CUDA_CHECK(cudaGetLastError());
@@ -1656,11 +1904,20 @@ namespace omplcu
         trig_rows_ = 0;  // slots moved: the chain trig table is rebuilt on the next query
         h_ids_.swap(nids);
         h_alive_.assign(nslots_, 1);
-        if (fast_space_)
+        if (fast_space_ || embed_)
         {
             // rebuild the filter copy for the surviving rows, kill the vacated ones
             if (nslots_)
             {
+                if (embed_)
+                {
+                    CUDA_CHECK(cudaMemsetAsync(embed_bad_.p, 0, sizeof(unsigned), stream_));  // the offender may be gone
+                    embed_ver_ = 0;
+                    filt_append_embed_kernel<<<nblk(nslots_, 128), 128, 0, stream_>>>(sp_, pts64_.p, center_.p, filt_.p,
+                                                                                      pmax2_.p, D_, rowf_, 0, nslots_,
+                                                                                      embed_bad_.p);
+                }
+                else
                 filt_append_kernel<<<nblk(nslots_, 256), 256, 0, stream_>>>(pts64_.p, center_.p, filt_.p, pmax2_.p,
                                                                             D_, rowf_, 0, nslots_);
                 launches_++;
@@ -1679,11 +1936,13 @@ namespace omplcu
     {
         std::unique_lock<std::shared_mutex> lk(rw_);
         DeviceGuard g(device_);
-        if (fast_space_ && nslots_)
+        if ((fast_space_ || embed_) && nslots_)
         {
             filt_fill_dead_kernel<<<nblk(nslots_ * rowf_, 256), 256, 0, stream_>>>(filt_.p, rowf_, D_, 0, nslots_);
             launches_++;
             CUDA_CHECK(cudaMemsetAsync(pmax2_.p, 0, sizeof(unsigned), stream_));
+            CUDA_CHECK(cudaMemsetAsync(embed_bad_.p, 0, sizeof(unsigned), stream_));
+            embed_ver_ = 0;
             CUDA_CHECK(cudaStreamSynchronize(stream_));
         }
         have_center_ = false;
@@ -2575,8 +2834,26 @@ namespace omplcu
 
     bool NNIndex::filter_usable() const
     {
-        return fast_space_ && !force_exact_ && D_ <= TC_MAX_DIM && tc_mode_ != 0 && nslots_ >= 4096 &&
+        return (fast_space_ || embed_) && !force_exact_ && D_ <= TC_MAX_DIM && tc_mode_ != 0 && nslots_ >= 4096 &&
                tc_thr_pick_stages(tc_shape(D_)) > 0;
+    }
+
+    // Embedded spaces: has any stored state broken the embedding's assumptions (embed_state)?  Read once per
+    // mutation; the flag only ever goes up between compactions.
+    bool NNIndex::embed_ok(cudaStream_t s)
+    {
+        if (!embed_)
+            return true;
+        std::lock_guard<std::mutex> pl(prep_mu_);
+        if (embed_ver_ != mut_version_)
+        {
+            unsigned bad = 0;
+            CUDA_CHECK(cudaMemcpyAsync(&bad, embed_bad_.p, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            embed_okay_ = bad == 0;
+            embed_ver_ = mut_version_;
+        }
+        return embed_okay_;
     }
 
     // See nn.cuh.  Returns smax (rows per query); *qpad_out = the row pitch of app_cnt_ / app_ids_.
@@ -2646,6 +2923,81 @@ namespace omplcu
         return smax;
     }
 
+    // Embedded spaces: tensor-core LIST scan of the embedded queries against the embedded roadmap (the lists of the
+    // fast path, no re-rank), then cand_bound_kernel: d_bound[b] = kk-th smallest exact distance among the listed slots.
+    void NNIndex::embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
+                                   double *d_bound, cudaStream_t s)
+    {
+        const PairMetric &pm = *static_cast<const PairMetric *>(pair_metric);
+        TcShape sh = tc_shape(D_);
+        const int L = kk <= 10 ? 16 : (kk <= 14 ? 24 : 48);
+        int stages = tc_pick_stages(sh, L);
+        while (stages < 3 && sh.na > 1)
+        {
+            sh.na /= 2;
+            stages = tc_pick_stages(sh, L);
+        }
+        while (sh.na > 1 && nq <= (size_t)TC_QT * (sh.na / 2))
+        {
+            sh.na /= 2;
+            stages = tc_pick_stages(sh, L);
+        }
+        REQUIRE(stages > 0, "embedded list scan: shape does not fit shared memory");
+        const size_t QT = (size_t)TC_QT * sh.na;
+        const size_t qtiles = (nq + QT - 1) / QT;
+        const uint32_t qpad = (uint32_t)(qtiles * QT);
+        const unsigned long long U = (nslots_ + TC_PT - 1) / TC_PT, TU = qtiles * U;
+        const unsigned max_seg = 512u / L;
+        unsigned long long G = std::min<unsigned long long>(sm_count_, TU);
+        G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
+        G = std::max<unsigned long long>(G, 1);
+        uint32_t smax = 1;
+        for (size_t t = 0; t < qtiles; ++t)
+        {
+            const unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
+            const unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
+            const unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
+            smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
+        }
+        REQUIRE((size_t)smax * L <= 512, "embedded list scan: too many segments per query tile");
+        c.qp_.reserve((size_t)D_ * qpad);
+        c.qaux_.reserve(2 * (size_t)qpad);
+        c.cand_vals_.reserve((size_t)smax * qpad);
+        c.cand_ids_.reserve((size_t)smax * L * qpad);
+        CUDA_CHECK(cudaMemsetAsync(c.cand_ids_.p, 0xFF, (size_t)smax * L * qpad * sizeof(uint32_t), s));
+        CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));
+        query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_qe, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
+        {
+            std::lock_guard<std::mutex> pl(prep_mu_);  // shared operand image, see knn_fast
+            if (tc_version_ != mut_version_)
+            {
+                tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
+                tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
+                CUDA_CHECK(cudaStreamSynchronize(s));
+                tc_version_ = mut_version_;
+                launches_++;
+            }
+        }
+        c.tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
+        tc_build_query_image(c.qp_.p, qpad, D_, c.tc_qimg_.p, s);
+        TcScanParams T{};
+        T.pimg = tc_pimg_.p;
+        T.qimg = c.tc_qimg_.p;
+        T.cand_thr = c.cand_vals_.p;
+        T.cand_ids = c.cand_ids_.p;
+        T.units = U;
+        T.total_units = TU;
+        T.qpad = qpad;
+        T.smax = smax;
+        T.sh = sh;
+        T.nstages = stages;
+        tc_launch_scan(L, T, (unsigned)G, s);
+        cand_bound_kernel<<<nblk(nq, 4), 128, 0, s>>>(c.cand_ids_.p, smax * (uint32_t)L, qpad, pm, q0, alive_.p, nq,
+                                                      (uint32_t)kk, d_bound);
+        launches_ += 4;
+        CUDA_CHECK(cudaGetLastError());
+    }
+
     // Large index (>= 32K slots), any k and any metric (FMT*'s k ~ 2100 of 100K; SE3 / chain kNN): sorting
     // every slot per query is the cost of the full path.  Here an exact distance bound per query comes from a strided sample (the R-th
     // smallest of m sample distances, R chosen 4 sigma above k*m/n), only slots within the bound are
@@ -2690,7 +3042,10 @@ namespace omplcu
         if (R > m / 4)
             return false;
         const size_t step = nslots_ / m;
-        const uint32_t cap = (uint32_t)(1.6 * (double)R / m * (double)nslots_) + 256;
+        // embedded spaces, k <= 40: the bound comes from a list scan on the embedding (embed_list_bound) and is tight:
+        // a few times kk slots lie within it, so the rows can be short
+        const bool tight = embed_ && kk <= 40 && d_sel == nullptr && nsel >= 16 && filter_usable() && embed_ok(s);
+        const uint32_t cap = tight ? 1024u : (uint32_t)(1.6 * (double)R / m * (double)nslots_) + 256;
         if (cap < kk)
             return false;
         const size_t budget = (size_t)1 << 26;
@@ -2707,7 +3062,8 @@ namespace omplcu
         CUDA_CHECK(cudaMemsetAsync(c.counters_.p + 1, 0, sizeof(unsigned), s));
         // filter rows: room for every survivor of a query in each of its rows (a query's neighbours are spread
         // over the point ranges of its segments in no particular way)
-        const bool filt = d_sel == nullptr && filter_usable();
+        // embedded spaces: a handful of queries is cheaper unfiltered (one distance pass + one sort)
+        const bool filt = d_sel == nullptr && filter_usable() && (!embed_ || nsel >= 16) && embed_ok(s);
         const uint32_t fcap = ((cap + 64 + 31) / 32) * 32;
         c.last_filter_ = filt ? 1 : 0;
         const bool tables = prepare_chain_tables(c, d_q, c.exact_nq_, s);
@@ -2719,8 +3075,20 @@ namespace omplcu
             const size_t items = nb * cap;
             REQUIRE(items < ((size_t)1 << 31), "exact path: batch too large");
             CUDA_CHECK(cudaMemsetAsync(c.col_cnt_.p, 0, nb * sizeof(uint32_t), s));
+            if (tight)
+            {
+                // embedded spaces, k <= 40: the bound comes from a list scan on the embedding instead of the sample
+                c.q_emb_.reserve(nb * (size_t)D_);
+                c.emb_bound_.reserve(nb);
+                embed_queries_kernel<<<nblk(nb, 128), 128, 0, s>>>(sp_, d_q + b0 * sp_.stride, nb, D_, embed_slack_,
+                                                                   c.col_bound_.p, c.q_emb_.p, c.emb_bound_.p);
+                embed_list_bound(c, c.q_emb_.p, &pm, b0, nb, kk, c.col_bound_.p, s);
+            }
+            else
+            {
             sample_dist_kernel<<<nblk(nb * m, 256), 256, 0, s>>>(pm, alive_.p, step, m, d_sel, b0, nb, c.col_sd_.p);
             rank_select_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.col_sd_.p, m, nb, R, c.col_bound_.p);
+            }
             if (filt)
             {
                 // Plain RealVector space: the tensor-core threshold scan keeps every slot whose scan value is
@@ -2729,10 +3097,26 @@ namespace omplcu
                 // exact distances, the same bound, the same redo rule.  The survivors arrive in slot order, so
                 // one stable sort by distance gives the (distance, slot) order.
                 uint32_t fq = 0;
+                if (embed_)
+                {
+                    // SO(2) / SO(3) / compound: the filter runs on the Euclidean lower-bound embedding (embed_state),
+                    // the kept slots get the space's own exact distance
+                    c.q_emb_.reserve(nb * (size_t)D_);
+                    c.emb_bound_.reserve(nb);
+                    embed_queries_kernel<<<nblk(nb, 128), 128, 0, s>>>(sp_, d_q + b0 * sp_.stride, nb, D_, embed_slack_,
+                                                                       c.col_bound_.p, c.q_emb_.p, c.emb_bound_.p);
+                    const uint32_t rows = filter_scan(c, c.q_emb_.p, nb, c.emb_bound_.p, fcap, &fq, s);
+                    kept_collect_metric_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pm,
+                                                                           b0, alive_.p, c.col_bound_.p, nb, cap,
+                                                                           c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p);
+                }
+                else
+                {
                 const uint32_t rows = filter_scan(c, d_q + b0 * sp_.stride, nb, c.col_bound_.p, fcap, &fq, s);
                 kept_collect_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pts64_.p,
                                                                 alive_.p, D_, d_q + b0 * sp_.stride, c.col_bound_.p,
                                                                 nb, cap, c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p);
+                }
                 collect_segments_kernel<<<nblk(nb, 256), 256, 0, s>>>(c.col_cnt_.p, cap, nb, beg, end);
                 CUDA_CHECK(cudaGetLastError());
                 size_t tmp2 = 0;
@@ -3000,7 +3384,7 @@ namespace omplcu
             // value is below the scan-value image of the radius (a superset of the slots within it); only those get
             // an FP64 distance and the inclusive test d <= r of NearestNeighborsLinear.h:139.  A batch in which
             // some query has more than RCAP neighbours (or an unbounded radius) takes the all-pairs path below.
-            const bool filt = filter_usable();
+            const bool filt = filter_usable() && embed_ok(s);
             constexpr uint32_t RCAP = 2048;
             c.last_filter_ = 0;
             const size_t nb_max = filt ? std::min<size_t>(nq, 8192)
@@ -3025,13 +3409,29 @@ namespace omplcu
                 if (filt)
                 {
                     uint32_t fq = 0;
-                    const uint32_t rows = filter_scan(c, c.q_stage_.p + b0 * st, nb, c.rad_r_.p + b0, RCAP, &fq, s);
                     c.col_sd_.reserve(nb_max * RCAP);
                     c.col_redo_.reserve(nb_max * RCAP);
+                    if (embed_)
+                    {
+                        // the filter runs on the lower-bound embedding, the kept slots get the space's own distance
+                        c.q_emb_.reserve(nb * (size_t)D_);
+                        c.emb_bound_.reserve(nb);
+                        embed_queries_kernel<<<nblk(nb, 128), 128, 0, s>>>(sp_, c.q_stage_.p + b0 * st, nb, D_, embed_slack_,
+                                                                           c.rad_r_.p + b0, c.q_emb_.p, c.emb_bound_.p);
+                        const uint32_t rows = filter_scan(c, c.q_emb_.p, nb, c.emb_bound_.p, RCAP, &fq, s);
+                        kept_collect_metric_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, RCAP, fq, pm,
+                                                                               b0, alive_.p, c.rad_r_.p + b0, nb, RCAP,
+                                                                               c.col_sd_.p, c.col_redo_.p, d_cnt);
+                        launches_++;
+                    }
+                    else
+                    {
+                    const uint32_t rows = filter_scan(c, c.q_stage_.p + b0 * st, nb, c.rad_r_.p + b0, RCAP, &fq, s);
                     kept_collect_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, RCAP, fq, pts64_.p,
                                                                     alive_.p, D_, c.q_stage_.p + b0 * st,
                                                                     c.rad_r_.p + b0, nb, RCAP, c.col_sd_.p,
                                                                     c.col_redo_.p, d_cnt);
+                    }
                     launches_++;
                     CUDA_CHECK(cudaGetLastError());
                     CUDA_CHECK(cudaMemcpyAsync(cnt.data(), d_cnt, nb * sizeof(uint32_t), cudaMemcpyDeviceToHost, s));

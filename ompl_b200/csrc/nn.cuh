@@ -107,6 +107,9 @@ namespace omplcu
         // bound of the large-k path, the radius of nearestR): every slot within d_bound[q] of query q ends up
         // in the query's rows of c.app_ids_ / c.app_cnt_ (smax rows of `cap` slots, in slot order).
         bool filter_usable() const;
+        bool embed_ok(cudaStream_t s);
+        void embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
+                              double *d_bound, cudaStream_t s);
         uint32_t filter_scan(QCtx &c, const double *d_q, size_t nq, const double *d_bound, uint32_t cap,
                              uint32_t *qpad_out, cudaStream_t s);
         void knn_fast_thr(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
@@ -148,6 +151,12 @@ namespace omplcu
         DevBuf<double> center_;
         DevBuf<unsigned> pmax2_;  // bits of max fl32(|pt|^2)
         bool have_center_ = false;
+        // SO(2) / SO(3) / compound spaces: filt_ holds a Euclidean lower-bound embedding of the states (nn.cu, embed_state);
+        // only the filter in front of the exact paths uses it
+        bool embed_ = false, embed_okay_ = true;
+        double embed_slack_ = 0.0;
+        unsigned long embed_ver_ = 0;
+        DevBuf<unsigned> embed_bad_;
 
         // shared, rebuilt lazily by the first query after a mutation (under prep_mu_, then synchronised):
         // BF16 split-operand images of the filter copy (knn_scan_tc.cuh), the strided sample image of the
@@ -189,6 +198,7 @@ namespace omplcu
             double *ho_dists_ = nullptr;
             size_t ho_entries_ = 0;
             bool ho_done_ = false;
+            DevBuf<double> q_emb_, emb_bound_;  // embedded queries and their filter bounds (embedded spaces)
             DevBuf<uint32_t> qs_keys_, qs_idx_, qs_bbox_;  // Morton order of a large query batch (knn_fast)
             DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered
             DevBuf<double> re_q_, re_d_;
