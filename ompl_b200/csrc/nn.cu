@@ -1439,6 +1439,56 @@ namespace omplcu
 
         // first kk of every sorted segment; segments that overflowed or came up short are queued for
         // the full sort (redo holds query indices)
+        // Short kept lists (the tight bounds of the embedded path): rank the survivors of a query by (distance, slot)
+        // in shared memory and emit the kk first, instead of a segmented radix sort over 65536 tiny segments (which was
+        // half of the SE(3) call).  More than MAXN survivors, or fewer than kk: the query is redone unfiltered.
+        template <int MAXN>
+        __global__ void __launch_bounds__(128) collect_rank_emit_kernel(const double *keys, const uint32_t *vals,
+                                                                        const uint32_t *cnt, uint32_t cap,
+                                                                        const uint64_t *slot_ids, size_t b0, size_t nb,
+                                                                        uint32_t kk, uint32_t kstride, uint64_t *out_ids,
+                                                                        double *out_dists, uint32_t *redo,
+                                                                        unsigned *redo_count)
+        {
+            __shared__ double s_key[4][MAXN];
+            __shared__ uint32_t s_slot[4][MAXN];
+            const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            const size_t b = blockIdx.x * 4ull + w;
+            if (b >= nb)
+                return;
+            const size_t qi = b0 + b;
+            const uint32_t n = cnt[b];
+            if (n > (uint32_t)MAXN || n > cap || n < kk)
+            {
+                if (lane == 0)
+                    redo[atomicAdd(redo_count, 1u)] = (uint32_t)qi;
+                return;
+            }
+            for (uint32_t i = lane; i < n; i += 32)
+            {
+                s_key[w][i] = keys[b * cap + i];
+                s_slot[w][i] = vals[b * cap + i];
+            }
+            __syncwarp();
+            for (uint32_t i = lane; i < n; i += 32)
+            {
+                const double key = s_key[w][i];
+                const uint32_t slot = s_slot[w][i];
+                uint32_t rank = 0;
+                for (uint32_t j = 0; j < n; ++j)
+                {
+                    const double kj = s_key[w][j];
+                    rank += (kj < key || (kj == key && s_slot[w][j] < slot)) ? 1u : 0u;
+                }
+                if (rank < kk)
+                {
+                    out_ids[qi * kstride + rank] = slot_ids[slot];
+                    if (out_dists)
+                        out_dists[qi * kstride + rank] = key;
+                }
+            }
+        }
+
         __global__ void collect_emit_kernel(const double *keys, const uint32_t *vals, const uint32_t *cnt,
                                             uint32_t cap, const uint64_t *slot_ids, const uint32_t *sel, size_t b0,
                                             size_t nb, uint32_t kk, uint32_t kstride, uint64_t *out_ids,
@@ -3109,6 +3159,15 @@ namespace omplcu
                     kept_collect_metric_kernel<<<nblk(nb, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pm,
                                                                            b0, alive_.p, c.col_bound_.p, nb, cap,
                                                                            c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p);
+                    if (tight)
+                    {
+                        collect_rank_emit_kernel<512><<<nblk(nb, 4), 128, 0, s>>>(
+                            c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p, cap, ids_.p, b0, nb, (uint32_t)kk, (uint32_t)kstride,
+                            d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1);
+                        CUDA_CHECK(cudaGetLastError());
+                        launches_ += 8;
+                        continue;
+                    }
                 }
                 else
                 {
