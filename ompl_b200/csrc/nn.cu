@@ -1316,6 +1316,212 @@ namespace omplcu
                 bound[b] = out;
         }
 
+        // ---- a handful of queries on ANY space (RRT's nn_->nearest on SE(3), rrt/src/RRT.cpp:170): exact brute force ----
+        // One pass, a lane per slot: every lane evaluates the space's exact FP64 distance of its slot to each query and
+        // the warp keeps, per query, the kk smallest (distance, slot) pairs it has seen (entry i in lane i).  A warp
+        // walks its slots in increasing order, so among equal distances the earlier slot is kept: the union of the
+        // warps' lists contains the exact answer, which exact_few_select_kernel extracts.  No filter, no proof.
+        constexpr int XFEW_MAXQ = 8, XFEW_MAXK = 32, XFEW_WARPS = 4;
+        __device__ __forceinline__ bool xfew_less(double da, uint32_t sa, double db, uint32_t sb)
+        {
+            return da < db || (da == db && sa < sb);
+        }
+        template <int NQ>
+        __global__ void __launch_bounds__(XFEW_WARPS * 32) exact_few_kernel(PairMetric pm, const uint8_t *alive, size_t nslots,
+                                                                           uint32_t nq, uint32_t kk, uint32_t qpad,
+                                                                           double *cand_d, uint32_t *cand_slot)
+        {
+            const unsigned full = 0xffffffffu;
+            const int lane = threadIdx.x & 31;
+            const size_t gw = blockIdx.x * (size_t)XFEW_WARPS + (threadIdx.x >> 5), GW = gridDim.x * (size_t)XFEW_WARPS;
+            const size_t nbatch = (nslots + 31) / 32;
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            double ld[NQ], maxd[NQ];       // list entry `lane` (lanes < kk) and the list maximum, per query
+            uint32_t ls[NQ], maxs[NQ];
+#pragma unroll
+            for (int j = 0; j < NQ; ++j)
+            {
+                ld[j] = maxd[j] = inf;
+                ls[j] = maxs[j] = SLOT_NONE;
+            }
+            for (size_t b = gw; b < nbatch; b += GW)
+            {
+                const size_t slot = b * 32 + lane;
+                const bool live = slot < nslots && alive[slot];
+#pragma unroll
+                for (int j = 0; j < NQ; ++j)
+                {
+                    if (j >= (int)nq)
+                        break;
+                    double d = live ? pm(slot, (size_t)j) : inf;
+                    if (!(d == d))
+                        d = inf;  // a NaN distance never enters a list (NearestNeighborsLinear's comparisons are false too)
+                    uint32_t sl = live ? (uint32_t)slot : SLOT_NONE;
+                    while (true)
+                    {
+                        // smallest (distance, slot) still on offer in this batch
+                        double md = d;
+                        uint32_t ms = sl;
+                        for (int o = 16; o > 0; o >>= 1)
+                        {
+                            const double od = __shfl_xor_sync(full, md, o);
+                            const uint32_t os = __shfl_xor_sync(full, ms, o);
+                            if (xfew_less(od, os, md, ms))
+                            {
+                                md = od;
+                                ms = os;
+                            }
+                        }
+                        if (!(md < inf) || !xfew_less(md, ms, maxd[j], maxs[j]))
+                            break;
+                        // replace the list's maximum
+                        const int dst = __ffs(__ballot_sync(full, lane < (int)kk && ld[j] == maxd[j] && ls[j] == maxs[j])) - 1;
+                        if (lane == dst)
+                        {
+                            ld[j] = md;
+                            ls[j] = ms;
+                        }
+                        if (sl == ms)
+                        {
+                            d = inf;
+                            sl = SLOT_NONE;
+                        }
+                        double xd = lane < (int)kk ? ld[j] : -1.0;
+                        uint32_t xs = lane < (int)kk ? ls[j] : 0u;
+                        for (int o = 16; o > 0; o >>= 1)
+                        {
+                            const double od = __shfl_xor_sync(full, xd, o);
+                            const uint32_t os = __shfl_xor_sync(full, xs, o);
+                            if (xfew_less(xd, xs, od, os))
+                            {
+                                xd = od;
+                                xs = os;
+                            }
+                        }
+                        maxd[j] = xd;
+                        maxs[j] = xs;
+                    }
+                }
+            }
+            if (lane < (int)kk)
+            {
+#pragma unroll
+                for (int j = 0; j < NQ; ++j)
+                {
+                    cand_d[(gw * kk + lane) * qpad + j] = ld[j];
+                    cand_slot[(gw * kk + lane) * qpad + j] = ls[j];
+                }
+            }
+        }
+
+        // the kk smallest (distance, slot) of n candidates per query, two levels as in knn_rerank_select_kernel
+        __global__ void __launch_bounds__(SEL_THREADS) exact_few_select_kernel(const double *cand_d, const uint32_t *cand_slot,
+                                                                              uint32_t n, uint32_t qpad,
+                                                                              const uint64_t *slot_ids, uint32_t kk,
+                                                                              uint32_t kstride, uint64_t *out_ids,
+                                                                              double *out_dists)
+        {
+            extern __shared__ __align__(16) unsigned char sel_smem[];
+            const int lane = threadIdx.x & 31;
+            const uint32_t warp = threadIdx.x >> 5;
+            const size_t qi = blockIdx.x;
+            double *s_key = reinterpret_cast<double *>(sel_smem);
+            double *s_key2 = s_key + n;
+            uint32_t *s_slot = reinterpret_cast<uint32_t *>(s_key2 + (size_t)(SEL_THREADS / 32) * kk);
+            uint32_t *s_slot2 = s_slot + n;
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            for (uint32_t c = threadIdx.x; c < n; c += SEL_THREADS)
+            {
+                s_key[c] = cand_d[(size_t)c * qpad + qi];
+                s_slot[c] = cand_slot[(size_t)c * qpad + qi];
+            }
+            __syncthreads();
+            double bk = inf;
+            uint32_t bs = SLOT_NONE, bi = 0;
+            auto rescan = [&](const double *key, const uint32_t *slot, uint32_t lo, uint32_t hi) {
+                bk = inf;
+                bs = SLOT_NONE;
+                bi = 0;
+                for (uint32_t c = lo + lane; c < hi; c += 32)
+                {
+                    const uint32_t sl = slot[c];
+                    if (sl == SLOT_NONE)
+                        continue;
+                    const double k = key[c];
+                    if (bs == SLOT_NONE || k < bk || (k == bk && sl < bs))
+                    {
+                        bk = k;
+                        bs = sl;
+                        bi = c;
+                    }
+                }
+            };
+            auto pick = [&](double &wk, uint32_t &ws, uint32_t &wi) {
+                wk = bk;
+                ws = bs;
+                wi = bi;
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    const double ok = __shfl_xor_sync(0xffffffffu, wk, o);
+                    const uint32_t os = __shfl_xor_sync(0xffffffffu, ws, o);
+                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, wi, o);
+                    if (os != SLOT_NONE && (ws == SLOT_NONE || ok < wk || (ok == wk && os < ws)))
+                    {
+                        wk = ok;
+                        ws = os;
+                        wi = oi;
+                    }
+                }
+                return ws != SLOT_NONE;
+            };
+            {
+                const uint32_t per = (n + SEL_THREADS / 32 - 1) / (SEL_THREADS / 32);
+                const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
+                rescan(s_key, s_slot, lo, hi);
+                for (uint32_t r = 0; r < kk; ++r)
+                {
+                    double wk;
+                    uint32_t ws, wi;
+                    const bool any = pick(wk, ws, wi);
+                    if (lane == 0)
+                    {
+                        s_key2[warp * kk + r] = any ? wk : inf;
+                        s_slot2[warp * kk + r] = any ? ws : SLOT_NONE;
+                    }
+                    if (any && ((wi - lo) & 31u) == (uint32_t)lane)
+                    {
+                        s_slot[wi] = SLOT_NONE;
+                        rescan(s_key, s_slot, lo, hi);
+                    }
+                    __syncwarp();
+                }
+            }
+            __syncthreads();
+            if (threadIdx.x >= 32)
+                return;
+            const uint32_t n2 = (SEL_THREADS / 32) * kk;
+            rescan(s_key2, s_slot2, 0, n2);
+            for (uint32_t r = 0; r < kk; ++r)
+            {
+                double wk;
+                uint32_t ws, wi;
+                if (!pick(wk, ws, wi))
+                    break;  // fewer than kk live elements: the caller pads the row
+                if (lane == 0)
+                {
+                    out_ids[qi * kstride + r] = slot_ids[ws];
+                    if (out_dists)
+                        out_dists[qi * kstride + r] = wk;
+                }
+                if ((wi & 31u) == (uint32_t)lane)
+                {
+                    s_slot2[wi] = SLOT_NONE;
+                    rescan(s_key2, s_slot2, 0, n2);
+                }
+                __syncwarp();
+            }
+        }
+
         // out[row][2i] = cos(theta_i), out[row][2i+1] = sin(theta_i), theta_i = s_0 + ... + s_i
         __global__ void chain_trig_kernel(const double *rows, size_t n, int d, double *out)
         {
@@ -3223,6 +3429,36 @@ namespace omplcu
         return true;
     }
 
+    // Up to 8 queries, k <= 32, any space: exact_few_kernel + exact_few_select_kernel (one pass, no sort of all slots).
+    void NNIndex::knn_exact_few(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+                                double *d_dists, cudaStream_t s)
+    {
+        const uint32_t qpad = XFEW_MAXQ;
+        const unsigned grid = (unsigned)std::max<size_t>(
+            1, std::min<size_t>({(size_t)sm_count_, (size_t)8192 / (XFEW_WARPS * kk), (nslots_ + 127) / 128}));
+        const uint32_t n = grid * XFEW_WARPS * (uint32_t)kk;
+        c.xf_d_.reserve((size_t)n * qpad);
+        c.xf_s_.reserve((size_t)n * qpad);
+        const bool tables = prepare_chain_tables(c, d_q, nq, s);
+        const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
+        if (nq == 1)
+            exact_few_kernel<1><<<grid, XFEW_WARPS * 32, 0, s>>>(pm, alive_.p, nslots_, (uint32_t)nq, (uint32_t)kk, qpad,
+                                                                  c.xf_d_.p, c.xf_s_.p);
+        else if (nq <= 4)
+            exact_few_kernel<4><<<grid, XFEW_WARPS * 32, 0, s>>>(pm, alive_.p, nslots_, (uint32_t)nq, (uint32_t)kk, qpad,
+                                                                  c.xf_d_.p, c.xf_s_.p);
+        else
+            exact_few_kernel<XFEW_MAXQ><<<grid, XFEW_WARPS * 32, 0, s>>>(pm, alive_.p, nslots_, (uint32_t)nq, (uint32_t)kk,
+                                                                          qpad, c.xf_d_.p, c.xf_s_.p);
+        const size_t smem = (size_t)n * 12 + (size_t)(SEL_THREADS / 32) * kk * 12 + 16;
+        CUDA_CHECK(cudaFuncSetAttribute(exact_few_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        exact_few_select_kernel<<<(unsigned)nq, SEL_THREADS, smem, s>>>(c.xf_d_.p, c.xf_s_.p, n, qpad, ids_.p, (uint32_t)kk,
+                                                                        (uint32_t)kstride, d_ids, d_dists);
+        launches_ += 2;
+        CUDA_CHECK(cudaGetLastError());
+        c.last_few_ = 2;
+    }
+
     void NNIndex::knn_exact(QCtx &c, const double *d_q, const uint32_t *d_sel, size_t nsel, size_t kk, size_t kstride,
                             uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
@@ -3321,7 +3557,12 @@ namespace omplcu
             else
             {
                 c.last_path_ = 2;
-                knn_exact(c, d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
+                c.last_few_ = 0;
+                if (few_mode_ && !force_exact_ && nq <= (size_t)XFEW_MAXQ && kk <= (size_t)XFEW_MAXK && nslots_ >= 1024 &&
+                    nslots_ < ((size_t)1 << 32) - 64)
+                    knn_exact_few(c, d_q, nq, kk, k, d_ids, d_dists, s);
+                else
+                    knn_exact(c, d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
             }
         }
         if (kk < k)

@@ -102,6 +102,8 @@ namespace omplcu
                       cudaStream_t s, bool no_tc = false);
         void knn_few(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
                      cudaStream_t s);
+        void knn_exact_few(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids,
+                           double *d_dists, cudaStream_t s);
         // tensor-core threshold path: sample scan -> per-query bound -> append scan -> exact epilogue
         // Tensor-core filter in front of an exact path that has a per-query exact distance bound (the sample
         // bound of the large-k path, the radius of nearestR): every slot within d_bound[q] of query q ends up
@@ -198,6 +200,8 @@ namespace omplcu
             double *ho_dists_ = nullptr;
             size_t ho_entries_ = 0;
             bool ho_done_ = false;
+            DevBuf<double> xf_d_;       // exact few-query path: per-warp lists of (distance, slot)
+            DevBuf<uint32_t> xf_s_;
             DevBuf<double> q_emb_, emb_bound_;  // embedded queries and their filter bounds (embedded spaces)
             DevBuf<uint32_t> qs_keys_, qs_idx_, qs_bbox_;  // Morton order of a large query batch (knn_fast)
             DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered

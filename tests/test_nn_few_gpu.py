@@ -85,3 +85,58 @@ def test_few_queries_dense_low_dimensional_set(gpu):
     nn.add_rows(pts)
     _check(nn, d, pts, np.arange(n), qs, 10)
     assert nn.stat("last_few") == 1 and nn.stat("last_fallbacks") <= 1
+
+
+# ---------------------------------------------------------------- any space: the exact few-query pass
+def _space_and_states(name, seed, n):
+    if name == "so2":
+        return ob.SO2StateSpace(), orc.space_so2(), helpers.rng(seed).uniform(-np.pi, np.pi, (n, 1))
+    if name == "so3":
+        return ob.SO3StateSpace(), orc.space_so3(), helpers.random_quaternions(seed, n)
+    if name == "se2":
+        return ob.SE2StateSpace(), orc.space_se2(), helpers.se2_states(seed, n)
+    if name == "se3":
+        return ob.SE3StateSpace(), orc.space_se3(), helpers.se3_states(seed, n, 0, 1)
+    return ob.KinematicChainSpace(10, 0.1), orc.space_chain(10, 0.1), helpers.rng(seed).uniform(-np.pi, np.pi, (n, 10))
+
+
+@pytest.mark.parametrize("name", ["so2", "so3", "se2", "se3", "chain"])
+@pytest.mark.parametrize("nq,k", [(1, 1), (1, 10), (5, 32), (8, 10)])
+def test_exact_few_queries_on_every_space(gpu, name, nq, k):
+    """nn_->nearest / nearestK of RRT and PRM on rotation, compound and chain spaces (rrt/src/RRT.cpp:170): one pass
+    with the space's exact distance, per-warp (distance, slot) lists, no sort of all slots.  Duplicates test the
+    insertion-order tie-break across warps."""
+    n = 20000
+    sp, osp, pts = _space_and_states(name, 60, n)
+    pts = helpers.with_duplicates(pts, 61, frac=0.05)
+    qs = np.vstack([pts[7:8], _space_and_states(name, 62, 8)[2]])[:nq]
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.add_rows(pts)
+    ids, d = nn.nearestKBatch(qs, k)
+    assert nn.stat("last_path") == 2 and nn.stat("last_few") == 2
+    oi, od = orc.knn(osp, pts, qs, k, nthreads=8)
+    assert (ids == oi).all()
+    if name in ("so2", "se2"):
+        assert (d == od).all()
+    else:
+        assert np.allclose(d, od, rtol=4e-16 if name != "chain" else 1e-13, atol=1e-15)
+    # the sort path gives the same bits
+    nn.set_option("few_scan", 0)
+    ids0, d0 = nn.nearestKBatch(qs, k)
+    assert nn.stat("last_few") == 0
+    assert (ids == ids0).all() and (d == d0).all()
+
+
+def test_exact_few_queries_follow_removals_and_small_sets(gpu):
+    sp, osp, pts = _space_and_states("se3", 70, 3000)
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.add_rows(pts)
+    live = list(range(3000))
+    for i in helpers.rng(71).choice(3000, 1200, replace=False):
+        assert nn.remove_id(int(i))
+        live.remove(int(i))
+    qs = _space_and_states("se3", 72, 3)[2]
+    ids, d = nn.nearestKBatch(qs, 20)
+    oi, od = orc.knn(osp, pts[live], qs, 20, nthreads=4)
+    assert (ids == np.asarray(live, dtype=np.uint64)[oi.astype(np.int64)]).all()
+    assert np.allclose(d, od, rtol=4e-16, atol=1e-15)
