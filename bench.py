@@ -502,6 +502,8 @@ def run_gpu_arm(args):
             out["roofline_fp32_scan"] = roofline_fp32
         if motion is not None:
             out["motion"] = motion
+        if world == 1 and not args.no_motion:
+            out["other_calls"] = other_calls(nn, pts, qs, local)
         if world == 1 and not args.no_cpu:
             cores = host_threads()
             kind, what, build_s, run = build_cpu_reference(pts)
@@ -513,6 +515,60 @@ def run_gpu_arm(args):
         print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
+
+
+def other_calls(nn, pts, qs, local):
+    """Secondary figures, N = 1: the literal one-query call a planner makes (PRM::addMilestone, prm/src/PRM.cpp:575;
+    RRT's nn_->nearest, rrt/src/RRT.cpp:170) and kNN on an SE(3) roadmap, all through the host-pointer C-ABI call
+    (wall clock, pageable host buffers as a caller has them).  Every figure comes with a parity check against the
+    oracle on a sample."""
+    import ompl_b200 as ob
+    from ompl_b200._lib import check, lib
+    from oracle import oracle_py as orc
+
+    L = lib()
+    out = {}
+
+    def per_call(h, q, k, reps):
+        nq = len(q)
+        ib, db, cb = np.empty((nq, k), np.uint64), np.empty((nq, k)), np.empty(nq, np.uint32)
+        check(L.omplcu_nn_knn(h, q.ctypes.data, nq, k, ib.ctypes.data, db.ctypes.data, cb.ctypes.data))
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            check(L.omplcu_nn_knn(h, q.ctypes.data, nq, k, ib.ctypes.data, db.ctypes.data, cb.ctypes.data))
+        return (time.perf_counter() - t0) / reps, ib, db
+
+    # one nearestK on the metric's own roadmap (1M x 7-D)
+    q1 = qs[:1].copy()  # pageable, as a caller has it
+    t, ib, db = per_call(nn.handle, q1, K, 200)
+    oi, od = orc.knn(orc.space_rv(DIM), pts, q1, K, nthreads=host_threads())
+    out["single_nearestK_rv7_1M"] = {"ms_per_call": t * 1e3, "matches_oracle": bool((ib == oi).all() and (db == od).all()),
+                                     "kernel": "knn_few_kernel<1> + knn_rerank_select_kernel"}
+    # SE(3): 1M states, uniform positions in [-1,1]^3 and uniform rotations
+    r = np.random.default_rng(77)
+
+    def se3(m):
+        q = r.normal(size=(m, 4))
+        q /= np.linalg.norm(q, axis=1, keepdims=True)
+        return np.ascontiguousarray(np.hstack([r.uniform(-1, 1, (m, 3)), q]))
+
+    n3, nq3 = 1_000_000, 4096
+    p3, q3 = se3(n3), se3(nq3)
+    sp = ob.SE3StateSpace(-1.0, 1.0, device=local)
+    nn3 = ob.NearestNeighborsCUDA(sp)
+    nn3.add_rows(p3)
+    t, ib, db = per_call(nn3.handle, q3, K, 5)
+    osp = orc.space_se3(-1.0, 1.0)
+    oi, od = orc.knn(osp, p3, q3[:32], K, nthreads=host_threads())
+    out["knn_se3_1M"] = {"queries_per_s": nq3 / t, "ms_per_call": t * 1e3, "n_queries": nq3, "k": K,
+                         "matches_oracle": bool((ib[:32] == oi).all() and np.allclose(db[:32], od, rtol=4e-16, atol=1e-15)),
+                         "filtered": int(nn3.stat("last_filter")),
+                         "path": "tensor-core list scan + threshold scan on the Euclidean lower-bound embedding, exact SE(3) "
+                                 "distance on the kept slots (DESIGN.md 3.8)"}
+    t, ib, db = per_call(nn3.handle, np.ascontiguousarray(q3[:1]), K, 100)
+    out["single_nearestK_se3_1M"] = {"ms_per_call": t * 1e3, "matches_oracle": bool((ib == oi[:1]).all()),
+                                     "kernel": "exact_few_kernel<1> + exact_few_select_kernel"}
+    return out
 
 
 def sharded_e2e(args, torch, world, pts, qs_all, with_motion):
@@ -646,6 +702,10 @@ def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
         ht[:] = dt.cpu().numpy()
     tot = torch.tensor([chk.stat("last_states"), chk.stat("last_states_evaluated"), int(hv.sum())],
                        dtype=torch.float64, device=dev)
+    for arr in (a, b, hv, ht):
+        # registrations outlive the arrays otherwise, and a later numpy allocation that lands on such a range makes
+        # cudaMemcpyAsync fail with "invalid argument"
+        torch.cuda.cudart().cudaHostUnregister(arr.ctypes.data)
     if world > 1:
         dist.all_reduce(tot, group=nccl)
     if rank != 0:
