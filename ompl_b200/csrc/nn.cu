@@ -3558,8 +3558,10 @@ namespace omplcu
             {
                 c.last_path_ = 2;
                 c.last_few_ = 0;
+                // the one-pass kernel evaluates every (query, slot) distance: it wins up to ~5M pairs (8 queries on 100K
+                // states, 4 on 1M: 0.24 / 0.43 ms), beyond that the sample-bounded collect path does (scripts/time_se3_small.py)
                 if (few_mode_ && !force_exact_ && nq <= (size_t)XFEW_MAXQ && kk <= (size_t)XFEW_MAXK && nslots_ >= 1024 &&
-                    nslots_ < ((size_t)1 << 32) - 64)
+                    nq * nslots_ <= (size_t)5000000 && nslots_ < ((size_t)1 << 32) - 64)
                     knn_exact_few(c, d_q, nq, kk, k, d_ids, d_dists, s);
                 else
                     knn_exact(c, d_q, nullptr, nq, kk, k, d_ids, d_dists, s);
