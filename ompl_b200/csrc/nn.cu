@@ -153,6 +153,22 @@ namespace omplcu
             bound_out[i] = (ok && b >= 0.0) ? b * (1.0 + 1e-9) + slack + 1e-12 : __longlong_as_double(0x7ff0000000000000ll);
         }
 
+        // the unproven queries of a batch, compacted for the threshold scan
+        __global__ void gather_unproven_kernel(const uint32_t *list, size_t n, int D, const double *q_emb, const double *bound,
+                                               double slack, double *q_out, double *ebound_out, double *bound_out)
+        {
+            const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
+            if (i >= n)
+                return;
+            const size_t src = list[i];
+            for (int c = 0; c < D; ++c)
+                q_out[i * D + c] = q_emb[src * D + c];
+            const double b = bound[src];
+            bound_out[i] = b;
+            // no bound (fewer than kk candidates) -> infinite: the row overflows and the query is redone unfiltered
+            ebound_out[i] = (b >= 0.0 && b < 1e300) ? b * (1.0 + 1e-9) + slack + 1e-12 : __longlong_as_double(0x7ff0000000000000ll);
+        }
+
         // ---- filter-copy maintenance ----
         // rows [first, first+n): coords 0, norm +inf  ("dead": never passes the filter)
         __global__ void filt_fill_dead_kernel(float *filt, int rowf, int D, size_t first, size_t n)
@@ -411,7 +427,8 @@ namespace omplcu
                 return;
             const size_t o = (size_t)sel[i / kk] * kstride + i % kk;
             out_ids[o] = ids[i];
-            out_dists[o] = dists[i];
+            if (out_dists)
+                out_dists[o] = dists[i];
         }
 
         // ---- query preparation for the scan ----
@@ -1221,12 +1238,14 @@ namespace omplcu
                                                                           uint32_t smax, uint32_t cap, uint32_t qpad,
                                                                           PairMetric pm, size_t q0, const uint8_t *alive,
                                                                           const double *bound, size_t nb, uint32_t cap2,
-                                                                          double *keys, uint32_t *vals, uint32_t *cnt)
+                                                                          double *keys, uint32_t *vals, uint32_t *cnt,
+                                                                          const uint32_t *sel = nullptr)
         {
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
             const size_t b = blockIdx.x * 4ull + w;
             if (b >= nb)
                 return;
+            const size_t qsrc = q0 + (sel ? sel[b] : b);  // row b of this scan is query qsrc of pm
             const double bd = bound[b];
             uint32_t n = 0;
             bool over = false;
@@ -1250,7 +1269,7 @@ namespace omplcu
                         slot = row[i];
                         if (alive[slot])
                         {
-                            d = pm(slot, q0 + b);
+                            d = pm(slot, qsrc);
                             keep = d <= bd;
                         }
                     }
@@ -1272,15 +1291,23 @@ namespace omplcu
         // on the embedding found for the query.  Any kk real points bound the kk-th nearest distance from above, and
         // the embedding's nearest are nearly the metric's nearest, so the bound is tight (a few times kk slots lie
         // within it, against thousands for a bound from a 1024-point sample).  Fewer than kk candidates: +inf.
-        __global__ void __launch_bounds__(128) cand_bound_kernel(const uint32_t *cand_ids, uint32_t n, uint32_t qpad,
-                                                                 PairMetric pm, size_t q0, const uint8_t *alive, size_t nb,
-                                                                 uint32_t kk, double *bound)
+        __global__ void __launch_bounds__(128) cand_bound_kernel(const uint32_t *cand_ids, const float *cand_thr, uint32_t smax,
+                                                                 uint32_t L, uint32_t qpad, PairMetric pm, size_t q0,
+                                                                 const uint8_t *alive, size_t nb, uint32_t kk, double *bound,
+                                                                 const double *qaux, const unsigned *pmax2_bits, int D,
+                                                                 double err_units, double slack, const uint64_t *slot_ids,
+                                                                 uint32_t kstride, uint64_t *out_ids, double *out_dists,
+                                                                 unsigned *unproven, uint32_t *unproven_list)
         {
             __shared__ double s_key[4][512];
+            __shared__ uint32_t s_slot[4][512];
+            __shared__ double s_wd[4][40];
+            __shared__ uint32_t s_ws[4][40];
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
             const size_t b = blockIdx.x * 4ull + w;
             if (b >= nb)
                 return;
+            const uint32_t n = smax * L;
             const double inf = __longlong_as_double(0x7ff0000000000000ll);
             for (uint32_t c = lane; c < n; c += 32)
             {
@@ -1293,27 +1320,106 @@ namespace omplcu
                         d = inf;
                 }
                 s_key[w][c] = d;
+                s_slot[w][c] = d < inf ? slot : SLOT_NONE;
             }
             __syncwarp();
-            double out = inf;
-            for (uint32_t c = lane; c < n; c += 32)
-            {
-                const double key = s_key[w][c];
-                if (!(key < inf))
-                    continue;
-                uint32_t rank = 0;
-                for (uint32_t o = 0; o < n; ++o)
+            // the kk best by (distance, slot): every lane caches the best of its own candidates, a shuffle tree picks
+            // the winner of a round, only the winning lane rescans (as knn_rerank_select_kernel)
+            double bk = inf;
+            uint32_t bs = SLOT_NONE, bi = 0;
+            auto rescan = [&]() {
+                bk = inf;
+                bs = SLOT_NONE;
+                bi = 0;
+                for (uint32_t c = lane; c < n; c += 32)
                 {
-                    const double ko = s_key[w][o];
-                    rank += (ko < key || (ko == key && o < c)) ? 1u : 0u;
+                    const uint32_t sl = s_slot[w][c];
+                    if (sl == SLOT_NONE)
+                        continue;
+                    const double k = s_key[w][c];
+                    if (bs == SLOT_NONE || k < bk || (k == bk && sl < bs))
+                    {
+                        bk = k;
+                        bs = sl;
+                        bi = c;
+                    }
                 }
-                if (rank == kk - 1)
-                    out = key;
+            };
+            rescan();
+            double dk = inf;
+            for (uint32_t r = 0; r < kk; ++r)
+            {
+                double wk = bk;
+                uint32_t ws = bs, wi = bi;
+                for (int o = 16; o > 0; o >>= 1)
+                {
+                    const double ok = __shfl_xor_sync(0xffffffffu, wk, o);
+                    const uint32_t os = __shfl_xor_sync(0xffffffffu, ws, o);
+                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, wi, o);
+                    if (os != SLOT_NONE && (ws == SLOT_NONE || ok < wk || (ok == wk && os < ws)))
+                    {
+                        wk = ok;
+                        ws = os;
+                        wi = oi;
+                    }
+                }
+                if (ws == SLOT_NONE)
+                    break;  // fewer than kk candidates: no bound
+                if (lane == 0)
+                {
+                    s_wd[w][r] = wk;
+                    s_ws[w][r] = ws;
+                }
+                if (r == kk - 1)
+                    dk = wk;
+                if ((wi & 31u) == (uint32_t)lane)
+                {
+                    s_slot[w][wi] = SLOT_NONE;
+                    rescan();
+                }
+                __syncwarp();
             }
-            for (int o = 16; o > 0; o >>= 1)
-                out = fmin(out, __shfl_xor_sync(0xffffffffu, out, o));
+            // Can anything the lists dropped be within dk?  A slot within dk in the space's metric is within
+            // dk' = dk (1 + 1e-9) + slack of the query in the embedding (embed_state), and the band formula of
+            // knn_rerank_kernel bounds the scan value of such a slot by tau(dk'); every full list's maximum must lie above it.
+            bool proven = dk < inf;
+            if (proven)
+            {
+                const double u = 5.9604644775390625e-08;  // 2^-24
+                const double de = dk * (1.0 + 1e-9) + slack + 1e-12;
+                const double qn = qaux[2 * b], qnorm = qaux[2 * b + 1];
+                const double pmax2 = (double)__uint_as_float(*pmax2_bits) * (1.0 + 2.0 * u);
+                const double pmax = sqrt(pmax2) * (1.0 + 1e-9);
+                const double delta = (double)(D + 4) * 1.1102230246251565e-16;
+                const double rho = 1.0000002 * u * (qnorm + pmax) + 1e-44;
+                const double A = de * (1.0 + delta) + rho + 1e-150;
+                const double e1 = err_units * u * 1.000001 * (pmax2 + 2.0 * qnorm * pmax) + 1e-43;
+                const double tau64 = A * A - qn + e1 + (double)D * 2.3e-16 * qn + 2e-15 * (A * A + qn);
+                bool bad = !(tau64 == tau64) || !(tau64 < 1e37);
+                for (uint32_t sg = lane; sg < smax; sg += 32)
+                {
+                    const double vmax = (double)cand_thr[(size_t)sg * qpad + b];
+                    if (vmax < 1e38 && !(vmax - fabs(vmax) * 1.52587890625e-05 - 1e-37 > tau64))
+                        bad = true;
+                }
+                proven = !__any_sync(0xffffffffu, bad);
+            }
+            if (proven)
+            {
+                // the listed slots contain every slot within dk: the answer is their kk best by (distance, slot)
+                for (uint32_t r = lane; r < kk; r += 32)
+                {
+                    out_ids[(q0 + b) * kstride + r] = slot_ids[s_ws[w][r]];
+                    if (out_dists)
+                        out_dists[(q0 + b) * kstride + r] = s_wd[w][r];
+                }
+            }
             if (lane == 0)
-                bound[b] = out;
+            {
+                bound[b] = dk;
+                if (!proven)
+                    unproven_list[atomicAdd(unproven, 1u)] = (uint32_t)b;
+            }
         }
 
         // ---- a handful of queries on ANY space (RRT's nn_->nearest on SE(3), rrt/src/RRT.cpp:170): exact brute force ----
@@ -1654,7 +1760,7 @@ namespace omplcu
                                                                         const uint64_t *slot_ids, size_t b0, size_t nb,
                                                                         uint32_t kk, uint32_t kstride, uint64_t *out_ids,
                                                                         double *out_dists, uint32_t *redo,
-                                                                        unsigned *redo_count)
+                                                                        unsigned *redo_count, const uint32_t *sel = nullptr)
         {
             __shared__ double s_key[4][MAXN];
             __shared__ uint32_t s_slot[4][MAXN];
@@ -1662,7 +1768,7 @@ namespace omplcu
             const size_t b = blockIdx.x * 4ull + w;
             if (b >= nb)
                 return;
-            const size_t qi = b0 + b;
+            const size_t qi = b0 + (sel ? sel[b] : b);
             const uint32_t n = cnt[b];
             if (n > (uint32_t)MAXN || n > cap || n < kk)
             {
@@ -1934,6 +2040,7 @@ namespace omplcu
         last_fallbacks_ = c.last_fallbacks_;
         last_rescans_ = c.last_rescans_;
         last_few_ = c.last_few_;
+        last_proven_ = c.last_proven_;
         last_path_ = c.last_path_;
         if (profile_ && c.last_path_ == 1)
         {
@@ -2297,6 +2404,8 @@ namespace omplcu
             return last_fallbacks_;
         if (!strcmp(key, "tc_demoted"))
             return tc_demoted_.load() ? 1 : 0;  // "auto" gave up on the tensor-core filter for this set (too dense)
+        if (!strcmp(key, "last_proven"))
+            return last_proven_;  // embedded spaces: queries the list scan alone proved (no threshold scan needed)
         if (!strcmp(key, "last_few"))
             return last_few_;  // the last query ran the few-query scan (knn_few_kernel)
         if (!strcmp(key, "last_rescans"))
@@ -3181,8 +3290,10 @@ namespace omplcu
 
     // Embedded spaces: tensor-core LIST scan of the embedded queries against the embedded roadmap (the lists of the
     // fast path, no re-rank), then cand_bound_kernel: d_bound[b] = kk-th smallest exact distance among the listed slots.
-    void NNIndex::embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
-                                   double *d_bound, cudaStream_t s)
+    // Queries the lists alone prove (cand_bound_kernel) have their rows of d_ids / d_dists written; returns how many
+    // of the batch are left for the threshold scan.
+    unsigned NNIndex::embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
+                                       double *d_bound, size_t kstride, uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         const PairMetric &pm = *static_cast<const PairMetric *>(pair_metric);
         TcShape sh = tc_shape(D_);
@@ -3248,10 +3359,18 @@ namespace omplcu
         T.sh = sh;
         T.nstages = stages;
         tc_launch_scan(L, T, (unsigned)G, s);
-        cand_bound_kernel<<<nblk(nq, 4), 128, 0, s>>>(c.cand_ids_.p, smax * (uint32_t)L, qpad, pm, q0, alive_.p, nq,
-                                                      (uint32_t)kk, d_bound);
+        c.unp_list_.reserve(nq);
+        CUDA_CHECK(cudaMemsetAsync(c.counters_.p + 2, 0, sizeof(unsigned), s));
+        cand_bound_kernel<<<nblk(nq, 4), 128, 0, s>>>(c.cand_ids_.p, c.cand_vals_.p, smax,
+                                                      (uint32_t)L, qpad, pm, q0, alive_.p, nq, (uint32_t)kk, d_bound,
+                                                      c.qaux_.p, pmax2_.p, D_, tc_err_units(D_), embed_slack_, ids_.p,
+                                                      (uint32_t)kstride, d_ids, d_dists, c.counters_.p + 2, c.unp_list_.p);
         launches_ += 4;
         CUDA_CHECK(cudaGetLastError());
+        unsigned unproven = 0;
+        CUDA_CHECK(cudaMemcpyAsync(&unproven, c.counters_.p + 2, sizeof(unsigned), cudaMemcpyDeviceToHost, s));
+        CUDA_CHECK(cudaStreamSynchronize(s));
+        return unproven;
     }
 
     // Large index (>= 32K slots), any k and any metric (FMT*'s k ~ 2100 of 100K; SE3 / chain kNN): sorting
@@ -3322,6 +3441,7 @@ namespace omplcu
         const bool filt = d_sel == nullptr && filter_usable() && (!embed_ || nsel >= 16) && embed_ok(s);
         const uint32_t fcap = ((cap + 64 + 31) / 32) * 32;
         c.last_filter_ = filt ? 1 : 0;
+        c.last_proven_ = 0;
         const bool tables = prepare_chain_tables(c, d_q, c.exact_nq_, s);
         const PairMetric pm{sp_, pts64_.p, d_q, tables ? trig_.p : nullptr, tables ? c.qtrig_.p : nullptr};
         int *beg = c.ex_offs_.p, *end = c.ex_offs_.p + nb_max + 1;
@@ -3338,7 +3458,46 @@ namespace omplcu
                 c.emb_bound_.reserve(nb);
                 embed_queries_kernel<<<nblk(nb, 128), 128, 0, s>>>(sp_, d_q + b0 * sp_.stride, nb, D_, embed_slack_,
                                                                    c.col_bound_.p, c.q_emb_.p, c.emb_bound_.p);
-                embed_list_bound(c, c.q_emb_.p, &pm, b0, nb, kk, c.col_bound_.p, s);
+                const unsigned left = embed_list_bound(c, c.q_emb_.p, &pm, b0, nb, kk, c.col_bound_.p, kstride, d_ids, d_dists, s);
+                c.last_proven_ += (long)nb - (long)left;
+                if (left == 0)
+                    continue;  // many segments per query tile (batches of a few thousand): the list scan proves them all
+                if (few_mode_ && left <= (unsigned)XFEW_MAXQ && kk <= (size_t)XFEW_MAXK && (size_t)left * nslots_ <= (size_t)5000000)
+                {
+                    // a handful left: the exact one-pass kernel on them is cheaper than a scan of the whole image
+                    c.re_q_.reserve((size_t)left * sp_.stride);
+                    c.re_ids_.reserve((size_t)left * kk);
+                    c.re_d_.reserve((size_t)left * kk);
+                    gather_rows_kernel<<<nblk((size_t)left * sp_.stride, 256), 256, 0, s>>>(d_q + b0 * sp_.stride, c.unp_list_.p,
+                                                                                          left, sp_.stride, c.re_q_.p);
+                    knn_exact_few(c, c.re_q_.p, left, kk, kk, c.re_ids_.p, c.re_d_.p, s);
+                    scatter_results_kernel<<<nblk((size_t)left * kk, 256), 256, 0, s>>>(
+                        c.re_ids_.p, c.re_d_.p, c.unp_list_.p, left, (uint32_t)kk, (uint32_t)kstride, d_ids + b0 * kstride,
+                        d_dists ? d_dists + b0 * kstride : nullptr);
+                    c.last_few_ = 0;
+                    launches_ += 2;
+                    CUDA_CHECK(cudaGetLastError());
+                    continue;
+                }
+                // the threshold scan for the rest only (compacted; row i of the scan is query b0 + unp_list[i])
+                c.q_emb2_.reserve((size_t)left * D_);
+                c.emb_bound_.reserve(nb);
+                c.col_bound2_.reserve(left);
+                gather_unproven_kernel<<<nblk(left, 128), 128, 0, s>>>(c.unp_list_.p, left, D_, c.q_emb_.p, c.col_bound_.p,
+                                                                      embed_slack_, c.q_emb2_.p, c.emb_bound_.p,
+                                                                      c.col_bound2_.p);
+                uint32_t fq = 0;
+                const uint32_t rows = filter_scan(c, c.q_emb2_.p, left, c.emb_bound_.p, fcap, &fq, s);
+                kept_collect_metric_kernel<<<nblk(left, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pm, b0,
+                                                                         alive_.p, c.col_bound2_.p, left, cap, c.ex_keys2_.p,
+                                                                         c.ex_vals2_.p, c.col_cnt_.p, c.unp_list_.p);
+                collect_rank_emit_kernel<512><<<nblk(left, 4), 128, 0, s>>>(c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p, cap,
+                                                                            ids_.p, b0, left, (uint32_t)kk, (uint32_t)kstride,
+                                                                            d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1,
+                                                                            c.unp_list_.p);
+                CUDA_CHECK(cudaGetLastError());
+                launches_ += 10;
+                continue;
             }
             else
             {

@@ -110,8 +110,8 @@ namespace omplcu
         // in the query's rows of c.app_ids_ / c.app_cnt_ (smax rows of `cap` slots, in slot order).
         bool filter_usable() const;
         bool embed_ok(cudaStream_t s);
-        void embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
-                              double *d_bound, cudaStream_t s);
+        unsigned embed_list_bound(QCtx &c, const double *d_qe, const void *pair_metric, size_t q0, size_t nq, size_t kk,
+                                  double *d_bound, size_t kstride, uint64_t *d_ids, double *d_dists, cudaStream_t s);
         uint32_t filter_scan(QCtx &c, const double *d_q, size_t nq, const double *d_bound, uint32_t cap,
                              uint32_t *qpad_out, cudaStream_t s);
         void knn_fast_thr(QCtx &c, const double *d_q, size_t nq, size_t kk, size_t kstride, uint64_t *d_ids, double *d_dists,
@@ -202,12 +202,13 @@ namespace omplcu
             bool ho_done_ = false;
             DevBuf<double> xf_d_;       // exact few-query path: per-warp lists of (distance, slot)
             DevBuf<uint32_t> xf_s_;
-            DevBuf<double> q_emb_, emb_bound_;  // embedded queries and their filter bounds (embedded spaces)
+            DevBuf<double> q_emb_, emb_bound_, q_emb2_, col_bound2_;
+            DevBuf<uint32_t> unp_list_;  // queries the list scan on the embedding did not prove  // embedded queries and their filter bounds (embedded spaces)
             DevBuf<uint32_t> qs_keys_, qs_idx_, qs_bbox_;  // Morton order of a large query batch (knn_fast)
             DevBuf<uint32_t> re_sel_;   // second pass of knn_fast: the unproven queries, gathered
             DevBuf<double> re_q_, re_d_;
             DevBuf<uint64_t> re_ids_;
-            long last_rescans_ = 0, last_few_ = 0;
+            long last_rescans_ = 0, last_few_ = 0, last_proven_ = 0;
             long last_filter_ = 0;
             long last_collect_redo_ = 0, last_tc_ = 0, last_thr_ = 0, last_kept_ = 0, last_rank_ = 0;
             long last_sample_ns_ = 0, last_main_ns_ = 0, last_scan_ns_ = 0, last_fallbacks_ = 0, last_path_ = 0;
@@ -240,7 +241,7 @@ namespace omplcu
         std::atomic<size_t> tc_demote_slots_{0};
         bool sort_queries_ = true;  // large batches: scan the queries in Morton order
         bool few_mode_ = true;    // auto mode, up to 8 queries: knn_few_kernel
-        long last_few_ = 0;
+        long last_few_ = 0, last_proven_ = 0;
         bool tc_align_ = true;    // tensor-core scan: work pieces end on query-tile boundaries where that is nearly free
         int tc_grid_ = 0;         // experiments: upper limit on the tensor-core scan's work pieces (0: one per SM)
         int tc_pair_ = 1;         // with tc_ts_: clusters of 2 CTAs share the point chunks (TMA multicast)

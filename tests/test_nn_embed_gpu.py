@@ -55,6 +55,9 @@ def test_filtered_knn_on_rotation_and_compound_spaces(gpu, name, k):
     nn.add_rows(pts)
     _same(nn, osp, pts, qs, k, name in ("so2", "se2"))
     assert nn.stat("last_path") == 2 and nn.stat("last_filter") == 1
+    if k <= 40:
+        # one query tile cut into 31 segments: the list scan on the embedding proves (nearly) every query by itself
+        assert nn.stat("last_proven") > 0
     # the unfiltered path gives the same bits
     ids, d = nn.nearestKBatch(qs, k)
     nn.set_option("tc_scan", 0)
@@ -155,3 +158,19 @@ def test_filtered_radius_on_compound_spaces(gpu, name):
         assert np.allclose(gd[offs[i]:offs[i + 1]], od, rtol=4e-16, atol=1e-15)
         total += len(oi)
     assert total > 100
+
+
+def test_filtered_knn_large_batch_needs_the_threshold_scan(gpu):
+    """16384 queries on 200K SE(3) states: few segments per query tile, so the lists alone prove little and the
+    threshold scan on the embedding decides; same answers as the unfiltered path and (sampled) the oracle."""
+    n, nq = 200000, 16384
+    sp, osp = _space("se3")
+    pts, qs = _states("se3", 81, n), _states("se3", 82, nq)
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.add_rows(pts)
+    ids, d = nn.nearestKBatch(qs, 10)
+    assert nn.stat("last_filter") == 1 and nn.stat("last_proven") < nq
+    sub = helpers.rng(83).choice(nq, 128, replace=False)
+    oi, od = orc.knn(osp, pts, qs[sub], 10, nthreads=16)
+    assert (ids[sub] == oi).all() and np.allclose(d[sub], od, rtol=4e-16, atol=1e-15)
+    assert (np.diff(d, axis=1) >= 0).all()
