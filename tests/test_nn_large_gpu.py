@@ -137,3 +137,28 @@ def test_dense_low_dimensional_set_second_pass_on_the_fp32_scan(gpu, monkeypatch
     sub = helpers.rng(6).choice(nq, 256, replace=False)
     oi, od = orc.knn(orc.space_rv(d), pts, qs[sub], k, nthreads=16)
     assert (ids[sub] == oi).all() and (dist[sub] == od).all()
+
+
+@pytest.mark.parametrize("d,n,nq,opts", [
+    (7, 300_000, 8192, ["sort_queries", "tc_align"]),
+    (100, 60_000, 1024, ["tc_pair", "tc_ts"]),
+    (64, 60_000, 1024, ["tc_pair"]),
+])
+def test_scan_schedule_options_do_not_change_results(gpu, monkeypatch, d, n, nq, opts):
+    """Morton-ordered queries, aligned work pieces, CTA pairs and the TMEM-resident query tile only change how the
+    filter scan is scheduled: with each of them switched off the ids and distances must be the same bits, and a
+    sample must equal the oracle."""
+    monkeypatch.delenv("OMPLCU_TC_SCAN", raising=False)
+    pts, qs = helpers.uniform_points(31 + d, n, d), helpers.uniform_points(32 + d, nq, d)
+    nn = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    nn.add_rows(pts)
+    ids, dist = nn.nearestKBatch(qs, 10)
+    assert nn.stat("last_tc") == 1
+    sub = helpers.rng(33).choice(nq, 128, replace=False)
+    oi, od = orc.knn(orc.space_rv(d), pts, qs[sub], 10, nthreads=16)
+    assert (ids[sub] == oi).all() and (dist[sub] == od).all()
+    for o in opts:
+        nn.set_option(o, 0)
+        i2, d2 = nn.nearestKBatch(qs, 10)
+        assert (ids == i2).all() and (dist == d2).all(), o
+        nn.set_option(o, 1)
