@@ -25,11 +25,13 @@
 #ifndef OMPL_B200_NEAREST_NEIGHBORS_CUDA_H
 #define OMPL_B200_NEAREST_NEIGHBORS_CUDA_H
 
+#include <algorithm>
 #include <cstdint>
 #include <functional>
 #include <limits>
 #include <mutex>
 #include <string>
+#include <thread>
 #include <unordered_map>
 #include <vector>
 
@@ -320,6 +322,26 @@ namespace ompl
                 data.push_back(byId_[ids[i] - idOffset_]);
         }
 
+        /** f(lo, hi) over [0, n) on up to 8 host threads (one below 8192 items: a thread costs more than it saves). */
+        template <typename F>
+        static void parallelFor(std::size_t n, F f)
+        {
+            const unsigned hw = std::thread::hardware_concurrency();
+            const std::size_t nt = std::min<std::size_t>({(std::size_t)(hw ? hw : 1u), (std::size_t)8, n / 8192});
+            if (nt <= 1)
+            {
+                f((std::size_t)0, n);
+                return;
+            }
+            std::vector<std::thread> th;
+            th.reserve(nt - 1);
+            for (std::size_t t = 1; t < nt; ++t)
+                th.emplace_back(f, n * t / nt, n * (t + 1) / nt);
+            f((std::size_t)0, n / nt);
+            for (auto &x : th)
+                x.join();
+        }
+
         // ---- batch-submit entry points ----
         /** out[i] = the min(k, size()) nearest elements of queries[i], sorted by (distance, insertion order).
             dists (optional) receives the exact distances, row-major with out[i].size() entries per row. */
@@ -333,24 +355,95 @@ namespace ompl
                 dists->clear();
             if (nq == 0 || k == 0)
                 return;
-            std::vector<double> rows(nq * st);
-            for (std::size_t i = 0; i < nq; ++i)
-                rowFun_(queries[i], rows.data() + i * st);
-            std::vector<std::uint64_t> ids(nq * k);
-            std::vector<double> d(dists != nullptr ? nq * k : 0);
-            std::vector<std::uint32_t> counts(nq);
+            // call scratch lives per host thread and only grows: fresh 9 MB vectors cost a millisecond of page faults and
+            // zero-filling per 65536-query call
+            static thread_local std::vector<double> rows, d;
+            static thread_local std::vector<std::uint64_t> ids;
+            static thread_local std::vector<std::uint32_t> counts;
+            if (rows.size() < nq * st)
+                rows.resize(nq * st);
+            // (thread_local objects are not captured by a lambda: a worker would see its OWN empty vector, so the
+            // workers get plain pointers)
+            double *const rowp = rows.data();
+            // large batches: the host side (copyToReals of every query, one result vector per query) is spread over
+            // a few threads; the row function only reads the states
+            parallelFor(nq, [&, rowp](std::size_t lo, std::size_t hi) {
+                for (std::size_t i = lo; i < hi; ++i)
+                    rowFun_(queries[i], rowp + i * st);
+            });
+            if (ids.size() < nq * k)
+                ids.resize(nq * k);
+            if (dists != nullptr && d.size() < nq * k)
+                d.resize(nq * k);
+            if (counts.size() < nq)
+                counts.resize(nq);
             b200::check(omplcu_nn_knn(nn_, rows.data(), nq, k, ids.data(), dists != nullptr ? d.data() : nullptr,
                                       counts.data()));
-            for (std::size_t i = 0; i < nq; ++i)
-            {
-                out[i].reserve(counts[i]);
-                for (std::uint32_t j = 0; j < counts[i]; ++j)
+            const std::size_t kk = counts[0];  // min(k, size()): the same for every query of a call
+            if (dists != nullptr)
+                dists->resize(nq * kk);
+            const std::uint64_t *const idp = ids.data();
+            const double *const dp = d.data();
+            parallelFor(nq, [&, idp, dp](std::size_t lo, std::size_t hi) {
+                for (std::size_t i = lo; i < hi; ++i)
                 {
-                    out[i].push_back(byId_[ids[i * k + j] - idOffset_]);
-                    if (dists != nullptr)
-                        dists->push_back(d[i * k + j]);
+                    out[i].resize(kk);
+                    for (std::size_t j = 0; j < kk; ++j)
+                    {
+                        out[i][j] = byId_[idp[i * k + j] - idOffset_];
+                        if (dists != nullptr)
+                            (*dists)[i * kk + j] = dp[i * k + j];
+                    }
                 }
-            }
+            });
+        }
+
+        /** The same without a vector per query: flat[i * kk + j] is the j-th neighbour of queries[i], kk = min(k, size())
+            is returned.  What a batch call site that only walks the neighbours wants (no 65536 small allocations). */
+        std::size_t nearestKBatchFlat(const std::vector<_T> &queries, std::size_t k, std::vector<_T> &flat,
+                                      std::vector<double> *dists = nullptr) const
+        {
+            ready();
+            const std::size_t nq = queries.size(), st = space_.stride();
+            flat.clear();
+            if (dists != nullptr)
+                dists->clear();
+            if (nq == 0 || k == 0)
+                return 0;
+            static thread_local std::vector<double> rows, d;
+            static thread_local std::vector<std::uint64_t> ids;
+            static thread_local std::vector<std::uint32_t> counts;
+            if (rows.size() < nq * st)
+                rows.resize(nq * st);
+            double *const rowp = rows.data();
+            parallelFor(nq, [&, rowp](std::size_t lo, std::size_t hi) {
+                for (std::size_t i = lo; i < hi; ++i)
+                    rowFun_(queries[i], rowp + i * st);
+            });
+            if (ids.size() < nq * k)
+                ids.resize(nq * k);
+            if (dists != nullptr && d.size() < nq * k)
+                d.resize(nq * k);
+            if (counts.size() < nq)
+                counts.resize(nq);
+            b200::check(omplcu_nn_knn(nn_, rows.data(), nq, k, ids.data(), dists != nullptr ? d.data() : nullptr,
+                                      counts.data()));
+            const std::size_t kk = counts[0];
+            flat.resize(nq * kk);
+            if (dists != nullptr)
+                dists->resize(nq * kk);
+            const std::uint64_t *const idp = ids.data();
+            const double *const dp = d.data();
+            parallelFor(nq, [&, idp, dp](std::size_t lo, std::size_t hi) {
+                for (std::size_t i = lo; i < hi; ++i)
+                    for (std::size_t j = 0; j < kk; ++j)
+                    {
+                        flat[i * kk + j] = byId_[idp[i * k + j] - idOffset_];
+                        if (dists != nullptr)
+                            (*dists)[i * kk + j] = dp[i * k + j];
+                    }
+            });
+            return kk;
         }
 
         /** out[i] = all elements within radii[i] of queries[i] (inclusive), sorted. */
