@@ -23,6 +23,7 @@
 #include <cstring>
 #include <functional>
 #include <limits>
+#include <chrono>
 #include <map>
 #include <memory>
 #include <thread>
@@ -113,6 +114,8 @@ namespace omplcu
             std::unique_ptr<Worker> worker;
             DevBuf<double> q, out_d;     // queries and local results on this shard's device
             DevBuf<uint64_t> out_i;
+            DevBuf<double> blk_d, mrg_d;  // knn_host_distributed: every shard's lists for this shard's query block, merged block
+            DevBuf<uint64_t> blk_i, mrg_i;
             cudaEvent_t done = nullptr;  // local results are in the gather buffer
         };
     }  // namespace
@@ -143,6 +146,7 @@ namespace omplcu
         template <typename F>
         void on_all(F &&f);            // f(shard index) on every shard's worker, in parallel
         void knn_large_k(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists, cudaStream_t s);
+        void knn_host_distributed(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists);
 
         SpaceDesc sp_;
         std::vector<Shard> sh_;
@@ -154,7 +158,7 @@ namespace omplcu
         // first device: staging of host queries, gathered partial results, merged results
         DevBuf<double> q0_, gat_d_, mrg_d_;
         DevBuf<uint64_t> gat_i_, mrg_i_;
-        long last_merge_ns_ = 0;
+        long last_merge_ns_ = 0, last_scan_phase_ns_ = 0;
     };
 
     ShardedNN::ShardedNN(const SpaceDesc &sp, const int *devices, int ndev) : sp_(sp)
@@ -364,6 +368,15 @@ namespace omplcu
             return (long)sh_.size();
         if (!strcmp(key, "last_merge_ns"))
             return last_merge_ns_;
+        if (!strcmp(key, "last_scan_phase_ns"))
+            return last_scan_phase_ns_;  // large host batches: H2D + per-shard kNN, wall clock over all shards
+        if (!strcmp(key, "last_scan_ns"))
+        {
+            long m = 0;  // slowest shard's scan kernel (with option "profile")
+            for (const auto &h : sh_)
+                m = std::max(m, h.index->get_stat("last_scan_ns"));
+            return m;
+        }
         if (!strcmp(key, "launches") || !strcmp(key, "last_fallbacks") || !strcmp(key, "slots") ||
             !strcmp(key, "last_collect_redo") || !strcmp(key, "scan_ns_total") || !strcmp(key, "scan_count"))
         {
@@ -496,11 +509,71 @@ namespace omplcu
         CUDA_CHECK(cudaStreamSynchronize(s));
     }
 
+    // Large host-pointer batches: nothing funnels through the first GPU.  Every shard fetches the queries over its own
+    // PCIe link and answers them on its states; then shard i pulls every shard's lists for query block i (peer copies:
+    // an all-to-all of nq * k * 16 / nd bytes per pair over NVLink), merges them and copies its block to the caller,
+    // again over its own link.  One H2D of 3.7 MB to one GPU, a gather of 84 MB into it and one D2H of 10.5 MB from it
+    // were 0.7 of the 2.1 ms of a 65536-query call on 8 GPUs.
+    void ShardedNN::knn_host_distributed(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists)
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        const size_t nd = sh_.size(), st = (size_t)sp_.stride, part = nq * k;
+        const auto t0 = std::chrono::steady_clock::now();
+        on_all([&](int i) {
+            Shard &h = sh_[i];
+            DeviceGuard g(h.device);
+            cudaStream_t hs = h.index->stream();
+            h.q.reserve(nq * st);
+            h.out_i.reserve(part);
+            h.out_d.reserve(part);
+            CUDA_CHECK(cudaMemcpyAsync(h.q.p, q, nq * st * sizeof(double), cudaMemcpyHostToDevice, hs));
+            h.index->knn_device(h.q.p, nq, k, h.out_i.p, h.out_d.p, hs);
+            CUDA_CHECK(cudaStreamSynchronize(hs));
+        });
+        const auto t1 = std::chrono::steady_clock::now();
+        on_all([&](int i) {
+            Shard &h = sh_[i];
+            const size_t lo = nq * (size_t)i / nd, hi = nq * ((size_t)i + 1) / nd, nb = hi - lo;
+            if (nb == 0)
+                return;
+            DeviceGuard g(h.device);
+            cudaStream_t hs = h.index->stream();
+            h.blk_i.reserve(nd * nb * k);
+            h.blk_d.reserve(nd * nb * k);
+            h.mrg_i.reserve(nb * k);
+            h.mrg_d.reserve(nb * k);
+            for (size_t j = 0; j < nd; ++j)
+            {
+                CUDA_CHECK(cudaMemcpyPeerAsync(h.blk_i.p + j * nb * k, h.device, sh_[j].out_i.p + lo * k, sh_[j].device,
+                                               nb * k * sizeof(uint64_t), hs));
+                CUDA_CHECK(cudaMemcpyPeerAsync(h.blk_d.p + j * nb * k, h.device, sh_[j].out_d.p + lo * k, sh_[j].device,
+                                               nb * k * sizeof(double), hs));
+            }
+            merge_topk_device(h.device, h.blk_d.p, h.blk_i.p, (int)nd, nb * k, nb, k, h.mrg_d.p, h.mrg_i.p, hs);
+            CUDA_CHECK(cudaMemcpyAsync(ids + lo * k, h.mrg_i.p, nb * k * sizeof(uint64_t), cudaMemcpyDeviceToHost, hs));
+            if (dists)
+                CUDA_CHECK(cudaMemcpyAsync(dists + lo * k, h.mrg_d.p, nb * k * sizeof(double), cudaMemcpyDeviceToHost, hs));
+            CUDA_CHECK(cudaStreamSynchronize(hs));
+        });
+        last_scan_phase_ns_ = (long)std::chrono::duration_cast<std::chrono::nanoseconds>(t1 - t0).count();
+        last_merge_ns_ = (long)std::chrono::duration_cast<std::chrono::nanoseconds>(std::chrono::steady_clock::now() - t1).count();
+    }
+
     void ShardedNN::knn_host(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists, uint32_t *counts)
     {
         if (nq == 0)
             return;
         REQUIRE(q && ids, "omplcu_nn_knn: NULL buffer");
+        if (sh_.size() >= 2 && k > 0 && nq >= 4096 && 4 * sh_.size() * k * 16 <= 200 * 1024)
+        {
+            std::lock_guard<std::mutex> hl(host_mu_);
+            const size_t kk = std::min(k, size());
+            knn_host_distributed(q, nq, k, ids, dists);
+            if (counts)
+                for (size_t i = 0; i < nq; ++i)
+                    counts[i] = (uint32_t)kk;
+            return;
+        }
         const size_t st = (size_t)sp_.stride;
         const int dev0 = sh_[0].device;
         cudaStream_t s0 = sh_[0].index->stream();

@@ -117,3 +117,27 @@ def test_motion_batches_split_over_checkers(gpu):
     assert 0 < v1.sum() < n
     assert (v1 == v2).all() and (t1 == t2).all() and (s1 == s2).all()
     assert many.getCheckedMotionCount() == n
+
+
+@pytest.mark.parametrize("nshards,nq", [(2, 4096), (3, 5001), (8, 9000)])
+def test_sharded_large_host_batches_merge_per_query_block(gpu, nshards, nq):
+    """Host-pointer batches of 4096+ queries: every shard fetches the queries itself, answers them, merges ONE block of
+    the queries from all shards' lists and copies that block out (ShardedNN::knn_host_distributed).  Ragged block
+    sizes, duplicates (ties across shards), k larger than a shard's share."""
+    d, n = 7, 40000
+    pts = helpers.with_duplicates(helpers.uniform_points(5, n, d), 6, frac=0.05)
+    qs = np.vstack([pts[:500], helpers.uniform_points(6, nq - 500, d)])
+    one = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    many = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d), devices=_devices(nshards))
+    for nn in (one, many):
+        nn.add_rows(pts)
+    for k in (1, 10):
+        i1, d1 = one.nearestKBatch(qs, k)
+        i2, d2 = many.nearestKBatch(qs, k)
+        assert (i1 == i2).all() and (d1 == d2).all()
+    tiny = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d), devices=_devices(nshards))
+    tiny.add_rows(pts[:7])
+    ref = ob.NearestNeighborsCUDA(ob.RealVectorStateSpace(d))
+    ref.add_rows(pts[:7])
+    a, b = tiny.nearestKBatch(qs, 12), ref.nearestKBatch(qs, 12)
+    assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
