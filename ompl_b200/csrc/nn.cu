@@ -3410,16 +3410,18 @@ namespace omplcu
                                     uint64_t *d_ids, double *d_dists, cudaStream_t s)
     {
         const uint32_t m = 1024;
-        if (!collect_ || nslots_ < 32 * (size_t)m || nlive_ == 0 || nslots_ >= ((size_t)1 << 31))
+        if (!collect_ || nlive_ == 0 || nslots_ >= ((size_t)1 << 31))
+            return false;
+        // embedded spaces, k <= 40: the bound comes from a list scan on the embedding (embed_list_bound) and is tight:
+        // a few times kk slots lie within it, so the rows can be short; no sample, so it pays from 4096 slots on
+        const bool tight = embed_ && kk <= 40 && d_sel == nullptr && nsel >= 16 && filter_usable() && embed_ok(s);
+        if (!tight && nslots_ < 32 * (size_t)m)
             return false;
         const double mean = (double)kk / (double)nlive_ * m;
         const uint32_t R = (uint32_t)std::ceil(mean + 4.0 * std::sqrt(mean) + 6.0);
-        if (R > m / 4)
+        if (!tight && R > m / 4)
             return false;
-        const size_t step = nslots_ / m;
-        // embedded spaces, k <= 40: the bound comes from a list scan on the embedding (embed_list_bound) and is tight:
-        // a few times kk slots lie within it, so the rows can be short
-        const bool tight = embed_ && kk <= 40 && d_sel == nullptr && nsel >= 16 && filter_usable() && embed_ok(s);
+        const size_t step = std::max<size_t>(nslots_ / m, 1);
         const uint32_t cap = tight ? 1024u : (uint32_t)(1.6 * (double)R / m * (double)nslots_) + 256;
         if (cap < kk)
             return false;

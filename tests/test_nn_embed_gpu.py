@@ -174,3 +174,21 @@ def test_filtered_knn_large_batch_needs_the_threshold_scan(gpu):
     oi, od = orc.knn(osp, pts, qs[sub], 10, nthreads=16)
     assert (ids[sub] == oi).all() and np.allclose(d[sub], od, rtol=4e-16, atol=1e-15)
     assert (np.diff(d, axis=1) >= 0).all()
+
+
+@pytest.mark.parametrize("name", ["se2", "se3"])
+def test_filtered_knn_on_a_small_roadmap(gpu, name):
+    """From 4096 states on the embedded path needs no sample (its bound comes from the list scan), so small SE(2) / SE(3)
+    roadmaps are filtered too; removals included."""
+    n, nq = 6000, 300
+    sp, osp = _space(name)
+    pts, qs = _states(name, 91, n), _states(name, 92, nq)
+    nn = ob.NearestNeighborsCUDA(sp)
+    nn.add_rows(pts)
+    _same(nn, osp, pts, qs, 10, name == "se2")
+    assert nn.stat("last_filter") == 1
+    live = [i for i in range(n) if i % 5]
+    assert nn.remove_ids([i for i in range(n) if i % 5 == 0]) == n - len(live)
+    ids, d = nn.nearestKBatch(qs, 10)
+    oi, od = orc.knn(osp, pts[live], qs, 10, nthreads=8)
+    assert (ids == np.asarray(live, dtype=np.uint64)[oi.astype(np.int64)]).all()
