@@ -1297,7 +1297,8 @@ namespace omplcu
                                                                  const double *qaux, const unsigned *pmax2_bits, int D,
                                                                  double err_units, double slack, const uint64_t *slot_ids,
                                                                  uint32_t kstride, uint64_t *out_ids, double *out_dists,
-                                                                 unsigned *unproven, uint32_t *unproven_list)
+                                                                 unsigned *unproven, uint32_t *unproven_list,
+                                                                 uint32_t step, size_t nslots)
         {
             __shared__ double s_key[4][512];
             __shared__ uint32_t s_slot[4][512];
@@ -1311,16 +1312,18 @@ namespace omplcu
             const double inf = __longlong_as_double(0x7ff0000000000000ll);
             for (uint32_t c = lane; c < n; c += 32)
             {
-                const uint32_t slot = cand_ids[(size_t)c * qpad + b];
+                // step > 1: the scan ran on the image of every step-th state; its rows are slots / step
+                const uint32_t row = cand_ids[(size_t)c * qpad + b];
+                const size_t slot = row != SLOT_NONE ? (size_t)row * step : (size_t)SLOT_NONE;
                 double d = inf;
-                if (slot != SLOT_NONE && alive[slot])
+                if (row != SLOT_NONE && slot < nslots && alive[slot])
                 {
                     d = pm(slot, q0 + b);
                     if (!(d == d))
                         d = inf;
                 }
                 s_key[w][c] = d;
-                s_slot[w][c] = d < inf ? slot : SLOT_NONE;
+                s_slot[w][c] = d < inf ? (uint32_t)slot : SLOT_NONE;
             }
             __syncwarp();
             // the kk best by (distance, slot): every lane caches the best of its own candidates, a shuffle tree picks
@@ -1382,7 +1385,7 @@ namespace omplcu
             // Can anything the lists dropped be within dk?  A slot within dk in the space's metric is within
             // dk' = dk (1 + 1e-9) + slack of the query in the embedding (embed_state), and the band formula of
             // knn_rerank_kernel bounds the scan value of such a slot by tau(dk'); every full list's maximum must lie above it.
-            bool proven = dk < inf;
+            bool proven = dk < inf && step == 1;  // a sample's lists say nothing about the states outside the sample
             if (proven)
             {
                 const double u = 5.9604644775390625e-08;  // 2^-24
@@ -1751,10 +1754,11 @@ namespace omplcu
 
         // first kk of every sorted segment; segments that overflowed or came up short are queued for
         // the full sort (redo holds query indices)
-        // Short kept lists (the tight bounds of the embedded path): rank the survivors of a query by (distance, slot)
-        // in shared memory and emit the kk first, instead of a segmented radix sort over 65536 tiny segments (which was
-        // half of the SE(3) call).  More than MAXN survivors, or fewer than kk: the query is redone unfiltered.
-        template <int MAXN>
+        // Kept lists of the embedded path (a few dozen to a few hundred survivors per query, at most `cap`): one warp per
+        // query extracts the kk best by (distance, slot) from shared memory -- every lane caches the best of its own
+        // entries, a shuffle tree picks the winner of a round, only the winning lane rescans -- instead of a segmented
+        // radix sort over 65536 tiny segments (which was half of the SE(3) call).  More than `cap` survivors, or fewer
+        // than kk: the query is redone unfiltered.  Dynamic shared memory: 4 warps x cap x 12 bytes.
         __global__ void __launch_bounds__(128) collect_rank_emit_kernel(const double *keys, const uint32_t *vals,
                                                                         const uint32_t *cnt, uint32_t cap,
                                                                         const uint64_t *slot_ids, size_t b0, size_t nb,
@@ -1762,15 +1766,16 @@ namespace omplcu
                                                                         double *out_dists, uint32_t *redo,
                                                                         unsigned *redo_count, const uint32_t *sel = nullptr)
         {
-            __shared__ double s_key[4][MAXN];
-            __shared__ uint32_t s_slot[4][MAXN];
+            extern __shared__ __align__(16) unsigned char cre_smem[];
             const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+            double *s_key = reinterpret_cast<double *>(cre_smem) + (size_t)w * cap;
+            uint32_t *s_slot = reinterpret_cast<uint32_t *>(reinterpret_cast<double *>(cre_smem) + (size_t)4 * cap) + (size_t)w * cap;
             const size_t b = blockIdx.x * 4ull + w;
             if (b >= nb)
                 return;
             const size_t qi = b0 + (sel ? sel[b] : b);
             const uint32_t n = cnt[b];
-            if (n > (uint32_t)MAXN || n > cap || n < kk)
+            if (n > cap || n < kk)
             {
                 if (lane == 0)
                     redo[atomicAdd(redo_count, 1u)] = (uint32_t)qi;
@@ -1778,26 +1783,62 @@ namespace omplcu
             }
             for (uint32_t i = lane; i < n; i += 32)
             {
-                s_key[w][i] = keys[b * cap + i];
-                s_slot[w][i] = vals[b * cap + i];
+                s_key[i] = keys[b * cap + i];
+                s_slot[i] = vals[b * cap + i];
             }
             __syncwarp();
-            for (uint32_t i = lane; i < n; i += 32)
+            const double inf = __longlong_as_double(0x7ff0000000000000ll);
+            double bk = inf;
+            uint32_t bs = SLOT_NONE, bi = 0;
+            auto rescan = [&]() {
+                bk = inf;
+                bs = SLOT_NONE;
+                bi = 0;
+                for (uint32_t c = lane; c < n; c += 32)
+                {
+                    const uint32_t sl = s_slot[c];
+                    if (sl == SLOT_NONE)
+                        continue;
+                    const double k = s_key[c];
+                    if (bs == SLOT_NONE || k < bk || (k == bk && sl < bs))
+                    {
+                        bk = k;
+                        bs = sl;
+                        bi = c;
+                    }
+                }
+            };
+            rescan();
+            for (uint32_t r = 0; r < kk; ++r)
             {
-                const double key = s_key[w][i];
-                const uint32_t slot = s_slot[w][i];
-                uint32_t rank = 0;
-                for (uint32_t j = 0; j < n; ++j)
+                double wk = bk;
+                uint32_t ws = bs, wi = bi;
+                for (int o = 16; o > 0; o >>= 1)
                 {
-                    const double kj = s_key[w][j];
-                    rank += (kj < key || (kj == key && s_slot[w][j] < slot)) ? 1u : 0u;
+                    const double ok = __shfl_xor_sync(0xffffffffu, wk, o);
+                    const uint32_t os = __shfl_xor_sync(0xffffffffu, ws, o);
+                    const uint32_t oi = __shfl_xor_sync(0xffffffffu, wi, o);
+                    if (os != SLOT_NONE && (ws == SLOT_NONE || ok < wk || (ok == wk && os < ws)))
+                    {
+                        wk = ok;
+                        ws = os;
+                        wi = oi;
+                    }
                 }
-                if (rank < kk)
+                if (ws == SLOT_NONE)
+                    break;  // cannot happen (n >= kk live entries); the row would keep its previous content
+                if (lane == 0)
                 {
-                    out_ids[qi * kstride + rank] = slot_ids[slot];
+                    out_ids[qi * kstride + r] = slot_ids[ws];
                     if (out_dists)
-                        out_dists[qi * kstride + rank] = key;
+                        out_dists[qi * kstride + r] = wk;
                 }
+                if ((wi & 31u) == (uint32_t)lane)
+                {
+                    s_slot[wi] = SLOT_NONE;
+                    rescan();
+                }
+                __syncwarp();
             }
         }
 
@@ -3313,19 +3354,33 @@ namespace omplcu
         const size_t QT = (size_t)TC_QT * sh.na;
         const size_t qtiles = (nq + QT - 1) / QT;
         const uint32_t qpad = (uint32_t)(qtiles * QT);
-        const unsigned long long U = (nslots_ + TC_PT - 1) / TC_PT, TU = qtiles * U;
         const unsigned max_seg = 512u / L;
-        unsigned long long G = std::min<unsigned long long>(sm_count_, TU);
-        G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
-        G = std::max<unsigned long long>(G, 1);
+        unsigned long long U = 0, TU = 0, G = 1;
         uint32_t smax = 1;
-        for (size_t t = 0; t < qtiles; ++t)
-        {
-            const unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
-            const unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
-            const unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
-            smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
-        }
+        auto plan = [&](size_t rows) {
+            U = (rows + TC_PT - 1) / TC_PT;
+            TU = qtiles * U;
+            G = std::min<unsigned long long>(sm_count_, TU);
+            G = std::min<unsigned long long>(G, qtiles * (unsigned long long)(max_seg - 1));
+            G = std::max<unsigned long long>(G, 1);
+            smax = 1;
+            for (size_t t = 0; t < qtiles; ++t)
+            {
+                const unsigned long long x0 = t * U, x1 = (t + 1) * U - 1;
+                const unsigned long long g0 = ((x0 + 1) * G + TU - 1) / TU - 1;
+                const unsigned long long g1 = ((x1 + 1) * G + TU - 1) / TU - 1;
+                smax = std::max<uint32_t>(smax, (uint32_t)(g1 - g0 + 1));
+            }
+        };
+        plan(nslots_);
+        // (A bound from the image of every 8th state was tried for the big batches, where the lists prove next to
+        // nothing and this scan is only there for the bound: the threshold scan then kept more than its rows hold for
+        // many queries -- 13 of 65536 at k = 10, three quarters at k = 36 on 1M SE(3) states -- and every such query costs
+        // an exact pass.  The plumbing for a sampled image stays; step is 1.)
+        const size_t step = 1;
+        const size_t rows = (nslots_ + step - 1) / step;
+        if (step > 1)
+            plan(rows);
         REQUIRE((size_t)smax * L <= 512, "embedded list scan: too many segments per query tile");
         c.qp_.reserve((size_t)D_ * qpad);
         c.qaux_.reserve(2 * (size_t)qpad);
@@ -3335,8 +3390,20 @@ namespace omplcu
         CUDA_CHECK(cudaMemsetAsync(c.cand_vals_.p, 0x7F, (size_t)smax * qpad * sizeof(float), s));
         query_prep_kernel<<<nblk(qpad, 256), 256, 0, s>>>(d_qe, nq, center_.p, D_, c.qp_.p, c.qaux_.p, qpad);
         {
-            std::lock_guard<std::mutex> pl(prep_mu_);  // shared operand image, see knn_fast
-            if (tc_version_ != mut_version_)
+            std::lock_guard<std::mutex> pl(prep_mu_);  // shared operand images, see knn_fast
+            if (step > 1)
+            {
+                if (tc_sversion_ != mut_version_ || tc_sstep_ != step)
+                {
+                    tc_simg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
+                    tc_build_sample_image(filt_.p, rowf_, D_, nslots_, step, (size_t)U, tc_simg_.p, s);
+                    CUDA_CHECK(cudaStreamSynchronize(s));
+                    tc_sversion_ = mut_version_;
+                    tc_sstep_ = step;
+                    launches_++;
+                }
+            }
+            else if (tc_version_ != mut_version_)
             {
                 tc_pimg_.reserve((size_t)U * sh.nkc * sh.chunk_elems());
                 tc_build_point_image(filt_.p, rowf_, D_, (size_t)U, tc_pimg_.p, s);
@@ -3348,7 +3415,7 @@ namespace omplcu
         c.tc_qimg_.reserve((size_t)(qpad / TC_QT) * sh.nkc * sh.chunk_elems());
         tc_build_query_image(c.qp_.p, qpad, D_, c.tc_qimg_.p, s);
         TcScanParams T{};
-        T.pimg = tc_pimg_.p;
+        T.pimg = step > 1 ? tc_simg_.p : tc_pimg_.p;
         T.qimg = c.tc_qimg_.p;
         T.cand_thr = c.cand_vals_.p;
         T.cand_ids = c.cand_ids_.p;
@@ -3364,7 +3431,8 @@ namespace omplcu
         cand_bound_kernel<<<nblk(nq, 4), 128, 0, s>>>(c.cand_ids_.p, c.cand_vals_.p, smax,
                                                       (uint32_t)L, qpad, pm, q0, alive_.p, nq, (uint32_t)kk, d_bound,
                                                       c.qaux_.p, pmax2_.p, D_, tc_err_units(D_), embed_slack_, ids_.p,
-                                                      (uint32_t)kstride, d_ids, d_dists, c.counters_.p + 2, c.unp_list_.p);
+                                                      (uint32_t)kstride, d_ids, d_dists, c.counters_.p + 2, c.unp_list_.p,
+                                                      (uint32_t)step, nslots_);
         launches_ += 4;
         CUDA_CHECK(cudaGetLastError());
         unsigned unproven = 0;
@@ -3493,7 +3561,7 @@ namespace omplcu
                 kept_collect_metric_kernel<<<nblk(left, 4), 128, 0, s>>>(c.app_ids_.p, c.app_cnt_.p, rows, fcap, fq, pm, b0,
                                                                          alive_.p, c.col_bound2_.p, left, cap, c.ex_keys2_.p,
                                                                          c.ex_vals2_.p, c.col_cnt_.p, c.unp_list_.p);
-                collect_rank_emit_kernel<512><<<nblk(left, 4), 128, 0, s>>>(c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p, cap,
+                collect_rank_emit_kernel<<<nblk(left, 4), 128, (size_t)4 * cap * 12, s>>>(c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p, cap,
                                                                             ids_.p, b0, left, (uint32_t)kk, (uint32_t)kstride,
                                                                             d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1,
                                                                             c.unp_list_.p);
@@ -3528,7 +3596,7 @@ namespace omplcu
                                                                            c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p);
                     if (tight)
                     {
-                        collect_rank_emit_kernel<512><<<nblk(nb, 4), 128, 0, s>>>(
+                        collect_rank_emit_kernel<<<nblk(nb, 4), 128, (size_t)4 * cap * 12, s>>>(
                             c.ex_keys2_.p, c.ex_vals2_.p, c.col_cnt_.p, cap, ids_.p, b0, nb, (uint32_t)kk, (uint32_t)kstride,
                             d_ids, d_dists, c.col_redo_.p, c.counters_.p + 1);
                         CUDA_CHECK(cudaGetLastError());

@@ -33,6 +33,6 @@ for m in (1, 64, nq):
     for _ in range(reps):
         ids, d = nn.nearestKBatch(qs[:m], k)
     t = (time.perf_counter() - t0) / reps
-    print(f"{space} n={n} nq={m} k={k}: {t * 1e3:.3f} ms per call, {m / t / 1e3:.1f} K queries/s  path {nn.stat("last_path")} proven {nn.stat("last_proven")}", flush=True)
+    print(f"{space} n={n} nq={m} k={k}: {t * 1e3:.3f} ms per call, {m / t / 1e3:.1f} K queries/s  path {nn.stat("last_path")} proven {nn.stat("last_proven")} redo {nn.stat("last_collect_redo")}", flush=True)
 oi, od = orc.knn(osp, pts, qs[:64], k, nthreads=8)
 print("ids equal:", bool((ids[:64] == oi).all()))
