@@ -465,10 +465,10 @@ def run_gpu_arm(args):
                 "frac_executed": exe / (scan_ns * 1e-9) / 1e12 / tpeak,
                 "kernel_ms": scan_ns * 1e-6, "kernel_share_of_step": scan_ns * 1e-6 / t_step,
                 "vs_fp32_pipe_peak": ach / fp32_peak if fp32_peak else None,
-                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu round 2: 30 % busy) and neither is HBM: "
-                        "the kernel is bound by instruction issue and latency in the selection warps (issue slots 63 % busy; of the "
-                        "executed instructions 23 % are the FMNMX3 min-trees over the accumulators, 23 % branch / sync / nop overhead "
-                        "of the per-half-tile TMEM hand-over, 25 % integer bookkeeping and list insertions, 13 % compares, 12 % "
+                "note": "K = 32 per accumulator, so the tensor pipe is not the bound (ncu round 2: 38 % busy) and neither is HBM: "
+                        "the kernel is bound by instruction issue and latency in the selection warps (issue slots 56 % busy; of the "
+                        "executed instructions 30 % are the FMNMX3 min-trees over the accumulators, 23 % branch / sync / nop overhead "
+                        "of the per-half-tile TMEM hand-over, 19 % integer bookkeeping and list insertions, 9 % compares, 15 % "
                         "mbarrier polls; profiles/r2_scan_tc_d7_instruction_mix.txt). Every FP32 accumulator value costs at least 1 "
                         "issue clock per SM sub-partition whatever instruction looks at it (scripts/ubench_reduce.cu), i.e. 1.76 ms "
                         "for this launch; achieved exceeds the FP32 FMA peak (vs_fp32_pipe_peak > 1), which bounded the FP32 scan "
