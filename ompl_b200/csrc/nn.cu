@@ -1972,6 +1972,73 @@ namespace omplcu
             }
         }
 
+        // The same merge for candidate counts that do not fit shared memory (FMT*'s k ~ 2100 on 8 shards): every
+        // part is a list sorted by distance (absent entries last), so a candidate's rank among all candidates is the
+        // sum over the parts of a lower bound by distance plus the members of the run of equal distances with a
+        // smaller id -- nparts binary searches per candidate instead of a comparison with every other candidate, and
+        // no staging: the lists of one query (nparts * k * 16 bytes) are read through L1.  A search never looks past
+        // k - rank entries: a candidate that would reach rank k is dropped there, which is where most of them end.
+        // One block per query.
+        __global__ void __launch_bounds__(256) merge_sorted_kernel(const double *__restrict__ dists,
+                                                                   const uint64_t *__restrict__ ids, int nparts,
+                                                                   size_t part_stride, size_t nq, uint32_t k,
+                                                                   double *__restrict__ out_d, uint64_t *__restrict__ out_i)
+        {
+            for (size_t qi = blockIdx.x; qi < nq; qi += gridDim.x)
+            {
+                for (uint32_t r = threadIdx.x; r < k; r += blockDim.x)
+                {
+                    out_i[qi * k + r] = OMPLCU_ID_NONE;
+                    out_d[qi * k + r] = __longlong_as_double(0x7ff0000000000000ll);
+                }
+                __syncthreads();
+                const uint32_t n = (uint32_t)nparts * k;
+                for (uint32_t c = threadIdx.x; c < n; c += blockDim.x)
+                {
+                    const uint32_t p = c / k, j = c - p * k;
+                    const size_t own = (size_t)p * part_stride + qi * k;
+                    const uint64_t id = __ldg(ids + own + j);
+                    if (id == OMPLCU_ID_NONE)
+                        continue;
+                    const double key = __ldg(dists + own + j);
+                    uint32_t rank = 0;
+                    bool keep = true;
+                    for (int t = 0; t < nparts && keep; ++t)
+                    {
+                        const int pp = t == 0 ? (int)p : (t <= (int)p ? t - 1 : t);  // the own list first: rank ~ j at once
+                        const size_t base = (size_t)pp * part_stride + qi * k;
+                        const uint32_t lim = k - rank;
+                        uint32_t lo = 0, hi = lim;
+                        while (lo < hi)
+                        {
+                            const uint32_t mid = (lo + hi) >> 1;
+                            const bool less = __ldg(ids + base + mid) != OMPLCU_ID_NONE && __ldg(dists + base + mid) < key;
+                            if (less)
+                                lo = mid + 1;
+                            else
+                                hi = mid;
+                        }
+                        rank += lo;
+                        // equal distances: ordered by id whatever their order inside the list
+                        for (uint32_t e = lo; e < k && rank < k; ++e)
+                        {
+                            const uint64_t ie = __ldg(ids + base + e);
+                            if (ie == OMPLCU_ID_NONE || __ldg(dists + base + e) != key)
+                                break;
+                            rank += ie < id ? 1u : 0u;
+                        }
+                        keep = rank < k;
+                    }
+                    if (keep)
+                    {
+                        out_i[qi * k + rank] = id;
+                        out_d[qi * k + rank] = key;
+                    }
+                }
+                __syncthreads();
+            }
+        }
+
         inline unsigned nblk(size_t n, unsigned bs)
         {
             return (unsigned)((n + bs - 1) / bs);
@@ -4113,8 +4180,17 @@ namespace omplcu
         REQUIRE(part_stride >= nq * k, "omplcu_merge_topk: part stride smaller than one part");
         if (nq == 0 || k == 0)
             return;
+        REQUIRE(k < ((size_t)1 << 31) / (size_t)nparts, "omplcu_merge_topk: nparts * k too large");
         const size_t smem = 4 * (size_t)nparts * k * 16;
-        REQUIRE(smem <= 200 * 1024, "omplcu_merge_topk: nparts * k too large (limit 3200 candidates per query)");
+        if (smem > 200 * 1024)
+        {
+            // more candidates per query than shared memory stages: ranks by binary search in the sorted lists
+            merge_sorted_kernel<<<(unsigned)std::min<size_t>(nq, 148 * 64), 256, 0, s>>>(
+                d_dists, d_ids, nparts, part_stride, nq, (uint32_t)k, d_out_dists, d_out_ids);
+            CUDA_CHECK(cudaGetLastError());
+            CUDA_CHECK(cudaStreamSynchronize(s));
+            return;
+        }
         if (smem > 48 * 1024)
             CUDA_CHECK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         merge_topk_kernel<<<nblk(nq, 4), 128, smem, s>>>(d_dists, d_ids, nparts, part_stride, nq, (uint32_t)k,

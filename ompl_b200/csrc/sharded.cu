@@ -10,7 +10,9 @@
 //   kNN       queries land on the first device (one H2D), go to the other devices over NVLink
 //             (cudaMemcpyPeerAsync), every shard answers them on its own GPU from its own host thread
 //             (local exact top-k), the per-shard (distance, id) lists are peer-copied into one
-//             [part][query][k] buffer on the first device, merge_topk_kernel selects the k best, ONE D2H.
+//             [part][query][k] buffer on the first device, merge_topk_kernel selects the k best, ONE D2H
+//             (FMT*-sized k: merge_sorted_kernel, ranks by binary search in the sorted lists, and the
+//             batch goes in pieces that bound the gather buffer).
 //             It is the all-gather + merge of 8(e) with a single consumer: in one process only the
 //             caller's device needs the gathered lists, so the exchange is ndev - 1 peer copies into
 //             disjoint slices instead of a collective.
@@ -145,7 +147,7 @@ namespace omplcu
         int owner(uint64_t id) const;  // shard holding the block of `id`, -1 if none
         template <typename F>
         void on_all(F &&f);            // f(shard index) on every shard's worker, in parallel
-        void knn_large_k(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists, cudaStream_t s);
+        void knn_gather(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists, cudaStream_t s);
         void knn_host_distributed(const double *q, size_t nq, size_t k, uint64_t *ids, double *dists);
 
         SpaceDesc sp_;
@@ -159,6 +161,7 @@ namespace omplcu
         DevBuf<double> q0_, gat_d_, mrg_d_;
         DevBuf<uint64_t> gat_i_, mrg_i_;
         long last_merge_ns_ = 0, last_scan_phase_ns_ = 0;
+        size_t gather_entries_ = (size_t)1 << 27;  // 2 GB of gathered lists
     };
 
     ShardedNN::ShardedNN(const SpaceDesc &sp, const int *devices, int ndev) : sp_(sp)
@@ -357,6 +360,12 @@ namespace omplcu
     void ShardedNN::set_option(const char *key, long v)
     {
         std::lock_guard<std::mutex> lk(mu_);
+        if (!strcmp(key, "gather_entries"))
+        {
+            // (distance, id) entries the gather buffer on the first device may hold: larger batches go in pieces
+            gather_entries_ = (size_t)std::max<long>(v, 1);
+            return;
+        }
         for (auto &s : sh_)
             s.index->set_option(key, v);
     }
@@ -414,11 +423,17 @@ namespace omplcu
             sh_[0].index->knn_device(d_q, nq, k, d_ids, d_dists, s);
             return;
         }
-        if (4 * nd * k * 16 > 200 * 1024)
-        {
-            knn_large_k(d_q, nq, k, d_ids, d_dists, s);
-            return;
-        }
+        // FMT*-sized k: the gathered lists (nd * nq * k * 16 bytes) are bounded by answering the batch in pieces
+        const size_t piece = std::max<size_t>(1, gather_entries_ / (nd * k));
+        for (size_t q0 = 0; q0 < nq; q0 += piece)
+            knn_gather(d_q + q0 * st, std::min(piece, nq - q0), k, d_ids + q0 * k, d_dists ? d_dists + q0 * k : nullptr, s);
+    }
+
+    void ShardedNN::knn_gather(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
+                               cudaStream_t s)
+    {
+        const int dev0 = sh_[0].device;
+        const size_t nd = sh_.size(), st = (size_t)sp_.stride;
         const size_t part = nq * k;
         {
             DeviceGuard g(dev0);
@@ -447,66 +462,6 @@ namespace omplcu
             CUDA_CHECK(cudaStreamSynchronize(hs));
         });
         merge_topk_device(dev0, gat_d_.p, gat_i_.p, (int)nd, part, nq, k, d_dists ? d_dists : mrg_d_.p, d_ids, s);
-    }
-
-    // nparts * k beyond what merge_topk_kernel stages in shared memory (FMT*'s k ~ 2100 on 8 shards):
-    // the sorted per-shard lists are merged on the host, k-way by (distance, id).
-    void ShardedNN::knn_large_k(const double *d_q, size_t nq, size_t k, uint64_t *d_ids, double *d_dists,
-                                cudaStream_t s)
-    {
-        const int dev0 = sh_[0].device;
-        const size_t nd = sh_.size(), st = (size_t)sp_.stride, part = nq * k;
-        std::vector<std::vector<uint64_t>> hi(nd);
-        std::vector<std::vector<double>> hd(nd);
-        on_all([&](int i) {
-            Shard &h = sh_[i];
-            DeviceGuard g(h.device);
-            cudaStream_t hs = h.index->stream();
-            h.q.reserve(nq * st);
-            h.out_i.reserve(part);
-            h.out_d.reserve(part);
-            CUDA_CHECK(cudaMemcpyPeerAsync(h.q.p, h.device, d_q, dev0, nq * st * sizeof(double), hs));
-            h.index->knn_device(h.q.p, nq, k, h.out_i.p, h.out_d.p, hs);
-            hi[i].resize(part);
-            hd[i].resize(part);
-            CUDA_CHECK(cudaMemcpyAsync(hi[i].data(), h.out_i.p, part * sizeof(uint64_t), cudaMemcpyDeviceToHost, hs));
-            CUDA_CHECK(cudaMemcpyAsync(hd[i].data(), h.out_d.p, part * sizeof(double), cudaMemcpyDeviceToHost, hs));
-            CUDA_CHECK(cudaStreamSynchronize(hs));
-        });
-        std::vector<uint64_t> oi(part, OMPLCU_ID_NONE);
-        std::vector<double> od(part, std::numeric_limits<double>::infinity());
-        std::vector<size_t> pos(nd);
-        for (size_t q = 0; q < nq; ++q)
-        {
-            std::fill(pos.begin(), pos.end(), 0);
-            for (size_t r = 0; r < k; ++r)
-            {
-                int best = -1;
-                for (size_t p = 0; p < nd; ++p)
-                {
-                    if (pos[p] >= k || hi[p][q * k + pos[p]] == OMPLCU_ID_NONE)
-                        continue;
-                    if (best < 0)
-                    {
-                        best = (int)p;
-                        continue;
-                    }
-                    const double a = hd[p][q * k + pos[p]], b = hd[best][q * k + pos[best]];
-                    if (a < b || (a == b && hi[p][q * k + pos[p]] < hi[best][q * k + pos[best]]))
-                        best = (int)p;
-                }
-                if (best < 0)
-                    break;
-                oi[q * k + r] = hi[best][q * k + pos[best]];
-                od[q * k + r] = hd[best][q * k + pos[best]];
-                pos[best]++;
-            }
-        }
-        DeviceGuard g(dev0);
-        CUDA_CHECK(cudaMemcpyAsync(d_ids, oi.data(), part * sizeof(uint64_t), cudaMemcpyHostToDevice, s));
-        if (d_dists)
-            CUDA_CHECK(cudaMemcpyAsync(d_dists, od.data(), part * sizeof(double), cudaMemcpyHostToDevice, s));
-        CUDA_CHECK(cudaStreamSynchronize(s));
     }
 
     // Large host-pointer batches: nothing funnels through the first GPU.  Every shard fetches the queries over its own

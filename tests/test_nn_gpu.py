@@ -440,6 +440,39 @@ def test_merge_topk_equals_single_index(gpu):
     assert (oi.cpu().numpy().astype(np.uint64) == wi).all() and (od.cpu().numpy() == wd).all()
 
 
+def test_merge_topk_more_candidates_than_shared_memory_holds(gpu):
+    """nparts * k > 3200: merge_sorted_kernel (binary searches in the sorted lists) == one index, duplicates included."""
+    import torch
+
+    from ompl_b200._lib import check, lib
+
+    n, nq, k, parts = 12000, 300, 900, 5
+    pts = helpers.with_duplicates(helpers.uniform_points(13, n, 3), 5, 0.2)
+    qs = np.vstack([pts[:100], helpers.uniform_points(15, nq - 100, 3)])
+    sp = ob.RealVectorStateSpace(3)
+    whole = ob.NearestNeighborsCUDA(sp)
+    whole.add_rows(pts)
+    wi, wd = whole.nearestKBatch(qs, k)
+    dq = torch.from_numpy(qs).cuda()
+    pd = torch.empty((parts, nq, k), dtype=torch.float64, device="cuda")
+    pi = torch.empty((parts, nq, k), dtype=torch.int64, device="cuda")
+    # uneven shards; the last one holds fewer than k states, so its lists end in absent entries
+    bounds = np.array([0, 4000, 7000, 9500, 11500, n])
+    shards = []
+    for p in range(parts):
+        s = ob.NearestNeighborsCUDA(sp)
+        s.set_id_base(int(bounds[p]))
+        s.add_rows(pts[bounds[p]:bounds[p + 1]])
+        shards.append(s)
+        check(lib().omplcu_nn_knn_device(s.handle, dq.data_ptr(), nq, k, pi[p].data_ptr(), pd[p].data_ptr(), None))
+    od = torch.empty((nq, k), dtype=torch.float64, device="cuda")
+    oi = torch.empty((nq, k), dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    check(lib().omplcu_merge_topk_device(0, pd.data_ptr(), pi.data_ptr(), parts, nq, k, od.data_ptr(), oi.data_ptr(),
+                                         None))
+    assert (oi.cpu().numpy().astype(np.uint64) == wi).all() and (od.cpu().numpy() == wd).all()
+
+
 # ---------------------------------------------------------------- tensor-core scan (knn_scan_tc.cu)
 def _tc_err_units(d):
     k16 = (3 * d + 3 + 15) // 16  # tcgen05.mma instructions (K = 16) per pair of tiles

@@ -81,10 +81,21 @@ def test_sharded_radius_and_large_k(gpu):
     a, b = one.nearestRBatch(qs, r), many.nearestRBatch(qs, r)
     assert (a[2] == b[2]).all() and a[2][-1] > 1000
     assert (a[0] == b[0]).all() and (a[1] == b[1]).all()
-    # nparts * k beyond the device merge's shared-memory budget: host k-way merge (FMT*'s k ~ 2100)
+    # nparts * k beyond the device merge's shared-memory budget (FMT*'s k ~ 2100): ranks by binary search in the
+    # sorted per-shard lists; duplicates make runs of equal distances that cross shards
     k = 2100
     i1, d1 = one.nearestKBatch(qs[:16], k)
     i2, d2 = many.nearestKBatch(qs[:16], k)
+    assert (i1 == i2).all() and (d1 == d2).all()
+    # the same with a gather buffer that only holds 5 queries' lists at a time
+    many.set_option("gather_entries", 5 * 4 * k)
+    i3, d3 = many.nearestKBatch(qs[:16], k)
+    assert (i1 == i3).all() and (d1 == d3).all()
+    many.set_option("gather_entries", 1 << 27)
+    # more neighbours asked for than one shard holds: absent entries at the end of every list
+    k = 12000
+    i1, d1 = one.nearestKBatch(qs[:3], k)
+    i2, d2 = many.nearestKBatch(qs[:3], k)
     assert (i1 == i2).all() and (d1 == d2).all()
 
 
