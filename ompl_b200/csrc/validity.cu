@@ -425,8 +425,12 @@ namespace omplcu
         }
 
         // nd and the number of states to check per segment: (nd-1 interior if nd >= 2) + s2
+        // prep (optional): the per-segment constants of SO3StateSpace::interpolate (so3_prepare) of the first
+        // MAX_SO3_PREP SO(3) components, [component][segment] as (theta, d with the sign of `neg`): one thread per
+        // segment here, all lanes busy, instead of a lane group of motion_group_kernel repeating them while the
+        // other groups of its warp wait.
         __global__ void segment_count_kernel(SpaceDesc sp, const double *s1, const double *s2, size_t n, uint32_t *nd,
-                                             unsigned long long *cnt)
+                                             unsigned long long *cnt, double2 *prep)
         {
             const size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x;
             if (i >= n)
@@ -435,13 +439,29 @@ namespace omplcu
             nd[i] = v;
             if (cnt)
                 cnt[i] = (v >= 2 ? (unsigned long long)(v - 1) : 0ull) + 1ull;
+            if (prep && v >= 2)
+            {
+                So3Seg g[MAX_SO3_PREP] = {};
+                space_prepare(sp, s1 + i * sp.stride, s2 + i * sp.stride, g);
+                int k = 0;
+                for (int c = 0; c < sp.ncomp && k < MAX_SO3_PREP; ++c)
+                    if (sp.comp[c].type == OMPLCU_SO3)
+                    {
+                        prep[(size_t)k * n + i] = make_double2(g[k].theta, g[k].neg ? -g[k].d : g[k].d);
+                        ++k;
+                    }
+            }
         }
 
         // ctr[0]: next segment to hand out, ctr[1]: states evaluated (statistics)
-        template <int KIND, int MAXS, int G>
+        // SPEC = 1: the space is exactly SE(3) (RealVector(3) x SO(3), stride 7).  The state is then built by straight
+        // code on constant indices and lives in registers; the general path walks the component table with run-time
+        // offsets, which puts the state into local memory (86 STL / 22 LDL in the SASS of the general kernel).
+        template <int KIND, int MAXS, int G, int SPEC>
         __global__ void __launch_bounds__(128) motion_group_kernel(CheckerDesc c, SpaceDesc sp, const double *s1,
                                                                    const double *s2, size_t n, const uint32_t *nd,
-                                                                   unsigned *code, unsigned long long *ctr)
+                                                                   const double2 *prep_in, int nprep, unsigned *code,
+                                                                   unsigned long long *ctr)
         {
             extern __shared__ float4 smem_filt[];
             const Staged<KIND> sm = stage_filter<KIND>(c, smem_filt);
@@ -472,7 +492,34 @@ namespace omplcu
                         base = 0;
                         need = false;
                         if (cnt > 1)  // acos, 1/sin(theta): once per segment, not once per state
-                            space_prepare(sp, s1 + seg * sp.stride, s2 + seg * sp.stride, prep);
+                        {
+                            if (SPEC == 1)
+                            {
+                                if (prep_in)
+                                {
+                                    const double2 g = prep_in[seg];
+                                    prep[0].theta = g.x;
+                                    prep[0].d = fabs(g.y);
+                                    prep[0].neg = g.y < 0.0;
+                                }
+                                else
+                                    prep[0] = so3_prepare(s1 + seg * 7 + 3, s2 + seg * 7 + 3);
+                            }
+                            else if (prep_in)
+                            {
+                                // computed by segment_count_kernel
+                                for (int k = 0; k < MAX_SO3_PREP; ++k)
+                                    if (k < nprep)
+                                    {
+                                        const double2 g = prep_in[(size_t)k * n + seg];
+                                        prep[k].theta = g.x;
+                                        prep[k].d = fabs(g.y);
+                                        prep[k].neg = g.y < 0.0;
+                                    }
+                            }
+                            else
+                                space_prepare(sp, s1 + seg * sp.stride, s2 + seg * sp.stride, prep);
+                        }
                     }
                 }
                 if (__all_sync(FULL, done))
@@ -484,7 +531,26 @@ namespace omplcu
                 {
                     const double *a = s1 + seg * sp.stride, *b = s2 + seg * sp.stride;
                     double st[MAXS];
-                    if (m == cnt - 1)
+                    if (SPEC == 1)
+                    {
+                        if (m == cnt - 1)
+                        {
+#pragma unroll
+                            for (int d = 0; d < 7; ++d)
+                                st[d] = b[d];
+                        }
+                        else
+                        {
+                            const double t = ddiv((double)(m + 1), (double)ndv);
+                            // RealVectorStateSpace::interpolate, then SO3StateSpace::interpolate: the expressions of
+                            // space_interpolate_prepared for this component table
+#pragma unroll
+                            for (int d = 0; d < 3; ++d)
+                                st[d] = dadd(a[d], dmul(dsub(b[d], a[d]), t));
+                            so3_interpolate_prepared(prep[0], a + 3, b + 3, t, st + 3);
+                        }
+                    }
+                    else if (m == cnt - 1)
                     {
                         for (int d = 0; d < sp.stride && d < MAXS; ++d)
                             st[d] = b[d];
@@ -864,34 +930,52 @@ namespace omplcu
             check_states_kernel<KIND, MAXS><<<grid, 128, smem, s>>>(c, stride, st, n, v);
         }
 
-        template <int KIND, int MAXS, int G>
+        template <int KIND, int MAXS, int G, int SPEC>
         void launch_motion_g(const CheckerDesc &c, size_t smem, int sms, const SpaceDesc &sp, const double *s1,
-                             const double *s2, size_t n, const uint32_t *nd, unsigned *code, unsigned long long *ctr,
-                             cudaStream_t s)
+                             const double *s2, size_t n, const uint32_t *nd, const double2 *prep, int nprep, unsigned *code,
+                             unsigned long long *ctr, cudaStream_t s)
         {
             if (smem > 48 * 1024)
-                CUDA_CHECK(cudaFuncSetAttribute(motion_group_kernel<KIND, MAXS, G>,
+                CUDA_CHECK(cudaFuncSetAttribute(motion_group_kernel<KIND, MAXS, G, SPEC>,
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
             // persistent grid: a multiple of the SM count, no more groups than segments
             const size_t groups_per_cta = 128 / G;
             const unsigned want = (unsigned)std::min<size_t>((n + groups_per_cta - 1) / groups_per_cta,
                                                              (size_t)sms * 8u);
-            motion_group_kernel<KIND, MAXS, G><<<std::max(want, 1u), 128, smem, s>>>(c, sp, s1, s2, n, nd, code, ctr);
+            motion_group_kernel<KIND, MAXS, G, SPEC><<<std::max(want, 1u), 128, smem, s>>>(c, sp, s1, s2, n, nd, prep, nprep,
+                                                                                     code, ctr);
         }
 
         template <int KIND, int MAXS>
         void launch_motion(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
-                           const double *s1, const double *s2, size_t n, const uint32_t *nd, unsigned *code,
-                           unsigned long long *ctr, cudaStream_t s)
+                           const double *s1, const double *s2, size_t n, const uint32_t *nd, const double2 *prep,
+                           int nprep, unsigned *code, unsigned long long *ctr, cudaStream_t s)
         {
+            // exactly SE(3): RealVector(3) x SO(3), nothing else in the state
+            constexpr bool can_spec = KIND == OMPLCU_CHK_SE3 && MAXS == 8;
+            const bool spec = can_spec && sp.compound && sp.ncomp == 2 && sp.stride == 7 && sp.comp[0].type == OMPLCU_RV &&
+                              sp.comp[0].dim == 3 && sp.comp[1].type == OMPLCU_SO3 && (prep == nullptr || nprep == 1) &&
+                              getenv("OMPLCU_MOTION_GENERIC") == nullptr;
+            if (can_spec && spec)
+            {
+                if (group >= 32)
+                    launch_motion_g<KIND, MAXS, 32, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                else if (group >= 16)
+                    launch_motion_g<KIND, MAXS, 16, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                else if (group >= 8)
+                    launch_motion_g<KIND, MAXS, 8, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                else
+                    launch_motion_g<KIND, MAXS, 4, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                return;
+            }
             if (group >= 32)
-                launch_motion_g<KIND, MAXS, 32>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 32, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
             else if (group >= 16)
-                launch_motion_g<KIND, MAXS, 16>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 16, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
             else if (group >= 8)
-                launch_motion_g<KIND, MAXS, 8>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 8, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
             else
-                launch_motion_g<KIND, MAXS, 4>(c, smem, sms, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 4, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
         }
 
         template <int KIND>
@@ -908,15 +992,15 @@ namespace omplcu
 
         template <int KIND>
         void motion_by_stride(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
-                              const double *s1, const double *s2, size_t n, const uint32_t *nd, unsigned *code,
-                              unsigned long long *ctr, cudaStream_t s)
+                              const double *s1, const double *s2, size_t n, const uint32_t *nd, const double2 *prep,
+                              int nprep, unsigned *code, unsigned long long *ctr, cudaStream_t s)
         {
             if (sp.stride <= 8)
-                launch_motion<KIND, 8>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion<KIND, 8>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
             else if (sp.stride <= 32)
-                launch_motion<KIND, 32>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion<KIND, 32>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
             else
-                launch_motion<KIND, MAX_STRIDE>(c, smem, sms, group, sp, s1, s2, n, nd, code, ctr, s);
+                launch_motion<KIND, MAX_STRIDE>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
         }
 
         void check_stride(const CheckerDesc &c, int stride)
@@ -978,7 +1062,20 @@ namespace omplcu
         cnt_.reserve(n);
         offs_.reserve(1);
         code_.reserve(n);
-        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd_.p, cnt_.p);
+        int nprep = 0;
+        for (int i = 0; i < sp.ncomp; ++i)
+            nprep += sp.comp[i].type == OMPLCU_SO3 ? 1 : 0;
+        nprep = std::min(nprep, MAX_SO3_PREP);
+        if (const char *e = getenv("OMPLCU_MOTION_PREP"))  // tuning experiments only: 0 = per lane group, as before
+            if (atoi(e) == 0)
+                nprep = 0;
+        double2 *prep = nullptr;
+        if (nprep)
+        {
+            prep_.reserve((size_t)nprep * n);
+            prep = prep_.p;
+        }
+        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd_.p, cnt_.p, prep);
         CUDA_CHECK(cudaGetLastError());
         size_t tmp = 0;
         CUDA_CHECK(cub::DeviceReduce::Sum(nullptr, tmp, cnt_.p, offs_.p, (int)n, s));
@@ -1000,23 +1097,23 @@ namespace omplcu
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
                                                        ctr_.p, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p, ctr_.p,
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p, ctr_.p,
                                                    s);
                 break;
             case OMPLCU_CHK_SE3:
-                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
                                                  ctr_.p, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p, ctr_.p,
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p, ctr_.p,
                                                      s);
                 break;
             default:
-                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, code_.p,
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
                                                       ctr_.p, s);
         }
         CUDA_CHECK(cudaGetLastError());
@@ -1060,25 +1157,25 @@ namespace omplcu
         unsigned *code = reinterpret_cast<unsigned *>(noalloc_scratch_ + NOALLOC_HEAD +
                                                       4 * (size_t)OMPLCU_NOALLOC_MAX_SEGMENTS);
         CUDA_CHECK(cudaMemsetAsync(ctr, 0, 2 * sizeof(unsigned long long), s));
-        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, nullptr);
+        segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, nullptr, nullptr);
         CUDA_CHECK(cudaGetLastError());
         const int group = 8;
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
                 break;
             case OMPLCU_CHK_SE3:
-                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
                 break;
             default:
-                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
         }
         CUDA_CHECK(cudaGetLastError());
         motion_finalize_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, code, d_valid, d_last_t,
@@ -1313,7 +1410,7 @@ namespace omplcu
         dout.reserve(n);
         CUDA_CHECK(cudaMemcpyAsync(da.p, a, n * st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
         CUDA_CHECK(cudaMemcpyAsync(db.p, b, n * st * sizeof(double), cudaMemcpyHostToDevice, ts.s));
-        segment_count_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, da.p, db.p, n, dout.p, nullptr);
+        segment_count_kernel<<<nblk(n, 128), 128, 0, ts.s>>>(sp, da.p, db.p, n, dout.p, nullptr, nullptr);
         CUDA_CHECK(cudaGetLastError());
         CUDA_CHECK(cudaMemcpyAsync(out, dout.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, ts.s));
         CUDA_CHECK(cudaStreamSynchronize(ts.s));

@@ -82,6 +82,7 @@ namespace omplcu
         size_t smem_bytes_ = 0;
         // scratch
         DevBuf<uint32_t> nd_;
+        DevBuf<double2> prep_;  // per-segment SO(3) interpolation constants (segment_count_kernel)
         DevBuf<unsigned long long> cnt_, offs_;
         DevBuf<unsigned> code_;
         DevBuf<unsigned char> cub_tmp_;
