@@ -317,14 +317,23 @@ namespace omplcu
                 return false;
             if (ns == 0)
                 return true;
-            // Narrow phase, FP32 first: the robot sphere centre and the survivor's distance
-            // test in FP32 differ from the FP64 reference expressions by less than
-            // 476 u A^2 in the squared distance (centre: 64 u A per coordinate, 25 roundings
-            // on magnitudes <= 4 rho_rob plus the roundings of p, q, o; difference and
-            // squares: 3 u A more; threshold: 4 u T).  Outside a band of 2^-15 A^2 = 512 u A^2
-            // around the threshold the FP32 answer IS the FP64 answer; inside it, the FP64
-            // expressions decide.
-            const float m2 = A * A * 3.0517578125e-05f;
+            // Narrow phase, FP32 first.  The FP32 vector v_f the distance is taken of (obstacle centre minus robot
+            // sphere centre; for a box the clamped excess over the half extents, a 1-Lipschitz map of it) differs from
+            // the vector v of the FP64 reference expressions by less than 90 u A per coordinate (u = 2^-24; the centre
+            // c = p + (o + qw t + q x t), t = 2 q x o: 80 u |o| + 2 u A with p, q, o rounded to FP32 and |o| <= rho_rob
+            // <= A; 3 u A for the difference, 2 u A more for a box), so | |v_f| - |v| | < e := 2^-15 A = 512 u A, more
+            // than three times sqrt(3) 90 u A.  With D_f = fl(|v_f|^2) = |v_f|^2 (1 +- 4 u), R_f the FP32 sum of the
+            // radii = R (1 +- 2 u) and T_f = fl(R_f^2), take the band
+            //     m = 2.2 R_f e + 1.2 e^2 + 40 u T_f   >=   (R_f (1 + 16 u) + 1.04 e)^2 - R_f^2 .
+            // D_f < T_f - m gives sqrt(D_f) < R_f (1 - 16 u) - 1.04 e, hence |v| <= sqrt(D_f) (1 + 2 u) + e < R_f (1 - 13 u)
+            // < R: a hit in FP64 too.  D_f > T_f + m gives sqrt(D_f) > (R_f (1 + 16 u) + 1.04 e) (1 - u), hence
+            // |v| >= sqrt(D_f) (1 - 2 u) - e > R_f (1 + 12 u) > R: a miss in FP64 too.  (The FP64 expressions' own
+            // roundings, 2^-53 relative, disappear in the slack.)  Inside the band the FP64 expressions decide.  The
+            // band is per pair and proportional to R_f: 4e-6 for a 5 cm pair in the benchmark world, where one width
+            // for all pairs from |v| <= 2 A (2^-15 A^2 = 4.4e-5, the same size as the smallest thresholds) sent a
+            // quarter of the states into the FP64 expressions.
+            const float eband = A * 3.0517578125e-05f;
+            const float e2band = 1.2f * eband * eband;
             for (int i = 0; i < c.nrobot; ++i)
             {
                 const float4 ro = __ldg(c.robot32 + i);
@@ -338,7 +347,7 @@ namespace omplcu
                 for (int k = 0; k < ns; ++k)
                 {
                     const int j = (int)surv[k * stride];
-                    float D, T;
+                    float D, T, m2;
                     if (j < c.nsph)
                     {
                         const float4 o = __ldg(c.sph32 + j);
@@ -346,6 +355,7 @@ namespace omplcu
                         const float R = o.w + ro.w;
                         D = dx * dx + dy * dy + dz * dz;
                         T = R * R;
+                        m2 = fmaf(2.2f * R, eband, fmaf(T, 2.384185791015625e-06f, e2band));
                     }
                     else
                     {
@@ -356,6 +366,7 @@ namespace omplcu
                         const float ez = fmaxf(fabsf(czf - b0.z) - b1.y, 0.f);
                         D = ex * ex + ey * ey + ez * ez;
                         T = ro.w * ro.w;
+                        m2 = fmaf(2.2f * ro.w, eband, fmaf(T, 2.384185791015625e-06f, e2band));
                     }
                     if (D < T - m2)
                         return false;  // certain hit
@@ -458,7 +469,7 @@ namespace omplcu
         // code on constant indices and lives in registers; the general path walks the component table with run-time
         // offsets, which puts the state into local memory (86 STL / 22 LDL in the SASS of the general kernel).
         template <int KIND, int MAXS, int G, int SPEC>
-        __global__ void __launch_bounds__(128) motion_group_kernel(CheckerDesc c, SpaceDesc sp, const double *s1,
+        __global__ void __launch_bounds__(128, SPEC == 1 ? 8 : 1) motion_group_kernel(CheckerDesc c, SpaceDesc sp, const double *s1,
                                                                    const double *s2, size_t n, const uint32_t *nd,
                                                                    const double2 *prep_in, int nprep, unsigned *code,
                                                                    unsigned long long *ctr)
@@ -1092,6 +1103,11 @@ namespace omplcu
         // and fewer lanes repeat the per-segment setup; 8 is the best all-rounder.
         const double mean = (double)total / (double)n;
         int group = mean >= 6.0 ? 8 : 4;
+        // Feedback from the previous batch on this checker: when fewer than a quarter of the states of its segments had
+        // to be looked at (a sampling planner's long motions through clutter end within their first states), the next
+        // one takes the narrow groups: M3 1.06 -> 0.95 ms.  The results do not depend on the width.
+        if (group == 8 && last_states_ > 0 && last_evaluated_ * 4 < last_states_)
+            group = 4;
         if (const char *e = getenv("OMPLCU_MOTION_GROUP"))  // tuning experiments only
             group = atoi(e);
         switch (desc_.kind)
