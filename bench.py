@@ -46,7 +46,7 @@ MOTION_METRIC = "motion checks/sec (1M SE3 segments, 1000 obstacles, resolution 
 METRIC = "kNN queries/sec (k=10, 1M states)"
 TC_CAPTURE = "r2_scan_tc_d7_ncu_summary.csv"    # ncu --set full of the tensor-core scan (roofline.traffic is read from it)
 FP32_CAPTURE = "r1_scan_v3_ncu_summary.csv"     # ... of the FP32-pipe scan
-MOTION_CAPTURE = "r2_motion_v5_ncu_summary.csv"  # ... of motion_group_kernel
+MOTION_CAPTURE = "r2_motion_v6_ncu_summary.csv"  # ... of motion_group_kernel
 UNIT = "queries/s"
 
 
@@ -736,14 +736,16 @@ def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
                 "h2d_bytes_per_step": int(a.nbytes + b.nbytes), "d2h_bytes_per_step": int(hv.nbytes + ht.nbytes)},
         "gpu_launches": int(launches),
         "roofline": {
-            "bound": "hbm", "kernel": "motion_group_kernel<SE3,8,32>", "peak": hbm_peak, "unit": "GB/s",
+            "bound": "hbm", "kernel": "motion_group_kernel<SE3, 8, lanes_per_segment, SE(3)-specialised>", "peak": hbm_peak, "unit": "GB/s",
             "achieved": gbs, "frac": gbs / hbm_peak, "traffic": ncu_traffic(MOTION_CAPTURE) if world == 1 else None,
             "traffic_unit": f"bytes/launch (ncu, profiles/{MOTION_CAPTURE})",
             "brute_force_equivalent_tflops": alg / (t_step * 1e-3) / 1e12,
-            "note": "per rank. Inputs are read once (ncu: 116 MB in, 11 MB out per 1M segments), so HBM is the only "
+            "note": "per rank. Inputs are read once (ncu: 132 MB in, 8 MB out per 1M segments), so HBM is the only "
                     "hardware roof the algorithmic figure can be put against, and the kernel is nowhere near it: "
-                    "it is instruction-issue / latency bound (ncu: issue slots 69 % busy, FP64 pipe 11 %, FMA 27 %, "
-                    "18 of 32 lanes active). brute_force_equivalent_tflops is SURVEY 8(d)'s flop count (every state "
+                    "it is instruction-issue / latency bound (ncu, capture at 8 lanes per segment: issue slots 65 % "
+                    "busy, 700 M warp instructions, 16.5 of 32 lanes active; by source line "
+                    "profiles/r2_motion_v6_source_lines.txt: narrow phase 48 %, cell walk 17 %, interpolation 14 %). "
+                    "brute_force_equivalent_tflops is SURVEY 8(d)'s flop count (every state "
                     "x every robot/obstacle pair) over the time; the grid, the sphere filter and the early exit avoid "
                     "almost all of it, so it exceeds the FP32 pipe peak by construction.",
         },
