@@ -144,7 +144,12 @@ int omplcu_nn_knn_device(omplcu_nn_t nn, const double *d_queries, size_t nq, siz
                          double *d_dists, void *stream);
 /* Merge nparts partial results laid out [part][nq][k] (as produced by an
  * all-gather of omplcu_nn_knn_device outputs) into the k best per query by
- * (distance, id).  Device pointers. */
+ * (distance, id).  Device pointers.  Up to 3200 candidates per query
+ * (nparts * k) are ranked in shared memory in any order; beyond that every
+ * part's row must be sorted by distance with absent entries (OMPLCU_ID_NONE)
+ * last, as omplcu_nn_knn_device writes them, and ranks come from binary
+ * searches in the rows (equal distances are ordered by id wherever they
+ * stand).  nparts * k < 2^31. */
 int omplcu_merge_topk_device(int device, const double *d_dists, const uint64_t *d_ids, int nparts, size_t nq,
                              size_t k, double *d_out_dists, uint64_t *d_out_ids, void *stream);
 /* The same with `part_stride` elements between consecutive parts (>= nq * k): lets a rank keep its ids and
@@ -158,7 +163,9 @@ int omplcu_merge_topk_strided_device(int device, const double *d_dists, const ui
  * "scan_ctas_per_sm", "tc_tiles", "profile" (tuning); "few_scan" (1: calls of up to 8 queries in auto mode run the
  * lane-per-point scan, default), "tc_ts" (query tile in tensor memory), "tc_pair" (CTA pairs share the point chunks),
  * "tc_align" (work pieces end on query-tile boundaries), "thr_scan", "l2_window" (tuning);
- * "tc_scan_values_out" (diagnostics: device pointer that receives the raw scan values).  Stats: "last_fallbacks"
+ * "tc_scan_values_out" (diagnostics: device pointer that receives the raw scan values); sharded handles only:
+ * "gather_entries" ((distance, id) entries the gather buffer on the first device may hold, default 2^27 = 2 GB; larger
+ * batches are answered in pieces).  Stats: "last_fallbacks"
  * (queries redone by the exact path), "last_rescans" (queries the tensor-core filter passed on to the FP32-pipe scan),
  * "tc_demoted" (auto mode made the FP32-pipe scan the first filter: the set is too dense for the BF16 band),
  * "last_path" (1 filter scan + exact re-rank, 2 exact sort), "last_tc" (1 if the last scan ran on the tensor cores),
