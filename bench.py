@@ -690,9 +690,17 @@ def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
         check(L.omplcu_check_motions(chk.handle, sp.handle, a.ctypes.data, b.ctypes.data, n, hv.ctypes.data,
                                      ht.ctypes.data, None))
 
+    def step_device_bool():  # checkMotion(s1, s2): no lastValid, the states of a segment are visited in spread order
+        check(L.omplcu_check_motions_device(chk.handle, sp.handle, da.data_ptr(), db.data_ptr(), n, dvb.data_ptr(),
+                                            None, None, sptr))
+
+    dvb = torch.empty(n, dtype=torch.uint8, device=dev)
+    bool_ms, _, _ = timed(step_device_bool, args.steps, args.warmup)
+    bool_eval = chk.stat("last_states_evaluated")
     l0 = chk.stat("launches")
     dev_ms, _, _ = timed(step_device, args.steps, args.warmup)
     launches = (chk.stat("launches") - l0) * args.steps // (args.steps + args.warmup)
+    assert bool((dv == dvb).all()), "checkMotion(s1, s2) and checkMotion(s1, s2, lastValid) disagree"
     e2e_ms = float("nan")
     if world == 1:
         _, e2e_ms, _ = timed(step_e2e, args.steps, max(args.warmup, 1))
@@ -735,6 +743,11 @@ def motion_block(args, torch, dist, nccl, dev, local, rank, world, timed):
         "e2e": {"value": N_SEGMENTS / (e2e_ms / args.steps * 1e-3), "unit": "segments/s",
                 "h2d_bytes_per_step": int(a.nbytes + b.nbytes), "d2h_bytes_per_step": int(hv.nbytes + ht.nbytes)},
         "gpu_launches": int(launches),
+        "bool_overload": {"what": "checkMotion(s1, s2) without lastValid on the same segments (per rank, device-timed): "
+                                  "any failing state decides, so the states are visited in spread order",
+                          "value": n / (bool_ms / args.steps * 1e-3), "unit": "segments/s",
+                          "ms_per_step": bool_ms / args.steps, "states_evaluated": int(bool_eval),
+                          "equal_to_lastValid_overload": True},
         "roofline": {
             "bound": "hbm", "kernel": "motion_group_kernel<SE3, 8, lanes_per_segment, SE(3)-specialised>", "peak": hbm_peak, "unit": "GB/s",
             "achieved": gbs, "frac": gbs / hbm_peak, "traffic": ncu_traffic(MOTION_CAPTURE) if world == 1 else None,

@@ -471,8 +471,8 @@ namespace omplcu
         template <int KIND, int MAXS, int G, int SPEC>
         __global__ void __launch_bounds__(128, SPEC == 1 ? 8 : 1) motion_group_kernel(CheckerDesc c, SpaceDesc sp, const double *s1,
                                                                    const double *s2, size_t n, const uint32_t *nd,
-                                                                   const double2 *prep_in, int nprep, unsigned *code,
-                                                                   unsigned long long *ctr)
+                                                                   const double2 *prep_in, int nprep, int spread,
+                                                                   unsigned *code, unsigned long long *ctr)
         {
             extern __shared__ float4 smem_filt[];
             const Staged<KIND> sm = stage_filter<KIND>(c, smem_filt);
@@ -481,6 +481,12 @@ namespace omplcu
             const unsigned gmask = (G == 32) ? FULL : (((1u << G) - 1u) << gbase);
             size_t seg = 0;
             unsigned cnt = 0, base = 0, ndv = 0;
+            // spread (the bool overload: any failing state decides, DiscreteMotionValidator.cpp:106-134 visits them in
+            // bisection order for the same reason): lane gl owns the gl-th block of blk consecutive items and walks it
+            // in steps of ~0.62 blk, so the G states of a pass, and those of successive passes, lie far apart on the
+            // segment.  Neighbouring states fail together; states far apart fail independently, and a colliding
+            // segment is found out in fewer passes.
+            unsigned blk = 0, off = 0, stepc = 1;
             So3Seg prep[MAX_SO3_PREP] = {};
             unsigned long long evaluated = 0;
             bool need = true, done = false;
@@ -502,6 +508,26 @@ namespace omplcu
                         cnt = (ndv >= 2 ? ndv - 1 : 0u) + 1u;
                         base = 0;
                         need = false;
+                        if (spread)
+                        {
+                            blk = (cnt + G - 1) / G;
+                            off = 0;
+                            stepc = (blk * 5u + 4u) / 8u;
+                            if (stepc == 0)
+                                stepc = 1;
+                            for (;; ++stepc)  // coprime with blk: the walk visits every item of the block
+                            {
+                                unsigned x = stepc, y = blk;
+                                while (y)
+                                {
+                                    const unsigned r = x % y;
+                                    x = y;
+                                    y = r;
+                                }
+                                if (x == 1 || blk == 1)
+                                    break;
+                            }
+                        }
                         if (cnt > 1)  // acos, 1/sin(theta): once per segment, not once per state
                         {
                             if (SPEC == 1)
@@ -536,7 +562,7 @@ namespace omplcu
                 if (__all_sync(FULL, done))
                     break;
                 // item m < cnt-1 is the interior state j = m+1, item cnt-1 is s2
-                const unsigned m = base + gl;
+                const unsigned m = spread ? gl * blk + off : base + gl;
                 bool bad = false;
                 if (!done && m < cnt)
                 {
@@ -581,14 +607,22 @@ namespace omplcu
                     if (hit)
                     {
                         const unsigned first = base + (unsigned)(__ffs(hit) - 1) - gbase;
-                        if (gl == 0)
-                            code[seg] = (first == cnt - 1) ? CODE_S2 : first + 1;
+                        if (gl == 0)  // spread: only "not valid" is read (motion_finalize_kernel without last_t)
+                            code[seg] = spread ? 1u : ((first == cnt - 1) ? CODE_S2 : first + 1);
                         need = true;
                     }
                     else
                     {
-                        base += G;
-                        if (base >= cnt)
+                        if (spread)
+                        {
+                            base += 1;
+                            off += stepc;
+                            if (off >= blk)
+                                off -= blk;
+                        }
+                        else
+                            base += G;
+                        if (base >= (spread ? blk : cnt))
                         {
                             if (gl == 0)
                                 code[seg] = CODE_VALID;
@@ -943,8 +977,8 @@ namespace omplcu
 
         template <int KIND, int MAXS, int G, int SPEC>
         void launch_motion_g(const CheckerDesc &c, size_t smem, int sms, const SpaceDesc &sp, const double *s1,
-                             const double *s2, size_t n, const uint32_t *nd, const double2 *prep, int nprep, unsigned *code,
-                             unsigned long long *ctr, cudaStream_t s)
+                             const double *s2, size_t n, const uint32_t *nd, const double2 *prep, int nprep, int spread,
+                             unsigned *code, unsigned long long *ctr, cudaStream_t s)
         {
             if (smem > 48 * 1024)
                 CUDA_CHECK(cudaFuncSetAttribute(motion_group_kernel<KIND, MAXS, G, SPEC>,
@@ -954,13 +988,13 @@ namespace omplcu
             const unsigned want = (unsigned)std::min<size_t>((n + groups_per_cta - 1) / groups_per_cta,
                                                              (size_t)sms * 8u);
             motion_group_kernel<KIND, MAXS, G, SPEC><<<std::max(want, 1u), 128, smem, s>>>(c, sp, s1, s2, n, nd, prep, nprep,
-                                                                                     code, ctr);
+                                                                                     spread, code, ctr);
         }
 
         template <int KIND, int MAXS>
         void launch_motion(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
                            const double *s1, const double *s2, size_t n, const uint32_t *nd, const double2 *prep,
-                           int nprep, unsigned *code, unsigned long long *ctr, cudaStream_t s)
+                           int nprep, int spread, unsigned *code, unsigned long long *ctr, cudaStream_t s)
         {
             // exactly SE(3): RealVector(3) x SO(3), nothing else in the state
             constexpr bool can_spec = KIND == OMPLCU_CHK_SE3 && MAXS == 8;
@@ -970,23 +1004,23 @@ namespace omplcu
             if (can_spec && spec)
             {
                 if (group >= 32)
-                    launch_motion_g<KIND, MAXS, 32, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                    launch_motion_g<KIND, MAXS, 32, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
                 else if (group >= 16)
-                    launch_motion_g<KIND, MAXS, 16, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                    launch_motion_g<KIND, MAXS, 16, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
                 else if (group >= 8)
-                    launch_motion_g<KIND, MAXS, 8, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                    launch_motion_g<KIND, MAXS, 8, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
                 else
-                    launch_motion_g<KIND, MAXS, 4, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                    launch_motion_g<KIND, MAXS, 4, can_spec ? 1 : 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
                 return;
             }
             if (group >= 32)
-                launch_motion_g<KIND, MAXS, 32, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 32, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
             else if (group >= 16)
-                launch_motion_g<KIND, MAXS, 16, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 16, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
             else if (group >= 8)
-                launch_motion_g<KIND, MAXS, 8, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 8, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
             else
-                launch_motion_g<KIND, MAXS, 4, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion_g<KIND, MAXS, 4, 0>(c, smem, sms, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
         }
 
         template <int KIND>
@@ -1004,14 +1038,14 @@ namespace omplcu
         template <int KIND>
         void motion_by_stride(const CheckerDesc &c, size_t smem, int sms, int group, const SpaceDesc &sp,
                               const double *s1, const double *s2, size_t n, const uint32_t *nd, const double2 *prep,
-                              int nprep, unsigned *code, unsigned long long *ctr, cudaStream_t s)
+                              int nprep, int spread, unsigned *code, unsigned long long *ctr, cudaStream_t s)
         {
             if (sp.stride <= 8)
-                launch_motion<KIND, 8>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion<KIND, 8>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
             else if (sp.stride <= 32)
-                launch_motion<KIND, 32>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion<KIND, 32>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
             else
-                launch_motion<KIND, MAX_STRIDE>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, code, ctr, s);
+                launch_motion<KIND, MAX_STRIDE>(c, smem, sms, group, sp, s1, s2, n, nd, prep, nprep, spread, code, ctr, s);
         }
 
         void check_stride(const CheckerDesc &c, int stride)
@@ -1073,6 +1107,10 @@ namespace omplcu
         cnt_.reserve(n);
         offs_.reserve(1);
         code_.reserve(n);
+        // the bool overload: states in spread order (motion_group_kernel)
+        int spread = d_last_t == nullptr ? 1 : 0;
+        if (const char *e = getenv("OMPLCU_MOTION_SPREAD"))  // tuning experiments only
+            spread = spread && atoi(e) != 0;
         int nprep = 0;
         for (int i = 0; i < sp.ncomp; ++i)
             nprep += sp.comp[i].type == OMPLCU_SO3 ? 1 : 0;
@@ -1113,23 +1151,23 @@ namespace omplcu
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, spread, code_.p,
                                                        ctr_.p, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p, ctr_.p,
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, spread, code_.p, ctr_.p,
                                                    s);
                 break;
             case OMPLCU_CHK_SE3:
-                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, spread, code_.p,
                                                  ctr_.p, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p, ctr_.p,
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, spread, code_.p, ctr_.p,
                                                      s);
                 break;
             default:
-                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, code_.p,
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd_.p, prep, nprep, spread, code_.p,
                                                       ctr_.p, s);
         }
         CUDA_CHECK(cudaGetLastError());
@@ -1176,22 +1214,23 @@ namespace omplcu
         segment_count_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, nullptr, nullptr);
         CUDA_CHECK(cudaGetLastError());
         const int group = 8;
+        const int spread = d_last_t == nullptr ? 1 : 0;
         switch (desc_.kind)
         {
             case OMPLCU_CHK_HYPERCUBE:
-                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_HYPERCUBE>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, spread, code, ctr, s);
                 break;
             case OMPLCU_CHK_CHAIN:
-                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_CHAIN>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, spread, code, ctr, s);
                 break;
             case OMPLCU_CHK_SE3:
-                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_SE3>(desc_, smem_bytes_, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, spread, code, ctr, s);
                 break;
             case OMPLCU_CHK_CIRCLES:
-                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_CIRCLES>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, spread, code, ctr, s);
                 break;
             default:
-                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, code, ctr, s);
+                motion_by_stride<OMPLCU_CHK_ALLVALID>(desc_, 0, sms_, group, sp, d_s1, d_s2, n, nd, nullptr, 0, spread, code, ctr, s);
         }
         CUDA_CHECK(cudaGetLastError());
         motion_finalize_kernel<<<nblk(n, 128), 128, 0, s>>>(sp, d_s1, d_s2, n, nd, code, d_valid, d_last_t,
