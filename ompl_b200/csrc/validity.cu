@@ -19,7 +19,9 @@
 // the states j = 1, 2, ... in increasing order, G per pass, then s2; one warp
 // ballot per pass finds the first failing state, which ends the segment (early
 // exit) and is exactly what the lastValid overload reports
-// (DiscreteMotionValidator.cpp:60-72).  Groups pull segments from a global
+// (DiscreteMotionValidator.cpp:60-72).  Without lastValid any failing state
+// decides, and the lanes visit the states spread out over the segment instead
+// (see `spread` in motion_group_kernel).  Groups pull segments from a global
 // counter, so long and short segments balance across the persistent grid.
 //
 // Interpolation and the deciding predicate are FP64 with the reference's
