@@ -1146,7 +1146,7 @@ namespace omplcu
         // Feedback from the previous batch on this checker: when fewer than a quarter of the states of its segments had
         // to be looked at (a sampling planner's long motions through clutter end within their first states), the next
         // one takes the narrow groups: M3 1.06 -> 0.95 ms.  The results do not depend on the width.
-        if (group == 8 && last_states_ > 0 && last_evaluated_ * 4 < last_states_)
+        if (group == 8 && fb_states_ > 0 && fb_evaluated_ * 4 < fb_states_)
             group = 4;
         if (const char *e = getenv("OMPLCU_MOTION_GROUP"))  // tuning experiments only
             group = atoi(e);
@@ -1180,8 +1180,8 @@ namespace omplcu
         CUDA_CHECK(cudaMemcpyAsync(ctr_host, ctr_.p, sizeof(ctr_host), cudaMemcpyDeviceToHost, s));
         CUDA_CHECK(cudaStreamSynchronize(s));
         launches_ += 4;
-        last_states_ = (long)total;
-        last_evaluated_ = (long)ctr_host[1];
+        last_states_ = fb_states_ = (long)total;
+        last_evaluated_ = fb_evaluated_ = (long)ctr_host[1];
         last_group_ = group;
     }
 

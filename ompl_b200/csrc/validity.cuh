@@ -91,6 +91,7 @@ namespace omplcu
         long launches_ = 0;
         long last_states_ = 0;
         long last_evaluated_ = 0;
+        long fb_states_ = 0, fb_evaluated_ = 0;  // the previous motion batch (feedback for the lane-group width)
         long last_group_ = 0;
         unsigned char *noalloc_scratch_ = nullptr;  // device address of the static scratch array on device_
     };
